@@ -1,0 +1,83 @@
+"""CPU: the oracle (oracle/niti_oracle.c) against the golden vectors produced by the unmodified
+reference (tests/golden/make_golden.py).  This is the pin that makes the oracle trustworthy."""
+import numpy as np
+import pytest
+from oracle.oracle import ConvShape
+
+
+def conv_names(g):
+    return sorted({k.split(".")[0] for k in g.files})
+
+
+def load_case(g, name):
+    s = ConvShape(*[int(v) for v in g[name + ".shape"]])
+    return s, g[name + ".x"], g[name + ".w"], g[name + ".dy"]
+
+
+def test_golden_has_cases(golden_conv):
+    assert len(conv_names(golden_conv)) >= 10
+
+
+@pytest.mark.parametrize("name", [
+    "mnist_conv1", "mnist_conv2", "mnist_ip1", "mnist_ip2", "vgg_3x3_p1", "vgg_3x3_p1_b",
+    "odd_hw_3x3_p1", "s2_3x3_p1", "s2_1x1_p0", "small_mag_cast", "small_mag_shift1", "zero_dy"])
+def test_conv_ops_match_reference(oracle, golden_conv, name):
+    g = golden_conv
+    s, x, w, dy = load_case(g, name)
+    y, e, acc = oracle.conv_fwd(s, x, w, -7, -7)
+    assert np.array_equal(y, g[name + ".y"])
+    assert e == int(g[name + ".exp"])
+    dw, _ = oracle.conv_dw(s, x, dy)
+    assert np.array_equal(dw, g[name + ".dw"])
+    if name + ".dx" in g.files:
+        dx, _ = oracle.conv_dx(s, dy, w)
+        assert np.array_equal(dx, g[name + ".dx"])
+
+
+def test_rescale_edge_paths_are_covered(oracle, golden_conv):
+    """the golden set exercises all three branches of the forward shift rule and the b==0 dW rule"""
+    seen = set()
+    for name in conv_names(golden_conv):
+        s, x, w, dy = load_case(golden_conv, name)
+        acc, _ = oracle.conv_fwd_acc(s, x, w)
+        sh = oracle.range_estimate(acc) - 7
+        seen.add("gt1" if sh > 1 else ("eq1" if sh == 1 else "le0"))
+    assert seen == {"gt1", "eq1", "le0"}
+    s, x, w, dy = load_case(golden_conv, "zero_dy")
+    assert not oracle.conv_dw(s, x, dy)[0].any()
+
+
+def test_elementwise_match_reference(oracle, golden_ew):
+    g = golden_ew
+    x = g["relu.x"]
+    assert np.array_equal(oracle.relu(x), g["relu.y"])
+    assert np.array_equal(oracle.relu_grad(x, g["relu_grad.dy"]), g["relu_grad.dx"])
+    assert np.array_equal(oracle.maxpool(x, 2, 2), g["maxpool.y"])
+    assert np.array_equal(oracle.sgd_update(g["sgd.w"], g["sgd.dw"]), g["sgd.out"])
+    for a in (-9, -7, -5, -3, 0, 1):
+        got = oracle.loss_grad(g[f"loss_grad.{a}.logits"], a, g[f"loss_grad.{a}.labels"])
+        assert np.array_equal(got, g[f"loss_grad.{a}.grad"]), a
+
+
+def test_psto_properties(oracle):
+    rng = np.random.default_rng(3)
+    acc = rng.integers(-(2 ** 20), 2 ** 20, size=10000).astype(np.int32)
+    for shift in range(2, 16):
+        out = oracle.psto(acc, shift)
+        assert out.min() >= -127 and out.max() <= 127            # Q4 symmetric clip
+        q = np.trunc(acc / float(1 << shift)).astype(np.int64)
+        d = np.clip(out, -126, 126) - np.clip(q, -126, 126)
+        assert np.all(np.abs(d) <= 1)                             # rounds by at most one step
+        assert np.array_equal(oracle.psto(-acc, shift), -out)     # odd symmetry
+    # Q2: power-of-two maximum -> bitwidth k, non power-of-two -> next k
+    assert oracle.range_estimate(np.array([1], np.int32)) == 0
+    assert oracle.range_estimate(np.array([-128], np.int32)) == 7
+    assert oracle.range_estimate(np.array([129], np.int32)) == 8
+    assert oracle.range_estimate(np.zeros(4, np.int32)) == 0
+
+
+def test_ragged_and_empty(oracle):
+    assert oracle.relu(np.zeros((0,), np.int8)).size == 0
+    assert oracle.sgd_update(np.zeros((0,), np.int8), np.zeros((0,), np.int8)).size == 0
+    out, inc = oracle.rescale_act(np.zeros((0,), np.int32))
+    assert out.size == 0 and inc == 0
