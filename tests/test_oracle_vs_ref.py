@@ -15,7 +15,9 @@ def ref():
 
 @pytest.mark.parametrize("cfg", [
     (4, 4, 8, 8, 8, 3, 1, 1), (2, 8, 6, 6, 12, 3, 1, 0), (2, 20, 12, 12, 52, 5, 1, 0),
-    (8, 16, 1, 1, 12, 1, 1, 0), (4, 8, 10, 10, 8, 3, 2, 1), (3, 12, 5, 9, 16, 3, 1, 1)])
+    (8, 16, 1, 1, 12, 1, 1, 0), (4, 8, 10, 10, 8, 3, 2, 1), (3, 12, 7, 7, 16, 3, 1, 1)])
+# (non-square images are outside the reference's contract: its grad rule swaps kernelX/kernelY,
+#  grad/NITI_Conv_Int8_Grad.cpp:172-173, and the run crashes; the oracle and the CUDA path handle them.)
 @pytest.mark.parametrize("seed", [0, 1])
 def test_live_reference_conv(oracle, ref, cfg, seed):
     n, c, h, w, oc, k, st, p = cfg
