@@ -1,0 +1,134 @@
+/*
+ * niti_b200.h — C ABI of libniti_b200.so: the B200 (sm_100a) implementation of Mandheling's NITI
+ * int8 training hot path.  Plain C, raw device pointers + POD descriptors, int return codes
+ * (0 = success), no torch/MNN types.  Modelled on the reference's own accelerator boundary, the
+ * `struct HexagonNN` table of plain C calls loaded with dlopen/dlsym
+ * (execution-engine/include/MNN/hexagon/hexagon_nn/hexagon_implementation.h:24-130,
+ *  execution-engine/source/backend/cpu/hexagon_implementation.cpp:52-113), but op-level instead of
+ * graph-level.  The MNN Backend/Execution creator set in mnn_backend/ and the ctypes mirror in
+ * mandheling_dsp_training_b200/ are both thin callers of exactly these entry points.
+ *
+ * Data layout in HBM (all device memory, caller-owned):
+ *   activations / gradients : int8  NHWC  [n][h][w][c]
+ *   weights / weight grads  : int8  OHWI  [oc][kh][kw][c]
+ *   accumulators            : int32, same index order as the int8 tensor they rescale into
+ *   exponents               : int8 scalars in device memory (quirk Q7: carried beside each tensor)
+ *   max-abs                 : uint32 scalar in device memory (input of the shared-exponent step)
+ * Everything is asynchronous on the given stream and CUDA-graph capturable: no host sync, no
+ * allocation, no host-visible scalar on the path.
+ *
+ * There is NO CPU fallback: every entry point fails with NITI_ERR_CUDA when no device is usable.
+ */
+#ifndef NITI_B200_H
+#define NITI_B200_H
+#include <stdint.h>
+#include <stddef.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct niti_ctx niti_ctx;
+typedef void* niti_stream;           /* cudaStream_t */
+
+enum {
+    NITI_OK = 0,
+    NITI_ERR_ARG = 1,                /* bad descriptor / null pointer          */
+    NITI_ERR_CUDA = 2,               /* CUDA runtime error (see niti_last_error) */
+    NITI_ERR_UNSUPPORTED = 3         /* shape outside every kernel's contract  */
+};
+
+/* Convolution geometry; mirrors MNN's Convolution2DCommon as the reference's ops read it
+ * (schema/default/UserDefine.fbs:27-33; NITI_Conv_Int8.cpp:94-112): symmetric stride/pad/dilate. */
+typedef struct {
+    int32_t n, c, h, w;              /* input  [n,h,w,c]          */
+    int32_t oc, kh, kw;              /* weight [oc,kh,kw,c]       */
+    int32_t stride, pad, dil;
+} niti_conv_desc;
+
+/* Which kernel family to use.  AUTO picks tcgen05 when the shape qualifies (channel counts that are
+ * multiples of 16), else the SIMT kernels.  FORCE_* are for tests and benchmarks. */
+enum { NITI_PATH_AUTO = 0, NITI_PATH_SIMT = 1, NITI_PATH_TC = 2 };
+
+/* ---- context ------------------------------------------------------------------------------- */
+int         niti_ctx_create(int device, niti_ctx** out);
+int         niti_ctx_destroy(niti_ctx* ctx);
+const char* niti_last_error(niti_ctx* ctx);
+int         niti_set_path(niti_ctx* ctx, int path);
+int         niti_version(void);
+/* kernels launched through this context since creation (bench.py's gpu_launches evidence) */
+int64_t     niti_launch_count(niti_ctx* ctx);
+/* name of the kernel family the last conv/matmul call used: "tc" or "simt" */
+const char* niti_last_path(niti_ctx* ctx);
+
+/* ---- phase 1: int32 accumulators + running max|acc| ---------------------------------------
+ * Replaces the im2col + NITI_Int8GemmKernel loops of
+ *   NITI_Conv_Int8::onExecute         (source/backend/cpu/NITI_Conv_Int8.cpp:212-249)
+ *   NITI_DeConv_Int8::onExecute       (NITI_DeConv_Int8.cpp:208-290; rot180 folded into indexing)
+ *   NITI_GradientConv_Int8::onExecute (NITI_GradientConv_Int8.cpp:218-268)
+ *   NITI_Matmul_Int8::onExecute       (NITI_Matmul_Int8.cpp:186-208)
+ * `maxabs` (optional) receives max(|acc|) via atomicMax and must be zeroed by the caller
+ * (niti_zero_u32) or by a previous niti_rescale_* consuming it. */
+int niti_conv_fwd_acc(niti_ctx*, const niti_conv_desc*, const int8_t* x, const int8_t* w,
+                      int32_t* acc /*[n,oh,ow,oc]*/, uint32_t* maxabs, niti_stream);
+int niti_conv_dx_acc(niti_ctx*, const niti_conv_desc*, const int8_t* dy, const int8_t* w,
+                     int32_t* acc /*[n,h,w,c]*/, uint32_t* maxabs, niti_stream);
+int niti_conv_dw_acc(niti_ctx*, const niti_conv_desc*, const int8_t* x, const int8_t* dy,
+                     int32_t* acc /*[oc,kh,kw,c]*/, uint32_t* maxabs, niti_stream);
+/* C[e,h] = sum_l A[e,l] * B[h,l]   (A, B row-major int8) */
+int niti_matmul_nt_acc(niti_ctx*, int e, int h, int l, const int8_t* a, const int8_t* b,
+                       int32_t* acc, uint32_t* maxabs, niti_stream);
+
+/* ---- phase 2: shared exponent + pseudo-stochastic shift-round ------------------------------
+ * NITI_RangeEstimate + NITI_MNNPstoShiftInt32 (compute/CommonOptFunction.cpp:1565-1627) with the
+ * callers' rules.  Between phase 1 and phase 2 a data-parallel job all-reduces `acc` (sum, dW) or
+ * `maxabs` (max, activations). */
+int niti_zero_u32(niti_ctx*, uint32_t* p, int count, niti_stream);
+int niti_absmax(niti_ctx*, const int32_t* acc, size_t n, uint32_t* maxabs /*atomicMax*/, niti_stream);
+/* rule A — forward / dX (NITI_Conv_Int8.cpp:255-307, NITI_DeConv_Int8.cpp:292-329):
+ *   shift=b-7; >1: PSTO(shift); ==1: PSTO(2); else raw int8 cast.
+ *   exp_out (optional) = (int8)(*exp_a + *exp_b + inc); exp_a/exp_b may be NULL (treated as 0). */
+int niti_rescale_act(niti_ctx*, const int32_t* acc, size_t n, const uint32_t* maxabs,
+                     int8_t* out, const int8_t* exp_a, const int8_t* exp_b, int8_t* exp_out, niti_stream);
+/* rule B — dW / matmul (NITI_GradientConv_Int8.cpp:274-296 sub=2; NITI_Matmul_Int8.cpp:216-228 sub=3):
+ *   b==0: zeros; else PSTO(b-sub).  dw_out optional; when w_inout is given the int8 SGD step
+ *   w <- clip127(w - dw) (optimizer/NITI_SGD.hpp:49-52, BinaryUtils.hpp:276-299) is fused. */
+int niti_rescale_grad(niti_ctx*, const int32_t* acc, size_t n, const uint32_t* maxabs, int sub,
+                      int8_t* dw_out, int8_t* w_inout, niti_stream);
+int niti_sgd_update(niti_ctx*, int8_t* w, const int8_t* dw, size_t n, niti_stream);
+
+/* ---- whole ops = phase 1 + phase 2 on the context's workspace -------------------------------
+ * Drop-in for the four reference executions (same inputs/outputs, NHWC/OHWI instead of NC4HW4). */
+int niti_conv_fwd(niti_ctx*, const niti_conv_desc*, const int8_t* x, const int8_t* w,
+                  const int8_t* ex, const int8_t* ew, int8_t* y, int8_t* ey, niti_stream);
+int niti_conv_dx(niti_ctx*, const niti_conv_desc*, const int8_t* dy, const int8_t* w, int8_t* dx, niti_stream);
+int niti_conv_dw(niti_ctx*, const niti_conv_desc*, const int8_t* x, const int8_t* dy, int8_t* dw, niti_stream);
+int niti_matmul_nt(niti_ctx*, int e, int h, int l, const int8_t* a, const int8_t* b, int8_t* c, niti_stream);
+
+/* ---- element-wise ops of the training step, NHWC ---------------------- */
+int niti_relu(niti_ctx*, const int8_t* x, int8_t* y, size_t n, niti_stream);                 /* NITI_CPURelu_Int8.cpp:47-53 */
+int niti_relu_grad(niti_ctx*, const int8_t* x, const int8_t* dy, int8_t* dx, size_t n, niti_stream); /* NITI_CPUReluGrad_Int8.cpp:51-57 */
+int niti_maxpool(niti_ctx*, const int8_t* x, int n, int h, int w, int c, int k, int s, int8_t* y, niti_stream); /* NITI_Maxpool_Int8.cpp:24-70 */
+int niti_maxpool_grad(niti_ctx*, const int8_t* x, const int8_t* y, const int8_t* dy, int n, int h, int w, int c,
+                      int k, int s, int8_t* dx, niti_stream);                                 /* NITI_CPUPoolGrad_Int8.cpp:36-72 */
+int niti_loss_grad(niti_ctx*, const int8_t* logits, const int8_t* ascale, const int32_t* labels,
+                   int batch, int classes, int8_t* grad, niti_stream);                        /* NITI_CPULossGrad_Int8.cpp:82-201 */
+
+/* ---- layout conversion at the boundary ----------------------------------------------------- */
+int niti_nchw_to_nhwc(niti_ctx*, const int8_t* src, int n, int c, int h, int w, int8_t* dst, niti_stream);
+int niti_nhwc_to_nchw(niti_ctx*, const int8_t* src, int n, int c, int h, int w, int8_t* dst, niti_stream);
+/* the reference CPU path's int8 "NC4HW4" is [c/4][n][h*w][4] (NITI_Conv_Int8.cpp:111,191,229-230) */
+int niti_nc4hw4_to_nhwc(niti_ctx*, const int8_t* src, int n, int c, int h, int w, int8_t* dst, niti_stream);
+int niti_nhwc_to_nc4hw4(niti_ctx*, const int8_t* src, int n, int c, int h, int w, int8_t* dst, niti_stream);
+
+/* ---- host-buffer convenience (the e2e leg): H2D, op, D2H inside the call ------------------- */
+int niti_conv_fwd_host(niti_ctx*, const niti_conv_desc*, const int8_t* x_nhwc, const int8_t* w_ohwi,
+                       int8_t ex, int8_t ew, int8_t* y_nhwc, int8_t* ey);
+
+/* ---- probes ------------------------------------------------------------------------------- */
+/* dense tcgen05 kind::i8 issue-rate probe (no global traffic): returns achieved TOPS */
+int niti_probe_i8_peak(niti_ctx*, int iters, double* tops_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

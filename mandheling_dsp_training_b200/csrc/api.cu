@@ -1,0 +1,232 @@
+// api.cu — context, workspace and the C-ABI dispatch of libniti_b200.so (see include/niti_b200.h).
+#include "common.cuh"
+#include <cstdio>
+#include <cstring>
+#include <cstdlib>
+#include <new>
+
+// kernel families (conv_simt.cu / conv_tc.cu)
+int simt_conv_fwd_acc(niti_ctx*, const niti_conv_desc*, const int8_t*, const int8_t*, int32_t*, uint32_t*, cudaStream_t);
+int simt_conv_dx_acc(niti_ctx*, const niti_conv_desc*, const int8_t*, const int8_t*, int32_t*, uint32_t*, cudaStream_t);
+int simt_conv_dw_acc(niti_ctx*, const niti_conv_desc*, const int8_t*, const int8_t*, int32_t*, uint32_t*, cudaStream_t);
+bool tc_fwd_eligible(const niti_conv_desc*);
+bool tc_dx_eligible(const niti_conv_desc*);
+bool tc_dw_eligible(const niti_conv_desc*);
+int tc_conv_fwd_acc(niti_ctx*, const niti_conv_desc*, const int8_t*, const int8_t*, int32_t*, uint32_t*, cudaStream_t);
+int tc_conv_dx_acc(niti_ctx*, const niti_conv_desc*, const int8_t*, const int8_t*, int32_t*, uint32_t*, cudaStream_t);
+int tc_conv_dw_acc(niti_ctx*, const niti_conv_desc*, const int8_t*, const int8_t*, int32_t*, uint32_t*, cudaStream_t);
+int tc_probe_i8_peak(niti_ctx*, int iters, double* tops);
+
+int niti_fail(niti_ctx* ctx, int code, const char* what, cudaError_t e) {
+    if (ctx) {
+        if (e != cudaSuccess) snprintf(ctx->err, sizeof(ctx->err), "%s: %s", what, cudaGetErrorString(e));
+        else snprintf(ctx->err, sizeof(ctx->err), "%s", what);
+    }
+    return code;
+}
+
+int niti_check_launch(niti_ctx* ctx, const char* what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, what, e);
+    ctx->launches++;
+    return NITI_OK;
+}
+
+// Workspaces only grow, and only outside stream capture (cudaMalloc is not capturable): callers
+// that capture graphs warm up once eagerly, as the Python step and the MNN backend both do.
+int niti_ws_acc(niti_ctx* ctx, size_t bytes, int32_t** out) {
+    if (bytes > ctx->ws_acc_bytes) {
+        if (ctx->ws_acc) cudaFree(ctx->ws_acc);
+        ctx->ws_acc = nullptr; ctx->ws_acc_bytes = 0;
+        size_t want = bytes + bytes / 4;
+        cudaError_t e = cudaMalloc(&ctx->ws_acc, want);
+        if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "workspace (acc) cudaMalloc", e);
+        ctx->ws_acc_bytes = want;
+    }
+    *out = ctx->ws_acc;
+    return NITI_OK;
+}
+int niti_ws_i8(niti_ctx* ctx, size_t bytes, int8_t** out) {
+    if (bytes > ctx->ws_i8_bytes) {
+        if (ctx->ws_i8) cudaFree(ctx->ws_i8);
+        ctx->ws_i8 = nullptr; ctx->ws_i8_bytes = 0;
+        size_t want = bytes + bytes / 4;
+        cudaError_t e = cudaMalloc(&ctx->ws_i8, want);
+        if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "workspace (i8) cudaMalloc", e);
+        ctx->ws_i8_bytes = want;
+    }
+    *out = ctx->ws_i8;
+    return NITI_OK;
+}
+
+static bool desc_ok(const niti_conv_desc* d) {
+    if (!d) return false;
+    if (d->n <= 0 || d->c <= 0 || d->h <= 0 || d->w <= 0 || d->oc <= 0 || d->kh <= 0 || d->kw <= 0) return false;
+    if (d->stride <= 0 || d->dil <= 0 || d->pad < 0) return false;
+    return conv_out_h(d) > 0 && conv_out_w(d) > 0;
+}
+
+extern "C" {
+
+int niti_version(void) { return 100; }
+
+int niti_ctx_create(int device, niti_ctx** out) {
+    if (!out) return NITI_ERR_ARG;
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || device < 0 || device >= count) return NITI_ERR_CUDA;   // no CPU fallback
+    e = cudaSetDevice(device);
+    if (e != cudaSuccess) return NITI_ERR_CUDA;
+    cudaDeviceProp prop;
+    e = cudaGetDeviceProperties(&prop, device);
+    if (e != cudaSuccess) return NITI_ERR_CUDA;
+    niti_ctx* ctx = new (std::nothrow) niti_ctx();
+    if (!ctx) return NITI_ERR_CUDA;
+    memset(ctx, 0, sizeof(*ctx));
+    ctx->device = device;
+    ctx->sm_count = prop.multiProcessorCount;
+    ctx->path = NITI_PATH_AUTO;
+    const char* env = getenv("NITI_B200_PATH");
+    if (env && !strcmp(env, "simt")) ctx->path = NITI_PATH_SIMT;
+    if (env && !strcmp(env, "tc")) ctx->path = NITI_PATH_TC;
+    ctx->last_path = "none";
+    if (prop.major != 10) {
+        snprintf(ctx->err, sizeof(ctx->err), "device is sm_%d%d; this library is built for sm_100a only", prop.major, prop.minor);
+        delete ctx;
+        return NITI_ERR_UNSUPPORTED;
+    }
+    e = cudaMalloc(&ctx->ws_u32, 64 * sizeof(uint32_t));
+    if (e != cudaSuccess) { delete ctx; return NITI_ERR_CUDA; }
+    cudaMemset(ctx->ws_u32, 0, 64 * sizeof(uint32_t));
+    *out = ctx;
+    return NITI_OK;
+}
+
+int niti_ctx_destroy(niti_ctx* ctx) {
+    if (!ctx) return NITI_ERR_ARG;
+    cudaSetDevice(ctx->device);
+    if (ctx->ws_acc) cudaFree(ctx->ws_acc);
+    if (ctx->ws_i8) cudaFree(ctx->ws_i8);
+    if (ctx->ws_u32) cudaFree(ctx->ws_u32);
+    delete ctx;
+    return NITI_OK;
+}
+
+const char* niti_last_error(niti_ctx* ctx) { return ctx ? ctx->err : "null context"; }
+int niti_set_path(niti_ctx* ctx, int path) {
+    if (!ctx || path < NITI_PATH_AUTO || path > NITI_PATH_TC) return NITI_ERR_ARG;
+    ctx->path = path; return NITI_OK;
+}
+int64_t niti_launch_count(niti_ctx* ctx) { return ctx ? ctx->launches : -1; }
+const char* niti_last_path(niti_ctx* ctx) { return ctx ? ctx->last_path : "none"; }
+
+// ---- phase 1 ------------------------------------------------------------------------------------
+int niti_conv_fwd_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, const int8_t* w, int32_t* acc,
+                      uint32_t* maxabs, niti_stream st) {
+    if (!ctx || !desc_ok(d) || !x || !w || !acc) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_fwd_acc: bad argument");
+    bool tc = tc_fwd_eligible(d);
+    if (ctx->path == NITI_PATH_TC && !tc) return niti_fail(ctx, NITI_ERR_UNSUPPORTED, "conv_fwd: shape not eligible for tcgen05 path");
+    if (ctx->path == NITI_PATH_SIMT) tc = false;
+    ctx->last_path = tc ? "tc" : "simt";
+    return tc ? tc_conv_fwd_acc(ctx, d, x, w, acc, maxabs, (cudaStream_t)st)
+              : simt_conv_fwd_acc(ctx, d, x, w, acc, maxabs, (cudaStream_t)st);
+}
+
+int niti_conv_dx_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* dy, const int8_t* w, int32_t* acc,
+                     uint32_t* maxabs, niti_stream st) {
+    if (!ctx || !desc_ok(d) || !dy || !w || !acc) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_dx_acc: bad argument");
+    bool tc = tc_dx_eligible(d);
+    if (ctx->path == NITI_PATH_TC && !tc) return niti_fail(ctx, NITI_ERR_UNSUPPORTED, "conv_dx: shape not eligible for tcgen05 path");
+    if (ctx->path == NITI_PATH_SIMT) tc = false;
+    ctx->last_path = tc ? "tc" : "simt";
+    return tc ? tc_conv_dx_acc(ctx, d, dy, w, acc, maxabs, (cudaStream_t)st)
+              : simt_conv_dx_acc(ctx, d, dy, w, acc, maxabs, (cudaStream_t)st);
+}
+
+int niti_conv_dw_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, const int8_t* dy, int32_t* acc,
+                     uint32_t* maxabs, niti_stream st) {
+    if (!ctx || !desc_ok(d) || !x || !dy || !acc) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_dw_acc: bad argument");
+    bool tc = tc_dw_eligible(d);
+    if (ctx->path == NITI_PATH_TC && !tc) return niti_fail(ctx, NITI_ERR_UNSUPPORTED, "conv_dw: shape not eligible for tcgen05 path");
+    if (ctx->path == NITI_PATH_SIMT) tc = false;
+    ctx->last_path = tc ? "tc" : "simt";
+    return tc ? tc_conv_dw_acc(ctx, d, x, dy, acc, maxabs, (cudaStream_t)st)
+              : simt_conv_dw_acc(ctx, d, x, dy, acc, maxabs, (cudaStream_t)st);
+}
+
+// C[e,h] = sum_l A[e,l] B[h,l]  ==  1x1 convolution with e "pixels", l channels, h outputs
+int niti_matmul_nt_acc(niti_ctx* ctx, int e, int h, int l, const int8_t* a, const int8_t* b, int32_t* acc,
+                       uint32_t* maxabs, niti_stream st) {
+    if (!ctx || e <= 0 || h <= 0 || l <= 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_matmul_nt_acc: bad argument");
+    niti_conv_desc d{e, l, 1, 1, h, 1, 1, 1, 0, 1};
+    return niti_conv_fwd_acc(ctx, &d, a, b, acc, maxabs, st);
+}
+
+// ---- whole ops ------------------------------------------------------------------------------------
+int niti_conv_fwd(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, const int8_t* w, const int8_t* ex,
+                  const int8_t* ew, int8_t* y, int8_t* ey, niti_stream st) {
+    if (!ctx || !desc_ok(d) || !y) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_fwd: bad argument");
+    size_t n = (size_t)d->n * conv_out_h(d) * conv_out_w(d) * d->oc;
+    int32_t* acc; int rc = niti_ws_acc(ctx, n * 4, &acc); if (rc) return rc;
+    if ((rc = niti_zero_u32(ctx, ctx->ws_u32, 1, st))) return rc;
+    if ((rc = niti_conv_fwd_acc(ctx, d, x, w, acc, ctx->ws_u32, st))) return rc;
+    return niti_rescale_act(ctx, acc, n, ctx->ws_u32, y, ex, ew, ey, st);
+}
+
+int niti_conv_dx(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* dy, const int8_t* w, int8_t* dx, niti_stream st) {
+    if (!ctx || !desc_ok(d) || !dx) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_dx: bad argument");
+    size_t n = (size_t)d->n * d->h * d->w * d->c;
+    int32_t* acc; int rc = niti_ws_acc(ctx, n * 4, &acc); if (rc) return rc;
+    if ((rc = niti_zero_u32(ctx, ctx->ws_u32, 1, st))) return rc;
+    if ((rc = niti_conv_dx_acc(ctx, d, dy, w, acc, ctx->ws_u32, st))) return rc;
+    return niti_rescale_act(ctx, acc, n, ctx->ws_u32, dx, nullptr, nullptr, nullptr, st);
+}
+
+int niti_conv_dw(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, const int8_t* dy, int8_t* dw, niti_stream st) {
+    if (!ctx || !desc_ok(d) || !dw) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_dw: bad argument");
+    size_t n = (size_t)d->oc * d->kh * d->kw * d->c;
+    int32_t* acc; int rc = niti_ws_acc(ctx, n * 4, &acc); if (rc) return rc;
+    if ((rc = niti_zero_u32(ctx, ctx->ws_u32, 1, st))) return rc;
+    if ((rc = niti_conv_dw_acc(ctx, d, x, dy, acc, ctx->ws_u32, st))) return rc;
+    return niti_rescale_grad(ctx, acc, n, ctx->ws_u32, 2, dw, nullptr, st);
+}
+
+int niti_matmul_nt(niti_ctx* ctx, int e, int h, int l, const int8_t* a, const int8_t* b, int8_t* c, niti_stream st) {
+    if (!ctx || e <= 0 || h <= 0 || l <= 0 || !c) return niti_fail(ctx, NITI_ERR_ARG, "niti_matmul_nt: bad argument");
+    size_t n = (size_t)e * h;
+    int32_t* acc; int rc = niti_ws_acc(ctx, n * 4, &acc); if (rc) return rc;
+    if ((rc = niti_zero_u32(ctx, ctx->ws_u32, 1, st))) return rc;
+    if ((rc = niti_matmul_nt_acc(ctx, e, h, l, a, b, acc, ctx->ws_u32, st))) return rc;
+    return niti_rescale_grad(ctx, acc, n, ctx->ws_u32, 3, c, nullptr, st);
+}
+
+// ---- host-buffer convenience: the reference-facing call shape (host tensors in, host tensors out) --
+int niti_conv_fwd_host(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, const int8_t* w, int8_t ex, int8_t ew,
+                       int8_t* y, int8_t* ey) {
+    if (!ctx || !desc_ok(d) || !x || !w || !y) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_fwd_host: bad argument");
+    size_t nx = (size_t)d->n * d->h * d->w * d->c, nw = (size_t)d->oc * d->kh * d->kw * d->c;
+    size_t ny = (size_t)d->n * conv_out_h(d) * conv_out_w(d) * d->oc;
+    auto up = [](size_t v) { return (v + 255) / 256 * 256; };
+    int8_t* buf; int rc = niti_ws_i8(ctx, up(nx) + up(nw) + up(ny) + 256, &buf); if (rc) return rc;
+    int8_t *dx = buf, *dw = buf + up(nx), *dyv = dw + up(nw), *dexp = dyv + up(ny);
+    cudaError_t e;
+    if ((e = cudaMemcpyAsync(dx, x, nx, cudaMemcpyHostToDevice, 0)) != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "H2D x", e);
+    if ((e = cudaMemcpyAsync(dw, w, nw, cudaMemcpyHostToDevice, 0)) != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "H2D w", e);
+    int8_t hexp[2] = {ex, ew};
+    if ((e = cudaMemcpyAsync(dexp, hexp, 2, cudaMemcpyHostToDevice, 0)) != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "H2D exp", e);
+    if ((rc = niti_conv_fwd(ctx, d, dx, dw, dexp, dexp + 1, dyv, dexp + 2, 0))) return rc;
+    if ((e = cudaMemcpyAsync(y, dyv, ny, cudaMemcpyDeviceToHost, 0)) != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "D2H y", e);
+    int8_t out_e = 0;
+    if ((e = cudaMemcpyAsync(&out_e, dexp + 2, 1, cudaMemcpyDeviceToHost, 0)) != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "D2H exp", e);
+    if ((e = cudaStreamSynchronize(0)) != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "sync", e);
+    if (ey) *ey = out_e;
+    return NITI_OK;
+}
+
+int niti_probe_i8_peak(niti_ctx* ctx, int iters, double* tops_out) {
+    if (!ctx || !tops_out || iters <= 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_probe_i8_peak");
+    return tc_probe_i8_peak(ctx, iters, tops_out);
+}
+
+} // extern "C"

@@ -1,0 +1,87 @@
+// common.cuh — shared device helpers for libniti_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/niti_b200.h"
+
+#ifndef NITI_DEVICE_INLINE
+#define NITI_DEVICE_INLINE __device__ __forceinline__
+#endif
+
+struct niti_ctx {
+    int device;
+    int sm_count;
+    int path;                 // NITI_PATH_*
+    int64_t launches;
+    const char* last_path;
+    char err[256];
+    // workspace for the whole-op entry points
+    int32_t* ws_acc;  size_t ws_acc_bytes;
+    uint32_t* ws_u32;         // [0] max-abs slot of whole-op calls
+    int8_t* ws_i8;    size_t ws_i8_bytes;   // transposed weights for dX, host-call staging
+};
+
+int  niti_fail(niti_ctx* ctx, int code, const char* what, cudaError_t e = cudaSuccess);
+int  niti_check_launch(niti_ctx* ctx, const char* what);
+int  niti_ws_acc(niti_ctx* ctx, size_t bytes, int32_t** out);
+int  niti_ws_i8(niti_ctx* ctx, size_t bytes, int8_t** out);
+
+static inline int conv_out_h(const niti_conv_desc* d) {
+    return (d->h + 2 * d->pad - (d->dil * (d->kh - 1) + 1)) / d->stride + 1;
+}
+static inline int conv_out_w(const niti_conv_desc* d) {
+    return (d->w + 2 * d->pad - (d->dil * (d->kw - 1) + 1)) / d->stride + 1;
+}
+
+// ---------------------------------------------------------------------------------------------
+// NITI rescale arithmetic (device).  Restates compute/CommonOptFunction.cpp:1548-1627 of the
+// reference in unsigned form: C's `/` truncates toward zero, so x / 2^s == sign(x) * (|x| >> s)
+// and |x - q*2^s| == |x| & (2^s - 1).
+// ---------------------------------------------------------------------------------------------
+
+// ceil(log2(m)), 0 for m in {0,1}   (NITI_RangeEstimate, CommonOptFunction.cpp:1565-1576)
+NITI_DEVICE_INLINE int niti_bitwidth(uint32_t m) { return m <= 1u ? 0 : 32 - __clz(m - 1u); }
+
+// `1 << s` as the reference's x86-64 build evaluates it (count masked to 5 bits)
+NITI_DEVICE_INLINE int32_t niti_shl1(int s) { return (int32_t)(1u << ((unsigned)s & 31u)); }
+
+// NITI_MNNPstoShiftInt32 for shift >= 2 (the hot case)
+NITI_DEVICE_INLINE int32_t niti_psto_fast(int32_t x, int shift) {
+    const uint32_t ax = (uint32_t)(x < 0 ? -x : x);
+    const int hs = shift >> 1;
+    const uint32_t q = ax >> shift;
+    const uint32_t rem = ax & ((1u << shift) - 1u);
+    const uint32_t hi = rem >> hs;
+    uint32_t lo = rem & ((1u << hs) - 1u);
+    lo <<= (shift & 1);
+    uint32_t r = q + (hi > lo ? 1u : 0u);
+    r = r > 127u ? 127u : r;
+    return x < 0 ? -(int32_t)r : (int32_t)r;
+}
+
+// NITI_MNNPstoShiftInt32 for any shift, literal restatement (covers shift in {-2..1}, where the
+// reference's `1 << shift` wraps; see oracle/niti_oracle.c shl1)
+NITI_DEVICE_INLINE int32_t niti_psto_general(int32_t x, int shift) {
+    const int32_t full = niti_shl1(shift);
+    const int32_t half = niti_shl1(shift / 2);
+    const bool odd = (shift % 2) == 1;
+    // full/half are powers of two or INT_MIN; emulate idiv semantics without UB
+    int32_t q = (full == INT32_MIN) ? (x == INT32_MIN ? 1 : 0) : x / full;
+    int32_t prob = x - q * full;
+    prob = prob < 0 ? -prob : prob;
+    int32_t hi = (half == INT32_MIN) ? 0 : prob / half;
+    int32_t lo = prob - hi * half;
+    if (odd) lo *= 2;
+    int32_t r = q + ((hi > lo) ? (x > 0 ? 1 : (x < 0 ? -1 : 0)) : 0);
+    return r > 127 ? 127 : (r < -127 ? -127 : r);
+}
+
+NITI_DEVICE_INLINE int32_t niti_psto(int32_t x, int shift) {
+    return shift >= 2 ? niti_psto_fast(x, shift) : niti_psto_general(x, shift);
+}
+
+NITI_DEVICE_INLINE uint32_t niti_abs_u32(int32_t v) { return (uint32_t)(v < 0 ? -v : v); }
+
+NITI_DEVICE_INLINE uint32_t warp_max_u32(uint32_t v) {
+    return __reduce_max_sync(0xffffffffu, v);
+}

@@ -1,0 +1,246 @@
+// elementwise.cu — the non-contraction int8 ops of the NITI training step and
+// the layout conversions at the boundary.  All HBM-bound byte work on NHWC tensors.
+//
+// Reference behaviour restated (execution-engine/source/backend/cpu/):
+//   NITI_CPURelu_Int8.cpp:47-53, NITI_CPUReluGrad_Int8.cpp:51-57, NITI_Maxpool_Int8.cpp:24-70,
+//   NITI_CPUPoolGrad_Int8.cpp:36-72, NITI_CPULossGrad_Int8.cpp:82-201
+#include "common.cuh"
+
+namespace {
+constexpr int kThreads = 256;
+
+int grid_for(niti_ctx* ctx, size_t items) {
+    size_t blocks = (items + kThreads - 1) / kThreads;
+    size_t cap = (size_t)ctx->sm_count * 8;
+    if (blocks > cap) blocks = cap;
+    return (int)(blocks < 1 ? 1 : blocks);
+}
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// per-byte signed max with zero (relu) on packed int8x4
+__device__ __forceinline__ uint32_t relu4(uint32_t v) { return __vmaxs4(v, 0u); }
+// mask bytes of dy where x > 0
+__device__ __forceinline__ uint32_t relu_grad4(uint32_t x, uint32_t dy) {
+    uint32_t m = __vcmpgts4(x, 0u);     // 0xff where x > 0 (signed)
+    return dy & m;
+}
+
+__global__ void __launch_bounds__(kThreads) relu_kernel(const int8_t* __restrict__ x, int8_t* __restrict__ y, size_t n, bool vec) {
+    if (vec) {
+        const size_t ng = n / 16;
+        for (size_t g = blockIdx.x * (size_t)blockDim.x + threadIdx.x; g < ng; g += (size_t)gridDim.x * blockDim.x) {
+            uint4 v = reinterpret_cast<const uint4*>(x)[g];
+            reinterpret_cast<uint4*>(y)[g] = make_uint4(relu4(v.x), relu4(v.y), relu4(v.z), relu4(v.w));
+        }
+        if (blockIdx.x == 0)
+            for (size_t i = ng * 16 + threadIdx.x; i < n; i += blockDim.x) y[i] = x[i] >= 0 ? x[i] : (int8_t)0;
+    } else {
+        for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+            y[i] = x[i] >= 0 ? x[i] : (int8_t)0;
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) relu_grad_kernel(const int8_t* __restrict__ x, const int8_t* __restrict__ dy,
+                                                             int8_t* __restrict__ dx, size_t n, bool vec) {
+    if (vec) {
+        const size_t ng = n / 16;
+        for (size_t g = blockIdx.x * (size_t)blockDim.x + threadIdx.x; g < ng; g += (size_t)gridDim.x * blockDim.x) {
+            uint4 a = reinterpret_cast<const uint4*>(x)[g];
+            uint4 d = reinterpret_cast<const uint4*>(dy)[g];
+            reinterpret_cast<uint4*>(dx)[g] = make_uint4(relu_grad4(a.x, d.x), relu_grad4(a.y, d.y),
+                                                         relu_grad4(a.z, d.z), relu_grad4(a.w, d.w));
+        }
+        if (blockIdx.x == 0)
+            for (size_t i = ng * 16 + threadIdx.x; i < n; i += blockDim.x) dx[i] = x[i] > 0 ? dy[i] : (int8_t)0;
+    } else {
+        for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+            dx[i] = x[i] > 0 ? dy[i] : (int8_t)0;
+    }
+}
+
+// NHWC max pooling, window clipped to the image; one thread per output element (c fastest => coalesced)
+__global__ void __launch_bounds__(kThreads) maxpool_kernel(const int8_t* __restrict__ x, int n, int h, int w, int c,
+                                                           int k, int s, int oh, int ow, int8_t* __restrict__ y) {
+    const size_t total = (size_t)n * oh * ow * c;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        int ch = (int)(i % c); size_t p = i / c;
+        int ox = (int)(p % ow); p /= ow;
+        int oy = (int)(p % oh); int b = (int)(p / oh);
+        int m = -128;
+        for (int ky = 0; ky < k; ++ky) {
+            int iy = oy * s + ky; if (iy >= h) break;
+            for (int kx = 0; kx < k; ++kx) {
+                int ix = ox * s + kx; if (ix >= w) break;
+                int v = x[(((size_t)b * h + iy) * w + ix) * c + ch];
+                m = v > m ? v : m;
+            }
+        }
+        y[i] = (int8_t)m;
+    }
+}
+
+// First window element (row-major) with value >= max takes the gradient.  For non-overlapping
+// windows (s >= k, the only case the reference's models use) each input element belongs to one
+// window, so a gather formulation is exact: thread per input element.
+// For overlapping windows the contributions accumulate with int8 wrap-around, also reproduced.
+__global__ void __launch_bounds__(kThreads) maxpool_grad_kernel(const int8_t* __restrict__ x, const int8_t* __restrict__ y,
+                                                                const int8_t* __restrict__ dy, int n, int h, int w, int c,
+                                                                int k, int s, int oh, int ow, int8_t* __restrict__ dx) {
+    const size_t total = (size_t)n * h * w * c;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        int ch = (int)(i % c); size_t p = i / c;
+        int ix = (int)(p % w); p /= w;
+        int iy = (int)(p % h); int b = (int)(p / h);
+        int acc = 0;
+        const int v = x[i];
+        // windows (oy, ox) that contain (iy, ix): oy*s <= iy < oy*s + k
+        int oy_hi = iy / s, ox_hi = ix / s;
+        int oy_lo = (iy - k + s) / s; if (iy - k + 1 <= 0) oy_lo = 0;
+        int ox_lo = (ix - k + s) / s; if (ix - k + 1 <= 0) ox_lo = 0;
+        for (int oy = oy_lo; oy <= oy_hi && oy < oh; ++oy)
+            for (int ox = ox_lo; ox <= ox_hi && ox < ow; ++ox) {
+                size_t o = (((size_t)b * oh + oy) * ow + ox) * c + ch;
+                int m = y[o];
+                if (v < m) continue;
+                // am I the first element >= m in row-major window order?
+                bool first = true;
+                for (int ky = 0; ky < k && first; ++ky) {
+                    int yy = oy * s + ky; if (yy >= h) break;
+                    for (int kx = 0; kx < k; ++kx) {
+                        int xx = ox * s + kx; if (xx >= w) break;
+                        if (yy == iy && xx == ix) { ky = k; break; }
+                        if (x[(((size_t)b * h + yy) * w + xx) * c + ch] >= m) { first = false; break; }
+                    }
+                }
+                if (first) acc += dy[o];
+            }
+        dx[i] = (int8_t)acc;
+    }
+}
+
+// integer softmax cross-entropy gradient; one thread per sample (batch is small, classes ~10)
+__global__ void loss_grad_kernel(const int8_t* __restrict__ logits, const int8_t* __restrict__ ascale_p,
+                                 const int32_t* __restrict__ labels, int batch, int classes, int8_t* __restrict__ grad) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= batch) return;
+    const int a = (int)*ascale_p;
+    const int8_t* row = logits + (size_t)i * classes;
+    int8_t* out = grad + (size_t)i * classes;
+    long long sum = 0;
+    long long mx = 0;
+    if (a > -7) {
+        for (int j = 0; j < classes; ++j) {
+            long long t = (long long)row[j] * 47274; t = t / (1 << 15);
+            t = (a >= 0) ? t * (1 << a) : t / (1 << (-a));
+            if (j == 0 || mx < t) mx = t;
+        }
+        mx -= 10;
+    }
+    const long long base = (long long)niti_shl1(1 - 2 * a), shiftbase = (long long)niti_shl1(1 - a);
+    auto ev = [&](int j) -> long long {
+        if (a > -7) {
+            long long t = (long long)row[j] * 47274; t = t / (1 << 15);
+            t = (a >= 0) ? t * (1 << a) : t / (1 << (-a));
+            t -= mx; t = t > 0 ? t : 0;
+            return (long long)((1 << (int)t) - 1);
+        }
+        long long t = row[j];
+        return base + t * shiftbase + t * t;
+    };
+    for (int j = 0; j < classes; ++j) sum += ev(j);
+    long long gsum = 0;
+    for (int j = 0; j < classes; ++j) gsum += (ev(j) * (1 << 11)) / sum;
+    const int tgt = labels[i];
+    for (int j = 0; j < classes; ++j) {
+        long long g = (ev(j) * (1 << 11)) / sum;
+        if (j == tgt) g -= gsum;
+        out[j] = (int8_t)niti_psto((int32_t)g, 4);
+    }
+}
+
+// generic 4-d permutation of int8 tensors through index arithmetic (boundary only; small tensors)
+// dst[a][b][c][d] (sizes A,B,C,D) = src[a*sa + b*sb + c*sc + d*sd]
+__global__ void __launch_bounds__(kThreads) permute_kernel(const int8_t* __restrict__ src, int8_t* __restrict__ dst,
+                                                           int A, int B, int C, int D, long sa, long sb, long sc, long sd) {
+    const size_t total = (size_t)A * B * C * D;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        int d = (int)(i % D); size_t p = i / D;
+        int c = (int)(p % C); p /= C;
+        int b = (int)(p % B); int a = (int)(p / B);
+        dst[i] = src[a * sa + b * sb + c * sc + d * sd];
+    }
+}
+
+// reference "NC4HW4" int8 (batch inside the channel block): [c/4][n][h*w][4]
+__global__ void __launch_bounds__(kThreads) nc4_to_nhwc_kernel(const int8_t* __restrict__ src, int n, int c, int hw,
+                                                               int8_t* __restrict__ dst, bool to_nc4) {
+    const int c4 = (c + 3) / 4;
+    const size_t total = (size_t)c4 * n * hw * 4;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        int l = (int)(i & 3); size_t p = i >> 2;
+        int px = (int)(p % hw); p /= hw;
+        int b = (int)(p % n); int cb = (int)(p / n);
+        int ch = cb * 4 + l;
+        size_t nhwc = ((size_t)b * hw + px) * c + ch;
+        if (to_nc4) dst[i] = ch < c ? src[nhwc] : (int8_t)0;
+        else if (ch < c) dst[nhwc] = src[i];
+    }
+}
+} // namespace
+
+extern "C" int niti_relu(niti_ctx* ctx, const int8_t* x, int8_t* y, size_t n, niti_stream st) {
+    if (!ctx || (n && (!x || !y))) return niti_fail(ctx, NITI_ERR_ARG, "niti_relu");
+    if (!n) return NITI_OK;
+    bool vec = aligned16(x) && aligned16(y);
+    relu_kernel<<<grid_for(ctx, vec ? n / 16 + 1 : n), kThreads, 0, (cudaStream_t)st>>>(x, y, n, vec);
+    return niti_check_launch(ctx, "relu");
+}
+extern "C" int niti_relu_grad(niti_ctx* ctx, const int8_t* x, const int8_t* dy, int8_t* dx, size_t n, niti_stream st) {
+    if (!ctx || (n && (!x || !dy || !dx))) return niti_fail(ctx, NITI_ERR_ARG, "niti_relu_grad");
+    if (!n) return NITI_OK;
+    bool vec = aligned16(x) && aligned16(dy) && aligned16(dx);
+    relu_grad_kernel<<<grid_for(ctx, vec ? n / 16 + 1 : n), kThreads, 0, (cudaStream_t)st>>>(x, dy, dx, n, vec);
+    return niti_check_launch(ctx, "relu_grad");
+}
+extern "C" int niti_maxpool(niti_ctx* ctx, const int8_t* x, int n, int h, int w, int c, int k, int s, int8_t* y, niti_stream st) {
+    if (!ctx || !x || !y || n <= 0 || h < k || w < k || c <= 0 || k <= 0 || s <= 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_maxpool");
+    int oh = (h - k) / s + 1, ow = (w - k) / s + 1;
+    maxpool_kernel<<<grid_for(ctx, (size_t)n * oh * ow * c), kThreads, 0, (cudaStream_t)st>>>(x, n, h, w, c, k, s, oh, ow, y);
+    return niti_check_launch(ctx, "maxpool");
+}
+extern "C" int niti_maxpool_grad(niti_ctx* ctx, const int8_t* x, const int8_t* y, const int8_t* dy, int n, int h, int w, int c,
+                                 int k, int s, int8_t* dx, niti_stream st) {
+    if (!ctx || !x || !y || !dy || !dx || n <= 0 || h < k || w < k || c <= 0 || k <= 0 || s <= 0)
+        return niti_fail(ctx, NITI_ERR_ARG, "niti_maxpool_grad");
+    int oh = (h - k) / s + 1, ow = (w - k) / s + 1;
+    maxpool_grad_kernel<<<grid_for(ctx, (size_t)n * h * w * c), kThreads, 0, (cudaStream_t)st>>>(x, y, dy, n, h, w, c, k, s, oh, ow, dx);
+    return niti_check_launch(ctx, "maxpool_grad");
+}
+extern "C" int niti_loss_grad(niti_ctx* ctx, const int8_t* logits, const int8_t* ascale, const int32_t* labels,
+                              int batch, int classes, int8_t* grad, niti_stream st) {
+    if (!ctx || !logits || !ascale || !labels || !grad || batch <= 0 || classes <= 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_loss_grad");
+    loss_grad_kernel<<<(batch + 63) / 64, 64, 0, (cudaStream_t)st>>>(logits, ascale, labels, batch, classes, grad);
+    return niti_check_launch(ctx, "loss_grad");
+}
+extern "C" int niti_nchw_to_nhwc(niti_ctx* ctx, const int8_t* src, int n, int c, int h, int w, int8_t* dst, niti_stream st) {
+    if (!ctx || !src || !dst || n <= 0 || c <= 0 || h <= 0 || w <= 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_nchw_to_nhwc");
+    permute_kernel<<<grid_for(ctx, (size_t)n * c * h * w), kThreads, 0, (cudaStream_t)st>>>(
+        src, dst, n, h, w, c, (long)c * h * w, (long)w, 1L, (long)h * w);
+    return niti_check_launch(ctx, "nchw_to_nhwc");
+}
+extern "C" int niti_nhwc_to_nchw(niti_ctx* ctx, const int8_t* src, int n, int c, int h, int w, int8_t* dst, niti_stream st) {
+    if (!ctx || !src || !dst || n <= 0 || c <= 0 || h <= 0 || w <= 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_nhwc_to_nchw");
+    permute_kernel<<<grid_for(ctx, (size_t)n * c * h * w), kThreads, 0, (cudaStream_t)st>>>(
+        src, dst, n, c, h, w, (long)h * w * c, 1L, (long)w * c, (long)c);
+    return niti_check_launch(ctx, "nhwc_to_nchw");
+}
+extern "C" int niti_nc4hw4_to_nhwc(niti_ctx* ctx, const int8_t* src, int n, int c, int h, int w, int8_t* dst, niti_stream st) {
+    if (!ctx || !src || !dst || n <= 0 || c <= 0 || h <= 0 || w <= 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_nc4hw4_to_nhwc");
+    nc4_to_nhwc_kernel<<<grid_for(ctx, (size_t)((c + 3) / 4) * n * h * w * 4), kThreads, 0, (cudaStream_t)st>>>(src, n, c, h * w, dst, false);
+    return niti_check_launch(ctx, "nc4hw4_to_nhwc");
+}
+extern "C" int niti_nhwc_to_nc4hw4(niti_ctx* ctx, const int8_t* src, int n, int c, int h, int w, int8_t* dst, niti_stream st) {
+    if (!ctx || !src || !dst || n <= 0 || c <= 0 || h <= 0 || w <= 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_nhwc_to_nc4hw4");
+    nc4_to_nhwc_kernel<<<grid_for(ctx, (size_t)((c + 3) / 4) * n * h * w * 4), kThreads, 0, (cudaStream_t)st>>>(src, n, c, h * w, dst, true);
+    return niti_check_launch(ctx, "nhwc_to_nc4hw4");
+}

@@ -1,0 +1,219 @@
+"""ctypes binding of libniti_b200.so (include/niti_b200.h).  No fallback: importing works anywhere,
+but creating a context without the built library or without a B200 raises NitiError."""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIBPATH = os.path.join(_HERE, "libniti_b200.so")
+
+PATH_AUTO, PATH_SIMT, PATH_TC = 0, 1, 2
+
+
+class NitiError(RuntimeError):
+    pass
+
+
+class ConvDesc(C.Structure):
+    """niti_conv_desc: input [n,h,w,c] NHWC, weight [oc,kh,kw,c] OHWI"""
+    _fields_ = [(k, C.c_int32) for k in ("n", "c", "h", "w", "oc", "kh", "kw", "stride", "pad", "dil")]
+
+    @property
+    def oh(self):
+        return (self.h + 2 * self.pad - (self.dil * (self.kh - 1) + 1)) // self.stride + 1
+
+    @property
+    def ow(self):
+        return (self.w + 2 * self.pad - (self.dil * (self.kw - 1) + 1)) // self.stride + 1
+
+
+def desc(n, c, h, w, oc, kh, kw=None, stride=1, pad=0, dil=1):
+    return ConvDesc(n, c, h, w, oc, kh, kh if kw is None else kw, stride, pad, dil)
+
+
+_P = C.c_void_p
+_SIGS = {
+    "niti_ctx_create": (C.c_int, [C.c_int, C.POINTER(_P)]),
+    "niti_ctx_destroy": (C.c_int, [_P]),
+    "niti_last_error": (C.c_char_p, [_P]),
+    "niti_set_path": (C.c_int, [_P, C.c_int]),
+    "niti_version": (C.c_int, []),
+    "niti_launch_count": (C.c_int64, [_P]),
+    "niti_last_path": (C.c_char_p, [_P]),
+    "niti_conv_fwd_acc": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P]),
+    "niti_conv_dx_acc": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P]),
+    "niti_conv_dw_acc": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P]),
+    "niti_matmul_nt_acc": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P, _P, _P, _P]),
+    "niti_zero_u32": (C.c_int, [_P, _P, C.c_int, _P]),
+    "niti_absmax": (C.c_int, [_P, _P, C.c_size_t, _P, _P]),
+    "niti_rescale_act": (C.c_int, [_P, _P, C.c_size_t, _P, _P, _P, _P, _P, _P]),
+    "niti_rescale_grad": (C.c_int, [_P, _P, C.c_size_t, _P, C.c_int, _P, _P, _P]),
+    "niti_sgd_update": (C.c_int, [_P, _P, _P, C.c_size_t, _P]),
+    "niti_conv_fwd": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, _P]),
+    "niti_conv_dx": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P]),
+    "niti_conv_dw": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P]),
+    "niti_matmul_nt": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P, _P, _P]),
+    "niti_relu": (C.c_int, [_P, _P, _P, C.c_size_t, _P]),
+    "niti_relu_grad": (C.c_int, [_P, _P, _P, _P, C.c_size_t, _P]),
+    "niti_maxpool": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
+    "niti_maxpool_grad": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
+    "niti_loss_grad": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, _P, _P]),
+    "niti_nchw_to_nhwc": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
+    "niti_nhwc_to_nchw": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
+    "niti_nc4hw4_to_nhwc": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
+    "niti_nhwc_to_nc4hw4": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
+    "niti_conv_fwd_host": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, C.c_int8, C.c_int8, _P, _P]),
+    "niti_probe_i8_peak": (C.c_int, [_P, C.c_int, C.POINTER(C.c_double)]),
+}
+EXPORTED_SYMBOLS = tuple(_SIGS)
+
+
+def load_library(path=_LIBPATH):
+    if not os.path.exists(path):
+        raise NitiError(f"{path} is not built: run `python -m mandheling_dsp_training_b200.build` "
+                        "(there is no CPU fallback)")
+    lib = C.CDLL(path)
+    for name, (res, args) in _SIGS.items():
+        fn = getattr(lib, name)
+        fn.restype, fn.argtypes = res, args
+    return lib
+
+
+def _ptr(t):
+    """device pointer of a torch tensor (or None / int passthrough)"""
+    if t is None:
+        return None
+    if isinstance(t, int):
+        return t
+    return t.data_ptr()
+
+
+class NitiB200:
+    """One context per device.  Methods take torch CUDA tensors (int8 / int32 / uint32-as-int32) and
+    enqueue on the given (default: torch current) stream; nothing synchronizes."""
+
+    def __init__(self, device=0):
+        self.lib = load_library()
+        h = _P()
+        rc = self.lib.niti_ctx_create(int(device), C.byref(h))
+        if rc != 0:
+            raise NitiError(f"niti_ctx_create(device={device}) failed with code {rc}: no usable sm_100a "
+                            "device (there is no CPU fallback)")
+        self.h = h
+        self.device = int(device)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.niti_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _stream(self, stream):
+        if stream is not None:
+            return stream
+        import torch
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise NitiError(f"code {rc}: {self.lib.niti_last_error(self.h).decode()}")
+
+    def set_path(self, path):
+        self._ck(self.lib.niti_set_path(self.h, path))
+
+    @property
+    def launches(self):
+        return self.lib.niti_launch_count(self.h)
+
+    @property
+    def last_path(self):
+        return self.lib.niti_last_path(self.h).decode()
+
+    # ---- phase 1
+    def conv_fwd_acc(self, d, x, w, acc, maxabs=None, stream=None):
+        self._ck(self.lib.niti_conv_fwd_acc(self.h, C.byref(d), _ptr(x), _ptr(w), _ptr(acc), _ptr(maxabs), self._stream(stream)))
+
+    def conv_dx_acc(self, d, dy, w, acc, maxabs=None, stream=None):
+        self._ck(self.lib.niti_conv_dx_acc(self.h, C.byref(d), _ptr(dy), _ptr(w), _ptr(acc), _ptr(maxabs), self._stream(stream)))
+
+    def conv_dw_acc(self, d, x, dy, acc, maxabs=None, stream=None):
+        self._ck(self.lib.niti_conv_dw_acc(self.h, C.byref(d), _ptr(x), _ptr(dy), _ptr(acc), _ptr(maxabs), self._stream(stream)))
+
+    def matmul_nt_acc(self, e, h, l, a, b, acc, maxabs=None, stream=None):
+        self._ck(self.lib.niti_matmul_nt_acc(self.h, e, h, l, _ptr(a), _ptr(b), _ptr(acc), _ptr(maxabs), self._stream(stream)))
+
+    # ---- phase 2
+    def zero_u32(self, p, count=1, stream=None):
+        self._ck(self.lib.niti_zero_u32(self.h, _ptr(p), count, self._stream(stream)))
+
+    def absmax(self, acc, n, maxabs, stream=None):
+        self._ck(self.lib.niti_absmax(self.h, _ptr(acc), n, _ptr(maxabs), self._stream(stream)))
+
+    def rescale_act(self, acc, n, maxabs, out, exp_a=None, exp_b=None, exp_out=None, stream=None):
+        self._ck(self.lib.niti_rescale_act(self.h, _ptr(acc), n, _ptr(maxabs), _ptr(out), _ptr(exp_a), _ptr(exp_b),
+                                           _ptr(exp_out), self._stream(stream)))
+
+    def rescale_grad(self, acc, n, maxabs, sub, dw_out=None, w_inout=None, stream=None):
+        self._ck(self.lib.niti_rescale_grad(self.h, _ptr(acc), n, _ptr(maxabs), sub, _ptr(dw_out), _ptr(w_inout),
+                                            self._stream(stream)))
+
+    def sgd_update(self, w, dw, n, stream=None):
+        self._ck(self.lib.niti_sgd_update(self.h, _ptr(w), _ptr(dw), n, self._stream(stream)))
+
+    # ---- whole ops
+    def conv_fwd(self, d, x, w, ex, ew, y, ey, stream=None):
+        self._ck(self.lib.niti_conv_fwd(self.h, C.byref(d), _ptr(x), _ptr(w), _ptr(ex), _ptr(ew), _ptr(y), _ptr(ey), self._stream(stream)))
+
+    def conv_dx(self, d, dy, w, dx, stream=None):
+        self._ck(self.lib.niti_conv_dx(self.h, C.byref(d), _ptr(dy), _ptr(w), _ptr(dx), self._stream(stream)))
+
+    def conv_dw(self, d, x, dy, dw, stream=None):
+        self._ck(self.lib.niti_conv_dw(self.h, C.byref(d), _ptr(x), _ptr(dy), _ptr(dw), self._stream(stream)))
+
+    def matmul_nt(self, e, h, l, a, b, c, stream=None):
+        self._ck(self.lib.niti_matmul_nt(self.h, e, h, l, _ptr(a), _ptr(b), _ptr(c), self._stream(stream)))
+
+    # ---- element-wise
+    def relu(self, x, y, n, stream=None):
+        self._ck(self.lib.niti_relu(self.h, _ptr(x), _ptr(y), n, self._stream(stream)))
+
+    def relu_grad(self, x, dy, dx, n, stream=None):
+        self._ck(self.lib.niti_relu_grad(self.h, _ptr(x), _ptr(dy), _ptr(dx), n, self._stream(stream)))
+
+    def maxpool(self, x, n, h, w, c, k, s, y, stream=None):
+        self._ck(self.lib.niti_maxpool(self.h, _ptr(x), n, h, w, c, k, s, _ptr(y), self._stream(stream)))
+
+    def maxpool_grad(self, x, y, dy, n, h, w, c, k, s, dx, stream=None):
+        self._ck(self.lib.niti_maxpool_grad(self.h, _ptr(x), _ptr(y), _ptr(dy), n, h, w, c, k, s, _ptr(dx), self._stream(stream)))
+
+    def loss_grad(self, logits, ascale, labels, batch, classes, grad, stream=None):
+        self._ck(self.lib.niti_loss_grad(self.h, _ptr(logits), _ptr(ascale), _ptr(labels), batch, classes, _ptr(grad), self._stream(stream)))
+
+    # ---- layout
+    def nchw_to_nhwc(self, src, n, c, h, w, dst, stream=None):
+        self._ck(self.lib.niti_nchw_to_nhwc(self.h, _ptr(src), n, c, h, w, _ptr(dst), self._stream(stream)))
+
+    def nhwc_to_nchw(self, src, n, c, h, w, dst, stream=None):
+        self._ck(self.lib.niti_nhwc_to_nchw(self.h, _ptr(src), n, c, h, w, _ptr(dst), self._stream(stream)))
+
+    def nc4hw4_to_nhwc(self, src, n, c, h, w, dst, stream=None):
+        self._ck(self.lib.niti_nc4hw4_to_nhwc(self.h, _ptr(src), n, c, h, w, _ptr(dst), self._stream(stream)))
+
+    def nhwc_to_nc4hw4(self, src, n, c, h, w, dst, stream=None):
+        self._ck(self.lib.niti_nhwc_to_nc4hw4(self.h, _ptr(src), n, c, h, w, _ptr(dst), self._stream(stream)))
+
+    # ---- host-buffer call (numpy int8 arrays, NHWC / OHWI)
+    def conv_fwd_host(self, d, x_np, w_np, ex, ew, y_np):
+        ey = C.c_int8(0)
+        self._ck(self.lib.niti_conv_fwd_host(self.h, C.byref(d), x_np.ctypes.data, w_np.ctypes.data, ex, ew,
+                                             y_np.ctypes.data, C.addressof(ey)))
+        return ey.value
+
+    def probe_i8_peak(self, iters=2000):
+        t = C.c_double(0)
+        self._ck(self.lib.niti_probe_i8_peak(self.h, iters, C.byref(t)))
+        return t.value

@@ -1,0 +1,108 @@
+"""Helpers shared by the GPU parity tests, smoke() and bench.py: numpy (NCHW/OIHW, the oracle's
+layouts) <-> device tensors (NHWC/OHWI, the library's layouts) and thin op wrappers that return numpy."""
+import numpy as np
+import torch
+
+from mandheling_dsp_training_b200.lib import ConvDesc, PATH_AUTO, PATH_SIMT, PATH_TC  # noqa: F401
+
+
+def to_desc(s):
+    return ConvDesc(s.n, s.c, s.h, s.w, s.oc, s.kh, s.kw, s.stride, s.pad, s.dil)
+
+
+def dev(a, device="cuda:0"):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(device)
+
+
+def nhwc(x):            # NCHW numpy -> NHWC numpy
+    return np.ascontiguousarray(np.transpose(x, (0, 2, 3, 1)))
+
+
+def nchw(x):            # NHWC numpy -> NCHW numpy
+    return np.ascontiguousarray(np.transpose(x, (0, 3, 1, 2)))
+
+
+class Runner:
+    """Calls the C ABI on numpy inputs in the oracle's layouts and returns numpy in the same layouts."""
+
+    def __init__(self, nb, device="cuda:0"):
+        self.nb, self.device = nb, device
+
+    def _scalar(self, v, dt=torch.int8):
+        return torch.tensor([v], dtype=dt, device=self.device)
+
+    def conv_fwd_acc(self, s, x, w):
+        d = to_desc(s)
+        acc = torch.empty((s.n, d.oh, d.ow, s.oc), dtype=torch.int32, device=self.device)
+        mx = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.nb.conv_fwd_acc(d, dev(nhwc(x)), dev(nhwc(w)), acc, mx)
+        torch.cuda.synchronize()
+        return nchw(acc.cpu().numpy()), int(mx.item())
+
+    def conv_dx_acc(self, s, dy, w):
+        d = to_desc(s)
+        acc = torch.empty((s.n, s.h, s.w, s.c), dtype=torch.int32, device=self.device)
+        mx = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.nb.conv_dx_acc(d, dev(nhwc(dy)), dev(nhwc(w)), acc, mx)
+        torch.cuda.synchronize()
+        return nchw(acc.cpu().numpy()), int(mx.item())
+
+    def conv_dw_acc(self, s, x, dy):
+        d = to_desc(s)
+        acc = torch.empty((s.oc, s.kh, s.kw, s.c), dtype=torch.int32, device=self.device)
+        mx = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.nb.conv_dw_acc(d, dev(nhwc(x)), dev(nhwc(dy)), acc, mx)
+        torch.cuda.synchronize()
+        return nchw(acc.cpu().numpy()), int(mx.item())
+
+    def conv_fwd(self, s, x, w, ex, ew):
+        d = to_desc(s)
+        y = torch.empty((s.n, d.oh, d.ow, s.oc), dtype=torch.int8, device=self.device)
+        ey = self._scalar(0)
+        self.nb.conv_fwd(d, dev(nhwc(x)), dev(nhwc(w)), self._scalar(ex), self._scalar(ew), y, ey)
+        torch.cuda.synchronize()
+        return nchw(y.cpu().numpy()), int(ey.item())
+
+    def conv_dx(self, s, dy, w):
+        d = to_desc(s)
+        dx = torch.empty((s.n, s.h, s.w, s.c), dtype=torch.int8, device=self.device)
+        self.nb.conv_dx(d, dev(nhwc(dy)), dev(nhwc(w)), dx)
+        torch.cuda.synchronize()
+        return nchw(dx.cpu().numpy())
+
+    def conv_dw(self, s, x, dy):
+        d = to_desc(s)
+        dw = torch.empty((s.oc, s.kh, s.kw, s.c), dtype=torch.int8, device=self.device)
+        self.nb.conv_dw(d, dev(nhwc(x)), dev(nhwc(dy)), dw)
+        torch.cuda.synchronize()
+        return nchw(dw.cpu().numpy())
+
+    def matmul_nt(self, a, b):
+        e, l = a.shape
+        h = b.shape[0]
+        c = torch.empty((e, h), dtype=torch.int8, device=self.device)
+        self.nb.matmul_nt(e, h, l, dev(a), dev(b), c)
+        torch.cuda.synchronize()
+        return c.cpu().numpy()
+
+    def rescale_act(self, acc, ea=0, eb=0):
+        a = dev(acc.astype(np.int32).reshape(-1))
+        mx = torch.zeros(1, dtype=torch.int32, device=self.device)
+        out = torch.empty(a.numel(), dtype=torch.int8, device=self.device)
+        eo = self._scalar(0)
+        if a.numel():
+            self.nb.absmax(a, a.numel(), mx)
+        self.nb.rescale_act(a, a.numel(), mx, out, self._scalar(ea), self._scalar(eb), eo)
+        torch.cuda.synchronize()
+        return out.cpu().numpy().reshape(acc.shape), int(eo.item())
+
+    def rescale_grad(self, acc, sub, w=None):
+        a = dev(acc.astype(np.int32).reshape(-1))
+        mx = torch.zeros(1, dtype=torch.int32, device=self.device)
+        out = torch.empty(a.numel(), dtype=torch.int8, device=self.device)
+        wd = dev(w.reshape(-1)) if w is not None else None
+        self.nb.absmax(a, a.numel(), mx)
+        self.nb.rescale_grad(a, a.numel(), mx, sub, out, wd)
+        torch.cuda.synchronize()
+        o = out.cpu().numpy().reshape(acc.shape)
+        return (o, wd.cpu().numpy().reshape(w.shape)) if w is not None else o

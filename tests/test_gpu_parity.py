@@ -1,0 +1,254 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI (ctypes), against the CPU oracle
+and the committed golden vectors of the unmodified reference.  Bit-exact (integer work): every
+comparison is np.array_equal."""
+import numpy as np
+import pytest
+
+from oracle.oracle import ConvShape, shape
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = ["mnist_conv1", "mnist_conv2", "mnist_ip1", "mnist_ip2", "vgg_3x3_p1", "vgg_3x3_p1_b",
+          "odd_hw_3x3_p1", "s2_3x3_p1", "s2_1x1_p0", "small_mag_cast", "small_mag_shift1", "zero_dy"]
+
+
+@pytest.fixture(scope="module")
+def nb():
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    from mandheling_dsp_training_b200 import NitiB200
+    return NitiB200(0)
+
+
+@pytest.fixture(scope="module")
+def run(nb):
+    from tests.gpu_util import Runner
+    return Runner(nb)
+
+
+def _case(g, name):
+    s = ConvShape(*[int(v) for v in g[name + ".shape"]])
+    return s, g[name + ".x"], g[name + ".w"], g[name + ".dy"]
+
+
+def _rand(rng, shp, lo=-127, hi=127):
+    return rng.integers(lo, hi + 1, size=shp, dtype=np.int8)
+
+
+# ------------------------------------------------------------------ golden vectors of the reference
+@pytest.mark.parametrize("name", GOLDEN)
+def test_golden_reference_vectors(nb, run, golden_conv, name):
+    from tests.gpu_util import PATH_AUTO
+    nb.set_path(PATH_AUTO)
+    g = golden_conv
+    s, x, w, dy = _case(g, name)
+    y, e = run.conv_fwd(s, x, w, -7, -7)
+    assert np.array_equal(y, g[name + ".y"])
+    assert e == int(g[name + ".exp"])
+    assert np.array_equal(run.conv_dw(s, x, dy), g[name + ".dw"])
+    if name + ".dx" in g.files:
+        assert np.array_equal(run.conv_dx(s, dy, w), g[name + ".dx"])
+
+
+# ------------------------------------------------------------------ both kernel families vs the oracle
+TC_SHAPES = [
+    # n, c, h, w, oc, k, stride, pad
+    (2, 16, 8, 8, 32, 3, 1, 1),
+    (4, 64, 8, 8, 128, 3, 1, 1),      # one full 128-byte K row per tap-half
+    (2, 128, 6, 6, 256, 3, 1, 1),     # BN = 128/256, K = 1152
+    (3, 32, 9, 7, 48, 3, 1, 1),       # ragged M (189 pixels), non-square
+    (2, 16, 12, 12, 16, 5, 1, 0),     # 5x5, K = 400 (ragged K block)
+    (64, 832, 1, 1, 500, 1, 1, 0),    # MNIST ip1 as 1x1 conv (fwd eligible only)
+    (2, 32, 10, 10, 64, 3, 2, 1),     # stride 2
+    (2, 64, 8, 8, 64, 1, 2, 0),       # 1x1 stride 2 (ResNet downsample)
+    (1, 256, 4, 4, 512, 3, 1, 1),     # K = 2304, N = 512
+    (2, 48, 5, 5, 80, 3, 1, 2),       # pad 2 > (k-1)/2
+    (2, 16, 9, 9, 32, 3, 1, 2),       # dilation handled below with dil=2
+]
+
+
+@pytest.mark.parametrize("cfg", TC_SHAPES)
+@pytest.mark.parametrize("path", ["simt", "tc"])
+def test_accumulators_and_outputs_vs_oracle(nb, run, oracle, cfg, path):
+    from tests.gpu_util import PATH_SIMT, PATH_TC, to_desc
+    n, c, h, w, oc, k, st, p = cfg
+    dil = 2 if cfg == TC_SHAPES[-1] else 1
+    s = shape(n, c, h, w, oc, k, stride=st, pad=p, dil=dil)
+    rng = np.random.default_rng(hash(cfg) % (2 ** 31))
+    x = _rand(rng, (n, c, h, w)); wt = _rand(rng, (oc, c, k, k), -64, 64)
+    dy = _rand(rng, (n, oc, s.oh, s.ow), -50, 50)
+    nb.set_path(PATH_SIMT if path == "simt" else PATH_TC)
+    try:
+        fwd_ok = path == "simt" or (c % 16 == 0 and oc % 4 == 0)
+        dx_ok = path == "simt" or (oc % 16 == 0 and c % 4 == 0)
+        dw_ok = path == "simt" or (oc % 16 == 0 and c % 16 == 0)
+        if fwd_ok:
+            acc, mx = run.conv_fwd_acc(s, x, wt)
+            oacc, _ = oracle.conv_fwd_acc(s, x, wt)
+            assert np.array_equal(acc, oacc)
+            assert mx == int(np.abs(oacc.astype(np.int64)).max())
+            assert nb.last_path == path
+            y, e = run.conv_fwd(s, x, wt, -3, -9)
+            oy, oe, _ = oracle.conv_fwd(s, x, wt, -3, -9)
+            assert np.array_equal(y, oy) and e == oe
+        if dx_ok:
+            acc, mx = run.conv_dx_acc(s, dy, wt)
+            oacc, _ = oracle.conv_dx_acc(s, dy, wt)
+            assert np.array_equal(acc, oacc)
+            assert mx == int(np.abs(oacc.astype(np.int64)).max())
+            assert np.array_equal(run.conv_dx(s, dy, wt), oracle.conv_dx(s, dy, wt)[0])
+        if dw_ok:
+            acc, mx = run.conv_dw_acc(s, x, dy)
+            oacc, _ = oracle.conv_dw_acc(s, x, dy)
+            assert np.array_equal(acc, oacc)
+            assert mx == int(np.abs(oacc.astype(np.int64)).max())
+            assert np.array_equal(run.conv_dw(s, x, dy), oracle.conv_dw(s, x, dy)[0])
+    finally:
+        nb.set_path(0)
+
+
+def test_matmul_nt(nb, run, oracle):
+    rng = np.random.default_rng(5)
+    for (e, h, l) in [(64, 500, 832), (25, 52, 4096), (7, 12, 33)]:
+        a = _rand(rng, (e, l), -30, 30); b = _rand(rng, (h, l), -30, 30)
+        assert np.array_equal(run.matmul_nt(a, b), oracle.matmul_nt(a, b)[0])
+
+
+# ------------------------------------------------------------------ rescale / update kernels
+@pytest.mark.parametrize("n", [0, 1, 15, 16, 17, 4096, 100003])
+@pytest.mark.parametrize("mag", [0, 1, 3, 100, 128, 129, 255, 256, 257, 1 << 14, (1 << 23) + 7, (1 << 30) + 5])
+def test_rescale_rules(run, oracle, n, mag):
+    rng = np.random.default_rng(n * 131 + mag % 977)
+    acc = rng.integers(-mag, mag + 1, size=n).astype(np.int32)
+    if n:
+        acc[rng.integers(0, n)] = -mag if (mag % 2) else mag
+    out, eo = run.rescale_act(acc, -5, 2)
+    oout, inc = oracle.rescale_act(acc)
+    assert np.array_equal(out, oout)
+    assert eo == int(np.int8(-5 + 2 + inc))
+    if n:
+        w = _rand(rng, (n,), -128, 127)
+        for sub in (2, 3):
+            o, wnew = run.rescale_grad(acc, sub, w)
+            oo = oracle.rescale_grad(acc, sub)
+            assert np.array_equal(o, oo)
+            assert np.array_equal(wnew, oracle.sgd_update(w, oo))
+
+
+def test_sgd_update(nb, oracle):
+    import torch
+    rng = np.random.default_rng(11)
+    for n in (1, 31, 4096, 99999):
+        w = _rand(rng, (n,), -128, 127); dw = _rand(rng, (n,), -128, 127)
+        wd = torch.from_numpy(w.copy()).cuda(); dd = torch.from_numpy(dw).cuda()
+        nb.sgd_update(wd, dd, n)
+        assert np.array_equal(wd.cpu().numpy(), oracle.sgd_update(w, dw))
+
+
+# ------------------------------------------------------------------ element-wise ops of the step
+def test_elementwise_vs_oracle_and_golden(nb, oracle, golden_ew):
+    import torch
+    from tests.gpu_util import nhwc, nchw, dev
+    g = golden_ew
+    x = g["relu.x"]
+    n, c, h, w = x.shape
+    xd = dev(nhwc(x)); y = torch.empty_like(xd)
+    nb.relu(xd, y, xd.numel())
+    assert np.array_equal(nchw(y.cpu().numpy()), g["relu.y"])
+    dyd = dev(nhwc(g["relu_grad.dy"])); dx = torch.empty_like(xd)
+    nb.relu_grad(xd, dyd, dx, xd.numel())
+    assert np.array_equal(nchw(dx.cpu().numpy()), g["relu_grad.dx"])
+    yp = torch.empty((n, h // 2, w // 2, c), dtype=torch.int8, device="cuda")
+    nb.maxpool(xd, n, h, w, c, 2, 2, yp)
+    assert np.array_equal(nchw(yp.cpu().numpy()), g["maxpool.y"])
+    # pool grad vs oracle, including ties (post-relu zeros) and an overlapping window (k=3, s=2)
+    rng = np.random.default_rng(2)
+    for (k, s, src) in [(2, 2, x), (2, 2, oracle.relu(x)), (3, 2, oracle.relu(x))]:
+        oy = oracle.maxpool(src, k, s)
+        dyp = _rand(rng, oy.shape)
+        sd = dev(nhwc(src)); yd = dev(nhwc(oy)); gd = dev(nhwc(dyp)); out = torch.empty_like(sd)
+        nb.maxpool_grad(sd, yd, gd, n, h, w, c, k, s, out)
+        assert np.array_equal(nchw(out.cpu().numpy()), oracle.maxpool_grad(src, oy, dyp, k, s))
+    for a in (-9, -7, -5, -3, 0, 1):
+        lg, lab = g[f"loss_grad.{a}.logits"], g[f"loss_grad.{a}.labels"]
+        out = torch.empty(lg.shape, dtype=torch.int8, device="cuda")
+        nb.loss_grad(dev(lg), torch.tensor([a], dtype=torch.int8, device="cuda"), dev(lab.astype(np.int32)),
+                     lg.shape[0], lg.shape[1], out)
+        assert np.array_equal(out.cpu().numpy(), g[f"loss_grad.{a}.grad"]), a
+
+
+def test_layout_round_trips(nb):
+    import torch
+    rng = np.random.default_rng(9)
+    for (n, c, h, w) in [(3, 20, 5, 7), (2, 4, 3, 3), (1, 1, 28, 28), (4, 52, 8, 8)]:
+        x = _rand(rng, (n, c, h, w))
+        xd = torch.from_numpy(x).cuda()
+        a = torch.empty((n, h, w, c), dtype=torch.int8, device="cuda")
+        nb.nchw_to_nhwc(xd, n, c, h, w, a)
+        assert np.array_equal(a.cpu().numpy(), np.transpose(x, (0, 2, 3, 1)))
+        b = torch.empty_like(xd)
+        nb.nhwc_to_nchw(a, n, c, h, w, b)
+        assert np.array_equal(b.cpu().numpy(), x)
+        c4 = (c + 3) // 4
+        p = torch.empty((c4, n, h * w, 4), dtype=torch.int8, device="cuda")
+        nb.nhwc_to_nc4hw4(a, n, c, h, w, p)
+        ref = np.zeros((c4 * 4, n, h * w), np.int8)
+        ref[:c] = np.transpose(x.reshape(n, c, h * w), (1, 0, 2))
+        ref = np.transpose(ref.reshape(c4, 4, n, h * w), (0, 2, 3, 1))
+        assert np.array_equal(p.cpu().numpy(), ref)
+        back = torch.zeros_like(a)
+        nb.nc4hw4_to_nhwc(p, n, c, h, w, back)
+        assert np.array_equal(back.cpu().numpy(), a.cpu().numpy())
+
+
+def test_host_buffer_call(nb, oracle):
+    from tests.gpu_util import nhwc, nchw, to_desc
+    rng = np.random.default_rng(4)
+    s = shape(4, 32, 8, 8, 64, 3, pad=1)
+    x = _rand(rng, (4, 32, 8, 8)); w = _rand(rng, (64, 32, 3, 3), -40, 40)
+    y = np.empty((4, 8, 8, 64), np.int8)
+    e = nb.conv_fwd_host(to_desc(s), nhwc(x), nhwc(w), -7, -7, y)
+    oy, oe, _ = oracle.conv_fwd(s, x, w, -7, -7)
+    assert np.array_equal(nchw(y), oy) and e == oe
+
+
+# ------------------------------------------------------------------ full-size properties (BASELINE sizes)
+def test_full_size_vgg_layer_properties(nb):
+    """VGG-11 256->256 @ 8x8, batch 256 (M=16384, K=2304): too big for the CPU oracle in seconds, so
+    check size-independent properties on the device: (1) the tensor-core and SIMT kernels agree
+    element for element, (2) dW is additive over a batch split, (3) conv is odd in x."""
+    import torch
+    from tests.gpu_util import PATH_SIMT, PATH_TC
+    from mandheling_dsp_training_b200.lib import desc
+    torch.manual_seed(0)
+    n, c, hw, oc = 256, 256, 8, 256
+    d = desc(n, c, hw, hw, oc, 3, pad=1)
+    x = torch.randint(-127, 128, (n, hw, hw, c), dtype=torch.int8, device="cuda")
+    w = torch.randint(-20, 21, (oc, 3, 3, c), dtype=torch.int8, device="cuda")
+    dy = torch.randint(-30, 31, (n, hw, hw, oc), dtype=torch.int8, device="cuda")
+    outs = {}
+    for path in (PATH_SIMT, PATH_TC):
+        nb.set_path(path)
+        acc = torch.empty((n, hw, hw, oc), dtype=torch.int32, device="cuda")
+        dxa = torch.empty((n, hw, hw, c), dtype=torch.int32, device="cuda")
+        dwa = torch.empty((oc, 3, 3, c), dtype=torch.int32, device="cuda")
+        nb.conv_fwd_acc(d, x, w, acc); nb.conv_dx_acc(d, dy, w, dxa); nb.conv_dw_acc(d, x, dy, dwa)
+        torch.cuda.synchronize()
+        outs[path] = (acc, dxa, dwa)
+    nb.set_path(0)
+    for a, b in zip(outs[PATH_SIMT], outs[PATH_TC]):
+        assert torch.equal(a, b)
+    acc, dxa, dwa = outs[PATH_TC]
+    # (2) additivity of dW over the batch
+    nb.set_path(PATH_TC)
+    dh = desc(n // 2, c, hw, hw, oc, 3, pad=1)
+    p0 = torch.empty_like(dwa); p1 = torch.empty_like(dwa)
+    nb.conv_dw_acc(dh, x[: n // 2].contiguous(), dy[: n // 2].contiguous(), p0)
+    nb.conv_dw_acc(dh, x[n // 2:].contiguous(), dy[n // 2:].contiguous(), p1)
+    # (3) oddness: conv(-x) == -conv(x)   (x has no -128)
+    neg = torch.empty_like(acc)
+    nb.conv_fwd_acc(d, (-x).contiguous(), w, neg)
+    torch.cuda.synchronize()
+    nb.set_path(0)
+    assert torch.equal(p0 + p1, dwa)
+    assert torch.equal(neg, -acc)
