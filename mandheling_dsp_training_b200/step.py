@@ -1,0 +1,307 @@
+"""The NITI int8 training step on the device, built only from C-ABI calls (lib.NitiB200).
+
+Mirrors what the reference's express graph executes for one `sgd->step(loss)`
+(tools/train/source/demo/MnistUtils.cpp:79-147, demo/mnistTrain.cpp:159-181,
+grad/NITI_Conv_Int8_Grad.cpp:16-197, optimizer/NITI_SGD.hpp:20-54):
+
+  forward   conv -> [relu] -> [maxpool] ...      NITI_Conv_Int8 / NITI_CPURelu_Int8 / NITI_Maxpool_Int8
+  loss grad integer softmax-CE gradient          NITI_CPULossGrad_Int8
+  backward  pool grad / relu grad, dX, dW        NITI_CPUPoolGrad / NITI_CPUReluGrad / NITI_DeConv / NITI_GradientConv
+  update    W <- clip127(W - dW)                 NITI_SGD + int8 Binary SUB
+
+Everything stays resident in HBM (NHWC activations, OHWI weights); all buffers are allocated once, so
+the step is a fixed launch sequence (CUDA-graph capturable at world size 1).
+
+Data parallel (world size g): the batch is sharded; to stay bit-identical to the single-device run the
+two reductions that span the batch are all-reduced between phase 1 and phase 2 of each op:
+  * max|acc| of every forward / dX tensor  -> all_reduce(MAX) on one uint32
+  * the int32 dW accumulators              -> all_reduce(SUM), one bucket for the whole net
+Integer sums and maxima are order-independent, so g devices reproduce the 1-device result exactly.
+"""
+import numpy as np
+import torch
+
+from .lib import NitiB200, desc as make_desc
+
+# ---- layer lists ------------------------------------------------------------------------------------
+# ("conv", oc, k, stride, pad) | ("relu",) | ("pool", k, s) | ("flatten",)
+
+
+def lenet_spec():
+    """the reference's NITIInt8 model (demo/mnistTrain.cpp:131-181): 1x28x28 -> 12 logits"""
+    return [("conv", 20, 5, 1, 0), ("relu",), ("pool", 2, 2),
+            ("conv", 52, 5, 1, 0), ("relu",), ("pool", 2, 2), ("flatten",),
+            ("conv", 500, 1, 1, 0), ("relu",), ("conv", 12, 1, 1, 0)]
+
+
+def vgg11_spec(classes=12, first_c_pad=False):
+    """VGG-11 for 32x32 inputs (CIFAR-shaped), NITI style: no bias, no batch-norm, int8 everywhere"""
+    cfg = [64, "M", 128, "M", 256, 256, "M", 512, 512, "M", 512, 512, "M"]
+    spec = []
+    for v in cfg:
+        if v == "M":
+            spec.append(("pool", 2, 2))
+        else:
+            spec += [("conv", v, 3, 1, 1), ("relu",)]
+    spec += [("flatten",), ("conv", 512, 1, 1, 0), ("relu",), ("conv", 512, 1, 1, 0), ("relu",),
+             ("conv", classes, 1, 1, 0)]
+    return spec
+
+
+def resnet18_spec(classes=1000):
+    """ResNet-18 trunk as a plain int8 chain (7x7 s2 stem, 3x3 stages with stride-2 transitions).
+    The residual adds and fp32 batch-norm of the mixed-precision config are outside the int8 hot path
+    (SURVEY.md section 8 f); this list carries every int8 contraction of the network."""
+    spec = [("conv", 64, 7, 2, 3), ("relu",), ("pool", 2, 2)]
+    for oc, first_stride in [(64, 1), (128, 2), (256, 2), (512, 2)]:
+        for b in range(4):
+            spec += [("conv", oc, 3, first_stride if b == 0 else 1, 1), ("relu",)]
+    spec += [("pool", 7, 7), ("flatten",), ("conv", classes, 1, 1, 0)]
+    return spec
+
+
+SPECS = {"lenet": (lenet_spec, (1, 28, 28)), "vgg11": (vgg11_spec, (3, 32, 32)), "resnet18": (resnet18_spec, (3, 224, 224))}
+
+
+def niti_xavier_int8(rng, oc, c, kh, kw):
+    """the reference's weight recipe with an injectable seed (nn/Distributions.cpp:25-50,
+    nn/Initializer.cpp:118-134): N(0, sqrt(2/(fan_in+fan_out))) -> /max|w| * 127 -> round;
+    wscale = ceil(log2(max|w|)) - 7.  Returns (OIHW int8, wscale)."""
+    fan_in, fan_out = c * kh * kw, oc * kh * kw
+    w = rng.normal(0.0, np.sqrt(2.0 / (fan_in + fan_out)), size=(oc, c, kh, kw)).astype(np.float32)
+    r = float(np.abs(w).max())
+    wscale = int(np.ceil(np.log2(r))) - 7
+    return np.round(w / r * 127.0).astype(np.int8), wscale
+
+
+class _Conv:
+    pass
+
+
+class NitiNet:
+    def __init__(self, nb: NitiB200, spec, batch, in_chw, device=0, dist=None, classes_used=10):
+        self.nb, self.batch = nb, batch
+        self.dev = device if isinstance(device, torch.device) else torch.device("cuda", device)
+        self.dist = dist if (dist is not None and dist.is_initialized() and dist.get_world_size() > 1) else None
+        self.timer = None                      # optional callable(kind, fn) used by bench.py
+        c, h, w = in_chw
+        i8 = dict(dtype=torch.int8, device=self.dev)
+        i32 = dict(dtype=torch.int32, device=self.dev)
+        self.x_in = torch.zeros((batch, h, w, c), **i8)
+        self.ex_in = torch.zeros(1, **i8)
+        self.labels = torch.zeros(batch, **i32)
+        self.ops = []
+        self.convs = []
+        cur, cur_e = self.x_in, self.ex_in
+        dw_total = 0
+        for item in spec:
+            kind = item[0]
+            if kind == "conv":
+                _, oc, k, st, pad = item
+                L = _Conv()
+                L.kind, L.d = "conv", make_desc(batch, c, h, w, oc, k, stride=st, pad=pad)
+                L.x, L.ex = cur, cur_e
+                L.w = torch.zeros((oc, k, k, c), **i8)
+                L.ew = torch.zeros(1, **i8)
+                L.y = torch.zeros((batch, L.d.oh, L.d.ow, oc), **i8)
+                L.ey = torch.zeros(1, **i8)
+                L.n_y, L.n_x, L.n_w = L.y.numel(), cur.numel(), L.w.numel()
+                L.dw_off = dw_total
+                dw_total += (L.n_w + 63) // 64 * 64
+                L.index = len(self.convs)
+                self.convs.append(L); self.ops.append(L)
+                cur, cur_e, c, h, w = L.y, L.ey, oc, L.d.oh, L.d.ow
+            elif kind == "relu":
+                L = _Conv(); L.kind = "relu"; L.x = cur; L.y = torch.zeros_like(cur)
+                self.ops.append(L); cur = L.y
+            elif kind == "pool":
+                _, k, s = item
+                L = _Conv(); L.kind, L.k, L.s, L.geom = "pool", k, s, (batch, h, w, c)
+                oh, ow = (h - k) // s + 1, (w - k) // s + 1
+                L.x = cur; L.y = torch.zeros((batch, oh, ow, c), **i8)
+                self.ops.append(L); cur, h, w = L.y, oh, ow
+            elif kind == "flatten":
+                # the reference flattens in NCHW order (_Convert(NCHW) + _Reshape, mnistTrain.cpp:170-171)
+                L = _Conv(); L.kind, L.geom = "flatten", (batch, c, h, w)
+                L.x = cur; L.y = torch.zeros((batch, 1, 1, c * h * w), **i8)
+                self.ops.append(L); cur, c, h, w = L.y, c * h * w, 1, 1
+        self.logits, self.e_logits, self.classes = cur, cur_e, c
+        # backward buffers: one gradient tensor per op output
+        for L in self.ops:
+            L.dy = torch.zeros_like(L.y)
+        self.acc = torch.zeros(max(max(L.n_y, L.n_x) for L in self.convs), **i32)   # fwd / dX accumulators
+        self.dw_acc = torch.zeros(dw_total, **i32)                                   # one bucket: all dW accumulators
+        self.maxabs = torch.zeros(4 * len(self.convs) + 4, **i32)                    # one slot per reduction
+        self.dx_first = None
+
+    # ---- parameters -------------------------------------------------------------------------------
+    def init_weights(self, seed=1):
+        rng = np.random.default_rng(seed)
+        ws = []
+        for L in self.convs:
+            w, e = niti_xavier_int8(rng, L.d.oc, L.d.c, L.d.kh, L.d.kw)
+            ws.append((w, e))
+        self.load_weights(ws)
+        return ws
+
+    def load_weights(self, ws):
+        """ws: list of (OIHW int8 numpy, wscale)"""
+        for L, (w, e) in zip(self.convs, ws):
+            L.w.copy_(torch.from_numpy(np.ascontiguousarray(np.transpose(w, (0, 2, 3, 1)))))
+            L.ew.fill_(int(e))
+
+    def weights_oihw(self):
+        return [np.ascontiguousarray(np.transpose(L.w.cpu().numpy(), (0, 3, 1, 2))) for L in self.convs]
+
+    def set_input(self, x_nhwc, ascale, labels, non_blocking=True):
+        """host (pinned) or device tensors -> the step's input buffers (the e2e H2D leg)"""
+        self.x_in.copy_(x_nhwc, non_blocking=non_blocking)
+        self.labels.copy_(labels, non_blocking=non_blocking)
+        self.ex_in.fill_(int(ascale)) if not torch.is_tensor(ascale) else self.ex_in.copy_(ascale, non_blocking=non_blocking)
+
+    # ---- helpers ----------------------------------------------------------------------------------
+    def _timed(self, kind, ops, fn):
+        if self.timer is not None:
+            self.timer(kind, ops, fn)
+        else:
+            fn()
+
+    def _allreduce_max(self, slot):
+        if self.dist is not None:
+            self.dist.all_reduce(slot, op=self.dist.ReduceOp.MAX)
+
+    # ---- the step ---------------------------------------------------------------------------------
+    def forward(self):
+        nb = self.nb
+        nb.zero_u32(self.maxabs, self.maxabs.numel())
+        for L in self.ops:
+            if L.kind == "conv":
+                slot = self.maxabs[L.index: L.index + 1]
+                ops = 2.0 * L.n_y * L.d.c * L.d.kh * L.d.kw
+                self._timed("fwd", ops, lambda: nb.conv_fwd_acc(L.d, L.x, L.w, self.acc, slot))
+                self._allreduce_max(slot)
+                nb.rescale_act(self.acc, L.n_y, slot, L.y, L.ex, L.ew, L.ey)
+            elif L.kind == "relu":
+                nb.relu(L.x, L.y, L.x.numel())
+            elif L.kind == "pool":
+                n, h, w, c = L.geom
+                nb.maxpool(L.x, n, h, w, c, L.k, L.s, L.y)
+            elif L.kind == "flatten":
+                n, c, h, w = L.geom
+                if h * w == 1:
+                    L.y.copy_(L.x.view_as(L.y))
+                else:
+                    nb.nhwc_to_nchw(L.x, n, c, h, w, L.y)
+
+    def backward_and_update(self):
+        nb = self.nb
+        nconv = len(self.convs)
+        last = self.ops[-1]
+        nb.loss_grad(self.logits, self.e_logits, self.labels, self.batch, self.classes, last.dy)
+        for idx in range(len(self.ops) - 1, -1, -1):
+            L = self.ops[idx]
+            dy = L.dy
+            dx = self.ops[idx - 1].dy if idx > 0 else None      # gradient w.r.t. this op's input
+            if L.kind == "conv":
+                acc_dw = self.dw_acc[L.dw_off: L.dw_off + L.n_w]
+                ops = 2.0 * L.n_y * L.d.c * L.d.kh * L.d.kw
+                self._timed("dw", ops, lambda: nb.conv_dw_acc(L.d, L.x, dy, acc_dw, None))
+                if dx is not None:
+                    slot = self.maxabs[nconv + L.index: nconv + L.index + 1]
+                    self._timed("dx", ops, lambda: nb.conv_dx_acc(L.d, dy, L.w, self.acc, slot))
+                    self._allreduce_max(slot)
+                    nb.rescale_act(self.acc, L.n_x, slot, dx, None, None, None)
+            elif L.kind == "relu":
+                nb.relu_grad(L.x, dy, dx, L.x.numel())
+            elif L.kind == "pool":
+                n, h, w, c = L.geom
+                nb.maxpool_grad(L.x, L.y, dy, n, h, w, c, L.k, L.s, dx)
+            elif L.kind == "flatten":
+                n, c, h, w = L.geom
+                if h * w == 1:
+                    dx.copy_(dy.view_as(dx))
+                else:
+                    nb.nchw_to_nhwc(dy, n, c, h, w, dx)
+        # gradient exchange (one bucket), then shared exponent + PSTO + int8 SGD, fused per layer
+        if self.dist is not None:
+            self.dist.all_reduce(self.dw_acc, op=self.dist.ReduceOp.SUM)
+        for L in self.convs:
+            acc_dw = self.dw_acc[L.dw_off: L.dw_off + L.n_w]
+            slot = self.maxabs[2 * nconv + L.index: 2 * nconv + L.index + 1]
+            nb.absmax(acc_dw, L.n_w, slot)
+            nb.rescale_grad(acc_dw, L.n_w, slot, 2, None, L.w)
+
+    def step(self):
+        self.forward()
+        self.backward_and_update()
+
+    def capture(self):
+        """CUDA-graph the step (world size 1).  Returns a callable that replays it."""
+        assert self.dist is None
+        s = torch.cuda.Stream(self.dev)
+        s.wait_stream(torch.cuda.current_stream(self.dev))
+        with torch.cuda.stream(s):
+            self.step()                                   # warm-up: workspaces grow here, not under capture
+        torch.cuda.current_stream(self.dev).wait_stream(s)
+        torch.cuda.synchronize(self.dev)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self.step()
+        return g.replay
+
+    def algorithmic_ops(self):
+        """2*M*N*K of every contraction of one step (fwd + dW for every conv, dX for all but the first)"""
+        t = 0.0
+        for L in self.convs:
+            o = 2.0 * L.n_y * L.d.c * L.d.kh * L.d.kw
+            t += 2 * o + (o if L.index > 0 else 0.0)
+        return t
+
+
+# ---- CPU twin on the oracle (tests / cpu_baseline only) ------------------------------------------------
+def oracle_step(orc, spec, x_nchw, ascale, labels, weights, shape_fn):
+    """Same step on the CPU oracle; `weights` list of (OIHW int8, wscale) is updated in place.
+    Returns (logits, exponent).  Lives here so tests and bench share one definition; it is only ever
+    called from tests/, smoke() and bench.py's cpu_baseline / reference legs."""
+    acts = []
+    cur, e = x_nchw, int(ascale)
+    wi = 0
+    trace = []
+    for item in spec:
+        kind = item[0]
+        if kind == "conv":
+            _, oc, k, st, pad = item
+            n, c, h, w = cur.shape
+            s = shape_fn(n, c, h, w, oc, k, stride=st, pad=pad)
+            W, ew = weights[wi]
+            y, ey, _ = orc.conv_fwd(s, cur, W, e, ew)
+            trace.append(("conv", s, cur, wi)); wi += 1
+            cur, e = y, ey
+        elif kind == "relu":
+            trace.append(("relu", cur)); cur = orc.relu(cur)
+        elif kind == "pool":
+            y = orc.maxpool(cur, item[1], item[2])
+            trace.append(("pool", cur, y, item[1], item[2])); cur = y
+        elif kind == "flatten":
+            trace.append(("flatten", cur.shape)); cur = np.ascontiguousarray(cur.reshape(cur.shape[0], -1, 1, 1))
+    logits, e_logits = cur, e
+    g = orc.loss_grad(np.ascontiguousarray(logits.reshape(logits.shape[0], -1)), e_logits, labels)
+    g = g.reshape(logits.shape)
+    new_w = {}
+    for t in reversed(trace):
+        if t[0] == "conv":
+            _, s, xin, i = t
+            W, ew = weights[i]
+            dw, _ = orc.conv_dw(s, xin, g)
+            new_w[i] = orc.sgd_update(W, dw)
+            if i > 0:
+                g, _ = orc.conv_dx(s, g, W)
+        elif t[0] == "relu":
+            g = orc.relu_grad(t[1], g)
+        elif t[0] == "pool":
+            g = orc.maxpool_grad(t[1], t[2], g, t[3], t[4])
+        elif t[0] == "flatten":
+            g = np.ascontiguousarray(g.reshape(t[1]))
+    for i, W in new_w.items():
+        weights[i] = (W, weights[i][1])
+    return logits, e_logits

@@ -1,0 +1,60 @@
+"""GPU: the whole int8 training step (forward, loss grad, dX, dW, shared exponents, int8 SGD) on the
+device through the C ABI vs the CPU oracle twin, bit for bit, over several steps; eager vs CUDA graph."""
+import numpy as np
+import pytest
+import torch
+
+from oracle.oracle import shape
+from mandheling_dsp_training_b200.step import NitiNet, oracle_step, lenet_spec
+
+pytestmark = pytest.mark.gpu
+
+TC_NET = [("conv", 32, 3, 1, 1), ("relu",), ("pool", 2, 2), ("conv", 64, 3, 1, 1), ("relu",), ("pool", 2, 2),
+          ("flatten",), ("conv", 128, 1, 1, 0), ("relu",), ("conv", 16, 1, 1, 0)]
+
+
+@pytest.fixture(scope="module")
+def nb():
+    from mandheling_dsp_training_b200 import NitiB200
+    return NitiB200(0)
+
+
+def _data(batch, chw, seed):
+    rng = np.random.default_rng(seed)
+    x = rng.integers(-127, 128, size=(batch,) + chw, dtype=np.int8)
+    return x, rng.integers(0, 10, size=batch).astype(np.int32)
+
+
+@pytest.mark.parametrize("spec,chw,batch", [(lenet_spec(), (1, 28, 28), 8), (TC_NET, (16, 8, 8), 8)])
+def test_training_steps_bit_exact_vs_oracle(nb, oracle, spec, chw, batch):
+    net = NitiNet(nb, spec, batch, chw)
+    ws = [(w.copy(), e) for w, e in net.init_weights(seed=1)]
+    paths = set()
+    for it in range(3):
+        x, labels = _data(batch, chw, it)
+        net.set_input(torch.from_numpy(np.ascontiguousarray(np.transpose(x, (0, 2, 3, 1)))), -7, torch.from_numpy(labels))
+        net.step()
+        paths.add(nb.last_path)
+        torch.cuda.synchronize()
+        logits, e = oracle_step(oracle, spec, x, -7, labels, ws, shape)
+        assert np.array_equal(net.logits.cpu().numpy().reshape(batch, -1), logits.reshape(batch, -1)), it
+        assert int(net.e_logits.item()) == e
+        for i, (a, (b, _)) in enumerate(zip(net.weights_oihw(), ws)):
+            assert np.array_equal(a, b), (it, i)
+
+
+def test_cuda_graph_replay_equals_eager(nb):
+    spec, chw, batch = TC_NET, (16, 8, 8), 16
+    x, labels = _data(batch, chw, 0)
+    xin = torch.from_numpy(np.ascontiguousarray(np.transpose(x, (0, 2, 3, 1))))
+    a = NitiNet(nb, spec, batch, chw); a.init_weights(seed=3)
+    b = NitiNet(nb, spec, batch, chw); b.init_weights(seed=3)
+    a.set_input(xin, -7, torch.from_numpy(labels)); b.set_input(xin, -7, torch.from_numpy(labels))
+    replay = b.capture()            # warm-up step + captured step = 2 steps so far, none replayed
+    b.init_weights(seed=3)          # reset parameters after the warm-up/capture passes touched them
+    for _ in range(3):
+        a.step(); replay()
+    torch.cuda.synchronize()
+    for wa, wb in zip(a.weights_oihw(), b.weights_oihw()):
+        assert np.array_equal(wa, wb)
+    assert torch.equal(a.logits, b.logits)
