@@ -1,0 +1,357 @@
+#!/usr/bin/env python
+"""bench.py — int8 NITI training throughput on B200 (BASELINE.json metric: int8 train samples/sec).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload vgg11|lenet|resnet18] [--impl reference]
+
+A "step" is one full int8 training step (forward, integer loss gradient, dX, dW, shared-exponent
+rescale, int8 SGD update) of the hot path over one synthetic batch.  One process per GPU (torchrun for
+N>1, NCCL); prints ONE JSON line on rank 0.  `value` times steps whose inputs are already in HBM;
+`e2e` times the same step fed from pinned host memory with the logits read back every step.
+`--impl reference` times the unmodified reference (oracle/_ref, built from /root/reference by
+oracle/Makefile.ref) on the host cores, on a bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (spec key, default per-GPU batch, description)
+    "vgg11": ("vgg11", 256, "VGG-11 int8 NITI, CIFAR-shaped 3x32x32 synthetic, batch 256/GPU"),
+    "lenet": ("lenet", 64, "MNIST NITIInt8 LeNet-style CNN, 1x28x28 synthetic, batch 64/GPU"),
+    "resnet18": ("resnet18", 128, "ResNet-18 int8 contraction chain, 3x224x224 synthetic, batch 128/GPU"),
+}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default="vgg11", choices=sorted(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default: the workload's)")
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--ref-batch", type=int, default=4, help="bounded sample size for the CPU reference")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying a CUDA graph")
+    return ap.parse_args()
+
+
+# ----------------------------------------------------------------------------------------------------
+# CPU reference leg (cpu_baseline and --impl reference).  The only place bench.py touches oracle/.
+# ----------------------------------------------------------------------------------------------------
+def reference_step_fn(workload, batch):
+    """Returns (step_callable, kind, cores, note).  Uses the unmodified reference when oracle/_ref was
+    built (kind "reference"), else the C oracle port (kind "port", 1 core)."""
+    import numpy as np
+    from oracle.oracle import Oracle, Reference, shape
+    from mandheling_dsp_training_b200.step import SPECS, niti_xavier_int8, oracle_step
+    spec_fn, chw = SPECS[WORKLOADS[workload][0]]
+    spec = spec_fn()
+    rng = np.random.default_rng(0)
+    x = rng.integers(-127, 128, size=(batch,) + chw, dtype=np.int8)
+    labels = rng.integers(0, 10, size=batch).astype(np.int32)
+    wrng = np.random.default_rng(1)
+    ws, c = [], chw[0]
+    h, w_ = chw[1], chw[2]
+    for it in spec:                                     # walk shapes to size the weights
+        if it[0] == "conv":
+            ws.append(niti_xavier_int8(wrng, it[1], c, it[2], it[2]))
+            c = it[1]; h = (h + 2 * it[4] - it[2]) // it[3] + 1; w_ = (w_ + 2 * it[4] - it[2]) // it[3] + 1
+        elif it[0] == "pool":
+            h = (h - it[1]) // it[2] + 1; w_ = (w_ - it[1]) // it[2] + 1
+        elif it[0] == "flatten":
+            c, h, w_ = c * h * w_, 1, 1
+    if Reference.available():
+        cores = min(os.cpu_count() or 1, 32)            # MNN caps its pool at 32 threads (CPUBackend.cpp:29)
+        ref = Reference(threads=cores)
+        state = [(w.copy(), e) for w, e in ws]
+
+        def step():
+            cur, e, trace, wi = x, -7, [], 0
+            for it in spec:
+                if it[0] == "conv":
+                    n, c_, hh, ww = cur.shape
+                    s_ = shape(n, c_, hh, ww, it[1], it[2], stride=it[3], pad=it[4])
+                    W, ew = state[wi]
+                    y, e2 = ref.conv_fwd(s_, cur, W, e, ew)
+                    trace.append(("conv", s_, cur, wi)); wi += 1; cur, e = y, e2
+                elif it[0] == "relu":
+                    trace.append(("relu", cur)); cur = ref.relu(cur)
+                elif it[0] == "pool":
+                    trace.append(("pool", cur, it[1], it[2])); cur = ref.maxpool(cur, it[1], it[2])
+                elif it[0] == "flatten":
+                    trace.append(("flatten", cur.shape)); cur = np.ascontiguousarray(cur.reshape(cur.shape[0], -1, 1, 1))
+            g = ref.loss_grad(np.ascontiguousarray(cur.reshape(cur.shape[0], -1)), e, labels).reshape(cur.shape)
+            for t in reversed(trace):
+                if t[0] == "conv":
+                    _, s_, xin, i = t
+                    W, ew = state[i]
+                    dx_, dw_ = ref.conv_bwd(s_, xin, W, g)
+                    state[i] = (ref.sgd_update(W, dw_), ew)
+                    if i > 0:
+                        g = dx_
+                elif t[0] == "relu":
+                    g = ref.relu_grad(t[1], g)
+                elif t[0] == "pool":
+                    g = ref.maxpool_grad(t[1], g, t[2], t[3])
+                elif t[0] == "flatten":
+                    g = np.ascontiguousarray(g.reshape(t[1]))
+        return step, "reference", cores, f"unmodified reference ops (oracle/_ref) on {batch} samples, {cores} threads"
+    orc = Oracle()
+    state = [(w.copy(), e) for w, e in ws]
+    return (lambda: oracle_step(orc, spec, x, -7, labels, state, shape)), "port", 1, \
+        f"C oracle port on {batch} samples, 1 thread (oracle/_ref not built)"
+
+
+class _QuietStdout:
+    """the reference printf()s debug lines to stdout (e.g. shape/ShapeNITI_*.cpp); keep our stdout to the
+    one JSON line by pointing fd 1 at /dev/null while it runs"""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        self.null = os.open(os.devnull, os.O_WRONLY)
+        os.dup2(self.null, 1)
+
+    def __exit__(self, *a):
+        os.dup2(self.saved, 1)
+        os.close(self.null); os.close(self.saved)
+
+
+def time_reference(workload, batch, steps, warmup, budget_s=45.0):
+    with _QuietStdout():
+        step, kind, cores, note = reference_step_fn(workload, batch)
+        for _ in range(max(0, warmup)):
+            step()
+        t0 = time.perf_counter(); done = 0
+        while done < steps and (time.perf_counter() - t0 < budget_s or done == 0):
+            step(); done += 1
+        dt = time.perf_counter() - t0
+    return {"value": batch * done / dt, "unit": "samples/s", "cores": cores, "kind": kind,
+            "sample": f"{note}; {done} steps in {dt:.1f}s"}, dt / done
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cb, ms = time_reference(args.workload, args.ref_batch, args.steps, args.warmup, budget_s=150.0)
+    line = {"impl": "reference", "metric": "int8_train_samples_per_sec", "value": cb["value"], "unit": "samples/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+            "config": {"workload": WORKLOADS[args.workload][2], "sample_batch": args.ref_batch},
+            "cpu_baseline": cb,
+            "e2e": {"value": cb["value"], "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([f.strip() for f in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        self.stop_flag = True
+        sm = [int(s[0]) for s in self.samples if s[0].isdigit()]
+        mx = [int(s[1]) for s in self.samples if s[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for s in self.samples for n, v in zip(names, s[2:6]) if v.lower().startswith("active")})
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.samples)}
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from mandheling_dsp_training_b200 import NitiB200
+    from mandheling_dsp_training_b200.step import NitiNet, SPECS
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    spec_key, dbatch, desc_text = WORKLOADS[args.workload]
+    batch = args.batch or dbatch
+    spec_fn, chw = SPECS[spec_key]
+    nb = NitiB200(local)
+    net = NitiNet(nb, spec_fn(), batch, chw, device=local, dist=dist if world > 1 else None)
+    net.init_weights(seed=1)
+
+    # synthetic data: a few distinct pinned host batches (different shard per rank), rotated
+    rng = np.random.default_rng(1000 + rank)
+    nbuf = 4
+    hx = [torch.from_numpy(rng.integers(-127, 128, size=(batch, chw[1], chw[2], chw[0]), dtype=np.int8)).pin_memory() for _ in range(nbuf)]
+    hl = [torch.from_numpy(rng.integers(0, 10, size=batch).astype(np.int32)).pin_memory() for _ in range(nbuf)]
+    dx = [t.cuda() for t in hx]; dl = [t.cuda() for t in hl]
+    host_logits = torch.empty(net.logits.shape, dtype=torch.int8).pin_memory()
+
+    flush = torch.empty(256 << 20, dtype=torch.int8, device="cuda")      # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    use_graph = (world == 1) and not args.no_graph
+    step_fn = net.step
+    net.set_input(dx[0], -7, dl[0])
+    l0 = nb.launches
+    net.step()                                               # also grows the library workspaces
+    torch.cuda.synchronize()
+    launches_per_step = nb.launches - l0
+    if use_graph:
+        step_fn = net.capture()
+    net.init_weights(seed=1)
+
+    # ---- warm-up (through the e2e path, so pinned copies and the D2H are warm too)
+    for i in range(max(3, args.warmup)):
+        net.set_input(hx[i % nbuf], -7, hl[i % nbuf]); step_fn(); host_logits.copy_(net.logits, non_blocking=True)
+    barrier()
+
+    # ---- device-resident timed region: K steps, L2 flushed between steps, CUDA events per step
+    sampler = ClockSampler(local); sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    launches0 = nb.launches
+    barrier()
+    for i in range(args.steps):
+        net.set_input(dx[i % nbuf], -7, dl[i % nbuf])          # device-to-device: inputs already in HBM
+        flush.zero_()
+        ev[i][0].record(); step_fn(); ev[i][1].record()
+    barrier()
+    step_ms = [a.elapsed_time(b) for a, b in ev]
+    launches_timed = launches_per_step * args.steps         # graph replays launch the captured kernels
+    del launches0
+    total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+    total_ms = float(total_ms.item())
+    value = batch * world * args.steps / (total_ms * 1e-3)
+
+    # ---- per-kernel timing of the contraction kernels, live, same inputs (eager launches + events)
+    fam = {}
+    pend = []
+
+    def timer(kind, ops, fn):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); fn(); b.record()
+        pend.append((kind + ":" + nb.last_path, ops, a, b))
+    net.timer = timer
+    for i in range(min(args.steps, 5)):
+        net.set_input(dx[i % nbuf], -7, dl[i % nbuf]); flush.zero_(); net.step()
+    torch.cuda.synchronize()
+    net.timer = None
+    for k, ops, a, b in pend:
+        f = fam.setdefault(k, [0.0, 0.0, 0]); f[0] += ops; f[1] += a.elapsed_time(b) * 1e-3; f[2] += 1
+    clocks = sampler.summary()
+
+    # ---- end to end: pinned host input -> H2D -> step -> D2H logits, every step inside the timed region
+    barrier()
+    t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for i in range(args.steps):
+        net.set_input(hx[i % nbuf], -7, hl[i % nbuf])
+        step_fn()
+        host_logits.copy_(net.logits, non_blocking=True)
+        torch.cuda.current_stream().synchronize()              # the caller consumes the result every step
+    t1.record()
+    barrier()
+    e2e_ms = torch.tensor([t0.elapsed_time(t1)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
+    e2e_value = batch * world * args.steps / (float(e2e_ms.item()) * 1e-3)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel family (tcgen05 contractions)
+    peak_tops, peak_src = None, "unmeasured"
+    try:
+        peak_tops = nb.probe_i8_peak(4000); peak_src = "measured live: tcgen05.mma.kind::i8 128x256x32 issue-rate probe (niti_probe_i8_peak), all SMs"
+    except Exception as ex:          # pragma: no cover
+        peak_src = f"probe failed: {ex}"
+    tc_ops = sum(v[0] for k, v in fam.items() if k.endswith(":tc"))
+    tc_s = sum(v[1] for k, v in fam.items() if k.endswith(":tc"))
+    tc_n = sum(v[2] for k, v in fam.items() if k.endswith(":tc"))
+    all_s = sum(v[1] for v in fam.values())
+    achieved = tc_ops / tc_s / 1e12 if tc_s > 0 else 0.0
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        try:
+            traffic = json.load(open(tpath)).get(args.workload)
+        except Exception:
+            traffic = None
+    roofline = {"bound": "tensor", "kernel": "igemm_kmajor_kernel / dw_mnmajor_kernel (tcgen05 int8 implicit GEMM)",
+                "achieved": achieved, "peak": peak_tops, "unit": "TOP/s",
+                "frac": (achieved / peak_tops) if peak_tops else None, "traffic": traffic,
+                "peak_source": peak_src, "launches_timed": tc_n,
+                "share_of_contraction_time": (tc_s / all_s) if all_s else None,
+                "families": {k: {"TOP/s": (v[0] / v[1] / 1e12) if v[1] else None, "ms": v[1] * 1e3 / max(1, min(args.steps, 5)),
+                                 "launches": v[2] // max(1, min(args.steps, 5))} for k, v in sorted(fam.items())}}
+
+    cpu_baseline = None
+    if world == 1 and not args.no_cpu_baseline:
+        try:
+            cpu_baseline, _ = time_reference(args.workload, args.ref_batch, 3, 1, budget_s=25.0)
+        except Exception as ex:      # pragma: no cover
+            cpu_baseline = {"value": None, "unit": "samples/s", "cores": 0, "kind": "unavailable", "sample": str(ex)}
+
+    ws_mb = (sum(L.y.numel() * 2 for L in net.ops) + net.acc.numel() * 4 + net.dw_acc.numel() * 4) / 2 ** 20
+    line = {
+        "metric": "int8_train_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": world,
+        "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": total_ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+        "config": {"workload": desc_text, "per_gpu_batch": batch, "global_batch": batch * world,
+                   "parallelism": f"dp{world}", "launch": "cuda_graph" if use_graph else "eager",
+                   "l2": "flushed between timed steps (256 MiB write)", "step_working_set_mib": round(ws_mb, 1),
+                   "algorithmic_gop_per_step_per_gpu": net.algorithmic_ops() / 1e9},
+        "e2e": {"value": e2e_value, "unit": "samples/s",
+                "h2d_bytes_per_step": int(hx[0].numel() + hl[0].numel() * 4) * world,
+                "d2h_bytes_per_step": int(host_logits.numel()) * world},
+        "gpu_launches": int(launches_timed),
+        "clocks": clocks,
+        "roofline": roofline,
+        "cpu_baseline": cpu_baseline,
+        "tensor_frac_of_step": (net.algorithmic_ops() / (total_ms / args.steps * 1e-3) / 1e12 / peak_tops) if peak_tops else None,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
