@@ -89,6 +89,14 @@ int niti_absmax(niti_ctx*, const int32_t* acc, size_t n, uint32_t* maxabs /*atom
  *   exp_out (optional) = (int8)(*exp_a + *exp_b + inc); exp_a/exp_b may be NULL (treated as 0). */
 int niti_rescale_act(niti_ctx*, const int32_t* acc, size_t n, const uint32_t* maxabs,
                      int8_t* out, const int8_t* exp_a, const int8_t* exp_b, int8_t* exp_out, niti_stream);
+/* rule A with the neighbouring element-wise op folded into the store (one pass less over HBM):
+ *   relu != 0 : out = max(out, 0)                 (NITI_CPURelu_Int8 after a forward conv)
+ *   gate != 0 : out = gate[i] > 0 ? out : 0       (NITI_CPUReluGrad_Int8 after a dX conv; gate = the
+ *               forward tensor the gradient is taken against; relu(x) > 0 <=> x > 0)
+ * max|acc| and the exponent are those of the un-gated tensor, exactly as in the unfused sequence. */
+int niti_rescale_act_fused(niti_ctx*, const int32_t* acc, size_t n, const uint32_t* maxabs,
+                           int8_t* out, const int8_t* exp_a, const int8_t* exp_b, int8_t* exp_out,
+                           int relu, const int8_t* gate, niti_stream);
 /* rule B — dW / matmul (NITI_GradientConv_Int8.cpp:274-296 sub=2; NITI_Matmul_Int8.cpp:216-228 sub=3):
  *   b==0: zeros; else PSTO(b-sub).  dw_out optional; when w_inout is given the int8 SGD step
  *   w <- clip127(w - dw) (optimizer/NITI_SGD.hpp:49-52, BinaryUtils.hpp:276-299) is fused. */
@@ -110,6 +118,9 @@ int niti_relu_grad(niti_ctx*, const int8_t* x, const int8_t* dy, int8_t* dx, siz
 int niti_maxpool(niti_ctx*, const int8_t* x, int n, int h, int w, int c, int k, int s, int8_t* y, niti_stream); /* NITI_Maxpool_Int8.cpp:24-70 */
 int niti_maxpool_grad(niti_ctx*, const int8_t* x, const int8_t* y, const int8_t* dy, int n, int h, int w, int c,
                       int k, int s, int8_t* dx, niti_stream);                                 /* NITI_CPUPoolGrad_Int8.cpp:36-72 */
+/* same as niti_maxpool_grad, with NITI_CPUReluGrad_Int8 folded in when gate_relu != 0: dx = x > 0 ? dx : 0 */
+int niti_maxpool_grad_gated(niti_ctx*, const int8_t* x, const int8_t* y, const int8_t* dy, int n, int h, int w, int c,
+                            int k, int s, int8_t* dx, int gate_relu, niti_stream);
 int niti_loss_grad(niti_ctx*, const int8_t* logits, const int8_t* ascale, const int32_t* labels,
                    int batch, int classes, int8_t* grad, niti_stream);                        /* NITI_CPULossGrad_Int8.cpp:82-201 */
 

@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(kThreads) maxpool_kernel(const int8_t* __restr
 // For overlapping windows the contributions accumulate with int8 wrap-around, also reproduced.
 __global__ void __launch_bounds__(kThreads) maxpool_grad_kernel(const int8_t* __restrict__ x, const int8_t* __restrict__ y,
                                                                 const int8_t* __restrict__ dy, int n, int h, int w, int c,
-                                                                int k, int s, int oh, int ow, int8_t* __restrict__ dx) {
+                                                                int k, int s, int oh, int ow, int8_t* __restrict__ dx, int gate_relu) {
     const size_t total = (size_t)n * h * w * c;
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
         int ch = (int)(i % c); size_t p = i / c;
@@ -114,7 +114,59 @@ __global__ void __launch_bounds__(kThreads) maxpool_grad_kernel(const int8_t* __
                 }
                 if (first) acc += dy[o];
             }
-        dx[i] = (int8_t)acc;
+        dx[i] = (gate_relu && v <= 0) ? (int8_t)0 : (int8_t)acc;
+    }
+}
+
+// ---- vectorized variants: 16 channels (one 128-bit word) per thread, c % 16 == 0 -------------------
+__device__ __forceinline__ uint4 vmax4x4(uint4 a, uint4 b) {
+    return make_uint4(__vmaxs4(a.x, b.x), __vmaxs4(a.y, b.y), __vmaxs4(a.z, b.z), __vmaxs4(a.w, b.w));
+}
+
+__global__ void __launch_bounds__(kThreads) maxpool_vec_kernel(const uint4* __restrict__ x, int n, int h, int w, int c16,
+                                                               int k, int s, int oh, int ow, uint4* __restrict__ y) {
+    const size_t total = (size_t)n * oh * ow * c16;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        int cv = (int)(i % c16); size_t p = i / c16;
+        int ox = (int)(p % ow); p /= ow;
+        int oy = (int)(p % oh); int b = (int)(p / oh);
+        uint4 m = make_uint4(0x80808080u, 0x80808080u, 0x80808080u, 0x80808080u);
+        for (int ky = 0; ky < k; ++ky) {
+            int iy = oy * s + ky; if (iy >= h) break;
+            for (int kx = 0; kx < k; ++kx) {
+                int ix = ox * s + kx; if (ix >= w) break;
+                m = vmax4x4(m, x[(((size_t)b * h + iy) * w + ix) * c16 + cv]);
+            }
+        }
+        y[i] = m;
+    }
+}
+
+// non-overlapping windows (k == s): one thread owns a whole window x 16 channels, so the "first element
+// >= max in row-major order wins" rule is a running mask and every dx word is written exactly once.
+__global__ void __launch_bounds__(kThreads) maxpool_grad_vec_kernel(const uint4* __restrict__ x, const uint4* __restrict__ y,
+                                                                    const uint4* __restrict__ dy, int n, int h, int w, int c16,
+                                                                    int k, int oh, int ow, uint4* __restrict__ dx, int gate_relu) {
+    const size_t total = (size_t)n * oh * ow * c16;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        int cv = (int)(i % c16); size_t p = i / c16;
+        int ox = (int)(p % ow); p /= ow;
+        int oy = (int)(p % oh); int b = (int)(p / oh);
+        const uint4 m = y[i], g = dy[i];
+        uint4 done = make_uint4(0u, 0u, 0u, 0u);
+        for (int ky = 0; ky < k; ++ky) {
+            int iy = oy * k + ky; if (iy >= h) break;
+            for (int kx = 0; kx < k; ++kx) {
+                int ix = ox * k + kx; if (ix >= w) break;
+                const size_t o = (((size_t)b * h + iy) * w + ix) * c16 + cv;
+                const uint4 v = x[o];
+                uint4 ge = make_uint4(__vcmpges4(v.x, m.x), __vcmpges4(v.y, m.y), __vcmpges4(v.z, m.z), __vcmpges4(v.w, m.w));
+                uint4 r = make_uint4(g.x & ge.x & ~done.x, g.y & ge.y & ~done.y, g.z & ge.z & ~done.z, g.w & ge.w & ~done.w);
+                done = make_uint4(done.x | ge.x, done.y | ge.y, done.z | ge.z, done.w | ge.w);
+                if (gate_relu) { r.x &= __vcmpgts4(v.x, 0u); r.y &= __vcmpgts4(v.y, 0u); r.z &= __vcmpgts4(v.z, 0u); r.w &= __vcmpgts4(v.w, 0u); }
+                dx[o] = r;
+            }
+        }
     }
 }
 
@@ -205,16 +257,35 @@ extern "C" int niti_relu_grad(niti_ctx* ctx, const int8_t* x, const int8_t* dy, 
 extern "C" int niti_maxpool(niti_ctx* ctx, const int8_t* x, int n, int h, int w, int c, int k, int s, int8_t* y, niti_stream st) {
     if (!ctx || !x || !y || n <= 0 || h < k || w < k || c <= 0 || k <= 0 || s <= 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_maxpool");
     int oh = (h - k) / s + 1, ow = (w - k) / s + 1;
+    if (c % 16 == 0 && aligned16(x) && aligned16(y)) {
+        maxpool_vec_kernel<<<grid_for(ctx, (size_t)n * oh * ow * (c / 16)), kThreads, 0, (cudaStream_t)st>>>(
+            reinterpret_cast<const uint4*>(x), n, h, w, c / 16, k, s, oh, ow, reinterpret_cast<uint4*>(y));
+        return niti_check_launch(ctx, "maxpool_vec");
+    }
     maxpool_kernel<<<grid_for(ctx, (size_t)n * oh * ow * c), kThreads, 0, (cudaStream_t)st>>>(x, n, h, w, c, k, s, oh, ow, y);
     return niti_check_launch(ctx, "maxpool");
 }
-extern "C" int niti_maxpool_grad(niti_ctx* ctx, const int8_t* x, const int8_t* y, const int8_t* dy, int n, int h, int w, int c,
-                                 int k, int s, int8_t* dx, niti_stream st) {
+extern "C" int niti_maxpool_grad_gated(niti_ctx* ctx, const int8_t* x, const int8_t* y, const int8_t* dy, int n, int h, int w, int c,
+                                       int k, int s, int8_t* dx, int gate_relu, niti_stream st) {
     if (!ctx || !x || !y || !dy || !dx || n <= 0 || h < k || w < k || c <= 0 || k <= 0 || s <= 0)
         return niti_fail(ctx, NITI_ERR_ARG, "niti_maxpool_grad");
     int oh = (h - k) / s + 1, ow = (w - k) / s + 1;
-    maxpool_grad_kernel<<<grid_for(ctx, (size_t)n * h * w * c), kThreads, 0, (cudaStream_t)st>>>(x, y, dy, n, h, w, c, k, s, oh, ow, dx);
+    if (k == s && c % 16 == 0 && aligned16(x) && aligned16(y) && aligned16(dy) && aligned16(dx)) {
+        if (oh * k != h || ow * k != w) {         // rows / columns no window covers stay zero
+            cudaError_t e = cudaMemsetAsync(dx, 0, (size_t)n * h * w * c, (cudaStream_t)st);
+            if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "maxpool_grad memset", e);
+        }
+        maxpool_grad_vec_kernel<<<grid_for(ctx, (size_t)n * oh * ow * (c / 16)), kThreads, 0, (cudaStream_t)st>>>(
+            reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(y), reinterpret_cast<const uint4*>(dy),
+            n, h, w, c / 16, k, oh, ow, reinterpret_cast<uint4*>(dx), gate_relu);
+        return niti_check_launch(ctx, "maxpool_grad_vec");
+    }
+    maxpool_grad_kernel<<<grid_for(ctx, (size_t)n * h * w * c), kThreads, 0, (cudaStream_t)st>>>(x, y, dy, n, h, w, c, k, s, oh, ow, dx, gate_relu);
     return niti_check_launch(ctx, "maxpool_grad");
+}
+extern "C" int niti_maxpool_grad(niti_ctx* ctx, const int8_t* x, const int8_t* y, const int8_t* dy, int n, int h, int w, int c,
+                                 int k, int s, int8_t* dx, niti_stream st) {
+    return niti_maxpool_grad_gated(ctx, x, y, dy, n, h, w, c, k, s, dx, 0, st);
 }
 extern "C" int niti_loss_grad(niti_ctx* ctx, const int8_t* logits, const int8_t* ascale, const int32_t* labels,
                               int batch, int classes, int8_t* grad, niti_stream st) {

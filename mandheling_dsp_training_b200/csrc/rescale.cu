@@ -52,7 +52,8 @@ template <int MODE>
 __global__ void __launch_bounds__(kThreads)
 rescale_kernel(const int32_t* __restrict__ acc, size_t n, const uint32_t* __restrict__ maxabs, int sub,
                int8_t* __restrict__ out, int8_t* __restrict__ w_inout,
-               const int8_t* __restrict__ exp_a, const int8_t* __restrict__ exp_b, int8_t* __restrict__ exp_out) {
+               const int8_t* __restrict__ exp_a, const int8_t* __restrict__ exp_b, int8_t* __restrict__ exp_out,
+               int relu, const int8_t* __restrict__ gate) {
     const int b = niti_bitwidth(*maxabs);
     int shift;          // PSTO shift; kind: 0 = PSTO, 1 = raw cast, 2 = zeros
     int kind = 0;
@@ -82,6 +83,11 @@ rescale_kernel(const int32_t* __restrict__ acc, size_t n, const uint32_t* __rest
         if (out != nullptr) {
             uint4 o = make_uint4(pack4(r[0], r[1], r[2], r[3]), pack4(r[4], r[5], r[6], r[7]),
                                  pack4(r[8], r[9], r[10], r[11]), pack4(r[12], r[13], r[14], r[15]));
+            if (MODE == 0 && relu) { o.x = __vmaxs4(o.x, 0u); o.y = __vmaxs4(o.y, 0u); o.z = __vmaxs4(o.z, 0u); o.w = __vmaxs4(o.w, 0u); }
+            if (MODE == 0 && gate != nullptr) {       // fused NITI_CPUReluGrad: pass where the forward value was > 0
+                uint4 gv = reinterpret_cast<const uint4*>(gate)[g];
+                o.x &= __vcmpgts4(gv.x, 0u); o.y &= __vcmpgts4(gv.y, 0u); o.z &= __vcmpgts4(gv.z, 0u); o.w &= __vcmpgts4(gv.w, 0u);
+            }
             reinterpret_cast<uint4*>(out)[g] = o;
         }
         if (MODE == 1 && w_inout != nullptr) {
@@ -107,6 +113,12 @@ rescale_kernel(const int32_t* __restrict__ acc, size_t n, const uint32_t* __rest
     if (blockIdx.x == 0) {
         for (size_t i = ngrp * 16 + threadIdx.x; i < n; i += blockDim.x) {
             int32_t r = conv(acc[i]);
+            if (MODE == 0) {
+                int8_t v = (int8_t)r;
+                if (relu && v < 0) v = 0;
+                if (gate != nullptr && gate[i] <= 0) v = 0;
+                r = v;
+            }
             if (out != nullptr) out[i] = (int8_t)r;
             if (MODE == 1 && w_inout != nullptr) {
                 int32_t u = (int32_t)w_inout[i] - (int32_t)(int8_t)r;
@@ -179,8 +191,19 @@ extern "C" int niti_rescale_act(niti_ctx* ctx, const int32_t* acc, size_t n, con
     if (n && (!aligned16(acc) || !aligned16(out)))
         return niti_fail(ctx, NITI_ERR_ARG, "niti_rescale_act: buffers must be 16-byte aligned");
     rescale_kernel<0><<<grid_for(ctx, n / 16 + 1), kThreads, 0, (cudaStream_t)st>>>(
-        acc, n, maxabs, 0, out, nullptr, exp_a, exp_b, exp_out);
+        acc, n, maxabs, 0, out, nullptr, exp_a, exp_b, exp_out, 0, nullptr);
     return niti_check_launch(ctx, "rescale_act");
+}
+
+extern "C" int niti_rescale_act_fused(niti_ctx* ctx, const int32_t* acc, size_t n, const uint32_t* maxabs, int8_t* out,
+                                      const int8_t* exp_a, const int8_t* exp_b, int8_t* exp_out, int relu,
+                                      const int8_t* gate, niti_stream st) {
+    if (!ctx || !maxabs || (n && (!acc || !out))) return niti_fail(ctx, NITI_ERR_ARG, "niti_rescale_act_fused");
+    if (n && (!aligned16(acc) || !aligned16(out) || (gate && !aligned16(gate))))
+        return niti_fail(ctx, NITI_ERR_ARG, "niti_rescale_act_fused: buffers must be 16-byte aligned");
+    rescale_kernel<0><<<grid_for(ctx, n / 16 + 1), kThreads, 0, (cudaStream_t)st>>>(
+        acc, n, maxabs, 0, out, nullptr, exp_a, exp_b, exp_out, relu, gate);
+    return niti_check_launch(ctx, "rescale_act_fused");
 }
 
 extern "C" int niti_rescale_grad(niti_ctx* ctx, const int32_t* acc, size_t n, const uint32_t* maxabs, int sub,
@@ -190,7 +213,7 @@ extern "C" int niti_rescale_grad(niti_ctx* ctx, const int32_t* acc, size_t n, co
     if (!aligned16(acc) || (dw_out && !aligned16(dw_out)) || (w_inout && !aligned16(w_inout)))
         return niti_fail(ctx, NITI_ERR_ARG, "niti_rescale_grad: buffers must be 16-byte aligned");
     rescale_kernel<1><<<grid_for(ctx, n / 16 + 1), kThreads, 0, (cudaStream_t)st>>>(
-        acc, n, maxabs, sub, dw_out, w_inout, nullptr, nullptr, nullptr);
+        acc, n, maxabs, sub, dw_out, w_inout, nullptr, nullptr, nullptr, 0, nullptr);
     return niti_check_launch(ctx, "rescale_grad");
 }
 

@@ -47,6 +47,7 @@ _SIGS = {
     "niti_absmax": (C.c_int, [_P, _P, C.c_size_t, _P, _P]),
     "niti_rescale_act": (C.c_int, [_P, _P, C.c_size_t, _P, _P, _P, _P, _P, _P]),
     "niti_rescale_grad": (C.c_int, [_P, _P, C.c_size_t, _P, C.c_int, _P, _P, _P]),
+    "niti_rescale_act_fused": (C.c_int, [_P, _P, C.c_size_t, _P, _P, _P, _P, _P, C.c_int, _P, _P]),
     "niti_sgd_update": (C.c_int, [_P, _P, _P, C.c_size_t, _P]),
     "niti_conv_fwd": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, _P]),
     "niti_conv_dx": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P]),
@@ -56,6 +57,7 @@ _SIGS = {
     "niti_relu_grad": (C.c_int, [_P, _P, _P, _P, C.c_size_t, _P]),
     "niti_maxpool": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
     "niti_maxpool_grad": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
+    "niti_maxpool_grad_gated": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, C.c_int, _P]),
     "niti_loss_grad": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, _P, _P]),
     "niti_nchw_to_nhwc": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
     "niti_nhwc_to_nchw": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
@@ -157,6 +159,10 @@ class NitiB200:
         self._ck(self.lib.niti_rescale_act(self.h, _ptr(acc), n, _ptr(maxabs), _ptr(out), _ptr(exp_a), _ptr(exp_b),
                                            _ptr(exp_out), self._stream(stream)))
 
+    def rescale_act_fused(self, acc, n, maxabs, out, exp_a=None, exp_b=None, exp_out=None, relu=False, gate=None, stream=None):
+        self._ck(self.lib.niti_rescale_act_fused(self.h, _ptr(acc), n, _ptr(maxabs), _ptr(out), _ptr(exp_a), _ptr(exp_b),
+                                                 _ptr(exp_out), int(bool(relu)), _ptr(gate), self._stream(stream)))
+
     def rescale_grad(self, acc, n, maxabs, sub, dw_out=None, w_inout=None, stream=None):
         self._ck(self.lib.niti_rescale_grad(self.h, _ptr(acc), n, _ptr(maxabs), sub, _ptr(dw_out), _ptr(w_inout),
                                             self._stream(stream)))
@@ -189,6 +195,10 @@ class NitiB200:
 
     def maxpool_grad(self, x, y, dy, n, h, w, c, k, s, dx, stream=None):
         self._ck(self.lib.niti_maxpool_grad(self.h, _ptr(x), _ptr(y), _ptr(dy), n, h, w, c, k, s, _ptr(dx), self._stream(stream)))
+
+    def maxpool_grad_gated(self, x, y, dy, n, h, w, c, k, s, dx, gate_relu, stream=None):
+        self._ck(self.lib.niti_maxpool_grad_gated(self.h, _ptr(x), _ptr(y), _ptr(dy), n, h, w, c, k, s, _ptr(dx),
+                                                  int(bool(gate_relu)), self._stream(stream)))
 
     def loss_grad(self, logits, ascale, labels, batch, classes, grad, stream=None):
         self._ck(self.lib.niti_loss_grad(self.h, _ptr(logits), _ptr(ascale), _ptr(labels), batch, classes, _ptr(grad), self._stream(stream)))

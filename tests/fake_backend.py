@@ -78,6 +78,19 @@ class OracleBackend:
             e = (int(_np(exp_a)[0]) if exp_a is not None else 0) + (int(_np(exp_b)[0]) if exp_b is not None else 0) + inc
             _np(exp_out)[0] = np.int8(e)
 
+    def rescale_act_fused(self, acc, n, maxabs, out, exp_a=None, exp_b=None, exp_out=None, relu=False, gate=None, stream=None):
+        self.rescale_act(acc, n, maxabs, out, exp_a, exp_b, exp_out)
+        o = _np(out).reshape(-1)
+        if relu:
+            o[:n] = np.maximum(o[:n], 0)
+        if gate is not None:
+            o[:n] = np.where(_np(gate).reshape(-1)[:n] > 0, o[:n], 0)
+
+    def maxpool_grad_gated(self, x, y, dy, n, h, w, c, k, s, dx, gate_relu, stream=None):
+        self.maxpool_grad(x, y, dy, n, h, w, c, k, s, dx)
+        if gate_relu:
+            _np(dx)[:] = np.where(_np(x) > 0, _np(dx), 0)
+
     def rescale_grad(self, acc, n, maxabs, sub, dw_out=None, w_inout=None, stream=None):
         a = _np(acc)[:n]
         b = self._bits(int(_np(maxabs)[0]))

@@ -25,9 +25,14 @@ def _data(batch, chw, seed):
     return x, rng.integers(0, 10, size=batch).astype(np.int32)
 
 
-@pytest.mark.parametrize("spec,chw,batch", [(lenet_spec(), (1, 28, 28), 8), (TC_NET, (16, 8, 8), 8)])
-def test_training_steps_bit_exact_vs_oracle(nb, oracle, spec, chw, batch):
-    net = NitiNet(nb, spec, batch, chw)
+RGB_NET = [("conv", 32, 3, 1, 1), ("relu",), ("conv", 32, 3, 1, 1), ("relu",), ("pool", 2, 2), ("flatten",),
+           ("conv", 64, 1, 1, 0), ("relu",), ("conv", 12, 1, 1, 0)]
+
+
+@pytest.mark.parametrize("fuse", [True, False])
+@pytest.mark.parametrize("spec,chw,batch", [(lenet_spec(), (1, 28, 28), 8), (TC_NET, (16, 8, 8), 8), (RGB_NET, (3, 8, 8), 8)])
+def test_training_steps_bit_exact_vs_oracle(nb, oracle, spec, chw, batch, fuse):
+    net = NitiNet(nb, spec, batch, chw, fuse=fuse)
     ws = [(w.copy(), e) for w, e in net.init_weights(seed=1)]
     paths = set()
     for it in range(3):
