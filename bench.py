@@ -155,32 +155,55 @@ def run_reference_arm(args):
 
 # ----------------------------------------------------------------------------------------------------
 class ClockSampler(threading.Thread):
-    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
-        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    """SM clock + throttle reasons sampled through NVML every 20 ms while the benchmark runs."""
 
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.samples, self.stop_flag = index, [], False
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.max_mhz = None
 
     def run(self):
+        if not self.ok:
+            return
+        nv = self.nv
         while not self.stop_flag:
             try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.index)],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.samples.append([f.strip() for f in out.split(",")])
+                mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                try:
+                    reasons = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    reasons = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                util = nv.nvmlDeviceGetUtilizationRates(self.h).gpu
+                self.samples.append((mhz, reasons, util))
             except Exception:
                 pass
-            time.sleep(0.1)
+            time.sleep(0.02)
 
     def summary(self):
         self.stop_flag = True
-        sm = [int(s[0]) for s in self.samples if s[0].isdigit()]
-        mx = [int(s[1]) for s in self.samples if s[1].isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({n for s in self.samples for n, v in zip(names, s[2:6]) if v.lower().startswith("active")})
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(self.samples)}
+        nv = getattr(self, "nv", None)
+        busy = [s for s in self.samples if s[2] > 0] or self.samples
+        sm = [s[0] for s in busy]
+        names = {}
+        if nv is not None:
+            for key, label in (("nvmlClocksThrottleReasonHwSlowdown", "hw_slowdown"),
+                               ("nvmlClocksThrottleReasonHwThermalSlowdown", "hw_thermal_slowdown"),
+                               ("nvmlClocksThrottleReasonSwThermalSlowdown", "sw_thermal_slowdown"),
+                               ("nvmlClocksThrottleReasonSwPowerCap", "sw_power_cap")):
+                if hasattr(nv, key):
+                    names[getattr(nv, key)] = label
+        reasons = sorted({label for s in busy for bit, label in names.items() if s[1] & bit})
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": self.max_mhz,
+                "reasons": reasons, "samples": len(busy)}
 
 
 def main():
