@@ -45,9 +45,9 @@ typedef struct {
     int32_t stride, pad, dil;
 } niti_conv_desc;
 
-/* Which kernel family to use.  AUTO picks tcgen05 when the shape qualifies (channel counts that are
- * multiples of 16), else the SIMT kernels.  FORCE_* are for tests and benchmarks. */
-enum { NITI_PATH_AUTO = 0, NITI_PATH_SIMT = 1, NITI_PATH_TC = 2 };
+/* Which kernel family to use.  AUTO picks, in order: TMA-fed tcgen05 (channel counts multiple of 64),
+ * cp.async-fed tcgen05 (multiple of 16), SIMT.  The others force one family (tests, benchmarks). */
+enum { NITI_PATH_AUTO = 0, NITI_PATH_SIMT = 1, NITI_PATH_TC = 2, NITI_PATH_TMA = 3 };
 
 /* ---- context ------------------------------------------------------------------------------- */
 int         niti_ctx_create(int device, niti_ctx** out);
@@ -57,7 +57,7 @@ int         niti_set_path(niti_ctx* ctx, int path);
 int         niti_version(void);
 /* kernels launched through this context since creation (bench.py's gpu_launches evidence) */
 int64_t     niti_launch_count(niti_ctx* ctx);
-/* name of the kernel family the last conv/matmul call used: "tc" or "simt" */
+/* name of the kernel family the last conv/matmul call used: "tma", "tc" or "simt" */
 const char* niti_last_path(niti_ctx* ctx);
 
 /* ---- phase 1: int32 accumulators + running max|acc| ---------------------------------------

@@ -387,14 +387,22 @@ int tc_conv_fwd_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, con
     return dispatch_kmajor(ctx, p, st);
 }
 
-int tc_conv_dx_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* dy, const int8_t* w, int32_t* acc,
-                   uint32_t* maxabs, cudaStream_t st) {
-    const int oh = conv_out_h(d), ow = conv_out_w(d), taps = d->kh * d->kw;
-    int8_t* wt; int rc = niti_ws_i8(ctx, (size_t)d->oc * taps * d->c, &wt); if (rc) return rc;
+// OHWI -> [c][tap][oc] into the context's int8 workspace (the K-major B operand of dX)
+int tc_transpose_w(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* w, int8_t** wt_out, cudaStream_t st) {
+    const int taps = d->kh * d->kw;
     size_t total = (size_t)d->oc * taps * d->c;
+    int8_t* wt; int rc = niti_ws_i8(ctx, total, &wt); if (rc) return rc;
     int blocks = (int)((total + 255) / 256); if (blocks > ctx->sm_count * 8) blocks = ctx->sm_count * 8;
     transpose_w_kernel<<<blocks, 256, 0, st>>>(w, wt, d->oc, taps, d->c);
     if ((rc = niti_check_launch(ctx, "transpose_w"))) return rc;
+    *wt_out = wt;
+    return NITI_OK;
+}
+
+int tc_conv_dx_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* dy, const int8_t* w, int32_t* acc,
+                   uint32_t* maxabs, cudaStream_t st) {
+    const int oh = conv_out_h(d), ow = conv_out_w(d), taps = d->kh * d->kw;
+    int8_t* wt; int rc = tc_transpose_w(ctx, d, w, &wt, st); if (rc) return rc;
     TcParams p{};
     p.A = dy; p.B = wt; p.acc = acc; p.maxabs = maxabs;
     p.M = d->n * d->h * d->w; p.Ncols = d->c; p.Ktotal = taps * d->oc;

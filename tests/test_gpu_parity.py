@@ -63,25 +63,38 @@ TC_SHAPES = [
     (2, 64, 8, 8, 64, 1, 2, 0),       # 1x1 stride 2 (ResNet downsample)
     (1, 256, 4, 4, 512, 3, 1, 1),     # K = 2304, N = 512
     (2, 48, 5, 5, 80, 3, 1, 2),       # pad 2 > (k-1)/2
+    (2, 64, 9, 9, 64, 3, 1, 1),       # TMA path, 64-byte swizzle, ragged M
+    (3, 128, 7, 5, 192, 3, 1, 1),     # TMA path, non-square, N = 192 (ragged N tile)
+    (2, 64, 12, 12, 128, 5, 1, 2),    # 5x5 pad 2
+    (2, 128, 9, 9, 64, 3, 2, 1),      # stride 2 forward / dW via TMA, dX via cp.async
+    (256, 512, 1, 1, 512, 1, 1, 0),   # FC as 1x1 conv, split-K
+    (2, 64, 10, 10, 64, 3, 1, 0),     # pad 0
     (2, 16, 9, 9, 32, 3, 1, 2),       # dilation handled below with dil=2
 ]
 
 
 @pytest.mark.parametrize("cfg", TC_SHAPES)
-@pytest.mark.parametrize("path", ["simt", "tc"])
+@pytest.mark.parametrize("path", ["simt", "tc", "tma"])
 def test_accumulators_and_outputs_vs_oracle(nb, run, oracle, cfg, path):
-    from tests.gpu_util import PATH_SIMT, PATH_TC, to_desc
+    from tests.gpu_util import PATH_SIMT, PATH_TC, PATH_TMA, to_desc
     n, c, h, w, oc, k, st, p = cfg
     dil = 2 if cfg == TC_SHAPES[-1] else 1
     s = shape(n, c, h, w, oc, k, stride=st, pad=p, dil=dil)
     rng = np.random.default_rng(hash(cfg) % (2 ** 31))
     x = _rand(rng, (n, c, h, w)); wt = _rand(rng, (oc, c, k, k), -64, 64)
     dy = _rand(rng, (n, oc, s.oh, s.ow), -50, 50)
-    nb.set_path(PATH_SIMT if path == "simt" else PATH_TC)
+    nb.set_path({"simt": PATH_SIMT, "tc": PATH_TC, "tma": PATH_TMA}[path])
     try:
-        fwd_ok = path == "simt" or (c % 16 == 0 and oc % 4 == 0)
-        dx_ok = path == "simt" or (oc % 16 == 0 and c % 4 == 0)
-        dw_ok = path == "simt" or (oc % 16 == 0 and c % 16 == 0)
+        if path == "tma":
+            fwd_ok = c % 64 == 0 and oc % 4 == 0
+            dx_ok = st == 1 and oc % 64 == 0 and c % 4 == 0 and (k - 1) * dil - p >= 0
+            dw_ok = oc % 16 == 0 and c % 64 == 0
+            if not (fwd_ok or dx_ok or dw_ok):
+                pytest.skip("shape not eligible for the TMA path")
+        else:
+            fwd_ok = path == "simt" or (c % 16 == 0 and oc % 4 == 0)
+            dx_ok = path == "simt" or (oc % 16 == 0 and c % 4 == 0)
+            dw_ok = path == "simt" or (oc % 16 == 0 and c % 16 == 0)
         if fwd_ok:
             acc, mx = run.conv_fwd_acc(s, x, wt)
             oacc, _ = oracle.conv_fwd_acc(s, x, wt)
@@ -218,7 +231,7 @@ def test_full_size_vgg_layer_properties(nb):
     check size-independent properties on the device: (1) the tensor-core and SIMT kernels agree
     element for element, (2) dW is additive over a batch split, (3) conv is odd in x."""
     import torch
-    from tests.gpu_util import PATH_SIMT, PATH_TC
+    from tests.gpu_util import PATH_SIMT, PATH_TC, PATH_TMA
     from mandheling_dsp_training_b200.lib import desc
     torch.manual_seed(0)
     n, c, hw, oc = 256, 256, 8, 256
@@ -227,7 +240,7 @@ def test_full_size_vgg_layer_properties(nb):
     w = torch.randint(-20, 21, (oc, 3, 3, c), dtype=torch.int8, device="cuda")
     dy = torch.randint(-30, 31, (n, hw, hw, oc), dtype=torch.int8, device="cuda")
     outs = {}
-    for path in (PATH_SIMT, PATH_TC):
+    for path in (PATH_SIMT, PATH_TC, PATH_TMA):
         nb.set_path(path)
         acc = torch.empty((n, hw, hw, oc), dtype=torch.int32, device="cuda")
         dxa = torch.empty((n, hw, hw, c), dtype=torch.int32, device="cuda")
@@ -236,11 +249,11 @@ def test_full_size_vgg_layer_properties(nb):
         torch.cuda.synchronize()
         outs[path] = (acc, dxa, dwa)
     nb.set_path(0)
-    for a, b in zip(outs[PATH_SIMT], outs[PATH_TC]):
-        assert torch.equal(a, b)
-    acc, dxa, dwa = outs[PATH_TC]
+    for a, b, c_ in zip(outs[PATH_SIMT], outs[PATH_TC], outs[PATH_TMA]):
+        assert torch.equal(a, b) and torch.equal(a, c_)
+    acc, dxa, dwa = outs[PATH_TMA]
     # (2) additivity of dW over the batch
-    nb.set_path(PATH_TC)
+    nb.set_path(PATH_TMA)
     dh = desc(n // 2, c, hw, hw, oc, 3, pad=1)
     p0 = torch.empty_like(dwa); p1 = torch.empty_like(dwa)
     nb.conv_dw_acc(dh, x[: n // 2].contiguous(), dy[: n // 2].contiguous(), p0)

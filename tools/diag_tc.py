@@ -8,12 +8,12 @@ import numpy as np
 import torch
 from oracle.oracle import Oracle, shape
 from mandheling_dsp_training_b200 import NitiB200
-from mandheling_dsp_training_b200.lib import PATH_SIMT, PATH_TC
+from mandheling_dsp_training_b200.lib import PATH_SIMT, PATH_TC, PATH_TMA
 from tests.gpu_util import Runner
 
 path = sys.argv[1] if len(sys.argv) > 1 else "tc"
 nb = NitiB200(0); run = Runner(nb); orc = Oracle()
-nb.set_path(PATH_SIMT if path == "simt" else PATH_TC)
+nb.set_path({"simt": PATH_SIMT, "tc": PATH_TC, "tma": PATH_TMA, "auto": 0}[path])
 
 
 def report(tag, got, want):
@@ -29,7 +29,9 @@ def report(tag, got, want):
         print(f"      wrong along {name}: {np.flatnonzero(wrong)[:40].tolist()} ({wrong.sum()}/{wrong.size})", flush=True)
 
 
-cases = [(2, 16, 8, 8, 32, 3, 1, 1), (4, 64, 8, 8, 128, 3, 1, 1), (2, 128, 6, 6, 256, 3, 1, 1),
+cases = [(2, 64, 8, 8, 64, 3, 1, 1), (2, 128, 8, 8, 128, 3, 1, 1), (2, 64, 9, 9, 64, 3, 1, 1), (2, 128, 9, 9, 64, 3, 2, 1),
+         (256, 512, 1, 1, 512, 1, 1, 0), (3, 128, 7, 5, 192, 3, 1, 1),
+         (2, 16, 8, 8, 32, 3, 1, 1), (4, 64, 8, 8, 128, 3, 1, 1), (2, 128, 6, 6, 256, 3, 1, 1),
          (3, 32, 9, 7, 48, 3, 1, 1), (2, 32, 10, 10, 64, 3, 2, 1), (1, 256, 4, 4, 512, 3, 1, 1),
          (64, 832, 1, 1, 512, 1, 1, 0)]
 for cfg in cases:
