@@ -103,6 +103,11 @@ int niti_rescale_act_fused(niti_ctx*, const int32_t* acc, size_t n, const uint32
 int niti_rescale_grad(niti_ctx*, const int32_t* acc, size_t n, const uint32_t* maxabs, int sub,
                       int8_t* dw_out, int8_t* w_inout, niti_stream);
 int niti_sgd_update(niti_ctx*, int8_t* w, const int8_t* dw, size_t n, niti_stream);
+/* rule B per output-channel slice + post-alignment — NITI_GradientSplitConv_Int8.cpp:318-372 (sub = 3):
+ *   acc holds `slices` equal contiguous slices of n_per_slice words; maxabs[s] = max|acc_s| (niti_absmax per slice);
+ *   out_s = b_s==0 ? 0 : PSTO(acc_s, b_s-sub), then out_s /= 2^(max_s b - b_s) (C truncation). */
+int niti_rescale_grad_split(niti_ctx*, const int32_t* acc, size_t n_per_slice, int slices,
+                            const uint32_t* maxabs, int sub, int8_t* out, niti_stream);
 
 /* ---- whole ops = phase 1 + phase 2 on the context's workspace -------------------------------
  * Drop-in for the four reference executions (same inputs/outputs, NHWC/OHWI instead of NC4HW4). */
@@ -130,6 +135,23 @@ int niti_nhwc_to_nchw(niti_ctx*, const int8_t* src, int n, int c, int h, int w, 
 /* the reference CPU path's int8 "NC4HW4" is [c/4][n][h*w][4] (NITI_Conv_Int8.cpp:111,191,229-230) */
 int niti_nc4hw4_to_nhwc(niti_ctx*, const int8_t* src, int n, int c, int h, int w, int8_t* dst, niti_stream);
 int niti_nhwc_to_nc4hw4(niti_ctx*, const int8_t* src, int n, int c, int h, int w, int8_t* dst, niti_stream);
+
+/* generic strided gather (layout conversion for the MNN plug-in: NC4HW4 / NCHW / transposed / rot180
+ * operands as the reference's grad rule hands them over, tools/train/source/grad/NITI_Conv_Int8_Grad.cpp:84-191):
+ *   dst is contiguous [dims[0]]..[dims[4]];  dst[i0..i4] = src[base + sum_k i_k * strides[k]]
+ *   when split_hi >= 0 the pair (split_hi, split_lo) is one logical axis cut in blocks of dims[split_lo]
+ *   (the 4-lane channel block of NC4HW4): positions with i_hi*dims[split_lo] + i_lo >= split_limit read as 0. */
+int niti_gather_i8(niti_ctx*, const int8_t* src, int64_t base, int8_t* dst, const int32_t dims[5],
+                   const int64_t strides[5], int split_hi, int split_lo, int split_limit, niti_stream);
+
+/* ---- device memory for hosts that own no CUDA runtime (the MNN plug-in links no CUDA library) -- */
+int niti_dev_alloc(niti_ctx*, size_t bytes, void** out);
+int niti_dev_free(niti_ctx*, void* p);
+int niti_dev_memset(niti_ctx*, void* p, int value, size_t bytes, niti_stream);
+int niti_copy_h2d(niti_ctx*, void* dst_dev, const void* src_host, size_t bytes, niti_stream);
+int niti_copy_d2h(niti_ctx*, void* dst_host, const void* src_dev, size_t bytes, niti_stream);
+int niti_copy_d2d(niti_ctx*, void* dst_dev, const void* src_dev, size_t bytes, niti_stream);
+int niti_stream_sync(niti_ctx*, niti_stream);
 
 /* ---- host-buffer convenience (the e2e leg): H2D, op, D2H inside the call ------------------- */
 int niti_conv_fwd_host(niti_ctx*, const niti_conv_desc*, const int8_t* x_nhwc, const int8_t* w_ohwi,

@@ -247,6 +247,38 @@ int niti_conv_fwd_host(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, 
     return NITI_OK;
 }
 
+// ---- device memory for CUDA-free hosts (mnn_backend/ links no CUDA library) ------------------------
+int niti_dev_alloc(niti_ctx* ctx, size_t bytes, void** out) {
+    if (!ctx || !out) return niti_fail(ctx, NITI_ERR_ARG, "niti_dev_alloc");
+    *out = nullptr;
+    cudaError_t e = cudaMalloc(out, bytes ? bytes : 1);
+    return e == cudaSuccess ? NITI_OK : niti_fail(ctx, NITI_ERR_CUDA, "niti_dev_alloc", e);
+}
+int niti_dev_free(niti_ctx* ctx, void* p) {
+    if (!ctx) return NITI_ERR_ARG;
+    cudaError_t e = cudaFree(p);
+    return e == cudaSuccess ? NITI_OK : niti_fail(ctx, NITI_ERR_CUDA, "niti_dev_free", e);
+}
+int niti_dev_memset(niti_ctx* ctx, void* p, int value, size_t bytes, niti_stream st) {
+    if (!ctx || (!p && bytes)) return niti_fail(ctx, NITI_ERR_ARG, "niti_dev_memset");
+    cudaError_t e = cudaMemsetAsync(p, value, bytes, (cudaStream_t)st);
+    return e == cudaSuccess ? NITI_OK : niti_fail(ctx, NITI_ERR_CUDA, "niti_dev_memset", e);
+}
+static int copy_kind(niti_ctx* ctx, void* dst, const void* src, size_t bytes, cudaMemcpyKind k, niti_stream st, const char* what) {
+    if (!ctx || (bytes && (!dst || !src))) return niti_fail(ctx, NITI_ERR_ARG, what);
+    if (!bytes) return NITI_OK;
+    cudaError_t e = cudaMemcpyAsync(dst, src, bytes, k, (cudaStream_t)st);
+    return e == cudaSuccess ? NITI_OK : niti_fail(ctx, NITI_ERR_CUDA, what, e);
+}
+int niti_copy_h2d(niti_ctx* ctx, void* d, const void* s, size_t n, niti_stream st) { return copy_kind(ctx, d, s, n, cudaMemcpyHostToDevice, st, "niti_copy_h2d"); }
+int niti_copy_d2h(niti_ctx* ctx, void* d, const void* s, size_t n, niti_stream st) { return copy_kind(ctx, d, s, n, cudaMemcpyDeviceToHost, st, "niti_copy_d2h"); }
+int niti_copy_d2d(niti_ctx* ctx, void* d, const void* s, size_t n, niti_stream st) { return copy_kind(ctx, d, s, n, cudaMemcpyDeviceToDevice, st, "niti_copy_d2d"); }
+int niti_stream_sync(niti_ctx* ctx, niti_stream st) {
+    if (!ctx) return NITI_ERR_ARG;
+    cudaError_t e = cudaStreamSynchronize((cudaStream_t)st);
+    return e == cudaSuccess ? NITI_OK : niti_fail(ctx, NITI_ERR_CUDA, "niti_stream_sync", e);
+}
+
 int niti_probe_i8_peak(niti_ctx* ctx, int iters, double* tops_out) {
     if (!ctx || !tops_out || iters <= 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_probe_i8_peak");
     return tc_probe_i8_peak(ctx, iters, tops_out);

@@ -238,6 +238,23 @@ __global__ void __launch_bounds__(kThreads) nc4_to_nhwc_kernel(const int8_t* __r
         else if (ch < c) dst[nhwc] = src[i];
     }
 }
+
+// generic 5-d strided gather with an optional split-axis bound (see niti_gather_i8 in niti_b200.h)
+struct GatherArgs { int dims[5]; long long strides[5]; long long base; int split_hi, split_lo, split_limit; };
+__global__ void __launch_bounds__(kThreads) gather_kernel(const int8_t* __restrict__ src, int8_t* __restrict__ dst, GatherArgs g) {
+    const size_t total = (size_t)g.dims[0] * g.dims[1] * g.dims[2] * g.dims[3] * g.dims[4];
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        int idx[5]; size_t p = i;
+#pragma unroll
+        for (int k = 4; k >= 0; --k) { idx[k] = (int)(p % g.dims[k]); p /= g.dims[k]; }
+        long long off = g.base;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) off += idx[k] * g.strides[k];
+        bool ok = true;
+        if (g.split_hi >= 0) ok = idx[g.split_hi] * g.dims[g.split_lo] + idx[g.split_lo] < g.split_limit;
+        dst[i] = ok ? src[off] : (int8_t)0;
+    }
+}
 } // namespace
 
 extern "C" int niti_relu(niti_ctx* ctx, const int8_t* x, int8_t* y, size_t n, niti_stream st) {
@@ -314,4 +331,17 @@ extern "C" int niti_nhwc_to_nc4hw4(niti_ctx* ctx, const int8_t* src, int n, int 
     if (!ctx || !src || !dst || n <= 0 || c <= 0 || h <= 0 || w <= 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_nhwc_to_nc4hw4");
     nc4_to_nhwc_kernel<<<grid_for(ctx, (size_t)((c + 3) / 4) * n * h * w * 4), kThreads, 0, (cudaStream_t)st>>>(src, n, c, h * w, dst, true);
     return niti_check_launch(ctx, "nhwc_to_nc4hw4");
+}
+extern "C" int niti_gather_i8(niti_ctx* ctx, const int8_t* src, int64_t base, int8_t* dst, const int32_t dims[5],
+                              const int64_t strides[5], int split_hi, int split_lo, int split_limit, niti_stream st) {
+    if (!ctx || !src || !dst || !dims || !strides || split_hi > 4 || split_lo > 4 || (split_hi >= 0 && split_lo < 0))
+        return niti_fail(ctx, NITI_ERR_ARG, "niti_gather_i8");
+    GatherArgs g; size_t total = 1;
+    for (int k = 0; k < 5; ++k) {
+        if (dims[k] <= 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_gather_i8: dims");
+        g.dims[k] = dims[k]; g.strides[k] = strides[k]; total *= (size_t)dims[k];
+    }
+    g.base = base; g.split_hi = split_hi; g.split_lo = split_lo; g.split_limit = split_limit;
+    gather_kernel<<<grid_for(ctx, total), kThreads, 0, (cudaStream_t)st>>>(src, dst, g);
+    return niti_check_launch(ctx, "gather_i8");
 }

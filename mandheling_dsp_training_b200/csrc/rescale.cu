@@ -154,6 +154,25 @@ __global__ void __launch_bounds__(kThreads) sgd_kernel(int8_t* __restrict__ w, c
     }
 }
 
+
+// rule B per OC slice with the post-alignment of NITI_GradientSplitConv_Int8 (NITI_GradientSplitConv_Int8.cpp:318-372):
+// slice s: b_s = bitwidth(max|acc_s|); v = b_s == 0 ? 0 : PSTO(acc, b_s - sub); then slices whose b_s is below the
+// largest one are integer-divided (C truncation) by 2^(max b - b_s).
+__global__ void __launch_bounds__(kThreads)
+rescale_split_kernel(const int32_t* __restrict__ acc, size_t per, int slices, const uint32_t* __restrict__ maxabs, int sub,
+                     int8_t* __restrict__ out) {
+    int bmax = 0;
+    for (int s = 0; s < slices; ++s) bmax = max(bmax, niti_bitwidth(maxabs[s]));
+    const size_t n = per * (size_t)slices;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const int b = niti_bitwidth(maxabs[i / per]);
+        int32_t v = b == 0 ? 0 : niti_psto(acc[i], b - sub);
+        v = (int32_t)(int8_t)v;
+        if (bmax > b) { const int32_t dv = niti_shl1(bmax - b); v = dv == INT32_MIN ? 0 : v / dv; }
+        out[i] = (int8_t)v;
+    }
+}
+
 __global__ void zero_u32_kernel(uint32_t* p, int count) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < count) p[i] = 0u;
@@ -223,4 +242,11 @@ extern "C" int niti_sgd_update(niti_ctx* ctx, int8_t* w, const int8_t* dw, size_
     if (!aligned16(w) || !aligned16(dw)) return niti_fail(ctx, NITI_ERR_ARG, "niti_sgd_update: 16-byte alignment");
     sgd_kernel<<<grid_for(ctx, n / 16 + 1), kThreads, 0, (cudaStream_t)st>>>(w, dw, n);
     return niti_check_launch(ctx, "sgd_update");
+}
+
+extern "C" int niti_rescale_grad_split(niti_ctx* ctx, const int32_t* acc, size_t n_per_slice, int slices,
+                                       const uint32_t* maxabs, int sub, int8_t* out, niti_stream st) {
+    if (!ctx || !acc || !maxabs || !out || slices <= 0 || n_per_slice == 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_rescale_grad_split");
+    rescale_split_kernel<<<grid_for(ctx, n_per_slice * slices), kThreads, 0, (cudaStream_t)st>>>(acc, n_per_slice, slices, maxabs, sub, out);
+    return niti_check_launch(ctx, "rescale_grad_split");
 }

@@ -189,7 +189,7 @@ class Reference:
         return os.path.exists(os.path.join(_REF_DIR, "libniti_ref_driver.so"))
 
     def __init__(self, threads=4, workdir=None):
-        self.lib = L = C.CDLL(os.path.join(_REF_DIR, "libniti_ref_driver.so"))
+        self.lib = L = C.CDLL(os.path.join(_REF_DIR, "libniti_ref_driver.so"), mode=C.RTLD_GLOBAL)  # plug-ins resolve MNN core symbols against it
         workdir = workdir or os.path.join(_REF_DIR, "_cwd")
         os.makedirs(workdir, exist_ok=True)
         rc = L.ref_init(workdir.encode(), threads)
@@ -257,3 +257,51 @@ class Reference:
         rc = self.lib.ref_loss_grad(_c(logits), int(ascale), onehot, b, k, g)
         assert rc == 0, rc
         return g
+
+    # ---- whole training steps through the reference's Module / OpGrad / NITI_SGD (ref_driver.cpp) ----
+    def use_backend(self, forward_type, plugin=None, threads=4):
+        """Switch the reference's global executor to another forward type (0 = CPU, 14 = MNN_FORWARD_USER_0,
+        include/MNN/MNNForwardType.h) after dlopen-ing an MNN backend plug-in.  Raises when no runtime
+        creator answers for that type — the reference itself would silently stay on the CPU."""
+        self.lib.ref_use_backend.argtypes = [C.c_int, C.c_char_p, C.c_int]
+        rc = self.lib.ref_use_backend(int(forward_type), plugin.encode() if plugin else None, threads)
+        if rc != 0:
+            raise RuntimeError(f"ref_use_backend({forward_type}, {plugin}) failed: {rc}")
+
+    def net_train(self, spec, x_steps, ascale, labels_steps, weights, tclasses=None):
+        """spec: step.py layer list; x_steps [steps, n, c, h, w] int8; labels_steps [steps, n];
+        weights: list of (OIHW int8, wscale).  Returns dict(logits [steps, n, classes], e_logits [steps],
+        loss [steps], weights [list of OIHW], ms [steps])."""
+        kinds = {"conv": 0, "relu": 1, "pool": 2, "flatten": 3}
+        rows = []
+        for it in spec:
+            r = [kinds[it[0]]] + [int(v) for v in it[1:]]
+            rows.append(r + [0] * (5 - len(r)))
+        sp = np.asarray(rows, np.int32).reshape(-1)
+        x_steps = _c(x_steps)
+        steps, n, c, h, w = x_steps.shape
+        classes = [it for it in spec if it[0] == "conv"][-1][1]
+        tclasses = tclasses or classes
+        onehot = np.zeros((steps, n, tclasses), np.int32)
+        for s in range(steps):
+            onehot[s, np.arange(n), labels_steps[s]] = 1
+        wcat = np.concatenate([_c(W).reshape(-1) for W, _ in weights])
+        wsc = np.asarray([e for _, e in weights], np.int8)
+        logits = np.empty((steps, n, classes), np.int8)
+        elog = np.empty(steps, np.int8)
+        loss = np.empty(steps, np.float32)
+        wout = np.empty_like(wcat)
+        ms = np.empty(steps, np.float32)
+        chw = np.asarray([c, h, w], np.int32)
+        f = self.lib.ref_net_train
+        f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+        f.argtypes = [_i32p, C.c_int, C.c_int, _i32p, C.c_int, C.c_int, _i8p, _i32p, C.c_int, _i8p, _i8p,
+                      _i8p, _i8p, f32p, _i8p, f32p]
+        rc = f(sp, len(rows), n, chw, int(ascale), steps, x_steps, onehot, tclasses, wcat, wsc,
+               logits, elog, loss, wout, ms)
+        if rc != classes:
+            raise RuntimeError(f"ref_net_train failed: {rc}")
+        outw, off = [], 0
+        for W, _ in weights:
+            outw.append(wout[off:off + W.size].reshape(W.shape).copy()); off += W.size
+        return {"logits": logits, "e_logits": elog, "loss": loss, "weights": outw, "ms": ms}

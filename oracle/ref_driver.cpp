@@ -12,13 +12,24 @@
 //                                                 -> NITI_DeConv_Int8 / NITI_GradientConv_Int8
 //   int8 Binary SUB (NITI_SGD.hpp:49-52)          -> NITI_CPUBinary_Int8
 //   _NITI_Relu_Int8 / _NITI_Maxpool_Int8 / OpGrad of those / NITI_LOSS_Grad
+//   whole training steps: NN::NITI_Conv_Int8 modules + _NITI_LOSS_SUM + NITI_SGD::step, the op sequence of
+//   demo/mnistTrain.cpp:131-182 and demo/MnistUtils.cpp:79-147 with injected weights, data and labels
+//   (ref_net_train); ref_use_backend switches the executor to another registered forward type, which is
+//   how tests/test_gpu_mnn_backend.py runs the SAME reference graph on the B200 plug-in (mnn_backend/).
 // The reference reads DSP.txt / parallel.txt from the cwd with unchecked fopen
 // (hexagon_implementation.cpp:33-39, CPUBackend.cpp:155-157): ref_init() writes them (2 and 0).
 #include <MNN/expr/Expr.hpp>
 #include <MNN/expr/ExprCreator.hpp>
 #include <MNN/expr/Executor.hpp>
 #include "OpGrad.hpp"
+#include "NN.hpp"
+#include "core/Backend.hpp"
+#include "NITI_SGD.hpp"
 #include "MNN_generated.h"
+#include <MNN/expr/Module.hpp>
+#include <dlfcn.h>
+#include <chrono>
+#include <memory>
 #include <cstdio>
 #include <cstring>
 #include <vector>
@@ -136,6 +147,120 @@ int ref_loss_grad(const int8_t* logits, int ascale, const int* onehot, int b, in
     if (grads.empty() || grads[0].get() == nullptr) return -3;
     copyOut(grads[0], grad);
     return 0;
+}
+
+
+// ---- backend selection ----------------------------------------------------------------------------
+// dlopen an MNN backend plug-in (its static registrar calls MNNInsertExtraRuntimeCreator) and make
+// `forwardType` the executor's backend.  Returns 0 when the executor really switched (the reference's
+// Executor::setGlobalExecutorConfig silently keeps the old runtime when no creator answers,
+// express/Executor.cpp:81-86, so the switch is verified through the runtime's compiler/forward type).
+int ref_use_backend(int forwardType, const char* plugin, int threads) {
+    if (plugin && plugin[0]) {
+        void* h = ::dlopen(plugin, RTLD_NOW | RTLD_GLOBAL);
+        if (!h) { ::fprintf(stderr, "ref_use_backend: %s\n", ::dlerror()); return -1; }
+    }
+    if (forwardType != (int)MNN_FORWARD_CPU && MNNGetExtraRuntimeCreator((MNNForwardType)forwardType) == nullptr) return -2;
+    BackendConfig config;
+    Executor::getGlobalExecutor()->setGlobalExecutorConfig((MNNForwardType)forwardType, config, threads);
+    return 0;
+}
+
+} // extern "C"
+
+// ---- whole training steps through the reference's Module / OpGrad / NITI_SGD ------------------------
+// layer list: 5 ints per layer {kind, a, b, c, d}: 0 conv(oc,k,stride,pad) 1 relu 2 maxpool(k,s) 3 flatten
+namespace {
+struct LayerSpec { int kind, a, b, c, d; };
+class SpecNet : public Module {
+public:
+    SpecNet(const std::vector<LayerSpec>& layers, int inChannels, const int* chw, const int8_t* weights, const int8_t* wscales) : mLayers(layers) {
+        int c = inChannels, h = chw[1], w = chw[2];
+        size_t off = 0; int wi = 0;
+        std::vector<std::shared_ptr<Module>> children;
+        for (auto& L : mLayers) {
+            if (L.kind == 0) {
+                NN::NITI_Conv_Int8_Parameters p;
+                p.option.kernelSize = {L.b, L.b}; p.option.channel = {c, L.a};
+                p.option.stride = {L.c, L.c}; p.option.pads = {L.d, L.d}; p.option.padMode = Express::CAFFE;
+                p.weight = _Const(weights + off, {L.a, c, L.b, L.b}, NCHW, halide_type_of<int8_t>());
+                p.weight.fix(VARP::TRAINABLE);
+                p.wscale = wscales[wi]; p.group = 1; p.name = "conv" + std::to_string(wi);
+                off += (size_t)L.a * c * L.b * L.b; ++wi;
+                std::shared_ptr<Module> m(NN::NITI_Conv_Int8(p, 8, false));
+                mConvs.emplace_back(m); children.emplace_back(m);
+                h = (h + 2 * L.d - L.b) / L.c + 1; w = (w + 2 * L.d - L.b) / L.c + 1; c = L.a;
+            } else if (L.kind == 2) {
+                h = (h - L.a) / L.b + 1; w = (w - L.a) / L.b + 1;
+            } else if (L.kind == 3) {
+                c = c * h * w; h = w = 1;
+            }
+        }
+        registerModel(children);
+    }
+    virtual std::vector<VARP> onForward(const std::vector<VARP>& inputs) override {
+        std::vector<VARP> x = inputs;
+        int ci = 0;
+        for (auto& L : mLayers) {
+            switch (L.kind) {
+                case 0: x = mConvs[ci++]->multioutput_forward({x[0], x[1]}); break;
+                case 1: x[0] = _NITI_Relu_Int8(x[0]); break;
+                case 2: x = _NITI_Maxpool_Int8(x[0], x[1], {L.a, L.a}, {L.b, L.b}); break;
+                case 3: x[0] = _Reshape(_Convert(x[0], NCHW), {0, -1, 1, 1}); break;
+            }
+        }
+        x[0] = _Reshape(_Convert(x[0], NCHW), {0, -1});
+        return x;
+    }
+    std::vector<std::shared_ptr<Module>> mConvs;
+private:
+    std::vector<LayerSpec> mLayers;
+};
+} // namespace
+
+extern "C" {
+
+// Runs `steps` iterations of: forward, _NITI_LOSS_SUM, NITI_SGD::step (OpGrad over the whole graph, int8 SUB update).
+//   x       steps x [n, c, h, w] int8 NCHW, ascale the input exponent; onehot steps x [n, tclasses] int32
+//   weights concatenated OIHW int8 of the conv layers in order (in), wscales one per conv layer
+//   out: logits steps x [n, classes] int8, logit exponents [steps], losses [steps] float, final weights (same packing),
+//        ms_per_step [steps] wall time of each iteration
+int ref_net_train(const int* spec, int nlayers, int n, const int* chw, int ascale, int steps, const int8_t* x,
+                  const int* onehot, int tclasses, const int8_t* weights, const int8_t* wscales,
+                  int8_t* logits_out, int8_t* elogits_out, float* loss_out, int8_t* weights_out, float* ms_out) {
+    std::vector<LayerSpec> layers(nlayers);
+    for (int i = 0; i < nlayers; ++i) layers[i] = LayerSpec{spec[5 * i], spec[5 * i + 1], spec[5 * i + 2], spec[5 * i + 3], spec[5 * i + 4]};
+    std::shared_ptr<Module> model(new SpecNet(layers, chw[0], chw, weights, wscales));
+    model->setIsTraining(true);
+    std::shared_ptr<MNN::Train::SGD> sgd(new MNN::Train::NITI_SGD(model));
+    const size_t xs = (size_t)n * chw[0] * chw[1] * chw[2];
+    int classes = 0;
+    for (int s = 0; s < steps; ++s) {
+        auto t0 = std::chrono::steady_clock::now();
+        auto xv = _Const(x + s * xs, {n, chw[0], chw[1], chw[2]}, NCHW, halide_type_of<int8_t>());
+        auto tv = _Const(onehot + (size_t)s * n * tclasses, {n, tclasses}, NCHW, halide_type_of<int32_t>());
+        auto predict = model->multioutput_forward({xv, _Scalar<int8_t>((int8_t)ascale)});
+        auto info = predict[0]->getInfo();
+        if (!info || info->dim.size() != 2) return -1;
+        classes = info->dim[1];
+        auto loss = _NITI_LOSS_SUM(predict[0], predict[1], tv, n, tclasses, 1, 1);
+        auto lp = loss->readMap<float>();
+        if (!lp) return -2;
+        if (loss_out) loss_out[s] = lp[0];
+        if (logits_out) ::memcpy(logits_out + (size_t)s * n * classes, predict[0]->readMap<int8_t>(), (size_t)n * classes);
+        if (elogits_out) elogits_out[s] = predict[1]->readMap<int8_t>()[0];
+        if (!sgd->step(loss)) return -3;
+        if (ms_out) ms_out[s] = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    }
+    if (weights_out) {
+        size_t off = 0;
+        for (auto& p : model->parameters()) {
+            auto pi = p->getInfo();
+            ::memcpy(weights_out + off, p->readMap<int8_t>(), pi->size);
+            off += pi->size;
+        }
+    }
+    return classes;
 }
 
 } // extern "C"

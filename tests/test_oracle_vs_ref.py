@@ -39,3 +39,30 @@ def test_live_reference_conv(oracle, ref, cfg, seed):
         # tensor (grad/NITI_Conv_Int8_Grad.cpp:164-166), which permutes the dW entries; the values
         # (accumulate + shared exponent + PSTO) are identical, so compare them as a multiset.
         assert np.array_equal(np.sort(dw.ravel()), np.sort(rdw.ravel()))
+
+
+def _lenet_case(steps, n, seed=0):
+    from mandheling_dsp_training_b200.step import lenet_spec, niti_xavier_int8
+    rng = np.random.default_rng(seed + 1)
+    ws = [niti_xavier_int8(rng, oc, ic, k, k) for oc, ic, k in [(20, 1, 5), (52, 20, 5), (500, 832, 1), (12, 500, 1)]]
+    rng = np.random.default_rng(seed)
+    x = rng.integers(-127, 128, size=(steps, n, 1, 28, 28), dtype=np.int8)
+    lab = rng.integers(0, 10, size=(steps, n)).astype(np.int32)
+    return lenet_spec(), ws, x, lab
+
+
+def test_live_reference_training_steps(oracle, ref):
+    """Whole training steps of the reference's NITIInt8 MNIST model (demo/mnistTrain.cpp:131-182) through its own
+    Module / OpGrad / NITI_SGD code with injected weights, against oracle_step: logits, exponents and every
+    updated weight tensor identical after 3 steps (the full-loop pin of SURVEY.md section 8c(2))."""
+    from mandheling_dsp_training_b200.step import oracle_step
+    spec, ws, x, lab = _lenet_case(3, 8)
+    out = ref.net_train(spec, x, -7, lab, ws, tclasses=10)
+    w2 = [(w.copy(), e) for w, e in ws]
+    for s in range(3):
+        lg, e = oracle_step(oracle, spec, x[s], -7, lab[s], w2, shape)
+        assert np.array_equal(lg.reshape(8, -1), out["logits"][s])
+        assert e == out["e_logits"][s]
+    for a, (b, _) in zip(out["weights"], w2):
+        assert np.array_equal(a, b)
+    assert np.all(np.isfinite(out["loss"]))
