@@ -1,0 +1,86 @@
+"""Worker for tests/test_gpu_mnn_backend.py — runs in its OWN process, without torch.
+
+The unmodified reference (oracle/_ref/libMNN_ref.so) has to be loaded RTLD_GLOBAL so the MNN plug-in's core
+symbols resolve against it, exactly as in a real MNN host process; doing that inside the pytest process clashes
+with libtorch's own copies of common third-party symbols, hence the subprocess.
+
+Evaluates every case twice through the reference's express API / OpGrad / Module / NITI_SGD — first on the
+reference CPU backend, then on the B200 plug-in (MNN_FORWARD_USER_0) — and writes both result sets to an .npz."""
+import ctypes
+import os
+import sys
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle.oracle import Reference, shape          # noqa: E402  (numpy + ctypes only)
+
+PLUGIN = os.path.join(ROOT, "mnn_backend", "libMNN_niti_b200.so")
+MNN_FORWARD_USER_0 = 8          # include/MNN/MNNForwardType.h:38
+CONV_CASES = [(4, 4, 8, 8, 8, 3, 1, 1), (2, 8, 6, 6, 12, 3, 1, 0), (2, 20, 12, 12, 52, 5, 1, 0),
+              (8, 16, 1, 1, 12, 1, 1, 0), (3, 12, 7, 7, 16, 3, 1, 1), (16, 64, 16, 16, 128, 3, 1, 1),
+              (4, 8, 10, 10, 8, 3, 2, 1)]
+LENET = [("conv", 20, 5, 1, 0), ("relu",), ("pool", 2, 2), ("conv", 52, 5, 1, 0), ("relu",), ("pool", 2, 2),
+         ("flatten",), ("conv", 500, 1, 1, 0), ("relu",), ("conv", 12, 1, 1, 0)]      # demo/mnistTrain.cpp:131-181
+
+
+def xavier_int8(rng, oc, c, k):
+    w = rng.normal(0.0, np.sqrt(2.0 / ((c + oc) * k * k)), size=(oc, c, k, k)).astype(np.float32)
+    r = float(np.abs(w).max())
+    return np.round(w / r * 127.0).astype(np.int8), int(np.ceil(np.log2(r))) - 7
+
+
+def evaluate(ref, tag, out, steps, batch):
+    for i, cfg in enumerate(CONV_CASES):
+        n, c, h, w, oc, k, st, p = cfg
+        s = shape(n, c, h, w, oc, k, stride=st, pad=p)
+        rng = np.random.default_rng(i)
+        x = rng.integers(-127, 128, size=(n, c, h, w), dtype=np.int8)
+        wt = rng.integers(-64, 65, size=(oc, c, k, k), dtype=np.int8)
+        dy = rng.integers(-40, 41, size=(n, oc, s.oh, s.ow), dtype=np.int8)
+        y, e = ref.conv_fwd(s, x, wt, -5, -9)
+        dx, dw = ref.conv_bwd(s, x, wt, dy)
+        out[f"{tag}_fwd{i}_y"], out[f"{tag}_fwd{i}_e"] = y, np.int32(e)
+        out[f"{tag}_bwd{i}_dx"], out[f"{tag}_bwd{i}_dw"] = dx, dw
+    rng = np.random.default_rng(7)
+    a = rng.integers(-127, 128, size=(4, 8, 8, 8), dtype=np.int8)
+    g = rng.integers(-127, 128, size=(4, 8, 8, 8), dtype=np.int8)
+    out[f"{tag}_relu"] = ref.relu(a)
+    out[f"{tag}_relu_grad"] = ref.relu_grad(a, g)
+    out[f"{tag}_maxpool"] = ref.maxpool(a, 2, 2)
+    rng = np.random.default_rng(1)
+    ws = [xavier_int8(rng, oc, ic, k) for oc, ic, k in [(20, 1, 5), (52, 20, 5), (500, 832, 1), (12, 500, 1)]]
+    rng = np.random.default_rng(0)
+    x = rng.integers(-127, 128, size=(steps, batch, 1, 28, 28), dtype=np.int8)
+    lab = rng.integers(0, 10, size=(steps, batch)).astype(np.int32)
+    r = ref.net_train(LENET, x, -7, lab, ws, tclasses=10)
+    for k in ("logits", "e_logits", "loss", "ms"):
+        out[f"{tag}_lenet_{k}"] = r[k]
+    for i, w in enumerate(r["weights"]):
+        out[f"{tag}_lenet_w{i}"] = w
+
+
+def main():
+    dst = os.path.abspath(sys.argv[1])          # Reference() changes the cwd (DSP.txt / parallel.txt live there)
+    steps = int(sys.argv[2]) if len(sys.argv) > 2 else 3
+    batch = int(sys.argv[3]) if len(sys.argv) > 3 else 64
+    out = {"n_conv": np.int32(len(CONV_CASES))}
+    ref = Reference(threads=4)
+    evaluate(ref, "cpu", out, steps, batch)
+    ref.use_backend(MNN_FORWARD_USER_0, PLUGIN)
+    plug = ctypes.CDLL(PLUGIN)
+    plug.MNNNitiB200LaunchCount.restype = ctypes.c_longlong
+    before = plug.MNNNitiB200LaunchCount()
+    evaluate(ref, "b200", out, steps, batch)
+    out["launches"] = np.int64(plug.MNNNitiB200LaunchCount() - before)
+    np.savez(dst, **{k: (v if v is not None else np.zeros(0, np.int8)) for k, v in out.items()})
+    same = [k[4:] for k in out if k.startswith("cpu_") and not k.endswith("_ms") and out[k] is not None
+            and np.array_equal(out[k], out["b200_" + k[4:]])]
+    diff = [k[4:] for k in out if k.startswith("cpu_") and not k.endswith("_ms") and out[k] is not None
+            and not np.array_equal(out[k], out["b200_" + k[4:]])]
+    print("identical:", len(same), "different:", diff)
+    print("worker ok: launches", int(out["launches"]), "cpu ms/step", out["cpu_lenet_ms"], "b200 ms/step", out["b200_lenet_ms"])
+
+
+if __name__ == "__main__":
+    main()
