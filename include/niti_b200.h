@@ -47,7 +47,7 @@ typedef struct {
 
 /* Which kernel family to use.  AUTO picks, in order: TMA-fed tcgen05 (channel counts multiple of 64),
  * cp.async-fed tcgen05 (multiple of 16), SIMT.  The others force one family (tests, benchmarks). */
-enum { NITI_PATH_AUTO = 0, NITI_PATH_SIMT = 1, NITI_PATH_TC = 2, NITI_PATH_TMA = 3 };
+enum { NITI_PATH_AUTO = 0, NITI_PATH_SIMT = 1, NITI_PATH_TC = 2, NITI_PATH_TMA = 3, NITI_PATH_TMA2 = 4 };
 
 /* ---- context ------------------------------------------------------------------------------- */
 int         niti_ctx_create(int device, niti_ctx** out);

@@ -5,7 +5,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libniti_b200.so")
-SOURCES = ["api.cu", "rescale.cu", "elementwise.cu", "conv_simt.cu", "conv_tc.cu", "conv_tma.cu"]
+SOURCES = ["api.cu", "rescale.cu", "elementwise.cu", "conv_simt.cu", "conv_tc.cu", "conv_tma.cu", "conv_tma2.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]
 

@@ -23,18 +23,25 @@ bool tma_dw_eligible(const niti_conv_desc*);
 int tma_conv_fwd_acc(niti_ctx*, const niti_conv_desc*, const int8_t*, const int8_t*, int32_t*, uint32_t*, cudaStream_t);
 int tma_conv_dx_acc(niti_ctx*, const niti_conv_desc*, const int8_t* dy, const int8_t* wt, int32_t*, uint32_t*, cudaStream_t);
 int tma_conv_dw_acc(niti_ctx*, const niti_conv_desc*, const int8_t*, const int8_t*, int32_t*, uint32_t*, cudaStream_t);
+// conv_tma2.cu: persistent CTA-pair (cta_group::2) generation of the forward / dX kernels
+bool tma2_fwd_eligible(const niti_conv_desc*);
+bool tma2_dx_eligible(const niti_conv_desc*);
+int tma2_conv_fwd_acc(niti_ctx*, const niti_conv_desc*, const int8_t*, const int8_t*, int32_t*, uint32_t*, cudaStream_t);
+int tma2_conv_dx_acc(niti_ctx*, const niti_conv_desc*, const int8_t* dy, const int8_t* wt, int32_t*, uint32_t*, cudaStream_t);
 
 // kernel family selection: TMA-fed tcgen05 > cp.async-fed tcgen05 > SIMT, subject to shape eligibility
-// and the context's forced path.  Returns 0 simt, 1 tc (cp.async), 2 tma, -1 unsupported under the forced path.
-static int pick_path(niti_ctx* ctx, bool tma_ok, bool tc_ok) {
+// and the context's forced path.  Returns 0 simt, 1 tc (cp.async), 2 tma, 3 tma2 (CTA pair), -1 unsupported under the
+// forced path.
+static int pick_path(niti_ctx* ctx, bool tma_ok, bool tc_ok, bool tma2_ok = false) {
     switch (ctx->path) {
         case NITI_PATH_SIMT: return 0;
         case NITI_PATH_TC: return tc_ok ? 1 : -1;
         case NITI_PATH_TMA: return tma_ok ? 2 : -1;
-        default: return tma_ok ? 2 : (tc_ok ? 1 : 0);
+        case NITI_PATH_TMA2: return tma2_ok ? 3 : -1;
+        default: return (tma2_ok && ctx->auto_tma2) ? 3 : (tma_ok ? 2 : (tc_ok ? 1 : 0));
     }
 }
-static const char* path_name(int p) { return p == 2 ? "tma" : (p == 1 ? "tc" : "simt"); }
+static const char* path_name(int p) { return p == 3 ? "tma2" : (p == 2 ? "tma" : (p == 1 ? "tc" : "simt")); }
 
 int niti_fail(niti_ctx* ctx, int code, const char* what, cudaError_t e) {
     if (ctx) {
@@ -110,6 +117,9 @@ int niti_ctx_create(int device, niti_ctx** out) {
     if (env && !strcmp(env, "simt")) ctx->path = NITI_PATH_SIMT;
     if (env && !strcmp(env, "tc")) ctx->path = NITI_PATH_TC;
     if (env && !strcmp(env, "tma")) ctx->path = NITI_PATH_TMA;
+    if (env && !strcmp(env, "tma2")) ctx->path = NITI_PATH_TMA2;
+    const char* a2 = getenv("NITI_B200_AUTO_TMA2");
+    ctx->auto_tma2 = a2 ? atoi(a2) : 1;
     ctx->last_path = "none";
     if (prop.major != 10) {
         snprintf(ctx->err, sizeof(ctx->err), "device is sm_%d%d; this library is built for sm_100a only", prop.major, prop.minor);
@@ -135,7 +145,7 @@ int niti_ctx_destroy(niti_ctx* ctx) {
 
 const char* niti_last_error(niti_ctx* ctx) { return ctx ? ctx->err : "null context"; }
 int niti_set_path(niti_ctx* ctx, int path) {
-    if (!ctx || path < NITI_PATH_AUTO || path > NITI_PATH_TMA) return NITI_ERR_ARG;
+    if (!ctx || path < NITI_PATH_AUTO || path > NITI_PATH_TMA2) return NITI_ERR_ARG;
     ctx->path = path; return NITI_OK;
 }
 int64_t niti_launch_count(niti_ctx* ctx) { return ctx ? ctx->launches : -1; }
@@ -145,9 +155,10 @@ const char* niti_last_path(niti_ctx* ctx) { return ctx ? ctx->last_path : "none"
 int niti_conv_fwd_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, const int8_t* w, int32_t* acc,
                       uint32_t* maxabs, niti_stream st) {
     if (!ctx || !desc_ok(d) || !x || !w || !acc) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_fwd_acc: bad argument");
-    const int path = pick_path(ctx, tma_fwd_eligible(d), tc_fwd_eligible(d));
+    const int path = pick_path(ctx, tma_fwd_eligible(d), tc_fwd_eligible(d), tma2_fwd_eligible(d));
     if (path < 0) return niti_fail(ctx, NITI_ERR_UNSUPPORTED, "conv_fwd: shape not eligible for the forced kernel path");
     ctx->last_path = path_name(path);
+    if (path == 3) return tma2_conv_fwd_acc(ctx, d, x, w, acc, maxabs, (cudaStream_t)st);
     if (path == 2) return tma_conv_fwd_acc(ctx, d, x, w, acc, maxabs, (cudaStream_t)st);
     if (path == 1) return tc_conv_fwd_acc(ctx, d, x, w, acc, maxabs, (cudaStream_t)st);
     return simt_conv_fwd_acc(ctx, d, x, w, acc, maxabs, (cudaStream_t)st);
@@ -156,9 +167,13 @@ int niti_conv_fwd_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, c
 int niti_conv_dx_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* dy, const int8_t* w, int32_t* acc,
                      uint32_t* maxabs, niti_stream st) {
     if (!ctx || !desc_ok(d) || !dy || !w || !acc) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_dx_acc: bad argument");
-    const int path = pick_path(ctx, tma_dx_eligible(d), tc_dx_eligible(d));
+    const int path = pick_path(ctx, tma_dx_eligible(d), tc_dx_eligible(d), tma2_dx_eligible(d));
     if (path < 0) return niti_fail(ctx, NITI_ERR_UNSUPPORTED, "conv_dx: shape not eligible for the forced kernel path");
     ctx->last_path = path_name(path);
+    if (path == 3) {
+        int8_t* wt; int rc = tc_transpose_w(ctx, d, w, &wt, (cudaStream_t)st); if (rc) return rc;
+        return tma2_conv_dx_acc(ctx, d, dy, wt, acc, maxabs, (cudaStream_t)st);
+    }
     if (path == 2) {
         int8_t* wt; int rc = tc_transpose_w(ctx, d, w, &wt, (cudaStream_t)st); if (rc) return rc;
         return tma_conv_dx_acc(ctx, d, dy, wt, acc, maxabs, (cudaStream_t)st);

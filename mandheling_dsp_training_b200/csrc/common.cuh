@@ -12,6 +12,7 @@ struct niti_ctx {
     int device;
     int sm_count;
     int path;                 // NITI_PATH_*
+    int auto_tma2;            // AUTO prefers the CTA-pair kernels where eligible
     int64_t launches;
     const char* last_path;
     char err[256];

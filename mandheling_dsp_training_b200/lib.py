@@ -6,7 +6,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIBPATH = os.path.join(_HERE, "libniti_b200.so")
 
-PATH_AUTO, PATH_SIMT, PATH_TC, PATH_TMA = 0, 1, 2, 3
+PATH_AUTO, PATH_SIMT, PATH_TC, PATH_TMA, PATH_TMA2 = 0, 1, 2, 3, 4
 
 
 class NitiError(RuntimeError):

@@ -3,7 +3,7 @@ layouts) <-> device tensors (NHWC/OHWI, the library's layouts) and thin op wrapp
 import numpy as np
 import torch
 
-from mandheling_dsp_training_b200.lib import ConvDesc, PATH_AUTO, PATH_SIMT, PATH_TC, PATH_TMA  # noqa: F401
+from mandheling_dsp_training_b200.lib import ConvDesc, PATH_AUTO, PATH_SIMT, PATH_TC, PATH_TMA, PATH_TMA2  # noqa: F401
 
 
 def to_desc(s):

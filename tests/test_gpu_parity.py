@@ -74,21 +74,21 @@ TC_SHAPES = [
 
 
 @pytest.mark.parametrize("cfg", TC_SHAPES)
-@pytest.mark.parametrize("path", ["simt", "tc", "tma"])
+@pytest.mark.parametrize("path", ["simt", "tc", "tma", "tma2"])
 def test_accumulators_and_outputs_vs_oracle(nb, run, oracle, cfg, path):
-    from tests.gpu_util import PATH_SIMT, PATH_TC, PATH_TMA, to_desc
+    from tests.gpu_util import PATH_SIMT, PATH_TC, PATH_TMA, PATH_TMA2, to_desc
     n, c, h, w, oc, k, st, p = cfg
     dil = 2 if cfg == TC_SHAPES[-1] else 1
     s = shape(n, c, h, w, oc, k, stride=st, pad=p, dil=dil)
     rng = np.random.default_rng(hash(cfg) % (2 ** 31))
     x = _rand(rng, (n, c, h, w)); wt = _rand(rng, (oc, c, k, k), -64, 64)
     dy = _rand(rng, (n, oc, s.oh, s.ow), -50, 50)
-    nb.set_path({"simt": PATH_SIMT, "tc": PATH_TC, "tma": PATH_TMA}[path])
+    nb.set_path({"simt": PATH_SIMT, "tc": PATH_TC, "tma": PATH_TMA, "tma2": PATH_TMA2}[path])
     try:
-        if path == "tma":
+        if path in ("tma", "tma2"):
             fwd_ok = c % 64 == 0 and oc % 4 == 0
             dx_ok = st == 1 and oc % 64 == 0 and c % 4 == 0 and (k - 1) * dil - p >= 0
-            dw_ok = oc % 16 == 0 and c % 64 == 0
+            dw_ok = oc % 16 == 0 and c % 64 == 0 and path == "tma"      # tma2 = forward / dX generation
             if not (fwd_ok or dx_ok or dw_ok):
                 pytest.skip("shape not eligible for the TMA path")
         else:
