@@ -74,6 +74,12 @@ int niti_conv_dx_acc(niti_ctx*, const niti_conv_desc*, const int8_t* dy, const i
                      int32_t* acc /*[n,h,w,c]*/, uint32_t* maxabs, niti_stream);
 int niti_conv_dw_acc(niti_ctx*, const niti_conv_desc*, const int8_t* x, const int8_t* dy,
                      int32_t* acc /*[oc,kh,kw,c]*/, uint32_t* maxabs, niti_stream);
+/* niti_conv_dx_acc for callers that keep the transposed weights wt = [c][kh][kw][oc] resident (the K-major B operand
+ * of the tensor-core dX kernels; the reference re-derives it per call: rot180 + transpose, NITI_DeConv_Int8.cpp:179-219).
+ * niti_update_batched maintains wt next to w, so a training step launches no transposes.  wt may be NULL (then as
+ * niti_conv_dx_acc). */
+int niti_conv_dx_acc_wt(niti_ctx*, const niti_conv_desc*, const int8_t* dy, const int8_t* w, const int8_t* wt,
+                        int32_t* acc /*[n,h,w,c]*/, uint32_t* maxabs, niti_stream);
 /* C[e,h] = sum_l A[e,l] * B[h,l]   (A, B row-major int8) */
 int niti_matmul_nt_acc(niti_ctx*, int e, int h, int l, const int8_t* a, const int8_t* b,
                        int32_t* acc, uint32_t* maxabs, niti_stream);
@@ -103,6 +109,19 @@ int niti_rescale_act_fused(niti_ctx*, const int32_t* acc, size_t n, const uint32
 int niti_rescale_grad(niti_ctx*, const int32_t* acc, size_t n, const uint32_t* maxabs, int sub,
                       int8_t* dw_out, int8_t* w_inout, niti_stream);
 int niti_sgd_update(niti_ctx*, int8_t* w, const int8_t* dw, size_t n, niti_stream);
+/* The weight-update tail of a whole training step in ONE launch: for every segment (= conv layer)
+ *   *maxabs = max|acc| (atomicMax into a zeroed slot), b = ceil_log2, dW = b==0 ? 0 : PSTO(acc, b-sub),
+ *   w <- clip127(w - dW), and, when wt != NULL, wt[c][tap][oc] <- the same updated weights (transposed copy).
+ * Same arithmetic as niti_absmax + niti_rescale_grad(w_inout) per layer (NITI_GradientConv_Int8.cpp:274-296,
+ * optimizer/NITI_SGD.hpp:20-54).  `segs` is a HOST array read at call time (captured by value: graph-safe). */
+typedef struct {
+    const int32_t* acc;              /* [oc][taps][c] int32 dW accumulator (already all-reduced when data-parallel) */
+    int8_t* w;                       /* [oc][taps][c] in/out   */
+    int8_t* wt;                      /* [c][taps][oc] out, optional */
+    uint32_t* maxabs;                /* zeroed slot; holds max|acc| afterwards */
+    int32_t oc, taps, c, sub;
+} niti_update_seg;
+int niti_update_batched(niti_ctx*, const niti_update_seg* segs, int nseg, niti_stream);
 /* rule B per output-channel slice + post-alignment — NITI_GradientSplitConv_Int8.cpp:318-372 (sub = 3):
  *   acc holds `slices` equal contiguous slices of n_per_slice words; maxabs[s] = max|acc_s| (niti_absmax per slice);
  *   out_s = b_s==0 ? 0 : PSTO(acc_s, b_s-sub), then out_s /= 2^(max_s b - b_s) (C truncation). */

@@ -182,6 +182,16 @@ int niti_conv_dx_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* dy, c
     return simt_conv_dx_acc(ctx, d, dy, w, acc, maxabs, (cudaStream_t)st);
 }
 
+int niti_conv_dx_acc_wt(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* dy, const int8_t* w, const int8_t* wt,
+                        int32_t* acc, uint32_t* maxabs, niti_stream st) {
+    if (!wt) return niti_conv_dx_acc(ctx, d, dy, w, acc, maxabs, st);
+    if (!ctx || !desc_ok(d) || !dy || !w || !acc) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_dx_acc_wt: bad argument");
+    const int path = pick_path(ctx, tma_dx_eligible(d), tc_dx_eligible(d), tma2_dx_eligible(d));
+    if (path == 3) { ctx->last_path = path_name(path); return tma2_conv_dx_acc(ctx, d, dy, wt, acc, maxabs, (cudaStream_t)st); }
+    if (path == 2) { ctx->last_path = path_name(path); return tma_conv_dx_acc(ctx, d, dy, wt, acc, maxabs, (cudaStream_t)st); }
+    return niti_conv_dx_acc(ctx, d, dy, w, acc, maxabs, st);
+}
+
 int niti_conv_dw_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, const int8_t* dy, int32_t* acc,
                      uint32_t* maxabs, niti_stream st) {
     if (!ctx || !desc_ok(d) || !x || !dy || !acc) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_dw_acc: bad argument");

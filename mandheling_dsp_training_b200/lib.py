@@ -31,6 +31,14 @@ def desc(n, c, h, w, oc, kh, kw=None, stride=1, pad=0, dil=1):
 
 
 _P = C.c_void_p
+
+
+class UpdateSeg(C.Structure):
+    """niti_update_seg: one conv layer of niti_update_batched"""
+    _fields_ = [("acc", _P), ("w", _P), ("wt", _P), ("maxabs", _P),
+                ("oc", C.c_int32), ("taps", C.c_int32), ("c", C.c_int32), ("sub", C.c_int32)]
+
+
 _SIGS = {
     "niti_ctx_create": (C.c_int, [C.c_int, C.POINTER(_P)]),
     "niti_ctx_destroy": (C.c_int, [_P]),
@@ -42,6 +50,8 @@ _SIGS = {
     "niti_conv_fwd_acc": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P]),
     "niti_conv_dx_acc": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P]),
     "niti_conv_dw_acc": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P]),
+    "niti_conv_dx_acc_wt": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P]),
+    "niti_update_batched": (C.c_int, [_P, _P, C.c_int, _P]),
     "niti_matmul_nt_acc": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P, _P, _P, _P]),
     "niti_zero_u32": (C.c_int, [_P, _P, C.c_int, _P]),
     "niti_absmax": (C.c_int, [_P, _P, C.c_size_t, _P, _P]),
@@ -141,6 +151,27 @@ class NitiB200:
 
     def conv_dx_acc(self, d, dy, w, acc, maxabs=None, stream=None):
         self._ck(self.lib.niti_conv_dx_acc(self.h, C.byref(d), _ptr(dy), _ptr(w), _ptr(acc), _ptr(maxabs), self._stream(stream)))
+
+    def conv_dx_acc_wt(self, d, dy, w, wt, acc, maxabs=None, stream=None):
+        self._ck(self.lib.niti_conv_dx_acc_wt(self.h, C.byref(d), _ptr(dy), _ptr(w), _ptr(wt), _ptr(acc), _ptr(maxabs),
+                                              self._stream(stream)))
+
+    def update_layers(self, layers, stream=None):
+        """layers: list of (acc, w, wt|None, maxabs slot, oc, taps, c, sub) torch tensors / ints; the ctypes segment
+        array is built once per list object and reused (the tensors must stay alive, as they do in step.NitiNet)"""
+        cache = self.__dict__.setdefault("_seg_cache", {})
+        segs = cache.get(id(layers))
+        if segs is None:
+            segs = (UpdateSeg * len(layers))()
+            for s_, (acc, w, wt, slot, oc, taps, c, sub) in zip(segs, layers):
+                s_.acc, s_.w, s_.wt, s_.maxabs = _ptr(acc), _ptr(w), _ptr(wt), _ptr(slot)
+                s_.oc, s_.taps, s_.c, s_.sub = oc, taps, c, sub
+            cache[id(layers)] = segs
+        self.update_batched(segs, stream)
+
+    def update_batched(self, segs, stream=None):
+        """segs: ctypes array of UpdateSeg (host); read at call time"""
+        self._ck(self.lib.niti_update_batched(self.h, C.cast(segs, _P), len(segs), self._stream(stream)))
 
     def conv_dw_acc(self, d, x, dy, acc, maxabs=None, stream=None):
         self._ck(self.lib.niti_conv_dw_acc(self.h, C.byref(d), _ptr(x), _ptr(dy), _ptr(acc), _ptr(maxabs), self._stream(stream)))

@@ -129,6 +129,9 @@ class NitiNet:
                 L.relu = relu
                 L.x, L.ex = cur, cur_e
                 L.w = torch.zeros((oc, k, k, c), **i8)
+                # transposed copy [c][kh][kw][oc]: the K-major B operand of the tensor-core dX kernels, kept in sync
+                # by the batched update (no per-step transposes); the first conv has no dX
+                L.wt = torch.zeros((c, k, k, oc), **i8) if (fuse and self.convs) else None
                 L.ew = torch.zeros(1, **i8)
                 L.y = torch.zeros((batch, L.d.oh, L.d.ow, oc), **i8)
                 L.ey = torch.zeros(1, **i8)
@@ -159,6 +162,12 @@ class NitiNet:
         self.acc = torch.zeros(max(max(L.n_y, L.n_x) for L in self.convs), **i32)   # fwd / dX accumulators
         self.dw_acc = torch.zeros(dw_total, **i32)                                   # one bucket: all dW accumulators
         self.maxabs = torch.zeros(4 * len(self.convs) + 4, **i32)                    # one slot per reduction
+        self.batched_update = bool(fuse)
+        nconv = len(self.convs)
+        # (acc, w, wt, max-abs slot, oc, taps, c, sub) per layer: the segments of the one-launch weight update
+        self._upd_layers = [(self.dw_acc[L.dw_off: L.dw_off + L.n_w], L.w, L.wt,
+                             self.maxabs[2 * nconv + L.index: 2 * nconv + L.index + 1],
+                             L.d.oc, L.d.kh * L.d.kw, L.d.c, 2) for L in self.convs]
 
     # ---- parameters -------------------------------------------------------------------------------
     def init_weights(self, seed=1):
@@ -172,6 +181,8 @@ class NitiNet:
         for L, (w, e) in zip(self.convs, ws):
             L.w.zero_()
             L.w[..., :L.c_real].copy_(torch.from_numpy(np.ascontiguousarray(np.transpose(w, (0, 2, 3, 1)))))
+            if L.wt is not None:
+                L.wt.copy_(L.w.permute(3, 1, 2, 0))
             L.ew.fill_(int(e))
 
     def weights_oihw(self):
@@ -243,7 +254,10 @@ class NitiNet:
                 self._timed("dw", L.ops, lambda: nb.conv_dw_acc(L.d, L.x, dy, acc_dw, None))
                 if dx is not None:
                     slot = self.maxabs[nconv + L.index: nconv + L.index + 1]
-                    self._timed("dx", L.ops, lambda: nb.conv_dx_acc(L.d, dy, L.w, self.acc, slot))
+                    if L.wt is not None:
+                        self._timed("dx", L.ops, lambda: nb.conv_dx_acc_wt(L.d, dy, L.w, L.wt, self.acc, slot))
+                    else:
+                        self._timed("dx", L.ops, lambda: nb.conv_dx_acc(L.d, dy, L.w, self.acc, slot))
                     self._allreduce_max(slot)
                     if gate:
                         nb.rescale_act_fused(self.acc, L.n_x, slot, dx, relu=False, gate=L.x)
@@ -267,6 +281,9 @@ class NitiNet:
         # gradient exchange (one bucket), then shared exponent + PSTO + int8 SGD, fused per layer
         if self.dist is not None:
             self.dist.all_reduce(self.dw_acc, op=self.dist.ReduceOp.SUM)
+        if self.batched_update:
+            nb.update_layers(self._upd_layers)               # one launch: max|acc|, rule B, SGD, transposed copies
+            return
         for L in self.convs:
             acc_dw = self.dw_acc[L.dw_off: L.dw_off + L.n_w]
             slot = self.maxabs[2 * nconv + L.index: 2 * nconv + L.index + 1]

@@ -101,6 +101,18 @@ class OracleBackend:
             w = _np(w_inout).reshape(-1)
             w[:n] = self.o.sgd_update(w[:n].copy(), r)
 
+    def conv_dx_acc_wt(self, d, dy, w, wt, acc, maxabs=None, stream=None):
+        assert np.array_equal(_np(wt), np.transpose(_np(w), (3, 1, 2, 0))), "transposed weight copy out of sync"
+        self.conv_dx_acc(d, dy, w, acc, maxabs)
+
+    def update_layers(self, layers, stream=None):
+        for acc, w, wt, slot, oc, taps, c, sub in layers:
+            n = oc * taps * c
+            self.absmax(acc, n, slot)
+            self.rescale_grad(acc, n, slot, sub, None, w)
+            if wt is not None:
+                _np(wt)[:] = np.transpose(_np(w), (3, 1, 2, 0))
+
     def relu(self, x, y, n, stream=None):
         _np(y).reshape(-1)[:] = self.o.relu(_np(x).reshape(-1))
 

@@ -158,6 +158,38 @@ def test_sgd_update(nb, oracle):
         assert np.array_equal(wd.cpu().numpy(), oracle.sgd_update(w, dw))
 
 
+def test_update_batched_vs_oracle(nb, oracle):
+    """one launch for every layer: max|acc| -> rule B (sub 2) -> int8 SGD -> transposed copy; full 32x32 tiles, ragged
+    rows / columns, a zero segment (b == 0) and magnitudes on both sides of the shift rules, twice (barrier re-arm)"""
+    import torch
+    rng = np.random.default_rng(21)
+    shapes = [(64, 9, 64, 1 << 20, True), (12, 1, 512, 300, True), (20, 25, 16, 5, False), (52, 25, 20, 129, True),
+              (96, 9, 32, 0, True), (500, 1, 832, (1 << 23) + 3, True), (33, 3, 7, 2, True), (512, 9, 512, 70000, True)]
+    for rep in range(2):
+        layers, ref = [], []
+        slots = torch.zeros(len(shapes), dtype=torch.int32, device="cuda")
+        for i, (oc, taps, c, mag, with_wt) in enumerate(shapes):
+            n = oc * taps * c
+            acc = rng.integers(-mag, mag + 1, size=n).astype(np.int32)
+            if mag:
+                acc[rng.integers(0, n)] = mag
+            w = _rand(rng, (oc, taps, c), -127, 127)
+            n_pad = (n + 63) // 64 * 64
+            accd = torch.zeros(n_pad, dtype=torch.int32, device="cuda"); accd[:n] = torch.from_numpy(acc).cuda()
+            wd = torch.from_numpy(w.copy()).cuda()
+            wtd = torch.full((c, taps, oc), 77, dtype=torch.int8, device="cuda") if with_wt else None
+            layers.append((accd[:n], wd, wtd, slots[i:i + 1], oc, taps, c, 2))
+            ref.append((acc, w, mag))
+        nb.update_layers(layers)
+        torch.cuda.synchronize()
+        for (accd, wd, wtd, slot, oc, taps, c, _), (acc, w, mag) in zip(layers, ref):
+            assert int(slot.item()) == mag
+            want = oracle.sgd_update(w.reshape(-1), oracle.rescale_grad(acc, 2)).reshape(oc, taps, c)
+            assert np.array_equal(wd.cpu().numpy(), want), (oc, taps, c, mag)
+            if wtd is not None:
+                assert np.array_equal(wtd.cpu().numpy(), np.transpose(want, (2, 1, 0))), (oc, taps, c, mag)
+
+
 # ------------------------------------------------------------------ element-wise ops of the step
 def test_elementwise_vs_oracle_and_golden(nb, oracle, golden_ew):
     import torch
