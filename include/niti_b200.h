@@ -103,6 +103,23 @@ int niti_rescale_act(niti_ctx*, const int32_t* acc, size_t n, const uint32_t* ma
 int niti_rescale_act_fused(niti_ctx*, const int32_t* acc, size_t n, const uint32_t* maxabs,
                            int8_t* out, const int8_t* exp_a, const int8_t* exp_b, int8_t* exp_out,
                            int relu, const int8_t* gate, niti_stream);
+/* Data-parallel variant of niti_rescale_act_fused: the max|acc| that fixes the exponent is the max over all ranks,
+ * exchanged INSIDE this kernel over NVLink peer memory (one 8-byte store per peer + a spin on local memory; see
+ * csrc/dp.cuh) instead of a NCCL all-reduce per scalar.  dp_slot in [0,256) names the exchange word; a step must use
+ * each slot at most once and at least two different slots.  Without niti_dp_connect (world 1) it equals the plain call. */
+int niti_rescale_act_dp(niti_ctx*, const int32_t* acc, size_t n, const uint32_t* maxabs,
+                        int8_t* out, const int8_t* exp_a, const int8_t* exp_b, int8_t* exp_out,
+                        int relu, const int8_t* gate, int dp_slot, niti_stream);
+/* peer-memory plumbing for the call above (one process per GPU, all GPUs of one NVLink box):
+ *   niti_dp_alloc    allocates this rank's exchange buffer and returns its 64-byte CUDA IPC handle
+ *   niti_dp_connect  maps every rank's buffer (handles = world x 64 bytes, rank-ordered, gathered by the host)
+ *   niti_dp_step_begin bumps the device-side step epoch; call once at the start of every step (graph-capturable)
+ *   niti_dp_error    *out != 0 when a peer never answered (its process died): results since then are invalid */
+int niti_dp_alloc(niti_ctx*, unsigned char handle_out[64]);
+int niti_dp_connect(niti_ctx*, int rank, int world, const unsigned char* handles);
+int niti_dp_close(niti_ctx*);
+int niti_dp_step_begin(niti_ctx*, niti_stream);
+int niti_dp_error(niti_ctx*, int* out);
 /* rule B — dW / matmul (NITI_GradientConv_Int8.cpp:274-296 sub=2; NITI_Matmul_Int8.cpp:216-228 sub=3):
  *   b==0: zeros; else PSTO(b-sub).  dw_out optional; when w_inout is given the int8 SGD step
  *   w <- clip127(w - dw) (optimizer/NITI_SGD.hpp:49-52, BinaryUtils.hpp:276-299) is fused. */

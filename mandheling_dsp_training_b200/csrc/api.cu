@@ -139,6 +139,8 @@ int niti_ctx_destroy(niti_ctx* ctx) {
     if (ctx->ws_acc) cudaFree(ctx->ws_acc);
     if (ctx->ws_i8) cudaFree(ctx->ws_i8);
     if (ctx->ws_u32) cudaFree(ctx->ws_u32);
+    niti_dp_close(ctx);
+    if (ctx->dp_buf) cudaFree(ctx->dp_buf);
     delete ctx;
     return NITI_OK;
 }

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include "../../include/niti_b200.h"
+#include "dp.cuh"
 
 #ifndef NITI_DEVICE_INLINE
 #define NITI_DEVICE_INLINE __device__ __forceinline__
@@ -20,6 +21,9 @@ struct niti_ctx {
     int32_t* ws_acc;  size_t ws_acc_bytes;
     uint32_t* ws_u32;         // [0] max-abs slot of whole-op calls
     int8_t* ws_i8;    size_t ws_i8_bytes;   // transposed weights for dX, host-call staging
+    // data-parallel scalar exchange over peer memory (dp.cuh); world <= 1 when not connected
+    DpBuffer* dp_buf;
+    DpView dp;
 };
 
 int  niti_fail(niti_ctx* ctx, int code, const char* what, cudaError_t e = cudaSuccess);

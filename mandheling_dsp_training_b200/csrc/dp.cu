@@ -1,0 +1,66 @@
+// dp.cu — host side of the peer-memory scalar exchange (dp.cuh): buffer allocation, CUDA IPC export/open, epoch bump.
+// One process per GPU; the handles travel between processes through whatever the host already has
+// (torch.distributed all_gather in step.py, any byte transport elsewhere) — the C ABI only sees 64-byte blobs.
+#include "common.cuh"
+#include <cstring>
+
+namespace {
+__global__ void dp_step_begin_kernel(DpBuffer* b) { b->epoch = b->epoch + 1u; }
+}
+
+extern "C" int niti_dp_alloc(niti_ctx* ctx, unsigned char handle_out[64]) {
+    if (!ctx || !handle_out) return niti_fail(ctx, NITI_ERR_ARG, "niti_dp_alloc");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    if (!ctx->dp_buf) {
+        cudaError_t e = cudaMalloc(&ctx->dp_buf, sizeof(DpBuffer));
+        if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "niti_dp_alloc: cudaMalloc", e);
+        cudaMemset(ctx->dp_buf, 0, sizeof(DpBuffer));
+        cudaDeviceSynchronize();
+    }
+    cudaIpcMemHandle_t h;
+    cudaError_t e = cudaIpcGetMemHandle(&h, ctx->dp_buf);
+    if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "niti_dp_alloc: cudaIpcGetMemHandle", e);
+    memcpy(handle_out, &h, 64);
+    return NITI_OK;
+}
+
+extern "C" int niti_dp_connect(niti_ctx* ctx, int rank, int world, const unsigned char* handles /* world x 64 */) {
+    if (!ctx || !handles || world < 1 || world > kDpMaxWorld || rank < 0 || rank >= world || !ctx->dp_buf)
+        return niti_fail(ctx, NITI_ERR_ARG, "niti_dp_connect: bad argument (call niti_dp_alloc first; world <= 8)");
+    DpView v{};
+    v.world = world; v.rank = rank;
+    for (int r = 0; r < world; ++r) {
+        if (r == rank) { v.peer[r] = ctx->dp_buf; continue; }
+        cudaIpcMemHandle_t h;
+        memcpy(&h, handles + 64 * r, 64);
+        void* p = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "niti_dp_connect: cudaIpcOpenMemHandle", e);
+        v.peer[r] = reinterpret_cast<DpBuffer*>(p);
+    }
+    ctx->dp = v;
+    return NITI_OK;
+}
+
+extern "C" int niti_dp_close(niti_ctx* ctx) {
+    if (!ctx) return NITI_ERR_ARG;
+    for (int r = 0; r < ctx->dp.world; ++r)
+        if (r != ctx->dp.rank && ctx->dp.peer[r]) cudaIpcCloseMemHandle(ctx->dp.peer[r]);
+    ctx->dp = DpView{};
+    return NITI_OK;
+}
+
+extern "C" int niti_dp_step_begin(niti_ctx* ctx, niti_stream st) {
+    if (!ctx || !ctx->dp_buf) return niti_fail(ctx, NITI_ERR_ARG, "niti_dp_step_begin: no exchange buffer");
+    dp_step_begin_kernel<<<1, 1, 0, (cudaStream_t)st>>>(ctx->dp_buf);
+    return niti_check_launch(ctx, "dp_step_begin");
+}
+
+extern "C" int niti_dp_error(niti_ctx* ctx, int* out) {
+    if (!ctx || !out || !ctx->dp_buf) return niti_fail(ctx, NITI_ERR_ARG, "niti_dp_error");
+    uint32_t v = 0;
+    cudaError_t e = cudaMemcpy(&v, &ctx->dp_buf->error, sizeof(v), cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "niti_dp_error", e);
+    *out = (int)v;
+    return NITI_OK;
+}

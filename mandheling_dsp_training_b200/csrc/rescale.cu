@@ -53,8 +53,11 @@ __global__ void __launch_bounds__(kThreads)
 rescale_kernel(const int32_t* __restrict__ acc, size_t n, const uint32_t* __restrict__ maxabs, int sub,
                int8_t* __restrict__ out, int8_t* __restrict__ w_inout,
                const int8_t* __restrict__ exp_a, const int8_t* __restrict__ exp_b, int8_t* __restrict__ exp_out,
-               int relu, const int8_t* __restrict__ gate) {
-    const int b = niti_bitwidth(*maxabs);
+               int relu, const int8_t* __restrict__ gate, const DpView dp, int dp_slot) {
+    __shared__ uint32_t dp_sh;
+    uint32_t mglobal = *maxabs;
+    if (MODE == 0) mglobal = dp_allreduce_max(dp, dp_slot, mglobal, &dp_sh);     // data parallel: max over ranks (dp.cuh)
+    const int b = niti_bitwidth(mglobal);
     int shift;          // PSTO shift; kind: 0 = PSTO, 1 = raw cast, 2 = zeros
     int kind = 0;
     if (MODE == 0) {
@@ -210,7 +213,7 @@ extern "C" int niti_rescale_act(niti_ctx* ctx, const int32_t* acc, size_t n, con
     if (n && (!aligned16(acc) || !aligned16(out)))
         return niti_fail(ctx, NITI_ERR_ARG, "niti_rescale_act: buffers must be 16-byte aligned");
     rescale_kernel<0><<<grid_for(ctx, n / 16 + 1), kThreads, 0, (cudaStream_t)st>>>(
-        acc, n, maxabs, 0, out, nullptr, exp_a, exp_b, exp_out, 0, nullptr);
+        acc, n, maxabs, 0, out, nullptr, exp_a, exp_b, exp_out, 0, nullptr, DpView{}, 0);
     return niti_check_launch(ctx, "rescale_act");
 }
 
@@ -221,8 +224,20 @@ extern "C" int niti_rescale_act_fused(niti_ctx* ctx, const int32_t* acc, size_t 
     if (n && (!aligned16(acc) || !aligned16(out) || (gate && !aligned16(gate))))
         return niti_fail(ctx, NITI_ERR_ARG, "niti_rescale_act_fused: buffers must be 16-byte aligned");
     rescale_kernel<0><<<grid_for(ctx, n / 16 + 1), kThreads, 0, (cudaStream_t)st>>>(
-        acc, n, maxabs, 0, out, nullptr, exp_a, exp_b, exp_out, relu, gate);
+        acc, n, maxabs, 0, out, nullptr, exp_a, exp_b, exp_out, relu, gate, DpView{}, 0);
     return niti_check_launch(ctx, "rescale_act_fused");
+}
+
+extern "C" int niti_rescale_act_dp(niti_ctx* ctx, const int32_t* acc, size_t n, const uint32_t* maxabs, int8_t* out,
+                                   const int8_t* exp_a, const int8_t* exp_b, int8_t* exp_out, int relu,
+                                   const int8_t* gate, int dp_slot, niti_stream st) {
+    if (!ctx || !maxabs || (n && (!acc || !out))) return niti_fail(ctx, NITI_ERR_ARG, "niti_rescale_act_dp");
+    if (dp_slot < 0 || dp_slot >= kDpSlots) return niti_fail(ctx, NITI_ERR_ARG, "niti_rescale_act_dp: slot out of range");
+    if (n && (!aligned16(acc) || !aligned16(out) || (gate && !aligned16(gate))))
+        return niti_fail(ctx, NITI_ERR_ARG, "niti_rescale_act_dp: buffers must be 16-byte aligned");
+    rescale_kernel<0><<<grid_for(ctx, n / 16 + 1), kThreads, 0, (cudaStream_t)st>>>(
+        acc, n, maxabs, 0, out, nullptr, exp_a, exp_b, exp_out, relu, gate, ctx->dp, dp_slot);
+    return niti_check_launch(ctx, "rescale_act_dp");
 }
 
 extern "C" int niti_rescale_grad(niti_ctx* ctx, const int32_t* acc, size_t n, const uint32_t* maxabs, int sub,
@@ -232,7 +247,7 @@ extern "C" int niti_rescale_grad(niti_ctx* ctx, const int32_t* acc, size_t n, co
     if (!aligned16(acc) || (dw_out && !aligned16(dw_out)) || (w_inout && !aligned16(w_inout)))
         return niti_fail(ctx, NITI_ERR_ARG, "niti_rescale_grad: buffers must be 16-byte aligned");
     rescale_kernel<1><<<grid_for(ctx, n / 16 + 1), kThreads, 0, (cudaStream_t)st>>>(
-        acc, n, maxabs, sub, dw_out, w_inout, nullptr, nullptr, nullptr, 0, nullptr);
+        acc, n, maxabs, sub, dw_out, w_inout, nullptr, nullptr, nullptr, 0, nullptr, DpView{}, 0);
     return niti_check_launch(ctx, "rescale_grad");
 }
 

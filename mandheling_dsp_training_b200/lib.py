@@ -58,6 +58,12 @@ _SIGS = {
     "niti_rescale_act": (C.c_int, [_P, _P, C.c_size_t, _P, _P, _P, _P, _P, _P]),
     "niti_rescale_grad": (C.c_int, [_P, _P, C.c_size_t, _P, C.c_int, _P, _P, _P]),
     "niti_rescale_act_fused": (C.c_int, [_P, _P, C.c_size_t, _P, _P, _P, _P, _P, C.c_int, _P, _P]),
+    "niti_rescale_act_dp": (C.c_int, [_P, _P, C.c_size_t, _P, _P, _P, _P, _P, C.c_int, _P, C.c_int, _P]),
+    "niti_dp_alloc": (C.c_int, [_P, _P]),
+    "niti_dp_connect": (C.c_int, [_P, C.c_int, C.c_int, _P]),
+    "niti_dp_close": (C.c_int, [_P]),
+    "niti_dp_step_begin": (C.c_int, [_P, _P]),
+    "niti_dp_error": (C.c_int, [_P, C.POINTER(C.c_int)]),
     "niti_sgd_update": (C.c_int, [_P, _P, _P, C.c_size_t, _P]),
     "niti_conv_fwd": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, _P]),
     "niti_conv_dx": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P]),
@@ -193,6 +199,34 @@ class NitiB200:
     def rescale_act_fused(self, acc, n, maxabs, out, exp_a=None, exp_b=None, exp_out=None, relu=False, gate=None, stream=None):
         self._ck(self.lib.niti_rescale_act_fused(self.h, _ptr(acc), n, _ptr(maxabs), _ptr(out), _ptr(exp_a), _ptr(exp_b),
                                                  _ptr(exp_out), int(bool(relu)), _ptr(gate), self._stream(stream)))
+
+    def rescale_act_dp(self, acc, n, maxabs, out, exp_a=None, exp_b=None, exp_out=None, relu=False, gate=None, dp_slot=0, stream=None):
+        self._ck(self.lib.niti_rescale_act_dp(self.h, _ptr(acc), n, _ptr(maxabs), _ptr(out), _ptr(exp_a), _ptr(exp_b),
+                                              _ptr(exp_out), int(bool(relu)), _ptr(gate), int(dp_slot), self._stream(stream)))
+
+    # ---- data-parallel scalar exchange over peer memory
+    def dp_connect(self, dist):
+        """gather every rank's IPC handle through torch.distributed and map the peers' exchange buffers"""
+        import torch
+        h = (C.c_ubyte * 64)()
+        self._ck(self.lib.niti_dp_alloc(self.h, C.cast(h, _P)))
+        world, rank = dist.get_world_size(), dist.get_rank()
+        mine = torch.tensor(list(bytes(h)), dtype=torch.uint8, device=f"cuda:{self.device}")
+        allh = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allh, mine)
+        blob = b"".join(bytes(t.cpu().tolist()) for t in allh)
+        buf = (C.c_ubyte * len(blob)).from_buffer_copy(blob)
+        self._ck(self.lib.niti_dp_connect(self.h, rank, world, C.cast(buf, _P)))
+        dist.barrier()
+        self.dp_connected = True
+
+    def dp_step_begin(self, stream=None):
+        self._ck(self.lib.niti_dp_step_begin(self.h, self._stream(stream)))
+
+    def dp_error(self):
+        v = C.c_int(0)
+        self._ck(self.lib.niti_dp_error(self.h, C.byref(v)))
+        return v.value
 
     def rescale_grad(self, acc, n, maxabs, sub, dw_out=None, w_inout=None, stream=None):
         self._ck(self.lib.niti_rescale_grad(self.h, _ptr(acc), n, _ptr(maxabs), sub, _ptr(dw_out), _ptr(w_inout),

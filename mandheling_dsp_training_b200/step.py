@@ -164,6 +164,22 @@ class NitiNet:
         self.maxabs = torch.zeros(4 * len(self.convs) + 4, **i32)                    # one slot per reduction
         self.batched_update = bool(fuse)
         nconv = len(self.convs)
+        # data parallel: exchange the exponent scalars inside the rescale kernels over NVLink peer memory when the
+        # backend offers it (lib.NitiB200.dp_connect); otherwise one all_reduce(MAX) per scalar
+        self.peer_max = False
+        if self.dist is not None and fuse and hasattr(nb, "dp_connect"):
+            if not getattr(nb, "dp_connected", False):
+                nb.dp_connect(self.dist)
+            self.peer_max = True
+        # dW all-reduce buckets, closed in backward order (last conv first) once they hold >= 8 MiB, so the exchange
+        # of the deep layers overlaps the rest of backward: list of (lowest conv index, start word, end word)
+        self._buckets, hi_end, size = {}, dw_total, 0
+        for L in reversed(self.convs):
+            size += L.n_w * 4
+            if size >= (8 << 20) or L.index == 0:
+                self._buckets[L.index] = (L.dw_off, hi_end)
+                hi_end, size = L.dw_off, 0
+        self._pending = []
         # (acc, w, wt, max-abs slot, oc, taps, c, sub) per layer: the segments of the one-launch weight update
         self._upd_layers = [(self.dw_acc[L.dw_off: L.dw_off + L.n_w], L.w, L.wt,
                              self.maxabs[2 * nconv + L.index: 2 * nconv + L.index + 1],
@@ -211,19 +227,30 @@ class NitiNet:
         if self.dist is not None:
             self.dist.all_reduce(slot, op=self.dist.ReduceOp.MAX)
 
+    def _rescale(self, n, slot_index, out, ex=None, ew=None, ey=None, relu=False, gate=None):
+        """phase 2 of a forward / dX op: global max|acc| -> shared exponent -> PSTO -> int8 (+ fused ReLU / gate)"""
+        nb = self.nb
+        slot = self.maxabs[slot_index: slot_index + 1]
+        if self.peer_max:
+            nb.rescale_act_dp(self.acc, n, slot, out, ex, ew, ey, relu=relu, gate=gate, dp_slot=slot_index)
+            return
+        self._allreduce_max(slot)
+        if relu or gate is not None:
+            nb.rescale_act_fused(self.acc, n, slot, out, ex, ew, ey, relu=relu, gate=gate)
+        else:
+            nb.rescale_act(self.acc, n, slot, out, ex, ew, ey)
+
     # ---- the step ---------------------------------------------------------------------------------
     def forward(self):
         nb = self.nb
         nb.zero_u32(self.maxabs, self.maxabs.numel())
+        if self.peer_max:
+            nb.dp_step_begin()
         for L in self.ops:
             if L.kind == "conv":
                 slot = self.maxabs[L.index: L.index + 1]
                 self._timed("fwd", L.ops, lambda: nb.conv_fwd_acc(L.d, L.x, L.w, self.acc, slot))
-                self._allreduce_max(slot)
-                if L.relu:
-                    nb.rescale_act_fused(self.acc, L.n_y, slot, L.y, L.ex, L.ew, L.ey, relu=True)
-                else:
-                    nb.rescale_act(self.acc, L.n_y, slot, L.y, L.ex, L.ew, L.ey)
+                self._rescale(L.n_y, L.index, L.y, L.ex, L.ew, L.ey, relu=L.relu)
             elif L.kind == "relu":
                 nb.relu(L.x, L.y, L.x.numel())
             elif L.kind == "pool":
@@ -252,17 +279,16 @@ class NitiNet:
             if L.kind == "conv":
                 acc_dw = self.dw_acc[L.dw_off: L.dw_off + L.n_w]
                 self._timed("dw", L.ops, lambda: nb.conv_dw_acc(L.d, L.x, dy, acc_dw, None))
+                if self.dist is not None and L.index in self._buckets:
+                    lo, hi = self._buckets[L.index]        # this bucket's dW sums are complete: start its exchange
+                    self._pending.append(self.dist.all_reduce(self.dw_acc[lo:hi], op=self.dist.ReduceOp.SUM, async_op=True))
                 if dx is not None:
                     slot = self.maxabs[nconv + L.index: nconv + L.index + 1]
                     if L.wt is not None:
                         self._timed("dx", L.ops, lambda: nb.conv_dx_acc_wt(L.d, dy, L.w, L.wt, self.acc, slot))
                     else:
                         self._timed("dx", L.ops, lambda: nb.conv_dx_acc(L.d, dy, L.w, self.acc, slot))
-                    self._allreduce_max(slot)
-                    if gate:
-                        nb.rescale_act_fused(self.acc, L.n_x, slot, dx, relu=False, gate=L.x)
-                    else:
-                        nb.rescale_act(self.acc, L.n_x, slot, dx, None, None, None)
+                    self._rescale(L.n_x, nconv + L.index, dx, gate=L.x if gate else None)
             elif L.kind == "relu":
                 nb.relu_grad(L.x, dy, dx, L.x.numel())
                 if gate:
@@ -279,8 +305,9 @@ class NitiNet:
                 if gate:
                     nb.relu_grad(L.x, dx, dx, L.x.numel())
         # gradient exchange (one bucket), then shared exponent + PSTO + int8 SGD, fused per layer
-        if self.dist is not None:
-            self.dist.all_reduce(self.dw_acc, op=self.dist.ReduceOp.SUM)
+        for work in self._pending:
+            work.wait()
+        self._pending = []
         if self.batched_update:
             nb.update_layers(self._upd_layers)               # one launch: max|acc|, rule B, SGD, transposed copies
             return
@@ -295,8 +322,8 @@ class NitiNet:
         self.backward_and_update()
 
     def capture(self):
-        """CUDA-graph the step (world size 1).  Returns a callable that replays it."""
-        assert self.dist is None
+        """CUDA-graph the step.  Returns a callable that replays it.  Data-parallel: the NCCL all-reduces are captured
+        into the graph with the kernels (every rank must capture and replay in lock-step)."""
         s = torch.cuda.Stream(self.dev)
         s.wait_stream(torch.cuda.current_stream(self.dev))
         with torch.cuda.stream(s):
