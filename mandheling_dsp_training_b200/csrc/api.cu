@@ -29,6 +29,10 @@ bool tma2_dx_eligible(const niti_conv_desc*);
 int tma2_conv_fwd_acc(niti_ctx*, const niti_conv_desc*, const int8_t*, const int8_t*, int32_t*, uint32_t*, cudaStream_t);
 int tma2_conv_dx_acc(niti_ctx*, const niti_conv_desc*, const int8_t* dy, const int8_t* wt, int32_t*, uint32_t*, cudaStream_t);
 
+// conv_dw2.cu: persistent, tap-grouped, TMA reduce-add generation of the dW kernel
+bool dw2_eligible(const niti_conv_desc*);
+int dw2_conv_dw_acc(niti_ctx*, const niti_conv_desc*, const int8_t*, const int8_t*, int32_t*, uint32_t*, cudaStream_t);
+
 // kernel family selection: TMA-fed tcgen05 > cp.async-fed tcgen05 > SIMT, subject to shape eligibility
 // and the context's forced path.  Returns 0 simt, 1 tc (cp.async), 2 tma, 3 tma2 (CTA pair), -1 unsupported under the
 // forced path.
@@ -197,9 +201,10 @@ int niti_conv_dx_acc_wt(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* dy
 int niti_conv_dw_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, const int8_t* dy, int32_t* acc,
                      uint32_t* maxabs, niti_stream st) {
     if (!ctx || !desc_ok(d) || !x || !dy || !acc) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_dw_acc: bad argument");
-    const int path = pick_path(ctx, tma_dw_eligible(d), tc_dw_eligible(d));
+    const int path = pick_path(ctx, tma_dw_eligible(d), tc_dw_eligible(d), dw2_eligible(d));
     if (path < 0) return niti_fail(ctx, NITI_ERR_UNSUPPORTED, "conv_dw: shape not eligible for the forced kernel path");
     ctx->last_path = path_name(path);
+    if (path == 3) return dw2_conv_dw_acc(ctx, d, x, dy, acc, maxabs, (cudaStream_t)st);
     if (path == 2) return tma_conv_dw_acc(ctx, d, x, dy, acc, maxabs, (cudaStream_t)st);
     if (path == 1) return tc_conv_dw_acc(ctx, d, x, dy, acc, maxabs, (cudaStream_t)st);
     return simt_conv_dw_acc(ctx, d, x, dy, acc, maxabs, (cudaStream_t)st);

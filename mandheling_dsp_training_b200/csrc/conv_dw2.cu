@@ -1,0 +1,264 @@
+// conv_dw2.cu — second-generation weight-gradient contraction (dW) on tcgen05.
+//
+//   dW[oc][tap][c] = sum over output pixels of dY[pixel][oc] * X[pixel shifted by tap][c]
+// (NITI_GradientConv_Int8.cpp:218-268 runs this as a convolution whose "kernel" is dY; grad wiring
+//  tools/train/source/grad/NITI_Conv_Int8_Grad.cpp:134-191).  The reduction runs over N*OH*OW pixels, the output is tiny,
+// so the kernel is split-K by construction.  Compared with conv_tma.cu MODE 1 this generation
+//   * groups the taps of one filter row: the dY tile (A operand, MN-major) is loaded once per K-block and multiplied
+//     with G shifted im2col tiles of X into G accumulators in TMEM (G x BKC columns) -> 1/3 fewer operand bytes at 3x3;
+//   * is persistent (grid <= #SMs, static item schedule), zeroes the output in-kernel behind one grid barrier, and
+//     combines split-K partials with TMA reduce-add (cp.reduce.async.bulk.tensor .add, 128-byte rows) instead of one
+//     red.global per element — integer adds commute, so the result is bit-exact in any order;
+//   * drains TMEM through swizzled shared memory + TMA like conv_tma2.cu.
+#include "tma_common.cuh"
+
+namespace {
+
+constexpr int kDwThreads = 192;      // warp 0: TMA producer, warp 1: MMA issuer + TMEM owner, warps 2-5: epilogue
+
+struct Dw2Params {
+    int oc, c, kh, kw, dil, stride;
+    int out_h, out_w, lower_h, lower_w;
+    int npix, num_kb, kb_per_split, splits;
+    int oc_tiles, c_tiles, gpr;       // gpr = tap groups per filter row
+    int items;
+    int32_t* acc; size_t nout;
+    uint32_t* sync;                   // {arrival counter, exit counter}
+};
+
+template <int BKC, int G> struct DwCfg {
+    static constexpr int A_BYTES = 128 * 128;                 // [128 pixels][128 oc]
+    static constexpr int B_BYTES = 128 * BKC;                 // [128 pixels][BKC c] per tap
+    static constexpr int STAGE = A_BYTES + G * B_BYTES;
+    static constexpr int EPI_BYTES = 4 * 2 * 4096;
+    static constexpr int BUDGET = 232448 - 1024 - 512 - EPI_BYTES;
+    static constexpr int STAGES = (BUDGET / STAGE) > 6 ? 6 : (BUDGET / STAGE);
+    static constexpr int ACC_COLS = G * BKC;
+    static constexpr int TMEM_COLS = ACC_COLS <= 32 ? 32 : (ACC_COLS <= 64 ? 64 : (ACC_COLS <= 128 ? 128 : (ACC_COLS <= 256 ? 256 : 512)));
+    static constexpr int SMEM = STAGES * STAGE + EPI_BYTES + 512 + 1024;
+    static_assert(ACC_COLS <= 512, "accumulators exceed TMEM");
+    static_assert(STAGES >= 2, "need at least a double buffer");
+};
+
+struct DwItem { int ct, ky, kx0, ng, ot, kb0, kb1; };
+
+template <int G>
+__device__ __forceinline__ DwItem decode_item(const Dw2Params& p, int item) {
+    DwItem it;
+    it.ct = item % p.c_tiles; int r = item / p.c_tiles;
+    const int grp = r % (p.kh * p.gpr); r /= (p.kh * p.gpr);
+    it.ot = r % p.oc_tiles; const int sp = r / p.oc_tiles;
+    it.ky = grp / p.gpr; it.kx0 = (grp % p.gpr) * G;
+    it.ng = min(G, p.kw - it.kx0);
+    it.kb0 = sp * p.kb_per_split; it.kb1 = min(p.num_kb, it.kb0 + p.kb_per_split);
+    return it;
+}
+
+template <int BKC, int G>
+__global__ void __launch_bounds__(kDwThreads, 1)
+dw2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
+           const __grid_constant__ CUtensorMap mapD, const Dw2Params p) {
+    using C = DwCfg<BKC, G>;
+    extern __shared__ uint8_t smem_raw_dw2[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw_dw2) + 1023) & ~(uintptr_t)1023);
+    uint8_t* epi = smem + C::STAGES * C::STAGE;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(epi + C::EPI_BYTES);
+    uint64_t* empty_bar = full_bar + C::STAGES;
+    uint64_t* tfull_bar = empty_bar + C::STAGES;
+    uint64_t* tempty_bar = tfull_bar + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 1);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+    if (tid == 0) {
+        for (int s = 0; s < C::STAGES; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], 1); }
+        tc::mbar_init(tfull_bar, 1); tc::mbar_init(tempty_bar, 4);
+        tc::fence_barrier_init();
+        tmax::prefetch_map(&mapA); tmax::prefetch_map(&mapB); tmax::prefetch_map(&mapD);
+    }
+    if (warp == 1) tc::tmem_alloc<C::TMEM_COLS>(tmem_slot);
+    tc::tc_fence_before();
+    __syncthreads();
+    tc::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ------------------------------ TMA producer ------------------------------
+            uint32_t n = 0;
+            for (int item = blockIdx.x; item < p.items; item += gridDim.x) {
+                const DwItem it = decode_item<G>(p, item);
+                for (int kb = it.kb0; kb < it.kb1; ++kb, ++n) {
+                    const int s = n % C::STAGES; const uint32_t ph = (n / C::STAGES) & 1u;
+                    tc::mbar_wait(&empty_bar[s], ph ^ 1u);
+                    const uint32_t a_dst = tc::smem_u32(smem + s * C::STAGE);
+                    tmax::mbar_expect_tx(&full_bar[s], (uint32_t)(C::A_BYTES + it.ng * C::B_BYTES));
+                    const int pix0 = kb * 128;
+                    const int q = pix0 % p.out_w; const int t = pix0 / p.out_w;
+                    const int pp = t % p.out_h; const int nn = t / p.out_h;
+                    tmax::load_2d(&mapA, a_dst, &full_bar[s], it.ot * 128, pix0);
+                    for (int g = 0; g < it.ng; ++g)
+                        tmax::load_im2col(&mapB, a_dst + C::A_BYTES + g * C::B_BYTES, &full_bar[s], it.ct * BKC,
+                                          q * p.stride + p.lower_w, pp * p.stride + p.lower_h, nn,
+                                          (uint16_t)((it.kx0 + g) * p.dil), (uint16_t)(it.ky * p.dil));
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // ------------------------------ MMA issuer ------------------------------
+            constexpr uint32_t idesc = tc::make_idesc_i8(128, BKC, 1, 1);
+            constexpr uint32_t lay = (BKC == 128) ? 2u : 4u;
+            uint32_t n = 0, tile_iter = 0;
+            for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++tile_iter) {
+                const DwItem it = decode_item<G>(p, item);
+                tc::mbar_wait(tempty_bar, (tile_iter & 1u) ^ 1u);          // epilogue drained the previous item
+                tc::tc_fence_after();
+                for (int kb = it.kb0; kb < it.kb1; ++kb, ++n) {
+                    const int s = n % C::STAGES; const uint32_t ph = (n / C::STAGES) & 1u;
+                    tc::mbar_wait(&full_bar[s], ph);
+                    tc::tc_fence_after();
+                    const uint32_t a_base = tc::smem_u32(smem + s * C::STAGE);
+                    for (int g = 0; g < it.ng; ++g) {
+                        const uint32_t b_base = a_base + C::A_BYTES + g * C::B_BYTES;
+#pragma unroll
+                        for (int kk = 0; kk < 4; ++kk) {                     // 128 pixels = 4 x K32
+                            const uint64_t ad = tmax::make_desc(a_base + kk * 32 * 128, 128 * 128, 1024, 2u);
+                            const uint64_t bd = tmax::make_desc(b_base + kk * 32 * BKC, 128 * BKC, 8 * BKC, lay);
+                            tc::umma_i8(tmem_base + g * BKC, ad, bd, idesc, (uint32_t)((kb != it.kb0) || (kk != 0)));
+                        }
+                    }
+                    tc::umma_commit(&empty_bar[s]);
+                }
+                tc::umma_commit(tfull_bar);
+            }
+        }
+    } else {
+        // ------------------------------ epilogue (warps 2..5) ------------------------------
+        const int quarter = warp & 3;
+        uint8_t* my_epi = epi + (warp - 2) * 8192;
+        const int etid = tid - 64;
+        uint32_t tile_iter = 0, nstore = 0;
+        if (p.splits > 1) {
+            const size_t n16 = p.nout >> 2;
+            int4* z = reinterpret_cast<int4*>(p.acc);
+            for (size_t i = (size_t)blockIdx.x * 128 + etid; i < n16; i += (size_t)gridDim.x * 128) z[i] = make_int4(0, 0, 0, 0);
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (etid == 0) tmax::grid_barrier(p.sync, gridDim.x);
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            tmax::fence_proxy_async_all();
+        }
+        for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++tile_iter) {
+            const DwItem it = decode_item<G>(p, item);
+            const int row0 = it.ot * 128 + quarter * 32;
+            tc::mbar_wait(tfull_bar, tile_iter & 1u);
+            tc::tc_fence_after();
+            if (row0 < p.oc) {                                   // warp-uniform
+                for (int g = 0; g < it.ng; ++g) {
+                    const int colbase = ((it.ky * p.kw + it.kx0 + g) * p.c) + it.ct * BKC;
+#pragma unroll 1
+                    for (int c0 = 0; c0 < BKC; c0 += 32) {
+                        uint32_t v[32];
+                        tc::tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(g * BKC + c0), v);
+                        tc::tmem_ld_wait();
+                        uint8_t* buf = my_epi + (nstore & 1u) * 4096;
+                        if (lane == 0) tmax::bulk_wait_read<1>();
+                        __syncwarp();
+                        const uint32_t rowaddr = tc::smem_u32(buf) + (uint32_t)lane * 128u;
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) {
+                            const uint32_t dst = rowaddr + (uint32_t)((q ^ (lane & 7)) << 4);
+                            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(v[4 * q]), "r"(v[4 * q + 1]),
+                                         "r"(v[4 * q + 2]), "r"(v[4 * q + 3]) : "memory");
+                        }
+                        tc::fence_proxy_async_smem();
+                        __syncwarp();
+                        if (lane == 0) {
+                            if (p.splits == 1) tmax::store_2d(&mapD, tc::smem_u32(buf), colbase + c0, row0);
+                            else tmax::reduce_add_2d(&mapD, tc::smem_u32(buf), colbase + c0, row0);
+                            tmax::bulk_commit();
+                        }
+                        ++nstore;
+                    }
+                }
+            }
+            tc::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) tc::mbar_arrive(tempty_bar);
+        }
+        if (lane == 0) tmax::bulk_wait<0>();
+        if (p.splits > 1) {
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (etid == 0) {                                     // last CTA out re-arms the barrier for the next launch
+                __threadfence();
+                if (atomicAdd(p.sync + 1, 1u) == gridDim.x - 1) { p.sync[0] = 0u; p.sync[1] = 0u; __threadfence(); }
+            }
+        }
+    }
+    __syncwarp();
+    tc::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tc::tmem_dealloc<C::TMEM_COLS>(tmem_base);
+}
+
+} // namespace
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+namespace {
+template <int BKC, int G>
+int launch_dw2(niti_ctx* ctx, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& d, const Dw2Params& p, int grid,
+               cudaStream_t st) {
+    using C = DwCfg<BKC, G>;
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(dw2_kernel<BKC, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "cudaFuncSetAttribute(dw2)", e);
+        configured = true;
+    }
+    dw2_kernel<BKC, G><<<grid, kDwThreads, C::SMEM, st>>>(a, b, d, p);
+    return niti_check_launch(ctx, "dw2");
+}
+} // namespace
+
+bool dw2_eligible(const niti_conv_desc* d) {
+    return d->oc % 16 == 0 && d->c % 64 == 0 && d->pad <= 127 && (d->kh - 1) * d->dil <= 255 && (d->kw - 1) * d->dil <= 255 &&
+           d->stride <= 8;
+}
+
+int dw2_conv_dw_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, const int8_t* dy, int32_t* acc,
+                    uint32_t* maxabs, cudaStream_t st) {
+    if (!tmax::driver_ok()) return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncode* entry points unavailable");
+    const int oh = conv_out_h(d), ow = conv_out_w(d);
+    const int bkc = d->c % 128 == 0 ? 128 : 64;
+    const int G = d->kw == 3 ? 3 : 1;
+    Dw2Params p{};
+    p.oc = d->oc; p.c = d->c; p.kh = d->kh; p.kw = d->kw; p.dil = d->dil; p.stride = d->stride;
+    p.out_h = oh; p.out_w = ow; p.lower_h = -d->pad; p.lower_w = -d->pad;
+    p.npix = d->n * oh * ow; p.num_kb = (p.npix + 127) / 128;
+    p.oc_tiles = (d->oc + 127) / 128; p.c_tiles = d->c / bkc; p.gpr = (d->kw + G - 1) / G;
+    const long tiles = (long)p.oc_tiles * p.kh * p.gpr * p.c_tiles;
+    int splits = (int)(ctx->sm_count / tiles);
+    if (splits > p.num_kb) splits = p.num_kb;
+    if (splits < 1) splits = 1;
+    p.kb_per_split = (p.num_kb + splits - 1) / splits;
+    p.splits = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;
+    p.items = (int)(tiles * p.splits);
+    p.acc = acc; p.nout = (size_t)d->oc * d->kh * d->kw * d->c; p.sync = ctx->ws_u32 + 44;
+    CUtensorMap ma, mb, md;
+    if (!tmax::make_tiled_u8(&ma, dy, (uint64_t)p.npix, (uint64_t)d->oc, 128, 128, 128))
+        return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncodeTiled(dy) failed");
+    if (!tmax::make_im2col_u8(&mb, x, d->n, d->h, d->w, d->c, -d->pad, -d->pad, d->pad - (d->kh - 1) * d->dil,
+                              d->pad - (d->kw - 1) * d->dil, d->stride, bkc, 128, bkc))
+        return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncodeIm2col(x) failed");
+    if (!tmax::make_tiled_i32(&md, acc, (uint64_t)d->oc, (uint64_t)d->kh * d->kw * d->c))
+        return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncodeTiled(dW) failed");
+    const int grid = p.items < ctx->sm_count ? p.items : ctx->sm_count;
+    int rc;
+    if (bkc == 128) rc = G == 3 ? launch_dw2<128, 3>(ctx, ma, mb, md, p, grid, st) : launch_dw2<128, 1>(ctx, ma, mb, md, p, grid, st);
+    else rc = G == 3 ? launch_dw2<64, 3>(ctx, ma, mb, md, p, grid, st) : launch_dw2<64, 1>(ctx, ma, mb, md, p, grid, st);
+    if (rc) return rc;
+    if (maxabs) return niti_absmax(ctx, acc, p.nout, maxabs, st);
+    return NITI_OK;
+}

@@ -162,18 +162,18 @@ class NitiB200:
         self._ck(self.lib.niti_conv_dx_acc_wt(self.h, C.byref(d), _ptr(dy), _ptr(w), _ptr(wt), _ptr(acc), _ptr(maxabs),
                                               self._stream(stream)))
 
+    @staticmethod
+    def make_update_segs(layers):
+        """layers: list of (acc, w, wt|None, maxabs slot, oc, taps, c, sub) torch tensors / ints -> ctypes array of
+        UpdateSeg for update_batched.  The caller keeps both the array and the tensors alive."""
+        segs = (UpdateSeg * len(layers))()
+        for s_, (acc, w, wt, slot, oc, taps, c, sub) in zip(segs, layers):
+            s_.acc, s_.w, s_.wt, s_.maxabs = _ptr(acc), _ptr(w), _ptr(wt), _ptr(slot)
+            s_.oc, s_.taps, s_.c, s_.sub = oc, taps, c, sub
+        return segs
+
     def update_layers(self, layers, stream=None):
-        """layers: list of (acc, w, wt|None, maxabs slot, oc, taps, c, sub) torch tensors / ints; the ctypes segment
-        array is built once per list object and reused (the tensors must stay alive, as they do in step.NitiNet)"""
-        cache = self.__dict__.setdefault("_seg_cache", {})
-        segs = cache.get(id(layers))
-        if segs is None:
-            segs = (UpdateSeg * len(layers))()
-            for s_, (acc, w, wt, slot, oc, taps, c, sub) in zip(segs, layers):
-                s_.acc, s_.w, s_.wt, s_.maxabs = _ptr(acc), _ptr(w), _ptr(wt), _ptr(slot)
-                s_.oc, s_.taps, s_.c, s_.sub = oc, taps, c, sub
-            cache[id(layers)] = segs
-        self.update_batched(segs, stream)
+        self.update_batched(self.make_update_segs(layers), stream)
 
     def update_batched(self, segs, stream=None):
         """segs: ctypes array of UpdateSeg (host); read at call time"""

@@ -184,6 +184,7 @@ class NitiNet:
         self._upd_layers = [(self.dw_acc[L.dw_off: L.dw_off + L.n_w], L.w, L.wt,
                              self.maxabs[2 * nconv + L.index: 2 * nconv + L.index + 1],
                              L.d.oc, L.d.kh * L.d.kw, L.d.c, 2) for L in self.convs]
+        self._upd_segs = nb.make_update_segs(self._upd_layers) if self.batched_update else None
 
     # ---- parameters -------------------------------------------------------------------------------
     def init_weights(self, seed=1):
@@ -309,7 +310,7 @@ class NitiNet:
             work.wait()
         self._pending = []
         if self.batched_update:
-            nb.update_layers(self._upd_layers)               # one launch: max|acc|, rule B, SGD, transposed copies
+            nb.update_batched(self._upd_segs)                 # one launch: max|acc|, rule B, SGD, transposed copies
             return
         for L in self.convs:
             acc_dw = self.dw_acc[L.dw_off: L.dw_off + L.n_w]

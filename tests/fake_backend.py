@@ -105,6 +105,13 @@ class OracleBackend:
         assert np.array_equal(_np(wt), np.transpose(_np(w), (3, 1, 2, 0))), "transposed weight copy out of sync"
         self.conv_dx_acc(d, dy, w, acc, maxabs)
 
+    @staticmethod
+    def make_update_segs(layers):
+        return layers
+
+    def update_batched(self, layers, stream=None):
+        self.update_layers(layers)
+
     def update_layers(self, layers, stream=None):
         for acc, w, wt, slot, oc, taps, c, sub in layers:
             n = oc * taps * c

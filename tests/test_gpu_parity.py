@@ -88,7 +88,7 @@ def test_accumulators_and_outputs_vs_oracle(nb, run, oracle, cfg, path):
         if path in ("tma", "tma2"):
             fwd_ok = c % 64 == 0 and oc % 4 == 0
             dx_ok = st == 1 and oc % 64 == 0 and c % 4 == 0 and (k - 1) * dil - p >= 0
-            dw_ok = oc % 16 == 0 and c % 64 == 0 and path == "tma"      # tma2 = forward / dX generation
+            dw_ok = oc % 16 == 0 and c % 64 == 0                         # "tma2" = second generation: conv_tma2.cu / conv_dw2.cu
             if not (fwd_ok or dx_ok or dw_ok):
                 pytest.skip("shape not eligible for the TMA path")
         else:
