@@ -20,7 +20,7 @@ struct Dw2Params {
     int oc, c, kh, kw, dil, stride;
     int out_h, out_w, lower_h, lower_w;
     int npix, num_kb, kb_per_split, splits;
-    int oc_tiles, c_tiles, gpr;       // gpr = tap groups per filter row
+    int oc_tiles, c_tiles, ngroups;   // tap groups (G consecutive taps in row-major tap order)
     int items;
     int32_t* acc; size_t nout;
     uint32_t* sync;                   // {arrival counter, exit counter}
@@ -40,16 +40,16 @@ template <int BKC, int G> struct DwCfg {
     static_assert(STAGES >= 2, "need at least a double buffer");
 };
 
-struct DwItem { int ct, ky, kx0, ng, ot, kb0, kb1; };
+struct DwItem { int ct, tap0, ng, ot, kb0, kb1; };
 
 template <int G>
 __device__ __forceinline__ DwItem decode_item(const Dw2Params& p, int item) {
     DwItem it;
     it.ct = item % p.c_tiles; int r = item / p.c_tiles;
-    const int grp = r % (p.kh * p.gpr); r /= (p.kh * p.gpr);
+    const int grp = r % p.ngroups; r /= p.ngroups;
     it.ot = r % p.oc_tiles; const int sp = r / p.oc_tiles;
-    it.ky = grp / p.gpr; it.kx0 = (grp % p.gpr) * G;
-    it.ng = min(G, p.kw - it.kx0);
+    it.tap0 = grp * G;
+    it.ng = min(G, p.kh * p.kw - it.tap0);
     it.kb0 = sp * p.kb_per_split; it.kb1 = min(p.num_kb, it.kb0 + p.kb_per_split);
     return it;
 }
@@ -97,10 +97,12 @@ dw2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
                     const int q = pix0 % p.out_w; const int t = pix0 / p.out_w;
                     const int pp = t % p.out_h; const int nn = t / p.out_h;
                     tmax::load_2d(&mapA, a_dst, &full_bar[s], it.ot * 128, pix0);
-                    for (int g = 0; g < it.ng; ++g)
+                    for (int g = 0; g < it.ng; ++g) {
+                        const int tap = it.tap0 + g, ky = tap / p.kw, kx = tap - ky * p.kw;
                         tmax::load_im2col(&mapB, a_dst + C::A_BYTES + g * C::B_BYTES, &full_bar[s], it.ct * BKC,
                                           q * p.stride + p.lower_w, pp * p.stride + p.lower_h, nn,
-                                          (uint16_t)((it.kx0 + g) * p.dil), (uint16_t)(it.ky * p.dil));
+                                          (uint16_t)(kx * p.dil), (uint16_t)(ky * p.dil));
+                    }
                 }
             }
         }
@@ -108,7 +110,7 @@ dw2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
         if (lane == 0) {
             // ------------------------------ MMA issuer ------------------------------
             constexpr uint32_t idesc = tc::make_idesc_i8(128, BKC, 1, 1);
-            constexpr uint32_t lay = (BKC == 128) ? 2u : 4u;
+            constexpr uint32_t lay = (BKC == 128) ? 2u : (BKC == 64 ? 4u : 0u);
             uint32_t n = 0, tile_iter = 0;
             for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++tile_iter) {
                 const DwItem it = decode_item<G>(p, item);
@@ -119,6 +121,19 @@ dw2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
                     tc::mbar_wait(&full_bar[s], ph);
                     tc::tc_fence_after();
                     const uint32_t a_base = tc::smem_u32(smem + s * C::STAGE);
+                    if (BKC == 16) {
+                        // stem layers (<= 16 input channels): the ng tap tiles [128 pixels][16 B] sit back to back, i.e. one
+                        // MN-major un-swizzled B operand of N = ng*16 columns: 16-byte column chunks SBO = 2048 B apart,
+                        // 8-pixel K groups LBO = 128 B apart -> ONE MMA per K32 covers every tap of the group
+                        const uint32_t idesc_n = tc::make_idesc_i8(128, it.ng * 16, 1, 1);
+                        const uint32_t b_base = a_base + C::A_BYTES;
+#pragma unroll
+                        for (int kk = 0; kk < 4; ++kk) {
+                            const uint64_t ad = tmax::make_desc(a_base + kk * 32 * 128, 128 * 128, 1024, 2u);
+                            const uint64_t bd = tmax::make_desc(b_base + kk * 32 * 16, 128, 2048, 0u);
+                            tc::umma_i8(tmem_base, ad, bd, idesc_n, (uint32_t)((kb != it.kb0) || (kk != 0)));
+                        }
+                    } else
                     for (int g = 0; g < it.ng; ++g) {
                         const uint32_t b_base = a_base + C::A_BYTES + g * C::B_BYTES;
 #pragma unroll
@@ -154,10 +169,14 @@ dw2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
             tc::mbar_wait(tfull_bar, tile_iter & 1u);
             tc::tc_fence_after();
             if (row0 < p.oc) {                                   // warp-uniform
-                for (int g = 0; g < it.ng; ++g) {
-                    const int colbase = ((it.ky * p.kw + it.kx0 + g) * p.c) + it.ct * BKC;
+                // BKC == 16 (c == 16): the group's ng*16 accumulator columns are contiguous in dW as well, drained in 32-column
+                // boxes; an odd ng only occurs in the last group, whose overhang lies outside the tensor map and is clipped
+                const int ngrp = BKC == 16 ? 1 : it.ng;
+                const int ncols = BKC == 16 ? it.ng * 16 : BKC;
+                for (int g = 0; g < ngrp; ++g) {
+                    const int colbase = ((it.tap0 + g) * p.c) + it.ct * BKC;
 #pragma unroll 1
-                    for (int c0 = 0; c0 < BKC; c0 += 32) {
+                    for (int c0 = 0; c0 < ncols; c0 += 32) {
                         uint32_t v[32];
                         tc::tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(g * BKC + c0), v);
                         tc::tmem_ld_wait();
@@ -223,7 +242,7 @@ int launch_dw2(niti_ctx* ctx, const CUtensorMap& a, const CUtensorMap& b, const 
 } // namespace
 
 bool dw2_eligible(const niti_conv_desc* d) {
-    return d->oc % 16 == 0 && d->c % 64 == 0 && d->pad <= 127 && (d->kh - 1) * d->dil <= 255 && (d->kw - 1) * d->dil <= 255 &&
+    return d->oc % 16 == 0 && (d->c % 64 == 0 || d->c == 16) && d->pad <= 127 && (d->kh - 1) * d->dil <= 255 && (d->kw - 1) * d->dil <= 255 &&
            d->stride <= 8;
 }
 
@@ -231,14 +250,14 @@ int dw2_conv_dw_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, con
                     uint32_t* maxabs, cudaStream_t st) {
     if (!tmax::driver_ok()) return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncode* entry points unavailable");
     const int oh = conv_out_h(d), ow = conv_out_w(d);
-    const int bkc = d->c % 128 == 0 ? 128 : 64;
-    const int G = d->kw == 3 ? 3 : 1;
+    const int bkc = d->c == 16 ? 16 : (d->c % 128 == 0 ? 128 : 64);
+    const int G = bkc == 16 ? 16 : (d->kw == 3 ? 3 : 1);
     Dw2Params p{};
     p.oc = d->oc; p.c = d->c; p.kh = d->kh; p.kw = d->kw; p.dil = d->dil; p.stride = d->stride;
     p.out_h = oh; p.out_w = ow; p.lower_h = -d->pad; p.lower_w = -d->pad;
     p.npix = d->n * oh * ow; p.num_kb = (p.npix + 127) / 128;
-    p.oc_tiles = (d->oc + 127) / 128; p.c_tiles = d->c / bkc; p.gpr = (d->kw + G - 1) / G;
-    const long tiles = (long)p.oc_tiles * p.kh * p.gpr * p.c_tiles;
+    p.oc_tiles = (d->oc + 127) / 128; p.c_tiles = d->c / bkc; p.ngroups = (d->kh * d->kw + G - 1) / G;
+    const long tiles = (long)p.oc_tiles * p.ngroups * p.c_tiles;
     int splits = (int)(ctx->sm_count / tiles);
     if (splits > p.num_kb) splits = p.num_kb;
     if (splits < 1) splits = 1;
@@ -250,13 +269,14 @@ int dw2_conv_dw_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, con
     if (!tmax::make_tiled_u8(&ma, dy, (uint64_t)p.npix, (uint64_t)d->oc, 128, 128, 128))
         return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncodeTiled(dy) failed");
     if (!tmax::make_im2col_u8(&mb, x, d->n, d->h, d->w, d->c, -d->pad, -d->pad, d->pad - (d->kh - 1) * d->dil,
-                              d->pad - (d->kw - 1) * d->dil, d->stride, bkc, 128, bkc))
+                              d->pad - (d->kw - 1) * d->dil, d->stride, bkc, 128, bkc == 16 ? 0 : bkc))
         return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncodeIm2col(x) failed");
     if (!tmax::make_tiled_i32(&md, acc, (uint64_t)d->oc, (uint64_t)d->kh * d->kw * d->c))
         return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncodeTiled(dW) failed");
     const int grid = p.items < ctx->sm_count ? p.items : ctx->sm_count;
     int rc;
-    if (bkc == 128) rc = G == 3 ? launch_dw2<128, 3>(ctx, ma, mb, md, p, grid, st) : launch_dw2<128, 1>(ctx, ma, mb, md, p, grid, st);
+    if (bkc == 16) rc = launch_dw2<16, 16>(ctx, ma, mb, md, p, grid, st);
+    else if (bkc == 128) rc = G == 3 ? launch_dw2<128, 3>(ctx, ma, mb, md, p, grid, st) : launch_dw2<128, 1>(ctx, ma, mb, md, p, grid, st);
     else rc = G == 3 ? launch_dw2<64, 3>(ctx, ma, mb, md, p, grid, st) : launch_dw2<64, 1>(ctx, ma, mb, md, p, grid, st);
     if (rc) return rc;
     if (maxabs) return niti_absmax(ctx, acc, p.nout, maxabs, st);

@@ -68,6 +68,9 @@ TC_SHAPES = [
     (2, 64, 12, 12, 128, 5, 1, 2),    # 5x5 pad 2
     (2, 128, 9, 9, 64, 3, 2, 1),      # stride 2 forward / dW via TMA, dX via cp.async
     (256, 512, 1, 1, 512, 1, 1, 0),   # FC as 1x1 conv, split-K
+    (4, 16, 32, 32, 64, 3, 1, 1),     # VGG stem (3 -> 16 padded channels): dW with all 9 taps in one MMA
+    (2, 16, 36, 36, 64, 7, 2, 3),     # ResNet stem 7x7 stride 2: 49 taps = 4 tap groups
+    (3, 16, 12, 12, 32, 5, 1, 2),     # 5x5 stem, 25 taps = 16 + 9, ragged pixel count
     (2, 64, 10, 10, 64, 3, 1, 0),     # pad 0
     (2, 16, 9, 9, 32, 3, 1, 2),       # dilation handled below with dil=2
 ]
@@ -88,7 +91,7 @@ def test_accumulators_and_outputs_vs_oracle(nb, run, oracle, cfg, path):
         if path in ("tma", "tma2"):
             fwd_ok = c % 64 == 0 and oc % 4 == 0
             dx_ok = st == 1 and oc % 64 == 0 and c % 4 == 0 and (k - 1) * dil - p >= 0
-            dw_ok = oc % 16 == 0 and c % 64 == 0                         # "tma2" = second generation: conv_tma2.cu / conv_dw2.cu
+            dw_ok = oc % 16 == 0 and (c % 64 == 0 or (c == 16 and path == "tma2"))   # "tma2": conv_tma2.cu / conv_dw2.cu
             if not (fwd_ok or dx_ok or dw_ok):
                 pytest.skip("shape not eligible for the TMA path")
         else:
