@@ -149,6 +149,15 @@ int niti_rescale_grad_split(niti_ctx*, const int32_t* acc, size_t n_per_slice, i
  * Drop-in for the four reference executions (same inputs/outputs, NHWC/OHWI instead of NC4HW4). */
 int niti_conv_fwd(niti_ctx*, const niti_conv_desc*, const int8_t* x, const int8_t* w,
                   const int8_t* ex, const int8_t* ew, int8_t* y, int8_t* ey, niti_stream);
+/* The forward op with everything of NITI_Conv_Int8::onExecute (+ the following NITI_CPURelu_Int8 when relu != 0) behind
+ * one call, data-parallel aware: y = rule A(conv(x, w)) with the exponent taken from the max over all ranks.
+ * Stem layers (c == 16: 1/3-channel inputs zero-padded to 16) run as ONE launch that recomputes the contraction instead
+ * of round-tripping int32 accumulators through HBM (csrc/conv_stem.cu); other shapes run phase 1 + niti_rescale_act_dp on
+ * `acc` (caller scratch of n*oh*ow*oc words, or NULL for the context workspace).  `maxabs`: zeroed slot, holds this
+ * rank's max|acc| afterwards; dp_slot as in niti_rescale_act_dp. */
+int niti_conv_fwd_fused(niti_ctx*, const niti_conv_desc*, const int8_t* x, const int8_t* w, const int8_t* ex,
+                        const int8_t* ew, int8_t* y, int8_t* ey, int relu, int32_t* acc, uint32_t* maxabs, int dp_slot,
+                        niti_stream);
 int niti_conv_dx(niti_ctx*, const niti_conv_desc*, const int8_t* dy, const int8_t* w, int8_t* dx, niti_stream);
 int niti_conv_dw(niti_ctx*, const niti_conv_desc*, const int8_t* x, const int8_t* dy, int8_t* dw, niti_stream);
 int niti_matmul_nt(niti_ctx*, int e, int h, int l, const int8_t* a, const int8_t* b, int8_t* c, niti_stream);

@@ -33,6 +33,11 @@ int tma2_conv_dx_acc(niti_ctx*, const niti_conv_desc*, const int8_t* dy, const i
 bool dw2_eligible(const niti_conv_desc*);
 int dw2_conv_dw_acc(niti_ctx*, const niti_conv_desc*, const int8_t*, const int8_t*, int32_t*, uint32_t*, cudaStream_t);
 
+// conv_stem.cu: single-launch forward op (conv + exponent + rescale) of <= 16-channel stem layers
+bool stem_fwd_eligible(const niti_conv_desc*);
+int stem_conv_fwd_fused(niti_ctx*, const niti_conv_desc*, const int8_t*, const int8_t*, const int8_t*, const int8_t*, int8_t*,
+                        int8_t*, int, uint32_t*, int, cudaStream_t);
+
 // kernel family selection: TMA-fed tcgen05 > cp.async-fed tcgen05 > SIMT, subject to shape eligibility
 // and the context's forced path.  Returns 0 simt, 1 tc (cp.async), 2 tma, 3 tma2 (CTA pair), -1 unsupported under the
 // forced path.
@@ -227,6 +232,22 @@ int niti_conv_fwd(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, const
     if ((rc = niti_zero_u32(ctx, ctx->ws_u32, 1, st))) return rc;
     if ((rc = niti_conv_fwd_acc(ctx, d, x, w, acc, ctx->ws_u32, st))) return rc;
     return niti_rescale_act(ctx, acc, n, ctx->ws_u32, y, ex, ew, ey, st);
+}
+
+int niti_conv_fwd_fused(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, const int8_t* w, const int8_t* ex,
+                        const int8_t* ew, int8_t* y, int8_t* ey, int relu, int32_t* acc, uint32_t* maxabs, int dp_slot,
+                        niti_stream st) {
+    if (!ctx || !desc_ok(d) || !x || !w || !y || !maxabs) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_fwd_fused: bad argument");
+    if (dp_slot < 0 || dp_slot >= kDpSlots) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_fwd_fused: slot out of range");
+    if ((ctx->path == NITI_PATH_AUTO || ctx->path == NITI_PATH_TMA2) && ctx->auto_tma2 && stem_fwd_eligible(d)) {
+        ctx->last_path = "stem";
+        return stem_conv_fwd_fused(ctx, d, x, w, ex, ew, y, ey, relu, maxabs, dp_slot, (cudaStream_t)st);
+    }
+    const size_t n = (size_t)d->n * conv_out_h(d) * conv_out_w(d) * d->oc;
+    int rc;
+    if (!acc && (rc = niti_ws_acc(ctx, n * 4, &acc))) return rc;
+    if ((rc = niti_conv_fwd_acc(ctx, d, x, w, acc, maxabs, st))) return rc;
+    return niti_rescale_act_dp(ctx, acc, n, maxabs, y, ex, ew, ey, relu, nullptr, dp_slot, st);
 }
 
 int niti_conv_dx(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* dy, const int8_t* w, int8_t* dx, niti_stream st) {

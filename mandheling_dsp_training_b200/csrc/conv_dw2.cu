@@ -22,6 +22,7 @@ struct Dw2Params {
     int npix, num_kb, kb_per_split, splits;
     int oc_tiles, c_tiles, ngroups;   // tap groups (G consecutive taps in row-major tap order)
     int items;
+    int rows_mode;                    // BKC == 16 only: X tiles loaded row-wise (tmax::make_rows16)
     int32_t* acc; size_t nout;
     uint32_t* sync;                   // {arrival counter, exit counter}
 };
@@ -99,9 +100,13 @@ dw2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
                     tmax::load_2d(&mapA, a_dst, &full_bar[s], it.ot * 128, pix0);
                     for (int g = 0; g < it.ng; ++g) {
                         const int tap = it.tap0 + g, ky = tap / p.kw, kx = tap - ky * p.kw;
-                        tmax::load_im2col(&mapB, a_dst + C::A_BYTES + g * C::B_BYTES, &full_bar[s], it.ct * BKC,
-                                          q * p.stride + p.lower_w, pp * p.stride + p.lower_h, nn,
-                                          (uint16_t)(kx * p.dil), (uint16_t)(ky * p.dil));
+                        if (BKC == 16 && p.rows_mode)
+                            tmax::load_3d(&mapB, a_dst + C::A_BYTES + g * C::B_BYTES, &full_bar[s], (kx + p.lower_w) * 2,
+                                          pp + ky + p.lower_h, nn);
+                        else
+                            tmax::load_im2col(&mapB, a_dst + C::A_BYTES + g * C::B_BYTES, &full_bar[s], it.ct * BKC,
+                                              q * p.stride + p.lower_w, pp * p.stride + p.lower_h, nn,
+                                              (uint16_t)(kx * p.dil), (uint16_t)(ky * p.dil));
                     }
                 }
             }
@@ -268,8 +273,12 @@ int dw2_conv_dw_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, con
     CUtensorMap ma, mb, md;
     if (!tmax::make_tiled_u8(&ma, dy, (uint64_t)p.npix, (uint64_t)d->oc, 128, 128, 128))
         return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncodeTiled(dy) failed");
-    if (!tmax::make_im2col_u8(&mb, x, d->n, d->h, d->w, d->c, -d->pad, -d->pad, d->pad - (d->kh - 1) * d->dil,
-                              d->pad - (d->kw - 1) * d->dil, d->stride, bkc, 128, bkc == 16 ? 0 : bkc))
+    p.rows_mode = (bkc == 16 && tmax::rows16_ok(d->c, d->stride, d->dil, oh, ow)) ? 1 : 0;
+    if (p.rows_mode) {
+        if (!tmax::make_rows16(&mb, x, d->n, d->h, d->w, ow))
+            return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncodeTiled(x rows) failed");
+    } else if (!tmax::make_im2col_u8(&mb, x, d->n, d->h, d->w, d->c, -d->pad, -d->pad, d->pad - (d->kh - 1) * d->dil,
+                                     d->pad - (d->kw - 1) * d->dil, d->stride, bkc, 128, bkc == 16 ? 0 : bkc))
         return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncodeIm2col(x) failed");
     if (!tmax::make_tiled_i32(&md, acc, (uint64_t)d->oc, (uint64_t)d->kh * d->kw * d->c))
         return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncodeTiled(dW) failed");

@@ -17,6 +17,10 @@ __device__ __forceinline__ void load_2d(const CUtensorMap* map, uint32_t dst, ui
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
                  ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(tc::smem_u32(bar)), "r"(x), "r"(y) : "memory");
 }
+__device__ __forceinline__ void load_3d(const CUtensorMap* map, uint32_t dst, uint64_t* bar, int x, int y, int z) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                 ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(tc::smem_u32(bar)), "r"(x), "r"(y), "r"(z) : "memory");
+}
 __device__ __forceinline__ void load_im2col(const CUtensorMap* map, uint32_t dst, uint64_t* bar, int c, int w, int h, int n,
                                             uint16_t off_w, uint16_t off_h) {
     asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes"
@@ -111,6 +115,23 @@ inline bool make_tiled_i32(CUtensorMap* m, void* base, uint64_t rows, uint64_t c
     cuuint32_t es[2] = {1, 1};
     return driver().tiled(m, CU_TENSOR_MAP_DATA_TYPE_INT32, 2, base, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                           CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+// 16-channel NHWC int8 tensor seen as rows of 8-byte words: dims {w*2, h, n}; box = {ow*2, rows, 1} with rows*ow == 128.
+// One request per image ROW (ow*16 contiguous bytes) instead of one per pixel as in im2col mode, which is what bounds the
+// stem kernels (16 B per pixel).  Lands in shared memory as [128 pixels][16 B], the same image an im2col box produces;
+// the filter tap is a coordinate shift ({(kx - pad)*2, h0 + ky - pad, n}); out-of-range words read as zero (= padding).
+// Valid for stride 1, dilation 1, ow | 128, (128/ow) | oh, ow <= 128.
+inline bool rows16_ok(int c, int stride, int dil, int oh, int ow) {
+    return c == 16 && stride == 1 && dil == 1 && ow <= 128 && 128 % ow == 0 && oh % (128 / ow) == 0;
+}
+inline bool make_rows16(CUtensorMap* m, const void* base, int n, int h, int w, int ow) {
+    cuuint64_t dims[3] = {(cuuint64_t)w * 2, (cuuint64_t)h, (cuuint64_t)n};
+    cuuint64_t strides[2] = {(cuuint64_t)w * 16, (cuuint64_t)h * w * 16};
+    cuuint32_t box[3] = {(cuuint32_t)ow * 2, (cuuint32_t)(128 / ow), 1};
+    cuuint32_t es[3] = {1, 1, 1};
+    return driver().tiled(m, CU_TENSOR_MAP_DATA_TYPE_UINT64, 3, const_cast<void*>(base), dims, strides, box, es,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 // NHWC int8 tensor [n][h][w][c]; box = `pixels` pixels x bkc channels, swizzle span = swz_bytes
 inline bool make_im2col_u8(CUtensorMap* m, const void* base, int n, int h, int w, int c, int lower_h, int lower_w, int upper_h,

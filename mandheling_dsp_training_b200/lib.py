@@ -66,6 +66,7 @@ _SIGS = {
     "niti_dp_error": (C.c_int, [_P, C.POINTER(C.c_int)]),
     "niti_sgd_update": (C.c_int, [_P, _P, _P, C.c_size_t, _P]),
     "niti_conv_fwd": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, _P]),
+    "niti_conv_fwd_fused": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, C.c_int, _P, _P, C.c_int, _P]),
     "niti_conv_dx": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P]),
     "niti_conv_dw": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P]),
     "niti_matmul_nt": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P, _P, _P]),
@@ -238,6 +239,10 @@ class NitiB200:
     # ---- whole ops
     def conv_fwd(self, d, x, w, ex, ew, y, ey, stream=None):
         self._ck(self.lib.niti_conv_fwd(self.h, C.byref(d), _ptr(x), _ptr(w), _ptr(ex), _ptr(ew), _ptr(y), _ptr(ey), self._stream(stream)))
+
+    def conv_fwd_fused(self, d, x, w, ex, ew, y, ey, relu, acc, maxabs, dp_slot=0, stream=None):
+        self._ck(self.lib.niti_conv_fwd_fused(self.h, C.byref(d), _ptr(x), _ptr(w), _ptr(ex), _ptr(ew), _ptr(y), _ptr(ey),
+                                              int(bool(relu)), _ptr(acc), _ptr(maxabs), int(dp_slot), self._stream(stream)))
 
     def conv_dx(self, d, dy, w, dx, stream=None):
         self._ck(self.lib.niti_conv_dx(self.h, C.byref(d), _ptr(dy), _ptr(w), _ptr(dx), self._stream(stream)))

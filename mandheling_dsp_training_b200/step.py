@@ -250,6 +250,11 @@ class NitiNet:
         for L in self.ops:
             if L.kind == "conv":
                 slot = self.maxabs[L.index: L.index + 1]
+                if self.batched_update and L.d.c == 16 and hasattr(nb, "conv_fwd_fused") and (self.dist is None or self.peer_max):
+                    # stem layer: conv + exponent + rescale (+ ReLU) in one launch (csrc/conv_stem.cu)
+                    self._timed("fwd", L.ops, lambda: nb.conv_fwd_fused(L.d, L.x, L.w, L.ex, L.ew, L.y, L.ey, L.relu,
+                                                                       self.acc, slot, dp_slot=L.index))
+                    continue
                 self._timed("fwd", L.ops, lambda: nb.conv_fwd_acc(L.d, L.x, L.w, self.acc, slot))
                 self._rescale(L.n_y, L.index, L.y, L.ex, L.ew, L.ey, relu=L.relu)
             elif L.kind == "relu":

@@ -63,6 +63,15 @@ class Runner:
         torch.cuda.synchronize()
         return nchw(y.cpu().numpy()), int(ey.item())
 
+    def conv_fwd_fused(self, s, x, w, ex, ew, relu):
+        d = to_desc(s)
+        y = torch.empty((s.n, d.oh, d.ow, s.oc), dtype=torch.int8, device=self.device)
+        ey = self._scalar(0)
+        mx = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.nb.conv_fwd_fused(d, dev(nhwc(x)), dev(nhwc(w)), self._scalar(ex), self._scalar(ew), y, ey, relu, None, mx)
+        torch.cuda.synchronize()
+        return nchw(y.cpu().numpy()), int(ey.item()), int(mx.item())
+
     def conv_dx(self, s, dy, w):
         d = to_desc(s)
         dx = torch.empty((s.n, s.h, s.w, s.c), dtype=torch.int8, device=self.device)

@@ -123,6 +123,34 @@ def test_accumulators_and_outputs_vs_oracle(nb, run, oracle, cfg, path):
         nb.set_path(0)
 
 
+STEM_SHAPES = [(4, 16, 32, 32, 64, 3, 1, 1), (2, 16, 36, 36, 64, 7, 2, 3), (3, 16, 12, 12, 32, 5, 1, 2),
+               (2, 16, 9, 7, 48, 3, 1, 1), (1, 16, 28, 28, 16, 5, 1, 0), (70, 16, 32, 32, 64, 3, 1, 1), (2, 64, 8, 8, 64, 3, 1, 1)]
+
+
+@pytest.mark.parametrize("cfg", STEM_SHAPES)
+@pytest.mark.parametrize("mag", [127, 3, 1])
+def test_conv_fwd_fused_vs_oracle(nb, run, oracle, cfg, mag):
+    """the one-launch forward op (stem kernel: recompute + grid barrier; other shapes: phase 1 + rescale) against the
+    oracle's NITI_Conv_Int8 (+ ReLU), over magnitudes that hit all three branches of the shift rule; the (70, ...) case
+    gives every CTA several tiles per pass, the last shape takes the generic two-phase route"""
+    n, c, h, w, oc, k, st, p = cfg
+    s = shape(n, c, h, w, oc, k, stride=st, pad=p)
+    rng = np.random.default_rng(hash(cfg) % (2 ** 31) + mag)
+    x = _rand(rng, (n, c, h, w), -mag, mag); wt = _rand(rng, (oc, c, k, k), -mag, mag)
+    if mag == 1:
+        x[:, 1:] = 0; wt[:, 1:] = 0; wt[:, :, 1:, :] = 0; wt[:, :, :, 1:] = 0      # max|acc| <= 1: the raw-cast branch
+    for relu in (False, True):
+        y, e, mx = run.conv_fwd_fused(s, x, wt, -3, -9, relu)
+        oy, oe, oacc = oracle.conv_fwd(s, x, wt, -3, -9)
+        if relu:
+            oy = oracle.relu(oy)
+        assert mx == int(np.abs(oacc.astype(np.int64)).max())
+        assert e == oe
+        assert np.array_equal(y, oy)
+    if c == 16:
+        assert nb.last_path == "stem"
+
+
 def test_matmul_nt(nb, run, oracle):
     rng = np.random.default_rng(5)
     for (e, h, l) in [(64, 500, 832), (25, 52, 4096), (7, 12, 33)]:
