@@ -330,7 +330,7 @@ def main():
         peak_tops = nb.probe_i8_peak(4000); peak_src = "measured live: tcgen05.mma.kind::i8 128x256x32 issue-rate probe (niti_probe_i8_peak), all SMs"
     except Exception as ex:          # pragma: no cover
         peak_src = f"probe failed: {ex}"
-    is_tc = lambda k: k.split(":")[1] in ("tc", "tma", "tma2")               # all three families are tcgen05 kernels
+    is_tc = lambda k: k.split(":")[1] in ("tc", "tma", "tma2", "fused", "stem")     # all of these are tcgen05 kernels
     tc_ops = sum(v[0] for k, v in fam.items() if is_tc(k))
     tc_s = sum(v[1] for k, v in fam.items() if is_tc(k))
     tc_n = sum(v[2] for k, v in fam.items() if is_tc(k))
@@ -343,7 +343,7 @@ def main():
             traffic = json.load(open(tpath)).get(args.workload)
         except Exception:
             traffic = None
-    roofline = {"bound": "tensor", "kernel": "igemm_tma2_kernel / igemm_tma_kernel (TMA im2col + tcgen05 kind::i8 implicit GEMM; fwd, dX, dW) incl. split-K clear + max|acc|",
+    roofline = {"bound": "tensor", "kernel": "igemm_fused_kernel / dw2_kernel / stem_fwd_kernel (TMA im2col + tcgen05 kind::i8 implicit GEMM). fwd and dX launches are whole ops: contraction + max|acc| + grid barrier + rescale to int8 in the timed launch; dW includes its split-K clear",
                 "achieved": achieved, "peak": peak_tops, "unit": "TOP/s",
                 "frac": (achieved / peak_tops) if peak_tops else None, "traffic": traffic,
                 "peak_source": peak_src, "launches_timed": tc_n,

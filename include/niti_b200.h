@@ -158,6 +158,13 @@ int niti_conv_fwd(niti_ctx*, const niti_conv_desc*, const int8_t* x, const int8_
 int niti_conv_fwd_fused(niti_ctx*, const niti_conv_desc*, const int8_t* x, const int8_t* w, const int8_t* ex,
                         const int8_t* ew, int8_t* y, int8_t* ey, int relu, int32_t* acc, uint32_t* maxabs, int dp_slot,
                         niti_stream);
+/* The dX op of NITI_DeConv_Int8::onExecute (+ the NITI_CPUReluGrad_Int8 that follows when gate != NULL: dx = gate > 0 ? dx : 0)
+ * behind one call, data-parallel aware.  When every output tile fits in tensor memory at once (csrc/conv_tma2.cu,
+ * igemm_fused_kernel; also used by niti_conv_fwd_fused) the accumulators never leave the SM: contraction, max|acc|, grid
+ * barrier (+ peer exchange), rescale and the int8 store are ONE launch.  Otherwise phase 1 + niti_rescale_act_dp on `acc`
+ * (caller scratch of n*h*w*c words or NULL).  wt: transposed weights as in niti_conv_dx_acc_wt (NULL: per-call transpose). */
+int niti_conv_dx_fused(niti_ctx*, const niti_conv_desc*, const int8_t* dy, const int8_t* w, const int8_t* wt, int8_t* dx,
+                       const int8_t* gate, int32_t* acc, uint32_t* maxabs, int dp_slot, niti_stream);
 int niti_conv_dx(niti_ctx*, const niti_conv_desc*, const int8_t* dy, const int8_t* w, int8_t* dx, niti_stream);
 int niti_conv_dw(niti_ctx*, const niti_conv_desc*, const int8_t* x, const int8_t* dy, int8_t* dw, niti_stream);
 int niti_matmul_nt(niti_ctx*, int e, int h, int l, const int8_t* a, const int8_t* b, int8_t* c, niti_stream);
@@ -203,6 +210,10 @@ int niti_conv_fwd_host(niti_ctx*, const niti_conv_desc*, const int8_t* x_nhwc, c
                        int8_t ex, int8_t ew, int8_t* y_nhwc, int8_t* ey);
 
 /* ---- probes ------------------------------------------------------------------------------- */
+/* phase trace for kernel development: when device_buf != NULL the fused kernels write %globaltimer (ns) stamps to
+ * device_buf[block * 8 + phase] (phases: 0 entry, 1 set-up done, 2 first tile accumulated, 3 max pass done, 4 grid barrier
+ * passed, 5 rescale + store done, 6 exit); device_buf must hold 8 words per CTA of the largest grid.  NULL disables. */
+int niti_debug_trace(niti_ctx*, unsigned long long* device_buf);
 /* dense tcgen05 kind::i8 issue-rate probe (no global traffic): returns achieved TOPS */
 int niti_probe_i8_peak(niti_ctx*, int iters, double* tops_out);
 

@@ -38,6 +38,13 @@ bool stem_fwd_eligible(const niti_conv_desc*);
 int stem_conv_fwd_fused(niti_ctx*, const niti_conv_desc*, const int8_t*, const int8_t*, const int8_t*, const int8_t*, int8_t*,
                         int8_t*, int, uint32_t*, int, cudaStream_t);
 
+// conv_tma2.cu, single-phase fused ops (accumulators stay in TMEM across the exponent barrier)
+bool fused_fwd_eligible(const niti_ctx*, const niti_conv_desc*);
+bool fused_dx_eligible(const niti_ctx*, const niti_conv_desc*);
+int fused_conv_fwd(niti_ctx*, const niti_conv_desc*, const int8_t*, const int8_t*, const int8_t*, const int8_t*, int8_t*, int8_t*,
+                   int, uint32_t*, int, cudaStream_t);
+int fused_conv_dx(niti_ctx*, const niti_conv_desc*, const int8_t*, const int8_t*, int8_t*, const int8_t*, uint32_t*, int, cudaStream_t);
+
 // kernel family selection: TMA-fed tcgen05 > cp.async-fed tcgen05 > SIMT, subject to shape eligibility
 // and the context's forced path.  Returns 0 simt, 1 tc (cp.async), 2 tma, 3 tma2 (CTA pair), -1 unsupported under the
 // forced path.
@@ -243,11 +250,30 @@ int niti_conv_fwd_fused(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x,
         ctx->last_path = "stem";
         return stem_conv_fwd_fused(ctx, d, x, w, ex, ew, y, ey, relu, maxabs, dp_slot, (cudaStream_t)st);
     }
+    if ((ctx->path == NITI_PATH_AUTO || ctx->path == NITI_PATH_TMA2) && ctx->auto_tma2 && fused_fwd_eligible(ctx, d)) {
+        ctx->last_path = "fused";
+        return fused_conv_fwd(ctx, d, x, w, ex, ew, y, ey, relu, maxabs, dp_slot, (cudaStream_t)st);
+    }
     const size_t n = (size_t)d->n * conv_out_h(d) * conv_out_w(d) * d->oc;
     int rc;
     if (!acc && (rc = niti_ws_acc(ctx, n * 4, &acc))) return rc;
     if ((rc = niti_conv_fwd_acc(ctx, d, x, w, acc, maxabs, st))) return rc;
     return niti_rescale_act_dp(ctx, acc, n, maxabs, y, ex, ew, ey, relu, nullptr, dp_slot, st);
+}
+
+int niti_conv_dx_fused(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* dy, const int8_t* w, const int8_t* wt, int8_t* dx,
+                       const int8_t* gate, int32_t* acc, uint32_t* maxabs, int dp_slot, niti_stream st) {
+    if (!ctx || !desc_ok(d) || !dy || !w || !dx || !maxabs) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_dx_fused: bad argument");
+    if (dp_slot < 0 || dp_slot >= kDpSlots) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_dx_fused: slot out of range");
+    if (wt && (ctx->path == NITI_PATH_AUTO || ctx->path == NITI_PATH_TMA2) && ctx->auto_tma2 && fused_dx_eligible(ctx, d)) {
+        ctx->last_path = "fused";
+        return fused_conv_dx(ctx, d, dy, wt, dx, gate, maxabs, dp_slot, (cudaStream_t)st);
+    }
+    const size_t n = (size_t)d->n * d->h * d->w * d->c;
+    int rc;
+    if (!acc && (rc = niti_ws_acc(ctx, n * 4, &acc))) return rc;
+    if ((rc = niti_conv_dx_acc_wt(ctx, d, dy, w, wt, acc, maxabs, st))) return rc;
+    return niti_rescale_act_dp(ctx, acc, n, maxabs, dx, nullptr, nullptr, nullptr, 0, gate, dp_slot, st);
 }
 
 int niti_conv_dx(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* dy, const int8_t* w, int8_t* dx, niti_stream st) {
@@ -330,6 +356,12 @@ int niti_stream_sync(niti_ctx* ctx, niti_stream st) {
     if (!ctx) return NITI_ERR_ARG;
     cudaError_t e = cudaStreamSynchronize((cudaStream_t)st);
     return e == cudaSuccess ? NITI_OK : niti_fail(ctx, NITI_ERR_CUDA, "niti_stream_sync", e);
+}
+
+int niti_debug_trace(niti_ctx* ctx, unsigned long long* device_buf) {
+    if (!ctx) return NITI_ERR_ARG;
+    ctx->trace = device_buf;
+    return NITI_OK;
 }
 
 int niti_probe_i8_peak(niti_ctx* ctx, int iters, double* tops_out) {

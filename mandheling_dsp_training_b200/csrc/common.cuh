@@ -24,7 +24,17 @@ struct niti_ctx {
     // data-parallel scalar exchange over peer memory (dp.cuh); world <= 1 when not connected
     DpBuffer* dp_buf;
     DpView dp;
+    // optional phase trace (niti_debug_trace): kernels that support it write %globaltimer stamps [block][8] here
+    unsigned long long* trace;
 };
+
+__device__ __forceinline__ void niti_trace(unsigned long long* trace, int slot) {
+    if (trace != nullptr) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        trace[(size_t)blockIdx.x * 8 + slot] = t;
+    }
+}
 
 int  niti_fail(niti_ctx* ctx, int code, const char* what, cudaError_t e = cudaSuccess);
 int  niti_check_launch(niti_ctx* ctx, const char* what);

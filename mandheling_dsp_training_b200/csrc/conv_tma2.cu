@@ -459,3 +459,336 @@ int tma2_conv_dx_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* dy, c
     const int ktotal = d->kh * d->kw * d->oc;
     return bkc == 128 ? run2<128>(ctx, ma, wt, acc, p, ktotal, st) : run2<64>(ctx, ma, wt, acc, p, ktotal, st);
 }
+
+// =====================================================================================================================
+// Single-phase fused op: contraction -> max|acc| -> shared exponent -> PSTO -> (ReLU | ReLU-grad gate) -> int8, ONE launch.
+//
+// The two-phase path writes every int32 accumulator to HBM/L2 and reads it back in a second kernel only because the
+// exponent needs max|acc| of the whole tensor first.  When all output tiles of the op fit in tensor memory at once
+// (512 columns x 128 lanes x 148 SMs = 9.7 M accumulators: every VGG-11 b256 layer but the stem) they can simply STAY
+// there: each CTA pair keeps its <= 512/BN tiles resident, the epilogue warps take the maximum straight from TMEM, one
+// grid barrier (plus the NVLink peer exchange when data-parallel, dp.cuh) publishes it, and the same warps rescale
+// TMEM -> int8 -> global.  No int32 tensor exists, no second launch, 1/4 of the store bytes.
+// 16 epilogue warps: the rescale arithmetic needs the issue slots of the whole SM (see conv_stem.cu).
+// =====================================================================================================================
+namespace {
+
+constexpr int kFusedThreads = 576;   // warp 0: TMA producer, warp 1: MMA issuer, warps 2-17: epilogue
+constexpr int kFusedMaxTiles = 8;
+
+struct FusedEpi {
+    int8_t* y; const int8_t* gate;
+    const int8_t* exp_a; const int8_t* exp_b; int8_t* exp_out;
+    int relu;
+    uint32_t* sync;                  // {arrival counter, exit counter}
+    DpView dp; int dp_slot;
+    unsigned long long* trace;
+};
+
+template <int BN, int BKC> struct CfgF {
+    static constexpr int A_BYTES = 128 * BKC;
+    static constexpr int B_BYTES = (BN / 2) * BKC;
+    static constexpr int STAGE = A_BYTES + B_BYTES;
+    static constexpr int BUDGET = 232448 - 1024 - 512;
+    static constexpr int STAGES = (BUDGET / STAGE) > 8 ? 8 : (BUDGET / STAGE);
+    static constexpr int SMEM = STAGES * STAGE + 512 + 1024;
+};
+
+__device__ __forceinline__ void tmem_ld_x16(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ uint32_t pack4f(int32_t a, int32_t b, int32_t c, int32_t d) {
+    return (uint32_t)(a & 0xff) | ((uint32_t)(b & 0xff) << 8) | ((uint32_t)(c & 0xff) << 16) | ((uint32_t)(d & 0xff) << 24);
+}
+
+template <int BN, int BKC>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kFusedThreads, 1)
+igemm_fused_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, const Tma2Params p,
+                   const FusedEpi e) {
+    using C = CfgF<BN, BKC>;
+    extern __shared__ uint8_t smem_raw_f[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw_f) + 1023) & ~(uintptr_t)1023);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE);       // used in the leader only
+    uint64_t* empty_bar = full_bar + C::STAGES;                                          // per CTA
+    uint64_t* tfull_bar = empty_bar + C::STAGES;                                         // per CTA, one per resident tile
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tfull_bar + kFusedMaxTiles);
+    uint32_t* bcast = tmem_slot + 1;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t rank = cluster_ctarank();
+    const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+    if (tid == 64) niti_trace(e.trace, 0);
+
+    if (tid == 0) {
+        for (int s = 0; s < C::STAGES; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], 1); }
+        for (int a = 0; a < kFusedMaxTiles; ++a) tc::mbar_init(&tfull_bar[a], 1);
+        tc::fence_barrier_init();
+        prefetch_tmap2(&mapA); prefetch_tmap2(&mapB);
+    }
+    if (warp == 1) tmem_alloc2<512>(tmem_slot);
+    tc::tc_fence_before();
+    cluster_sync_all();
+    tc::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ------------------------------ TMA producer (both CTAs) ------------------------------
+            uint32_t it = 0;
+            for (int item = pair; item < p.items; item += num_pairs) {
+                const int n_t = item % p.n_tiles; const int m_t = item / p.n_tiles;
+                int m0 = m_t * 256 + (int)rank * 128;
+                if (m0 >= p.M) m0 = 0;
+                const int nrow0 = n_t * BN + (int)rank * (BN / 2);
+                const int q = m0 % p.out_w; const int t = m0 / p.out_w;
+                const int pp = t % p.out_h; const int bn = t / p.out_h;
+                const int bw = q * p.stride + p.lower_w, bh = pp * p.stride + p.lower_h;
+                for (int kb = 0; kb < p.num_kb; ++kb, ++it) {
+                    const int s = it % C::STAGES; const uint32_t ph = (it / C::STAGES) & 1u;
+                    tc::mbar_wait(&empty_bar[s], ph ^ 1u);
+                    const uint32_t a_dst = tc::smem_u32(smem + s * C::STAGE);
+                    const uint32_t b_dst = a_dst + C::A_BYTES;
+                    if (rank == 0) mbar_expect_tx(&full_bar[s], 2u * (uint32_t)C::STAGE);
+                    const int tp = kb / p.cchunks, cc = kb - tp * p.cchunks;
+                    int ky = tp / p.kw, kx = tp - ky * p.kw;
+                    if (p.flip) { ky = p.kh - 1 - ky; kx = p.kw - 1 - kx; }
+                    tma2_load_im2col(&mapA, a_dst, &full_bar[s], cc * BKC, bw, bh, bn, (uint16_t)(kx * p.dil), (uint16_t)(ky * p.dil));
+                    tma2_load_2d(&mapB, b_dst, &full_bar[s], kb * BKC, nrow0);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && rank == 0) {
+            // ------------------------------ MMA issuer (leader CTA only) ------------------------------
+            constexpr uint32_t idesc = tc::make_idesc_i8(256, BN, 0, 0);
+            constexpr uint32_t lay = (BKC == 128) ? 2u : 4u;
+            uint32_t it = 0, tile_iter = 0;
+            for (int item = pair; item < p.items; item += num_pairs, ++tile_iter) {
+                const uint32_t d_tmem = tmem_base + tile_iter * BN;          // every tile keeps its own columns
+                for (int kb = 0; kb < p.num_kb; ++kb, ++it) {
+                    const int s = it % C::STAGES; const uint32_t ph = (it / C::STAGES) & 1u;
+                    tc::mbar_wait(&full_bar[s], ph);
+                    tc::tc_fence_after();
+                    const uint32_t a_base = tc::smem_u32(smem + s * C::STAGE);
+                    const uint32_t b_base = a_base + C::A_BYTES;
+#pragma unroll
+                    for (int kk = 0; kk < BKC / 32; ++kk) {
+                        const uint64_t ad = make_desc2(a_base + kk * 32, 16, 8 * BKC, lay);
+                        const uint64_t bd = make_desc2(b_base + kk * 32, 16, 8 * BKC, lay);
+                        umma2_i8(d_tmem, ad, bd, idesc, (uint32_t)((kb != 0) || (kk != 0)));
+                    }
+                    umma2_commit_mc(&empty_bar[s], 3);
+                }
+                umma2_commit_mc(&tfull_bar[tile_iter], 3);
+            }
+        }
+    } else {
+        // ------------------------------ epilogue (warps 2..17, both CTAs) ------------------------------
+        const int quarter = warp & 3;                        // TMEM lane quarter this warp may read
+        const int group = (warp - 2) >> 2;                   // four warps share a quarter: every 4th 16-column chunk each
+        const int etid = tid - 64;
+        int shift = 0, kind = 0;
+        uint32_t mx = 0;
+        if (etid == 0) niti_trace(e.trace, 1);
+        for (int pass = 0; pass < 2; ++pass) {
+            uint32_t tile_iter = 0;
+            for (int item = pair; item < p.items; item += num_pairs, ++tile_iter) {
+                const int n_t = item % p.n_tiles; const int m_t = item / p.n_tiles;
+                const int row0 = m_t * 256 + (int)rank * 128 + quarter * 32;
+                const int row = row0 + lane;
+                const int n0 = n_t * BN;
+                if (pass == 0) { tc::mbar_wait(&tfull_bar[tile_iter], 0); tc::tc_fence_after(); if (etid == 0 && tile_iter == 0) niti_trace(e.trace, 2); }
+                if (row0 >= p.M) continue;                   // warp-uniform
+                const bool row_ok = row < p.M;
+#pragma unroll 1
+                for (int c0 = group * 16; c0 < BN; c0 += 64) {
+                    if (n0 + c0 >= p.Ncols) break;           // warp-uniform (Ncols % 16 == 0)
+                    uint32_t v[16];
+                    tmem_ld_x16(tmem_base + ((uint32_t)(quarter * 32) << 16) + tile_iter * BN + (uint32_t)c0, v);
+                    tc::tmem_ld_wait();
+                    if (pass == 0) {
+                        if (row_ok) {
+#pragma unroll
+                            for (int q = 0; q < 16; ++q) mx = max(mx, niti_abs_u32((int32_t)v[q]));
+                        }
+                    } else if (row_ok) {
+                        uint32_t o[4];
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            int32_t r[4];
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) {
+                                const int32_t x = (int32_t)v[4 * q + k];
+                                r[k] = kind == 0 ? niti_psto_fast(x, shift) : x;      // kind 0 has shift >= 2; kind 1: raw cast (Q3)
+                            }
+                            o[q] = pack4f(r[0], r[1], r[2], r[3]);
+                        }
+                        const size_t off = (size_t)row * p.Ncols + n0 + c0;
+                        if (e.relu) { o[0] = __vmaxs4(o[0], 0u); o[1] = __vmaxs4(o[1], 0u); o[2] = __vmaxs4(o[2], 0u); o[3] = __vmaxs4(o[3], 0u); }
+                        if (e.gate != nullptr) {             // NITI_CPUReluGrad: pass where the forward value was > 0
+                            const uint4 g = *reinterpret_cast<const uint4*>(e.gate + off);
+                            o[0] &= __vcmpgts4(g.x, 0u); o[1] &= __vcmpgts4(g.y, 0u); o[2] &= __vcmpgts4(g.z, 0u); o[3] &= __vcmpgts4(g.w, 0u);
+                        }
+                        *reinterpret_cast<uint4*>(e.y + off) = make_uint4(o[0], o[1], o[2], o[3]);
+                    }
+                }
+            }
+            if (pass == 0) {
+                // ---- global max|acc|: warp max -> atomicMax -> grid barrier -> (data parallel: peer exchange) ----
+                mx = warp_max_u32(mx);
+                if (lane == 0 && mx) atomicMax(p.maxabs, mx);
+                asm volatile("bar.sync 1, 512;" ::: "memory");
+                if (etid == 0) {
+                    niti_trace(e.trace, 3);
+                    grid_barrier(e.sync, gridDim.x);
+                    niti_trace(e.trace, 4);
+                    uint32_t m = __ldcg(p.maxabs);
+                    if (e.dp.world > 1) {
+                        DpBuffer* mine = e.dp.peer[e.dp.rank];
+                        const uint32_t epoch = *reinterpret_cast<volatile uint32_t*>(&mine->epoch);
+                        if (blockIdx.x == 0) {
+                            const unsigned long long w = ((unsigned long long)epoch << 32) | (unsigned long long)m;
+                            for (int r = 0; r < e.dp.world; ++r) {
+                                unsigned long long* dst = &e.dp.peer[r]->word[e.dp_slot][e.dp.rank];
+                                asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(dst), "l"(w) : "memory");
+                            }
+                        }
+                        const long long t0 = clock64();
+                        for (int r = 0; r < e.dp.world; ++r) {
+                            if (r == e.dp.rank) continue;
+                            const unsigned long long* src = &mine->word[e.dp_slot][r];
+                            unsigned long long w;
+                            for (;;) {
+                                asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(w) : "l"(src) : "memory");
+                                if ((uint32_t)(w >> 32) == epoch) break;
+                                if (clock64() - t0 > 4000000000LL) { mine->error = 1u; w = 0; break; }
+                                __nanosleep(100);
+                            }
+                            m = max(m, (uint32_t)w);
+                        }
+                    }
+                    *bcast = m;
+                }
+                asm volatile("bar.sync 1, 512;" ::: "memory");
+                const int b = niti_bitwidth(*bcast);
+                const int s = b - 7;
+                if (s > 1) { shift = s; kind = 0; } else if (s == 1) { shift = 2; kind = 0; } else { shift = 0; kind = 1; }
+                if (blockIdx.x == 0 && etid == 0 && e.exp_out != nullptr)
+                    *e.exp_out = (int8_t)((e.exp_a ? (int)*e.exp_a : 0) + (e.exp_b ? (int)*e.exp_b : 0) + (kind == 1 ? 0 : shift));
+            }
+        }
+        asm volatile("bar.sync 1, 512;" ::: "memory");
+        if (etid == 0) {                                     // last CTA out re-arms the grid barrier for the next launch
+            niti_trace(e.trace, 5);
+            __threadfence();
+            if (atomicAdd(e.sync + 1, 1u) == gridDim.x - 1) { e.sync[0] = 0u; e.sync[1] = 0u; __threadfence(); }
+        }
+    }
+    __syncwarp();
+    tc::tc_fence_before();
+    cluster_sync_all();
+    if (warp == 1) tmem_dealloc2<512>(tmem_base);
+    if (tid == 64) niti_trace(e.trace, 6);
+}
+
+// tile shape + residency plan: the largest BN that still gives >= ~2/3 of the CTA pairs a tile; every pair must be able
+// to keep all its tiles in its 512 TMEM columns
+bool fused_plan(const niti_ctx* ctx, int M, int Ncols, int* bn_out, int* pairs_out, int* items_out) {
+    const int max_pairs = ctx->sm_count / 2;
+    const long m_tiles = (M + 255) / 256;
+    int bn = 64;
+    for (int cand : {256, 128}) {
+        if (Ncols > cand / 2 && m_tiles * ((Ncols + cand - 1) / cand) >= (2 * max_pairs) / 3) { bn = cand; break; }
+    }
+    if (Ncols <= 64) bn = 64; else if (Ncols <= 128 && bn > 128) bn = 128;
+    const long items = m_tiles * ((Ncols + bn - 1) / bn);
+    const int pairs = (int)(items < max_pairs ? items : max_pairs);
+    const long per_pair = (items + pairs - 1) / pairs;
+    if (per_pair * bn > 512 || per_pair > kFusedMaxTiles) return false;
+    *bn_out = bn; *pairs_out = pairs; *items_out = (int)items;
+    return true;
+}
+
+template <int BN, int BKC>
+int launch_fused(niti_ctx* ctx, const CUtensorMap& a, const CUtensorMap& b, const Tma2Params& p, const FusedEpi& e, int pairs,
+                 cudaStream_t st) {
+    using C = CfgF<BN, BKC>;
+    static bool configured = false;
+    if (!configured) {
+        cudaError_t err = cudaFuncSetAttribute(igemm_fused_kernel<BN, BKC>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        if (err != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "cudaFuncSetAttribute(igemm_fused)", err);
+        configured = true;
+    }
+    igemm_fused_kernel<BN, BKC><<<dim3(2 * pairs), kFusedThreads, C::SMEM, st>>>(a, b, p, e);
+    return niti_check_launch(ctx, "igemm_fused");
+}
+
+template <int BKC>
+int run_fused(niti_ctx* ctx, const CUtensorMap& ma, const void* bmat, Tma2Params& p, FusedEpi& e, int ktotal, cudaStream_t st) {
+    int bn, pairs, items;
+    if (!fused_plan(ctx, p.M, p.Ncols, &bn, &pairs, &items)) return niti_fail(ctx, NITI_ERR_UNSUPPORTED, "fused op: tiles do not fit in TMEM");
+    CUtensorMap mb;
+    if (!make_tiled_u8(&mb, bmat, (uint64_t)p.Ncols, (uint64_t)ktotal, (uint32_t)(bn / 2), BKC, BKC))
+        return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncodeTiled(B) failed");
+    p.m_tiles = (p.M + 255) / 256; p.n_tiles = (p.Ncols + bn - 1) / bn;
+    p.splits = 1; p.kb_per_split = p.num_kb; p.items = items;
+    e.sync = ctx->ws_u32 + 52;
+    if (bn == 64) return launch_fused<64, BKC>(ctx, ma, mb, p, e, pairs, st);
+    if (bn == 128) return launch_fused<128, BKC>(ctx, ma, mb, p, e, pairs, st);
+    return launch_fused<256, BKC>(ctx, ma, mb, p, e, pairs, st);
+}
+} // namespace
+
+bool fused_fwd_eligible(const niti_ctx* ctx, const niti_conv_desc* d) {
+    int a, b, c;
+    return tma2_fwd_eligible(d) && d->oc % 16 == 0 && fused_plan(ctx, d->n * conv_out_h(d) * conv_out_w(d), d->oc, &a, &b, &c);
+}
+bool fused_dx_eligible(const niti_ctx* ctx, const niti_conv_desc* d) {
+    int a, b, c;
+    return tma2_dx_eligible(d) && d->c % 16 == 0 && fused_plan(ctx, d->n * d->h * d->w, d->c, &a, &b, &c);
+}
+
+// y = ruleA(conv(x, w)) (+ ReLU), exponent out; maxabs: zeroed slot
+int fused_conv_fwd(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, const int8_t* w, const int8_t* ex, const int8_t* ew,
+                   int8_t* y, int8_t* ey, int relu, uint32_t* maxabs, int dp_slot, cudaStream_t st) {
+    if (!load_driver2()) return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncode* entry points unavailable");
+    const int oh = conv_out_h(d), ow = conv_out_w(d);
+    const int bkc = d->c % 128 == 0 ? 128 : 64;
+    Tma2Params p{};
+    p.maxabs = maxabs; p.M = d->n * oh * ow; p.Ncols = d->oc;
+    p.out_h = oh; p.out_w = ow; p.kh = d->kh; p.kw = d->kw; p.dil = d->dil; p.stride = d->stride;
+    p.lower_h = -d->pad; p.lower_w = -d->pad; p.flip = 0;
+    p.cchunks = d->c / bkc; p.num_kb = d->kh * d->kw * p.cchunks;
+    FusedEpi e{};
+    e.y = y; e.gate = nullptr; e.exp_a = ex; e.exp_b = ew; e.exp_out = ey; e.relu = relu; e.dp = ctx->dp; e.dp_slot = dp_slot; e.trace = ctx->trace;
+    CUtensorMap ma;
+    if (!make_im2col2(&ma, x, d->n, d->h, d->w, d->c, -d->pad, -d->pad, d->pad - (d->kh - 1) * d->dil, d->pad - (d->kw - 1) * d->dil, d->stride, bkc))
+        return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncodeIm2col(x) failed");
+    const int ktotal = d->kh * d->kw * d->c;
+    return bkc == 128 ? run_fused<128>(ctx, ma, w, p, e, ktotal, st) : run_fused<64>(ctx, ma, w, p, e, ktotal, st);
+}
+
+// dx = ruleA(dX(dy, wt)) (+ ReLU-grad gate against `gate`, the forward tensor dx is the gradient of); wt = [c][kh][kw][oc]
+int fused_conv_dx(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* dy, const int8_t* wt, int8_t* dx, const int8_t* gate,
+                  uint32_t* maxabs, int dp_slot, cudaStream_t st) {
+    if (!load_driver2()) return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncode* entry points unavailable");
+    const int oh = conv_out_h(d), ow = conv_out_w(d);
+    const int bkc = d->oc % 128 == 0 ? 128 : 64;
+    const int pph = (d->kh - 1) * d->dil - d->pad, ppw = (d->kw - 1) * d->dil - d->pad;
+    Tma2Params p{};
+    p.maxabs = maxabs; p.M = d->n * d->h * d->w; p.Ncols = d->c;
+    p.out_h = d->h; p.out_w = d->w; p.kh = d->kh; p.kw = d->kw; p.dil = d->dil; p.stride = 1;
+    p.lower_h = -pph; p.lower_w = -ppw; p.flip = 1;
+    p.cchunks = d->oc / bkc; p.num_kb = d->kh * d->kw * p.cchunks;
+    FusedEpi e{};
+    e.y = dx; e.gate = gate; e.relu = 0; e.dp = ctx->dp; e.dp_slot = dp_slot; e.trace = ctx->trace;
+    CUtensorMap ma;
+    if (!make_im2col2(&ma, dy, d->n, oh, ow, d->oc, -pph, -ppw, d->h - oh - pph, d->w - ow - ppw, 1, bkc))
+        return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncodeIm2col(dy) failed");
+    const int ktotal = d->kh * d->kw * d->oc;
+    return bkc == 128 ? run_fused<128>(ctx, ma, wt, p, e, ktotal, st) : run_fused<64>(ctx, ma, wt, p, e, ktotal, st);
+}

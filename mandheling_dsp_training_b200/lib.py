@@ -67,6 +67,7 @@ _SIGS = {
     "niti_sgd_update": (C.c_int, [_P, _P, _P, C.c_size_t, _P]),
     "niti_conv_fwd": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, _P]),
     "niti_conv_fwd_fused": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, C.c_int, _P, _P, C.c_int, _P]),
+    "niti_conv_dx_fused": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, _P, C.c_int, _P]),
     "niti_conv_dx": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P]),
     "niti_conv_dw": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P]),
     "niti_matmul_nt": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P, _P, _P]),
@@ -81,6 +82,7 @@ _SIGS = {
     "niti_nc4hw4_to_nhwc": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
     "niti_nhwc_to_nc4hw4": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
     "niti_conv_fwd_host": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, C.c_int8, C.c_int8, _P, _P]),
+    "niti_debug_trace": (C.c_int, [_P, _P]),
     "niti_probe_i8_peak": (C.c_int, [_P, C.c_int, C.POINTER(C.c_double)]),
 }
 EXPORTED_SYMBOLS = tuple(_SIGS)
@@ -244,6 +246,10 @@ class NitiB200:
         self._ck(self.lib.niti_conv_fwd_fused(self.h, C.byref(d), _ptr(x), _ptr(w), _ptr(ex), _ptr(ew), _ptr(y), _ptr(ey),
                                               int(bool(relu)), _ptr(acc), _ptr(maxabs), int(dp_slot), self._stream(stream)))
 
+    def conv_dx_fused(self, d, dy, w, wt, dx, gate, acc, maxabs, dp_slot=0, stream=None):
+        self._ck(self.lib.niti_conv_dx_fused(self.h, C.byref(d), _ptr(dy), _ptr(w), _ptr(wt), _ptr(dx), _ptr(gate), _ptr(acc),
+                                             _ptr(maxabs), int(dp_slot), self._stream(stream)))
+
     def conv_dx(self, d, dy, w, dx, stream=None):
         self._ck(self.lib.niti_conv_dx(self.h, C.byref(d), _ptr(dy), _ptr(w), _ptr(dx), self._stream(stream)))
 
@@ -292,6 +298,9 @@ class NitiB200:
         self._ck(self.lib.niti_conv_fwd_host(self.h, C.byref(d), x_np.ctypes.data, w_np.ctypes.data, ex, ew,
                                              y_np.ctypes.data, C.addressof(ey)))
         return ey.value
+
+    def debug_trace(self, buf):
+        self._ck(self.lib.niti_debug_trace(self.h, _ptr(buf)))
 
     def probe_i8_peak(self, iters=2000):
         t = C.c_double(0)

@@ -163,6 +163,7 @@ class NitiNet:
         self.dw_acc = torch.zeros(dw_total, **i32)                                   # one bucket: all dW accumulators
         self.maxabs = torch.zeros(4 * len(self.convs) + 4, **i32)                    # one slot per reduction
         self.batched_update = bool(fuse)
+        self.fused_ops = False       # set below: whole-op calls (one launch where the kernels allow)
         nconv = len(self.convs)
         # data parallel: exchange the exponent scalars inside the rescale kernels over NVLink peer memory when the
         # backend offers it (lib.NitiB200.dp_connect); otherwise one all_reduce(MAX) per scalar
@@ -180,6 +181,7 @@ class NitiNet:
                 self._buckets[L.index] = (L.dw_off, hi_end)
                 hi_end, size = L.dw_off, 0
         self._pending = []
+        self.fused_ops = bool(fuse) and hasattr(nb, "conv_fwd_fused") and (self.dist is None or self.peer_max)
         # (acc, w, wt, max-abs slot, oc, taps, c, sub) per layer: the segments of the one-launch weight update
         self._upd_layers = [(self.dw_acc[L.dw_off: L.dw_off + L.n_w], L.w, L.wt,
                              self.maxabs[2 * nconv + L.index: 2 * nconv + L.index + 1],
@@ -250,8 +252,9 @@ class NitiNet:
         for L in self.ops:
             if L.kind == "conv":
                 slot = self.maxabs[L.index: L.index + 1]
-                if self.batched_update and L.d.c == 16 and hasattr(nb, "conv_fwd_fused") and (self.dist is None or self.peer_max):
-                    # stem layer: conv + exponent + rescale (+ ReLU) in one launch (csrc/conv_stem.cu)
+                if self.fused_ops:
+                    # whole op (conv + exponent + rescale + ReLU) behind one call: one launch for stem layers
+                    # (conv_stem.cu) and whenever the output tiles fit in tensor memory (conv_tma2.cu, fused kernel)
                     self._timed("fwd", L.ops, lambda: nb.conv_fwd_fused(L.d, L.x, L.w, L.ex, L.ew, L.y, L.ey, L.relu,
                                                                        self.acc, slot, dp_slot=L.index))
                     continue
@@ -290,6 +293,10 @@ class NitiNet:
                     self._pending.append(self.dist.all_reduce(self.dw_acc[lo:hi], op=self.dist.ReduceOp.SUM, async_op=True))
                 if dx is not None:
                     slot = self.maxabs[nconv + L.index: nconv + L.index + 1]
+                    if self.fused_ops:
+                        self._timed("dx", L.ops, lambda: nb.conv_dx_fused(L.d, dy, L.w, L.wt, dx, L.x if gate else None,
+                                                                          self.acc, slot, dp_slot=nconv + L.index))
+                        continue
                     if L.wt is not None:
                         self._timed("dx", L.ops, lambda: nb.conv_dx_acc_wt(L.d, dy, L.w, L.wt, self.acc, slot))
                     else:

@@ -72,6 +72,16 @@ class Runner:
         torch.cuda.synchronize()
         return nchw(y.cpu().numpy()), int(ey.item()), int(mx.item())
 
+    def conv_dx_fused(self, s, dy, w, gate=None):
+        d = to_desc(s)
+        dx = torch.empty((s.n, s.h, s.w, s.c), dtype=torch.int8, device=self.device)
+        mx = torch.zeros(1, dtype=torch.int32, device=self.device)
+        wd = dev(nhwc(w))
+        wt = wd.permute(3, 1, 2, 0).contiguous()
+        self.nb.conv_dx_fused(d, dev(nhwc(dy)), wd, wt, dx, dev(nhwc(gate)) if gate is not None else None, None, mx)
+        torch.cuda.synchronize()
+        return nchw(dx.cpu().numpy()), int(mx.item())
+
     def conv_dx(self, s, dy, w):
         d = to_desc(s)
         dx = torch.empty((s.n, s.h, s.w, s.c), dtype=torch.int8, device=self.device)

@@ -151,6 +151,36 @@ def test_conv_fwd_fused_vs_oracle(nb, run, oracle, cfg, mag):
         assert nb.last_path == "stem"
 
 
+FUSED_SHAPES = [(4, 64, 8, 8, 128, 3, 1, 1), (2, 128, 6, 6, 256, 3, 1, 1), (3, 128, 7, 5, 192, 3, 1, 1), (1, 256, 4, 4, 512, 3, 1, 1),
+                (64, 64, 16, 16, 128, 3, 1, 1), (256, 512, 1, 1, 512, 1, 1, 0), (40, 64, 16, 16, 64, 3, 1, 1),
+                (2, 64, 12, 12, 128, 5, 1, 2), (2, 128, 9, 9, 64, 3, 2, 1)]
+
+
+@pytest.mark.parametrize("cfg", FUSED_SHAPES)
+def test_fused_single_phase_ops_vs_oracle(nb, run, oracle, cfg):
+    """accumulators resident in TMEM across the exponent barrier (igemm_fused_kernel): forward (+ReLU) and dX (+ReLU-grad
+    gate) against the oracle; BN 64/128/256, several resident tiles per CTA pair, ragged M and N"""
+    n, c, h, w, oc, k, st, p = cfg
+    s = shape(n, c, h, w, oc, k, stride=st, pad=p)
+    rng = np.random.default_rng(hash(cfg) % (2 ** 31))
+    x = _rand(rng, (n, c, h, w)); wt = _rand(rng, (oc, c, k, k), -64, 64)
+    dy = _rand(rng, (n, oc, s.oh, s.ow), -50, 50)
+    for relu in (False, True):
+        y, e, mx = run.conv_fwd_fused(s, x, wt, -3, -9, relu)
+        oy, oe, oacc = oracle.conv_fwd(s, x, wt, -3, -9)
+        assert mx == int(np.abs(oacc.astype(np.int64)).max()) and e == oe
+        assert np.array_equal(y, oracle.relu(oy) if relu else oy)
+    assert nb.last_path == "fused"
+    if st == 1:
+        odx, oacc = oracle.conv_dx(s, dy, wt)
+        dx, mx = run.conv_dx_fused(s, dy, wt)
+        assert mx == int(np.abs(oacc.astype(np.int64)).max())
+        assert np.array_equal(dx, odx)
+        assert nb.last_path == "fused"
+        dxg, _ = run.conv_dx_fused(s, dy, wt, gate=x)
+        assert np.array_equal(dxg, oracle.relu_grad(x, odx))
+
+
 def test_matmul_nt(nb, run, oracle):
     rng = np.random.default_rng(5)
     for (e, h, l) in [(64, 500, 832), (25, 52, 4096), (7, 12, 33)]:

@@ -19,6 +19,9 @@ def main():
     e = torch.full((1,), -7, dtype=torch.int8, device="cuda"); ey = torch.zeros(1, dtype=torch.int8, device="cuda")
     acc = torch.empty(max(y.numel(), x.numel(), wt.numel()), dtype=torch.int32, device="cuda")
     mx = torch.zeros(1, dtype=torch.int32, device="cuda")
+    trace = torch.zeros(148 * 8, dtype=torch.int64, device="cuda")
+    if os.environ.get("TRACE"):
+        nb.debug_trace(trace)
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     for i in range(4):
         mx.zero_()
@@ -33,6 +36,17 @@ def main():
             nb.conv_dw_acc(d, x, dy, acc, None)
         t1.record(); torch.cuda.synchronize()
         print(f"{op} {dims}: {t0.elapsed_time(t1) * 1e3:.1f} us  path={nb.last_path}", flush=True)
+
+    if os.environ.get("TRACE"):
+        t = trace.cpu().numpy().reshape(148, 8)
+        t = t[t[:, 0] > 0]
+        base = t[:, 0].min()
+        names = ["entry", "setup", "tile0 ready", "max pass", "grid barrier", "rescale+store", "exit"]
+        print("phase: min / median / max ns since first CTA entry, over", len(t), "CTAs")
+        for i, nme in enumerate(names):
+            col = t[:, i] - base
+            print(f"  {nme:14s} {col.min():7d} {int(np.median(col)):7d} {col.max():7d}")
+
 
 if __name__ == "__main__":
     main()
