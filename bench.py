@@ -224,6 +224,9 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     if world > 1:
+        # the dW all-reduce runs beside the persistent contraction kernels: keep NCCL to a few CTAs (the library leaves
+        # NITI_B200_DP_RESERVE_SMS = 8 SMs free for it, csrc/dp.cu); measured 2xB200: 0.873 -> 0.802 ms/step
+        os.environ.setdefault("NCCL_MAX_CTAS", "8")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     spec_key, dbatch, desc_text = WORKLOADS[args.workload]
     batch = args.batch or dbatch

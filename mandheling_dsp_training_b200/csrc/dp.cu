@@ -3,6 +3,7 @@
 // (torch.distributed all_gather in step.py, any byte transport elsewhere) — the C ABI only sees 64-byte blobs.
 #include "common.cuh"
 #include <cstring>
+#include <cstdlib>
 
 namespace {
 __global__ void dp_step_begin_kernel(DpBuffer* b) { b->epoch = b->epoch + 1u; }
@@ -39,6 +40,14 @@ extern "C" int niti_dp_connect(niti_ctx* ctx, int rank, int world, const unsigne
         v.peer[r] = reinterpret_cast<DpBuffer*>(p);
     }
     ctx->dp = v;
+    // leave a few SMs to the NCCL kernels of the dW all-reduce that runs concurrently with backward: the persistent
+    // contraction kernels otherwise occupy every SM (1 CTA/SM, ~200 KB smem) and the collective cannot start until one exits
+    if (world > 1) {
+        const char* env = getenv("NITI_B200_DP_RESERVE_SMS");
+        const int reserve = env ? atoi(env) : 8;
+        if (reserve >= 0 && reserve < ctx->sm_count / 2) ctx->sm_count -= reserve;
+        ctx->sm_count &= ~1;                              // CTA pairs
+    }
     return NITI_OK;
 }
 
