@@ -33,7 +33,7 @@ WORKLOADS = {
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--workload", default="vgg11", choices=sorted(WORKLOADS))
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default: the workload's)")
@@ -161,6 +161,7 @@ class ClockSampler(threading.Thread):
         super().__init__(daemon=True)
         self.index, self.samples, self.stop_flag = index, [], False
         self.ok = False
+        self.active = False            # set by the main thread around the timed regions
         try:
             import pynvml
             pynvml.nvmlInit()
@@ -182,16 +183,15 @@ class ClockSampler(threading.Thread):
                     reasons = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
                 except Exception:
                     reasons = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
-                util = nv.nvmlDeviceGetUtilizationRates(self.h).gpu
-                self.samples.append((mhz, reasons, util))
+                self.samples.append((mhz, reasons, self.active))
             except Exception:
                 pass
-            time.sleep(0.02)
+            time.sleep(0.002)
 
     def summary(self):
         self.stop_flag = True
         nv = getattr(self, "nv", None)
-        busy = [s for s in self.samples if s[2] > 0] or self.samples
+        busy = [s for s in self.samples if s[2]] or self.samples      # samples taken inside the timed regions
         sm = [s[0] for s in busy]
         names = {}
         if nv is not None:
@@ -203,7 +203,7 @@ class ClockSampler(threading.Thread):
                     names[getattr(nv, key)] = label
         reasons = sorted({label for s in busy for bit, label in names.items() if s[1] & bit})
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": self.max_mhz,
-                "reasons": reasons, "samples": len(busy)}
+                "reasons": reasons, "samples": len(busy), "samples_total": len(self.samples)}
 
 
 def main():
@@ -271,11 +271,13 @@ def main():
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     launches0 = nb.launches
     barrier()
+    sampler.active = True
     for i in range(args.steps):
         net.set_input(dx[i % nbuf], -7, dl[i % nbuf])          # device-to-device: inputs already in HBM
         flush.zero_()
         ev[i][0].record(); step_fn(); ev[i][1].record()
     barrier()
+    sampler.active = False
     step_ms = [a.elapsed_time(b) for a, b in ev]
     launches_timed = launches_per_step * args.steps         # graph replays launch the captured kernels
     del launches0
@@ -306,6 +308,7 @@ def main():
     # ---- end to end: pinned host input -> H2D -> step -> D2H logits, every step inside the timed region
     barrier()
     t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
+    sampler.active = True
     t0.record()
     for i in range(args.steps):
         net.set_input(hx[i % nbuf], -7, hl[i % nbuf])
@@ -314,6 +317,7 @@ def main():
         torch.cuda.current_stream().synchronize()              # the caller consumes the result every step
     t1.record()
     barrier()
+    sampler.active = False
     e2e_ms = torch.tensor([t0.elapsed_time(t1)], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
