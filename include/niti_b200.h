@@ -74,6 +74,11 @@ int niti_conv_dx_acc(niti_ctx*, const niti_conv_desc*, const int8_t* dy, const i
                      int32_t* acc /*[n,h,w,c]*/, uint32_t* maxabs, niti_stream);
 int niti_conv_dw_acc(niti_ctx*, const niti_conv_desc*, const int8_t* x, const int8_t* dy,
                      int32_t* acc /*[oc,kh,kw,c]*/, uint32_t* maxabs, niti_stream);
+/* acc += dW into a buffer the caller has zeroed (a training step clears its whole gradient bucket once).  Same
+ * contraction as niti_conv_dw_acc (NITI_GradientConv_Int8.cpp:218-268), but the launch holds no grid-wide barrier, so
+ * it may run on a second stream beside the dX chain of the same layer (both only read dY). */
+int niti_conv_dw_accumulate(niti_ctx*, const niti_conv_desc*, const int8_t* x, const int8_t* dy,
+                            int32_t* acc /*[oc,kh,kw,c]*/, niti_stream);
 /* niti_conv_dx_acc for callers that keep the transposed weights wt = [c][kh][kw][oc] resident (the K-major B operand
  * of the tensor-core dX kernels; the reference re-derives it per call: rot180 + transpose, NITI_DeConv_Int8.cpp:179-219).
  * niti_update_batched maintains wt next to w, so a training step launches no transposes.  wt may be NULL (then as

@@ -31,7 +31,8 @@ int tma2_conv_dx_acc(niti_ctx*, const niti_conv_desc*, const int8_t* dy, const i
 
 // conv_dw2.cu: persistent, tap-grouped, TMA reduce-add generation of the dW kernel
 bool dw2_eligible(const niti_conv_desc*);
-int dw2_conv_dw_acc(niti_ctx*, const niti_conv_desc*, const int8_t*, const int8_t*, int32_t*, uint32_t*, cudaStream_t);
+int dw2_conv_dw_acc(niti_ctx*, const niti_conv_desc*, const int8_t*, const int8_t*, int32_t*, uint32_t*, cudaStream_t,
+                    int accumulate = 0);
 
 // conv_stem.cu: single-launch forward op (conv + exponent + rescale) of <= 16-channel stem layers
 bool stem_fwd_eligible(const niti_conv_desc*);
@@ -220,6 +221,14 @@ int niti_conv_dw_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, co
     if (path == 2) return tma_conv_dw_acc(ctx, d, x, dy, acc, maxabs, (cudaStream_t)st);
     if (path == 1) return tc_conv_dw_acc(ctx, d, x, dy, acc, maxabs, (cudaStream_t)st);
     return simt_conv_dw_acc(ctx, d, x, dy, acc, maxabs, (cudaStream_t)st);
+}
+
+int niti_conv_dw_accumulate(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, const int8_t* dy, int32_t* acc,
+                            niti_stream st) {
+    if (!ctx || !desc_ok(d) || !x || !dy || !acc) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_dw_accumulate: bad argument");
+    const int path = pick_path(ctx, tma_dw_eligible(d), tc_dw_eligible(d), dw2_eligible(d));
+    if (path == 3) { ctx->last_path = path_name(path); return dw2_conv_dw_acc(ctx, d, x, dy, acc, nullptr, (cudaStream_t)st, 1); }
+    return niti_conv_dw_acc(ctx, d, x, dy, acc, nullptr, st);     // these kernels overwrite acc and hold no grid barrier
 }
 
 // C[e,h] = sum_l A[e,l] B[h,l]  ==  1x1 convolution with e "pixels", l channels, h outputs

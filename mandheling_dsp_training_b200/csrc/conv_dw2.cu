@@ -23,6 +23,7 @@ struct Dw2Params {
     int oc_tiles, c_tiles, ngroups;   // tap groups (G consecutive taps in row-major tap order)
     int items;
     int rows_mode;                    // BKC == 16 only: X tiles loaded row-wise (tmax::make_rows16)
+    int accumulate;                   // acc += dW into a caller-zeroed buffer: no in-kernel clear, no grid barrier
     int32_t* acc; size_t nout;
     uint32_t* sync;                   // {arrival counter, exit counter}
 };
@@ -159,7 +160,7 @@ dw2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
         uint8_t* my_epi = epi + (warp - 2) * 8192;
         const int etid = tid - 64;
         uint32_t tile_iter = 0, nstore = 0;
-        if (p.splits > 1) {
+        if (p.splits > 1 && !p.accumulate) {
             const size_t n16 = p.nout >> 2;
             int4* z = reinterpret_cast<int4*>(p.acc);
             for (size_t i = (size_t)blockIdx.x * 128 + etid; i < n16; i += (size_t)gridDim.x * 128) z[i] = make_int4(0, 0, 0, 0);
@@ -198,7 +199,7 @@ dw2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
                         tc::fence_proxy_async_smem();
                         __syncwarp();
                         if (lane == 0) {
-                            if (p.splits == 1) tmax::store_2d(&mapD, tc::smem_u32(buf), colbase + c0, row0);
+                            if (p.splits == 1 && !p.accumulate) tmax::store_2d(&mapD, tc::smem_u32(buf), colbase + c0, row0);
                             else tmax::reduce_add_2d(&mapD, tc::smem_u32(buf), colbase + c0, row0);
                             tmax::bulk_commit();
                         }
@@ -211,7 +212,7 @@ dw2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
             if (lane == 0) tc::mbar_arrive(tempty_bar);
         }
         if (lane == 0) tmax::bulk_wait<0>();
-        if (p.splits > 1) {
+        if (p.splits > 1 && !p.accumulate) {
             asm volatile("bar.sync 1, 128;" ::: "memory");
             if (etid == 0) {                                     // last CTA out re-arms the barrier for the next launch
                 __threadfence();
@@ -252,7 +253,7 @@ bool dw2_eligible(const niti_conv_desc* d) {
 }
 
 int dw2_conv_dw_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, const int8_t* dy, int32_t* acc,
-                    uint32_t* maxabs, cudaStream_t st) {
+                    uint32_t* maxabs, cudaStream_t st, int accumulate) {
     if (!tmax::driver_ok()) return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncode* entry points unavailable");
     const int oh = conv_out_h(d), ow = conv_out_w(d);
     const int bkc = d->c == 16 ? 16 : (d->c % 128 == 0 ? 128 : 64);
@@ -270,6 +271,7 @@ int dw2_conv_dw_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, con
     p.splits = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;
     p.items = (int)(tiles * p.splits);
     p.acc = acc; p.nout = (size_t)d->oc * d->kh * d->kw * d->c; p.sync = ctx->ws_u32 + 44;
+    p.accumulate = accumulate;
     CUtensorMap ma, mb, md;
     if (!tmax::make_tiled_u8(&ma, dy, (uint64_t)p.npix, (uint64_t)d->oc, 128, 128, 128))
         return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncodeTiled(dy) failed");

@@ -50,6 +50,7 @@ _SIGS = {
     "niti_conv_fwd_acc": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P]),
     "niti_conv_dx_acc": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P]),
     "niti_conv_dw_acc": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P]),
+    "niti_conv_dw_accumulate": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P]),
     "niti_conv_dx_acc_wt": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P]),
     "niti_update_batched": (C.c_int, [_P, _P, C.c_int, _P]),
     "niti_matmul_nt_acc": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P, _P, _P, _P]),
@@ -184,6 +185,10 @@ class NitiB200:
 
     def conv_dw_acc(self, d, x, dy, acc, maxabs=None, stream=None):
         self._ck(self.lib.niti_conv_dw_acc(self.h, C.byref(d), _ptr(x), _ptr(dy), _ptr(acc), _ptr(maxabs), self._stream(stream)))
+
+    def conv_dw_accumulate(self, d, x, dy, acc, stream=None):
+        """acc += dW (acc zeroed by the caller); barrier-free launch, safe on a side stream"""
+        self._ck(self.lib.niti_conv_dw_accumulate(self.h, C.byref(d), _ptr(x), _ptr(dy), _ptr(acc), self._stream(stream)))
 
     def matmul_nt_acc(self, e, h, l, a, b, acc, maxabs=None, stream=None):
         self._ck(self.lib.niti_matmul_nt_acc(self.h, e, h, l, _ptr(a), _ptr(b), _ptr(acc), _ptr(maxabs), self._stream(stream)))

@@ -18,6 +18,8 @@ two reductions that span the batch are all-reduced between phase 1 and phase 2 o
   * the int32 dW accumulators              -> all_reduce(SUM), one bucket for the whole net
 Integer sums and maxima are order-independent, so g devices reproduce the 1-device result exactly.
 """
+import contextlib
+
 import numpy as np
 import torch
 
@@ -187,6 +189,11 @@ class NitiNet:
                              self.maxabs[2 * nconv + L.index: 2 * nconv + L.index + 1],
                              L.d.oc, L.d.kh * L.d.kw, L.d.c, 2) for L in self.convs]
         self._upd_segs = nb.make_update_segs(self._upd_layers) if self.batched_update else None
+        # dW beside dX: both only read dY, and the dX chain is the critical path of backward, so dW (and, data parallel,
+        # the bucket all-reduces behind it) is enqueued on a second stream.  Needs the barrier-free accumulate entry
+        # point (niti_conv_dw_accumulate) and the gradient bucket cleared once per step (done beside forward).
+        self.overlap_dw = bool(fuse) and hasattr(nb, "conv_dw_accumulate") and self.dev.type == "cuda"
+        self.side = torch.cuda.Stream(self.dev) if self.overlap_dw else None
 
     # ---- parameters -------------------------------------------------------------------------------
     def init_weights(self, seed=1):
@@ -226,6 +233,14 @@ class NitiNet:
         else:
             fn()
 
+    def _beside(self):
+        """context that enqueues on the side stream once everything already on the current stream is done; the
+        per-kernel timing pass of bench.py (self.timer set) keeps everything on one stream"""
+        if not self.overlap_dw or self.timer is not None:
+            return contextlib.nullcontext()
+        self.side.wait_stream(torch.cuda.current_stream(self.dev))
+        return torch.cuda.stream(self.side)
+
     def _allreduce_max(self, slot):
         if self.dist is not None:
             self.dist.all_reduce(slot, op=self.dist.ReduceOp.MAX)
@@ -249,6 +264,9 @@ class NitiNet:
         nb.zero_u32(self.maxabs, self.maxabs.numel())
         if self.peer_max:
             nb.dp_step_begin()
+        if self.overlap_dw:
+            with self._beside():
+                self.dw_acc.zero_()
         for L in self.ops:
             if L.kind == "conv":
                 slot = self.maxabs[L.index: L.index + 1]
@@ -287,10 +305,14 @@ class NitiNet:
             gate = prev is not None and prev.relu            # input came through a folded ReLU
             if L.kind == "conv":
                 acc_dw = self.dw_acc[L.dw_off: L.dw_off + L.n_w]
-                self._timed("dw", L.ops, lambda: nb.conv_dw_acc(L.d, L.x, dy, acc_dw, None))
-                if self.dist is not None and L.index in self._buckets:
-                    lo, hi = self._buckets[L.index]        # this bucket's dW sums are complete: start its exchange
-                    self._pending.append(self.dist.all_reduce(self.dw_acc[lo:hi], op=self.dist.ReduceOp.SUM, async_op=True))
+                with self._beside():
+                    if self.overlap_dw:
+                        self._timed("dw", L.ops, lambda: nb.conv_dw_accumulate(L.d, L.x, dy, acc_dw))
+                    else:
+                        self._timed("dw", L.ops, lambda: nb.conv_dw_acc(L.d, L.x, dy, acc_dw, None))
+                    if self.dist is not None and L.index in self._buckets:
+                        lo, hi = self._buckets[L.index]    # this bucket's dW sums are complete: start its exchange
+                        self._pending.append(self.dist.all_reduce(self.dw_acc[lo:hi], op=self.dist.ReduceOp.SUM, async_op=True))
                 if dx is not None:
                     slot = self.maxabs[nconv + L.index: nconv + L.index + 1]
                     if self.fused_ops:
@@ -318,6 +340,8 @@ class NitiNet:
                 if gate:
                     nb.relu_grad(L.x, dx, dx, L.x.numel())
         # gradient exchange (one bucket), then shared exponent + PSTO + int8 SGD, fused per layer
+        if self.overlap_dw:
+            torch.cuda.current_stream(self.dev).wait_stream(self.side)
         for work in self._pending:
             work.wait()
         self._pending = []

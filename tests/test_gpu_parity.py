@@ -127,6 +127,36 @@ STEM_SHAPES = [(4, 16, 32, 32, 64, 3, 1, 1), (2, 16, 36, 36, 64, 7, 2, 3), (3, 1
                (2, 16, 9, 7, 48, 3, 1, 1), (1, 16, 28, 28, 16, 5, 1, 0), (70, 16, 32, 32, 64, 3, 1, 1), (2, 64, 8, 8, 64, 3, 1, 1)]
 
 
+@pytest.mark.parametrize("cfg", [c for c in TC_SHAPES if c[4] % 16 == 0] + [(4, 16, 6, 6, 12, 1, 1, 0)])
+def test_conv_dw_accumulate_adds_into_caller_zeroed_buffer(nb, oracle, cfg):
+    """niti_conv_dw_accumulate (the barrier-free dW launch the step runs beside dX): acc == dW after one call into a
+    zeroed buffer and 2*dW after a second call wherever the tcgen05 kernel ran (it adds); the SIMT kernel, taken for
+    shapes the tcgen05 kernel does not cover, overwrites.  Neighbouring words of the bucket stay untouched."""
+    import torch
+    from tests.gpu_util import dev, nhwc, nchw, to_desc
+    n, c, h, w, oc, k, st, p = cfg
+    dil = 2 if cfg == TC_SHAPES[-1] else 1
+    s = shape(n, c, h, w, oc, k, stride=st, pad=p, dil=dil)
+    rng = np.random.default_rng(hash(cfg) % (2 ** 31))
+    x = _rand(rng, (n, c, h, w)); dy = _rand(rng, (n, oc, s.oh, s.ow), -50, 50)
+    oacc, _ = oracle.conv_dw_acc(s, x, dy)
+    nw = oc * k * k * c
+    bucket = torch.zeros(nw + 128, dtype=torch.int32, device="cuda:0")
+    bucket[:64] = 7; bucket[64 + nw:] = -7
+    acc = bucket[64: 64 + nw]
+    dx_, dy_ = dev(nhwc(x)), dev(nhwc(dy))
+    nb.conv_dw_accumulate(to_desc(s), dx_, dy_, acc)
+    torch.cuda.synchronize()
+    got = nchw(acc.view(oc, k, k, c).cpu().numpy())
+    assert np.array_equal(got, oacc)
+    adds = nb.last_path == "tma2"
+    nb.conv_dw_accumulate(to_desc(s), dx_, dy_, acc)
+    torch.cuda.synchronize()
+    got = nchw(acc.view(oc, k, k, c).cpu().numpy())
+    assert np.array_equal(got, 2 * oacc if adds else oacc)
+    assert bool((bucket[:64] == 7).all()) and bool((bucket[64 + nw:] == -7).all())
+
+
 @pytest.mark.parametrize("cfg", STEM_SHAPES)
 @pytest.mark.parametrize("mag", [127, 3, 1])
 def test_conv_fwd_fused_vs_oracle(nb, run, oracle, cfg, mag):
