@@ -144,6 +144,14 @@ typedef struct {
     int32_t oc, taps, c, sub;
 } niti_update_seg;
 int niti_update_batched(niti_ctx*, const niti_update_seg* segs, int nseg, niti_stream);
+/* Requantisation of the DSP-named op types (OpType_NITI_DSP_*_Int8), which the reference runs as
+ * hexagon_nn graphs: shift = ceiling_log2(max|acc|) - 7, out = sat[-128,127](round-half-up(acc / 2^shift)) / post_div,
+ * exp_out = exp_a + exp_b + shift.  Replaces hexagon_nn/2.10.1/hexagon/ops/src/niti_op_supernode_new.c:4614-4634 +
+ * src/quantize.c:337-400 and the u8 <-> int8 re-bias loops of NITI_DSPConv_Int8.cpp:375-452; post_div = 32 / 16 are the
+ * gradient variants' divisions (NITI_DSPTransposeGradientConv_Int8.cpp:430-434, NITI_DSPMatmulGradientConv_Int8.cpp:548-550).
+ * Parity of this rule is UNPINNED (the DSP path needs a Snapdragon cDSP); see oracle/niti_oracle.c niti_o_rescale_dsp. */
+int niti_rescale_dsp(niti_ctx*, const int32_t* acc, size_t n, const uint32_t* maxabs, int post_div, int8_t* out,
+                     const int8_t* exp_a, const int8_t* exp_b, int8_t* exp_out, niti_stream);
 /* rule B per output-channel slice + post-alignment — NITI_GradientSplitConv_Int8.cpp:318-372 (sub = 3):
  *   acc holds `slices` equal contiguous slices of n_per_slice words; maxabs[s] = max|acc_s| (niti_absmax per slice);
  *   out_s = b_s==0 ? 0 : PSTO(acc_s, b_s-sub), then out_s /= 2^(max_s b - b_s) (C truncation). */

@@ -48,6 +48,9 @@ __global__ void __launch_bounds__(kThreads) absmax_kernel(const int32_t* __restr
 }
 
 // mode 0: rule A (activations).  mode 1: rule B (gradients; `sub`), optional fused SGD.
+// mode 2: the DSP-named op types' requantisation (hexagon_nn/2.10.1/hexagon/ops/src/niti_op_supernode_new.c:4614-4634,
+//         src/quantize.c:337-400): shift = ceiling_log2(max|acc|) - 7, round-half-up arithmetic shift, saturate to
+//         [-128, 127], then the gradient variants' truncating int8 division (`sub` = 1, 16 or 32).
 template <int MODE>
 __global__ void __launch_bounds__(kThreads)
 rescale_kernel(const int32_t* __restrict__ acc, size_t n, const uint32_t* __restrict__ maxabs, int sub,
@@ -60,7 +63,15 @@ rescale_kernel(const int32_t* __restrict__ acc, size_t n, const uint32_t* __rest
     const int b = niti_bitwidth(mglobal);
     int shift;          // PSTO shift; kind: 0 = PSTO, 1 = raw cast, 2 = zeros
     int kind = 0;
-    if (MODE == 0) {
+    if (MODE == 2) {
+        // quantize.h:260-265 ceiling_log2: v < 4 -> v - 1, else 32 - clz(v - 1); negative shifts are undefined in the
+        // reference (1 << shift) and kept at 0 here (oracle/niti_oracle.c niti_o_rescale_dsp)
+        const int cl = mglobal < 4u ? (int)mglobal - 1 : 32 - __clz(mglobal - 1u);
+        shift = cl - 7 < 0 ? 0 : cl - 7;
+        kind = 3;
+        if (exp_out != nullptr && blockIdx.x == 0 && threadIdx.x == 0)
+            *exp_out = (int8_t)((exp_a ? (int)*exp_a : 0) + (exp_b ? (int)*exp_b : 0) + shift);
+    } else if (MODE == 0) {
         const int s = b - 7;
         if (s > 1) shift = s; else if (s == 1) shift = 2; else { shift = 0; kind = 1; }
         if (exp_out != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
@@ -74,6 +85,11 @@ rescale_kernel(const int32_t* __restrict__ acc, size_t n, const uint32_t* __rest
     auto conv = [&](int32_t x) -> int32_t {
         if (kind == 0) return niti_psto(x, shift);
         if (kind == 1) return x;            // raw (int8_t) cast happens in pack / store (quirk Q3)
+        if (kind == 3) {
+            long long q = shift > 0 ? (((long long)x + (1ll << (shift - 1))) >> shift) : (long long)x;
+            int32_t v = q > 127 ? 127 : (q < -128 ? -128 : (int32_t)q);
+            return sub > 1 ? v / sub : v;
+        }
         return 0;
     };
     const size_t ngrp = n / 16;
@@ -249,6 +265,17 @@ extern "C" int niti_rescale_grad(niti_ctx* ctx, const int32_t* acc, size_t n, co
     rescale_kernel<1><<<grid_for(ctx, n / 16 + 1), kThreads, 0, (cudaStream_t)st>>>(
         acc, n, maxabs, sub, dw_out, w_inout, nullptr, nullptr, nullptr, 0, nullptr, DpView{}, 0);
     return niti_check_launch(ctx, "rescale_grad");
+}
+
+extern "C" int niti_rescale_dsp(niti_ctx* ctx, const int32_t* acc, size_t n, const uint32_t* maxabs, int post_div, int8_t* out,
+                                const int8_t* exp_a, const int8_t* exp_b, int8_t* exp_out, niti_stream st) {
+    if (!ctx || !maxabs || (n && (!acc || !out))) return niti_fail(ctx, NITI_ERR_ARG, "niti_rescale_dsp");
+    if (post_div != 1 && post_div != 16 && post_div != 32) return niti_fail(ctx, NITI_ERR_ARG, "niti_rescale_dsp: post_div must be 1, 16 or 32");
+    if (n && (!aligned16(acc) || !aligned16(out)))
+        return niti_fail(ctx, NITI_ERR_ARG, "niti_rescale_dsp: buffers must be 16-byte aligned");
+    rescale_kernel<2><<<grid_for(ctx, n / 16 + 1), kThreads, 0, (cudaStream_t)st>>>(
+        acc, n, maxabs, post_div, out, nullptr, exp_a, exp_b, exp_out, 0, nullptr, DpView{}, 0);
+    return niti_check_launch(ctx, "rescale_dsp");
 }
 
 extern "C" int niti_sgd_update(niti_ctx* ctx, int8_t* w, const int8_t* dw, size_t n, niti_stream st) {

@@ -58,6 +58,7 @@ _SIGS = {
     "niti_absmax": (C.c_int, [_P, _P, C.c_size_t, _P, _P]),
     "niti_rescale_act": (C.c_int, [_P, _P, C.c_size_t, _P, _P, _P, _P, _P, _P]),
     "niti_rescale_grad": (C.c_int, [_P, _P, C.c_size_t, _P, C.c_int, _P, _P, _P]),
+    "niti_rescale_dsp": (C.c_int, [_P, _P, C.c_size_t, _P, C.c_int, _P, _P, _P, _P, _P]),
     "niti_rescale_act_fused": (C.c_int, [_P, _P, C.c_size_t, _P, _P, _P, _P, _P, C.c_int, _P, _P]),
     "niti_rescale_act_dp": (C.c_int, [_P, _P, C.c_size_t, _P, _P, _P, _P, _P, C.c_int, _P, C.c_int, _P]),
     "niti_dp_alloc": (C.c_int, [_P, _P]),
@@ -185,6 +186,11 @@ class NitiB200:
 
     def conv_dw_acc(self, d, x, dy, acc, maxabs=None, stream=None):
         self._ck(self.lib.niti_conv_dw_acc(self.h, C.byref(d), _ptr(x), _ptr(dy), _ptr(acc), _ptr(maxabs), self._stream(stream)))
+
+    def rescale_dsp(self, acc, n, maxabs, out, post_div=1, ex=None, ew=None, ey=None, stream=None):
+        """DSP-named op types' requantisation (round-half-up shift, saturate, optional /16 or /32)"""
+        self._ck(self.lib.niti_rescale_dsp(self.h, _ptr(acc), n, _ptr(maxabs), int(post_div), _ptr(out), _ptr(ex), _ptr(ew),
+                                           _ptr(ey), self._stream(stream)))
 
     def conv_dw_accumulate(self, d, x, dy, acc, stream=None):
         """acc += dW (acc zeroed by the caller); barrier-free launch, safe on a side stream"""

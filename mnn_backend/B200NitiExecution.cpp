@@ -362,6 +362,138 @@ private:
 };
 
 // ------------------------------------------------------------------------------------------------
+// DSP-named op types.  The reference builds a hexagon_nn graph per op and ships it to the cDSP
+// over FastRPC; operands are NHWC and weights [KH,KW,C,OC] (tools/train/source/nn/NN.cpp:1155-1157), the int8 values are
+// re-biased to uint8 around the supernode and its int32 accumulators are requantised with round-to-nearest
+// (niti_op_supernode_new.c:4614-4634).  Here the same contractions run on tcgen05 and niti_rescale_dsp applies that rule.
+//   OpType_NITI_DSP_CONV_Int8    NITI_DSPConv_Int8::onExecute    source/backend/cpu/NITI_DSPConv_Int8.cpp:160-455
+//   OpType_NITI_DSP_DECONV_Int8  NITI_DSPDeConv_Int8::onExecute  NITI_DSPDeConv_Int8.cpp:120-402 (a forward convolution of
+//       dY with the rotated, transposed weights the grad rule hands it, grad/NITI_DSPConv_Int8_Grad.cpp:36-124)
+//   {x [N,H,W,C], w [KH,KW,C,OC], int8 exp, int8 exp} -> {y [N,OH,OW,OC], exp = e0 + e1 + shift}
+class B200NitiDspConv : public NitiExecution {
+public:
+    B200NitiDspConv(Backend* bn, const Convolution2DCommon* common) : NitiExecution(bn), mCommon(common) {}
+
+    virtual ErrorCode onResize(const std::vector<Tensor*>& inputs, const std::vector<Tensor*>& outputs) override {
+        auto x = inputs[0], w = inputs[1], y = outputs[0];
+        mPre.clear(); mPost.clear(); mScratch.clear();
+        if (!isInt8(x) || !isInt8(w) || formatOf(x) != MNN_DATA_FORMAT_NHWC || w->dimensions() != 4) return NOT_SUPPORT;
+        auto geo = readGeometry(mCommon, x, y);
+        if (!geo.ok) return NOT_SUPPORT;
+        const int n = x->batch(), c = x->channel(), h = x->height(), wd = x->width();
+        const int oc = y->channel(), oh = y->height(), ow = y->width();
+        if (w->length(0) != geo.kh || w->length(1) != geo.kw || w->length(2) != c || w->length(3) != oc) return NOT_SUPPORT;
+        mDesc = niti_conv_desc{n, c, h, wd, oc, geo.kh, geo.kw, geo.stride, geo.pad, geo.dil};
+        mOutCount = (size_t)n * oh * ow * oc;
+        const int kk = geo.kh * geo.kw;
+        mW = (int8_t*)mScratch.get((size_t)oc * kk * c);
+        mAcc = (int32_t*)mScratch.get(mOutCount * 4);
+        mMax = (uint32_t*)mScratch.get(256);
+        if (mScratch.failed()) return OUT_OF_MEMORY;
+        Gather gw; gw.src = dev(w); gw.dst = mW;              // [taps][c][oc] -> [oc][taps][c]
+        gw.set(0, oc, 1); gw.set(1, kk, (int64_t)c * oc); gw.set(2, c, oc);
+        mPre.emplace_back(gw);
+        mScratch.releaseAll();
+        return NO_ERROR;
+    }
+
+    virtual ErrorCode onExecute(const std::vector<Tensor*>& inputs, const std::vector<Tensor*>& outputs) override {
+        auto& a = bn()->api(); auto ctx = bn()->ctx(); auto st = bn()->stream();
+        auto code = runAll(mPre, "weight gather");
+        if (code != NO_ERROR) return code;
+        int rc = a.zero_u32(ctx, mMax, 1, st);
+        if (rc == NITI_OK) rc = a.conv_fwd_acc(ctx, &mDesc, dev(inputs[0]), mW, mAcc, mMax, st);   // NHWC in place: no copy
+        if (rc != NITI_OK) return check(rc, "niti_conv_fwd_acc");
+        const int8_t* e0 = inputs.size() > 2 ? dev(inputs[2]) : nullptr;
+        const int8_t* e1 = inputs.size() > 3 ? dev(inputs[3]) : nullptr;
+        int8_t* eo = outputs.size() > 1 ? dev(outputs[1]) : nullptr;
+        rc = a.rescale_dsp(ctx, mAcc, mOutCount, mMax, 1, dev(outputs[0]), e0, e1, eo, st);
+        return rc == NITI_OK ? NO_ERROR : check(rc, "niti_rescale_dsp");
+    }
+
+private:
+    const Convolution2DCommon* mCommon;
+    niti_conv_desc mDesc;
+    size_t mOutCount = 0;
+    int8_t* mW = nullptr;
+    int32_t* mAcc = nullptr;
+    uint32_t* mMax = nullptr;
+};
+
+// OpType_NITI_DSP_TRANSPOSEGRADIENT_CONV_Int8 / _PARALLEL_GRADIENTCONV / _GRADIENT_SPLITBatchCONV / _GRADIENTCONV:
+//   {xT [C,H,W,N] (x transposed {3,1,2,0}), dY [N,OH,OW,OC] (zero-inserted for stride-2 layers), exp, exp}
+//   -> {dW laid out [KH,KW,C,OC], exp}     (grad/NITI_DSPConv_Int8_Grad.cpp:126-222)
+// The reference convolves xT with dY transposed to [OH,OW,N,OC] as the filter and transposes the result back
+// (NITI_DSPTransposeGradientConv_Int8.cpp:262-270,324-330); that is the weight gradient niti_conv_dw_acc computes from
+// the natural operands.  The int8 result is divided by 32 (TRANSPOSEGRADIENT, :430-434) or 16 (the other variants,
+// NITI_DSPParallelGradientConv_Int8.cpp:432, NITI_DSPGradientSplitBatchConv_Int8.cpp:583, NITI_DSPGradientConv_Int8.cpp:430).
+// The batch / output-channel splitting of the PARALLEL and SPLITBatch variants exists to fit the cDSP's VTCM and to
+// co-run with the CPU; one B200 launch covers the whole contraction, so they share this execution.
+class B200NitiDspGradientConv : public NitiExecution {
+public:
+    B200NitiDspGradientConv(Backend* bn, const Convolution2DCommon* common, int postDiv, bool transposedX)
+        : NitiExecution(bn), mCommon(common), mPostDiv(postDiv), mTransposedX(transposedX) {}
+
+    virtual ErrorCode onResize(const std::vector<Tensor*>& inputs, const std::vector<Tensor*>& outputs) override {
+        auto xT = inputs[0], dy = inputs[1], dw = outputs[0];
+        mPre.clear(); mPost.clear(); mScratch.clear();
+        if (!isInt8(xT) || !isInt8(dy) || xT->dimensions() != 4 || dy->dimensions() != 4) { MNN_ERROR("[niti_b200] DSP gradient conv: unsupported operands (check %d)\n", 1); return NOT_SUPPORT; }
+        if (mCommon->strideX() != 1 || mCommon->strideY() != 1 || mCommon->dilateX() != 1 || mCommon->dilateY() != 1) { MNN_ERROR("[niti_b200] DSP gradient conv: unsupported operands (check %d)\n", 2); return NOT_SUPPORT; }
+        if (mCommon->padX() != mCommon->padY() || mCommon->padX() < 0 || mCommon->padMode() == PadMode_SAME) { MNN_ERROR("[niti_b200] DSP gradient conv: unsupported operands (check %d)\n", 3); return NOT_SUPPORT; }
+        // TRANSPOSEGRADIENT / SPLITBatch take x transposed {3,1,2,0}; PARALLEL / DSP_GRADIENTCONV take it as it is — the
+        // reference's shape rules say which: output dim 2 = input dim 0 resp. input dim 3
+        // (source/shape/ShapeNITI_Conv_Int8.cpp:220-224 and :312-315, registered at :527-531)
+        const int C = xT->length(mTransposedX ? 0 : 3), H = xT->length(1), W = xT->length(2), N = xT->length(mTransposedX ? 3 : 0);
+        const int OH = dy->length(1), OW = dy->length(2), OC = dy->length(3), pad = mCommon->padX();
+        const int KH = H + 2 * pad - OH + 1, KW = W + 2 * pad - OW + 1;
+        if (dy->length(0) != N || KH < 1 || KW < 1) { MNN_ERROR("[niti_b200] DSP gradient conv: unsupported operands (check %d)\n", 4); return NOT_SUPPORT; }
+        mCount = (size_t)OC * KH * KW * C;
+        if ((size_t)dw->elementSize() != mCount) { MNN_ERROR("[niti_b200] DSP gradient conv: unsupported operands (check %d)\n", 5); return NOT_SUPPORT; }
+        mDesc = niti_conv_desc{N, C, H, W, OC, KH, KW, 1, pad, 1};
+        mX = (int8_t*)mScratch.get((size_t)N * H * W * C);
+        mAcc = (int32_t*)mScratch.get(mCount * 4);
+        mDw = (int8_t*)mScratch.get(mCount);
+        mMax = (uint32_t*)mScratch.get(256);
+        if (mScratch.failed()) return OUT_OF_MEMORY;
+        if (mTransposedX) {
+            Gather gx; gx.src = dev(xT); gx.dst = mX;         // [C][H*W][N] -> [N][H*W][C]
+            gx.set(0, N, 1); gx.set(1, H * W, N); gx.set(2, C, (int64_t)H * W * N);
+            mPre.emplace_back(gx);
+        }
+        Gather go; go.src = mDw; go.dst = dev(dw);            // [OC][taps][C] -> [taps][C][OC]
+        go.set(0, KH * KW, C); go.set(1, C, 1); go.set(2, OC, (int64_t)KH * KW * C);
+        mPost.emplace_back(go);
+        mScratch.releaseAll();
+        return NO_ERROR;
+    }
+
+    virtual ErrorCode onExecute(const std::vector<Tensor*>& inputs, const std::vector<Tensor*>& outputs) override {
+        auto& a = bn()->api(); auto ctx = bn()->ctx(); auto st = bn()->stream();
+        auto code = runAll(mPre, "operand gather");
+        if (code != NO_ERROR) return code;
+        int rc = a.zero_u32(ctx, mMax, 1, st);
+        if (rc == NITI_OK) rc = a.conv_dw_acc(ctx, &mDesc, mTransposedX ? mX : dev(inputs[0]), dev(inputs[1]), mAcc, mMax, st);
+        if (rc != NITI_OK) return check(rc, "niti_conv_dw_acc");
+        const int8_t* e0 = inputs.size() > 2 ? dev(inputs[2]) : nullptr;
+        const int8_t* e1 = inputs.size() > 3 ? dev(inputs[3]) : nullptr;
+        int8_t* eo = outputs.size() > 1 ? dev(outputs[1]) : nullptr;
+        rc = a.rescale_dsp(ctx, mAcc, mCount, mMax, mPostDiv, mDw, e0, e1, eo, st);
+        if (rc != NITI_OK) return check(rc, "niti_rescale_dsp");
+        return runAll(mPost, "result gather");
+    }
+
+private:
+    const Convolution2DCommon* mCommon;
+    int mPostDiv;
+    bool mTransposedX;
+    niti_conv_desc mDesc;
+    size_t mCount = 0;
+    int8_t *mX = nullptr, *mDw = nullptr;
+    int32_t* mAcc = nullptr;
+    uint32_t* mMax = nullptr;
+};
+
+// ------------------------------------------------------------------------------------------------
 class ConvCreator : public B200Backend::Creator {
 public:
     virtual Execution* onCreate(const std::vector<Tensor*>& inputs, const std::vector<Tensor*>& outputs,
@@ -381,6 +513,20 @@ public:
             case OpType_NITI_GradientSplitCONV_Int8:
                 if (inputs.size() < 2) return nullptr;
                 return new B200NitiGradientConv(backend, conv->common(), true);
+            case OpType_NITI_DSP_CONV_Int8:
+            case OpType_NITI_DSP_DECONV_Int8:
+                if (inputs.size() < 2) return nullptr;
+                return new B200NitiDspConv(backend, conv->common());
+            case OpType_NITI_DSP_TRANSPOSEGRADIENT_CONV_Int8:
+                if (inputs.size() < 2) return nullptr;
+                return new B200NitiDspGradientConv(backend, conv->common(), 32, true);
+            case OpType_NITI_DSP_GRADIENT_SPLITBatchCONV_Int8:
+                if (inputs.size() < 2) return nullptr;
+                return new B200NitiDspGradientConv(backend, conv->common(), 16, true);
+            case OpType_NITI_DSP_GRADIENTCONV_Int8:
+            case OpType_NITI_DSP_PARALLEL_GRADIENTCONV_Int8:
+                if (inputs.size() < 2) return nullptr;
+                return new B200NitiDspGradientConv(backend, conv->common(), 16, false);
             default:
                 return nullptr;
         }
@@ -405,6 +551,18 @@ REGISTER_B200_OP_CREATOR(ConvDxCreator, OpType_NITI_DeCONV_Int8);
 REGISTER_B200_OP_CREATOR(ConvDwCreator, OpType_NITI_GradientCONV_Int8);
 REGISTER_B200_OP_CREATOR(ConvDwSplitCreator, OpType_NITI_GradientSplitCONV_Int8);
 REGISTER_B200_OP_CREATOR(MatMulCreator, OpType_NITI_MatMul_Int8);
+typedef ConvCreator DspConvCreator;
+typedef ConvCreator DspDeconvCreator;
+typedef ConvCreator DspDwCreator;
+typedef ConvCreator DspDwTransposeCreator;
+typedef ConvCreator DspDwParallelCreator;
+typedef ConvCreator DspDwSplitBatchCreator;
+REGISTER_B200_OP_CREATOR(DspConvCreator, OpType_NITI_DSP_CONV_Int8);
+REGISTER_B200_OP_CREATOR(DspDeconvCreator, OpType_NITI_DSP_DECONV_Int8);
+REGISTER_B200_OP_CREATOR(DspDwCreator, OpType_NITI_DSP_GRADIENTCONV_Int8);
+REGISTER_B200_OP_CREATOR(DspDwTransposeCreator, OpType_NITI_DSP_TRANSPOSEGRADIENT_CONV_Int8);
+REGISTER_B200_OP_CREATOR(DspDwParallelCreator, OpType_NITI_DSP_PARALLEL_GRADIENTCONV_Int8);
+REGISTER_B200_OP_CREATOR(DspDwSplitBatchCreator, OpType_NITI_DSP_GRADIENT_SPLITBatchCONV_Int8);
 
 } // namespace
 } // namespace B200

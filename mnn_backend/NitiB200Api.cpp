@@ -60,6 +60,7 @@ const NitiB200Api& nitiApi() {
     NITI_BIND(rescale_act, niti_rescale_act)
     NITI_BIND(rescale_grad, niti_rescale_grad)
     NITI_BIND(rescale_grad_split, niti_rescale_grad_split)
+    NITI_BIND(rescale_dsp, niti_rescale_dsp)
     NITI_BIND(sgd_update, niti_sgd_update)
     NITI_BIND(relu, niti_relu)
     NITI_BIND(relu_grad, niti_relu_grad)

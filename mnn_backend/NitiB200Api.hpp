@@ -24,6 +24,7 @@ struct NitiB200Api {
     decltype(&niti_rescale_act)       rescale_act       = nullptr;
     decltype(&niti_rescale_grad)      rescale_grad      = nullptr;
     decltype(&niti_rescale_grad_split) rescale_grad_split = nullptr;
+    decltype(&niti_rescale_dsp)       rescale_dsp       = nullptr;
     decltype(&niti_sgd_update)        sgd_update        = nullptr;
     decltype(&niti_relu)              relu              = nullptr;
     decltype(&niti_relu_grad)         relu_grad         = nullptr;

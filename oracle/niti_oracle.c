@@ -87,6 +87,43 @@ void niti_o_rescale_grad(const int32_t* acc, long n, int sub, int8_t* out) {
     free(tmp);
 }
 
+/* ---- DSP-named op types: requantisation of the Hexagon path.  PARITY UNPINNED: the code
+ * below restates the reference's sources, but the reference's DSP path only runs on a Snapdragon cDSP, so no output of
+ * it could be produced here to check the restatement against.
+ *   hexagon_nn/2.10.1/hexagon/include/quantize.h:260-265          ceiling_log2
+ *   hexagon_nn/2.10.1/hexagon/ops/src/niti_op_supernode_new.c:4614-4634
+ *        m = max|acc|; shift = ceiling_log2(m) - 7; requantize(acc, in_level_size = 1 / (1 << shift), -128, 127)
+ *   hexagon_nn/2.10.1/hexagon/src/quantize.c:337-400              gain < 1: sat_u8(asrrnd(x * 2^(31-shift), 31) + 128)
+ *        = round-half-up of x / 2^shift; gain == 1: sat_u8((int)(x + 128.5))
+ *   execution-engine/source/backend/cpu/NITI_DSPConv_Int8.cpp:447-452     int8 = u8 - 128, exponent += shift
+ *   NITI_DSPTransposeGradientConv_Int8.cpp:430-434 (/32), NITI_DSPMatmulGradientConv_Int8.cpp:548-550 (/16):
+ *        the gradient variants divide the int8 result (C truncation).
+ * shift < 0 (max|acc| <= 64) makes `1 << shift` undefined in the reference; the restatement (and the kernel) keep the
+ * accumulators as they are there (shift 0), which is what a zero shift count gives. */
+int niti_o_dsp_ceiling_log2(uint32_t v) {
+    if (v < 4) return (int)v - 1;
+    return 32 - __builtin_clz(v - 1);
+}
+
+int niti_o_rescale_dsp(const int32_t* acc, long n, int post_div, int8_t* out) {
+    uint32_t m = 0;
+    for (long i = 0; i < n; ++i) {
+        uint32_t a = acc[i] < 0 ? (uint32_t)(-(int64_t)acc[i]) : (uint32_t)acc[i];
+        if (a > m) m = a;
+    }
+    int shift = niti_o_dsp_ceiling_log2(m) - 7;
+    if (shift < 0) shift = 0;
+    for (long i = 0; i < n; ++i) {
+        int64_t q = shift > 0 ? (((int64_t)acc[i] + ((int64_t)1 << (shift - 1))) >> shift) : (int64_t)acc[i];
+        if (q > 127) q = 127;
+        if (q < -128) q = -128;
+        int v = (int)q;
+        if (post_div > 1) v = v / post_div;
+        out[i] = (int8_t)v;
+    }
+    return shift;
+}
+
 #define TRACK(acc_) do { int64_t a_ = (acc_) < 0 ? -(acc_) : (acc_); if (a_ > worst) worst = a_; } while (0)
 
 /* NITI_Conv_Int8.cpp:218-249 (im2col + 16x4 GEMM unit == this direct correlation) */

@@ -54,6 +54,11 @@ int  niti_o_rescale_act(const int32_t* acc, long n, int8_t* out);
 /* rule B (dW): b==0 -> zeros, else PSTO(b - sub) with sub = 2 (GradientConv) or 3 (Matmul). */
 void niti_o_rescale_grad(const int32_t* acc, long n, int sub, int8_t* out);
 
+/* DSP-named op types: round-half-up requantisation of the Hexagon path (niti_op_supernode_new.c:4614-4634,
+ * quantize.c:337-400); returns the shift (exponent increment).  post_div: 1, 16 or 32.  PARITY UNPINNED (no cDSP). */
+int  niti_o_dsp_ceiling_log2(uint32_t v);
+int  niti_o_rescale_dsp(const int32_t* acc, long n, int post_div, int8_t* out);
+
 /* int32 accumulators.  Returns the largest |partial sum| seen (Q1 check: must stay < 2^24 for the
  * reference's float accumulation to be exact). */
 int64_t niti_o_conv_fwd_acc(const niti_conv_shape* s, const int8_t* x, const int8_t* w, int32_t* acc);

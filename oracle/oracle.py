@@ -69,6 +69,10 @@ class Oracle:
         L.niti_o_matmul_nt_acc.argtypes = [C.c_int, C.c_int, C.c_int, _i8p, _i8p, _i32p]
         L.niti_o_rescale_act.restype = C.c_int
         L.niti_o_rescale_act.argtypes = [_i32p, C.c_long, _i8p]
+        L.niti_o_rescale_dsp.restype = C.c_int
+        L.niti_o_rescale_dsp.argtypes = [_i32p, C.c_long, C.c_int, _i8p]
+        L.niti_o_dsp_ceiling_log2.restype = C.c_int
+        L.niti_o_dsp_ceiling_log2.argtypes = [C.c_uint32]
         L.niti_o_rescale_grad.restype = None
         L.niti_o_rescale_grad.argtypes = [_i32p, C.c_long, C.c_int, _i8p]
         L.niti_o_range_estimate.restype = C.c_int
@@ -122,6 +126,13 @@ class Oracle:
         out = np.empty(a.shape, np.int8)
         inc = self.lib.niti_o_rescale_act(a.reshape(-1), a.size, out.reshape(-1))
         return out, inc
+
+    def rescale_dsp(self, acc, post_div=1):
+        """DSP-path requantisation (parity unpinned): returns (int8, shift)"""
+        a = np.ascontiguousarray(acc, dtype=np.int32)
+        out = np.empty(a.shape, dtype=np.int8)
+        shift = self.lib.niti_o_rescale_dsp(a.reshape(-1), a.size, int(post_div), out.reshape(-1))
+        return out, int(shift)
 
     def rescale_grad(self, acc, sub):
         a = _c(acc, np.int32)
@@ -267,6 +278,25 @@ class Reference:
         rc = self.lib.ref_use_backend(int(forward_type), plugin.encode() if plugin else None, threads)
         if rc != 0:
             raise RuntimeError(f"ref_use_backend({forward_type}, {plugin}) failed: {rc}")
+
+    def dsp_op(self, kind, geo, a, b, e0=0, e1=0, out_elems=None):
+        """One DSP-named op type through the reference's express API on the CURRENT backend (ref_driver.cpp ref_dsp_op).
+        kind: 0 DSP_CONV, 1 DSP_DECONV, 2 TRANSPOSEGRADIENT_CONV, 3 PARALLEL_GRADIENTCONV, 4 GRADIENT_SPLITBatchCONV,
+        5 DSP_GRADIENTCONV; geo = (kernelY, kernelX, stride, pad, inputCount, outputCount); a, b: 4-d int8 (NHWC order).
+        Returns (out int8 in the shape the reference's shape rule gives, exponent)."""
+        a = np.ascontiguousarray(a, dtype=np.int8); b = np.ascontiguousarray(b, dtype=np.int8)
+        out = np.zeros(out_elems if out_elems else max(a.size, b.size) * 64, dtype=np.int8)
+        od = (C.c_int * 4)()
+        f = self.lib.ref_dsp_op
+        f.restype = C.c_int
+        f.argtypes = [C.c_int, C.POINTER(C.c_int), _i8p, C.POINTER(C.c_int), _i8p, C.POINTER(C.c_int), C.c_int, C.c_int,
+                      _i8p, C.POINTER(C.c_int)]
+        rc = f(int(kind), (C.c_int * 6)(*[int(v) for v in geo]), a.reshape(-1), (C.c_int * 4)(*a.shape), b.reshape(-1),
+               (C.c_int * 4)(*b.shape), int(e0), int(e1), out, od)
+        if rc <= -1000:
+            raise RuntimeError(f"ref_dsp_op(kind={kind}) failed: {rc}")
+        dims = tuple(od)
+        return out[: int(np.prod(dims))].reshape(dims).copy(), rc
 
     def net_train(self, spec, x_steps, ascale, labels_steps, weights, tclasses=None):
         """spec: step.py layer list; x_steps [steps, n, c, h, w] int8; labels_steps [steps, n];

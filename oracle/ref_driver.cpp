@@ -31,6 +31,7 @@
 #include <chrono>
 #include <memory>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 #include <unistd.h>
@@ -155,6 +156,46 @@ int ref_loss_grad(const int8_t* logits, int ascale, const int* onehot, int b, in
 // `forwardType` the executor's backend.  Returns 0 when the executor really switched (the reference's
 // Executor::setGlobalExecutorConfig silently keeps the old runtime when no creator answers,
 // express/Executor.cpp:81-86, so the switch is verified through the runtime's compiler/forward type).
+// One DSP-named op through the reference's express API: Expr::create with the op type, a
+// Convolution2DCommon and NHWC operands, exactly the form grad/NITI_DSPConv_Int8_Grad.cpp:36-222 and
+// express/NeuralNetWorkOp.cpp:2031-2100 emit.  On the reference CPU backend these executions need the Hexagon FastRPC
+// library (not runnable here); tests/test_gpu_mnn_backend.py runs them on the B200 plug-in only.
+// kind: 0 DSP_CONV, 1 DSP_DECONV, 2 TRANSPOSEGRADIENT_CONV, 3 PARALLEL_GRADIENTCONV, 4 GRADIENT_SPLITBatchCONV, 5 DSP_GRADIENTCONV
+// geo = {kernelY, kernelX, stride, pad, inputCount, outputCount}; returns the exponent output, odims = output dims.
+int ref_dsp_op(int kind, const int* geo, const int8_t* a, const int* adims, const int8_t* b, const int* bdims, int e0, int e1,
+               int8_t* out, int* odims) {
+    static const OpType types[] = {OpType_NITI_DSP_CONV_Int8, OpType_NITI_DSP_DECONV_Int8,
+                                   OpType_NITI_DSP_TRANSPOSEGRADIENT_CONV_Int8, OpType_NITI_DSP_PARALLEL_GRADIENTCONV_Int8,
+                                   OpType_NITI_DSP_GRADIENT_SPLITBatchCONV_Int8, OpType_NITI_DSP_GRADIENTCONV_Int8};
+    if (kind < 0 || kind > 5) return -1000;
+    std::unique_ptr<OpT> op(new OpT);
+    op->type = types[kind];
+    op->main.type = OpParameter_NITI_CONV_Int8;
+    auto conv = new NITI_CONV_Int8T;
+    conv->common.reset(new Convolution2DCommonT);
+    conv->common->kernelY = geo[0]; conv->common->kernelX = geo[1];
+    conv->common->strideX = conv->common->strideY = geo[2];
+    conv->common->padX = conv->common->padY = geo[3];
+    conv->common->padMode = PadMode_CAFFE;
+    conv->common->dilateX = conv->common->dilateY = 1;
+    conv->common->group = 1;
+    conv->common->inputCount = geo[4]; conv->common->outputCount = geo[5];
+    op->main.value = conv;
+    auto av = constI8(a, {adims[0], adims[1], adims[2], adims[3]}, NHWC);
+    auto bv = constI8(b, {bdims[0], bdims[1], bdims[2], bdims[3]}, NHWC);
+    auto expr = Expr::create(std::move(op), {av, bv, _Scalar<int8_t>((int8_t)e0), _Scalar<int8_t>((int8_t)e1)}, 2);
+    auto y = Variable::create(expr, 0), e = Variable::create(expr, 1);
+    auto info = y->getInfo();
+    if (!info || info->dim.size() != 4) return -1001;
+    for (int i = 0; i < 4; ++i) odims[i] = info->dim[i];
+    if (::getenv("REF_DSP_SHAPE_ONLY")) return 0;         // shape inference only (the CPU executions need the Hexagon library)
+    auto ptr = y->readMap<int8_t>();
+    if (!ptr) return -1002;
+    ::memcpy(out, ptr, info->size);
+    auto ep = e->readMap<int8_t>();
+    return ep ? (int)ep[0] : -1003;
+}
+
 int ref_use_backend(int forwardType, const char* plugin, int threads) {
     if (plugin && plugin[0]) {
         void* h = ::dlopen(plugin, RTLD_NOW | RTLD_GLOBAL);

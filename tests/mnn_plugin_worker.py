@@ -13,7 +13,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-from oracle.oracle import Reference, shape          # noqa: E402  (numpy + ctypes only)
+from oracle.oracle import Oracle, Reference, shape          # noqa: E402  (numpy + ctypes only)
 
 PLUGIN = os.path.join(ROOT, "mnn_backend", "libMNN_niti_b200.so")
 MNN_FORWARD_USER_0 = 8          # include/MNN/MNNForwardType.h:38
@@ -60,12 +60,62 @@ def evaluate(ref, tag, out, steps, batch):
         out[f"{tag}_lenet_w{i}"] = w
 
 
+# DSP-named op types: (n, c, h, w, oc, k, pad) stride-1 layers
+DSP_CASES = [(2, 16, 8, 8, 32, 3, 1), (4, 64, 8, 8, 128, 3, 1), (3, 8, 6, 6, 12, 3, 0), (8, 32, 1, 1, 16, 1, 0)]
+
+
+def evaluate_dsp(ref, out):
+    """The DSP-named op types on the B200 plug-in against the oracle's restatement of the DSP arithmetic (the reference's
+    own executions for them need the Hexagon FastRPC library, so there is no CPU leg).  Operands in the forms the
+    reference's grad rule emits (grad/NITI_DSPConv_Int8_Grad.cpp:36-222): NHWC, weights [KH,KW,C,OC], x transposed
+    {3,1,2,0} for the TRANSPOSEGRADIENT / SPLITBatch variants."""
+    orc = Oracle()
+    bad = []
+    for i, (n, c, h, w, oc, k, p) in enumerate(DSP_CASES):
+        s = shape(n, c, h, w, oc, k, stride=1, pad=p)
+        rng = np.random.default_rng(100 + i)
+        x = rng.integers(-127, 128, size=(n, c, h, w), dtype=np.int8)
+        wt = rng.integers(-64, 65, size=(oc, c, k, k), dtype=np.int8)
+        dy = rng.integers(-40, 41, size=(n, oc, s.oh, s.ow), dtype=np.int8)
+        x_nhwc = np.ascontiguousarray(x.transpose(0, 2, 3, 1)); dy_nhwc = np.ascontiguousarray(dy.transpose(0, 2, 3, 1))
+        w_hwio = np.ascontiguousarray(wt.transpose(2, 3, 1, 0))
+        acc, _ = orc.conv_fwd_acc(s, x, wt)
+        want, shift = orc.rescale_dsp(acc, 1)
+        for kind in (0, 1):                                   # DSP_CONV, DSP_DECONV: forward-convolution form
+            y, e = ref.dsp_op(kind, (k, k, 1, p, c, oc), x_nhwc, w_hwio, -5, -9, out_elems=want.size)
+            ok = y.shape == (n, s.oh, s.ow, oc) and np.array_equal(y, want.transpose(0, 2, 3, 1)) and e == -14 + shift
+            out[f"dsp_conv{kind}_{i}"] = np.int32(ok)
+            if not ok:
+                bad.append(("conv", kind, i, y.shape, e, shift))
+        dacc, _ = orc.conv_dw_acc(s, x, dy)                   # [oc, c, kh, kw]
+        xT = np.ascontiguousarray(x_nhwc.transpose(3, 1, 2, 0))
+        for kind, div, xin in ((2, 32, xT), (3, 16, x_nhwc), (4, 16, xT), (5, 16, x_nhwc)):
+            wantw, shiftw = orc.rescale_dsp(dacc, div)
+            dw, e = ref.dsp_op(kind, (s.oh, s.ow, 1, p, n, oc), xin, dy_nhwc, 0, 0, out_elems=wantw.size)
+            ok = dw.shape == (k, k, c, oc) and np.array_equal(dw, wantw.transpose(2, 3, 1, 0)) and e == shiftw
+            out[f"dsp_dw{kind}_{i}"] = np.int32(ok)
+            if not ok:
+                bad.append(("dw", kind, i, dw.shape, e, shiftw))
+    out["n_dsp"] = np.int32(len(DSP_CASES))
+    print("dsp ops: mismatches", bad)
+
+
 def main():
     dst = os.path.abspath(sys.argv[1])          # Reference() changes the cwd (DSP.txt / parallel.txt live there)
     steps = int(sys.argv[2]) if len(sys.argv) > 2 else 3
     batch = int(sys.argv[3]) if len(sys.argv) > 3 else 64
     out = {"n_conv": np.int32(len(CONV_CASES))}
     ref = Reference(threads=4)
+    if len(sys.argv) > 4 and sys.argv[4] == "dsp":          # DSP-named op types only (own process: no CPU leg exists)
+        ref.use_backend(MNN_FORWARD_USER_0, PLUGIN)
+        plug = ctypes.CDLL(PLUGIN)
+        plug.MNNNitiB200LaunchCount.restype = ctypes.c_longlong
+        before = plug.MNNNitiB200LaunchCount()
+        evaluate_dsp(ref, out)
+        out["launches"] = np.int64(plug.MNNNitiB200LaunchCount() - before)
+        np.savez(dst, **out)
+        print("worker ok: dsp launches", int(out["launches"]))
+        return
     evaluate(ref, "cpu", out, steps, batch)
     ref.use_backend(MNN_FORWARD_USER_0, PLUGIN)
     plug = ctypes.CDLL(PLUGIN)

@@ -51,3 +51,27 @@ def test_lenet_training_steps_identical(res):
     weights equal between the reference CPU backend and the B200 backend."""
     for k in ("logits", "e_logits", "loss", "w0", "w1", "w2", "w3"):
         assert np.array_equal(res["cpu_lenet_" + k], res["b200_lenet_" + k]), k
+
+
+@pytest.fixture(scope="module")
+def res_dsp(tmp_path_factory):
+    dst = str(tmp_path_factory.mktemp("mnn_dsp") / "out.npz")
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "mnn_plugin_worker.py"), dst, "0", "0", "dsp"],
+                       capture_output=True, text=True, timeout=600)
+    print(p.stdout[-2000:]); print(p.stderr[-4000:])
+    assert p.returncode == 0, f"worker failed ({p.returncode}):\n{p.stdout[-2000:]}\n{p.stderr[-4000:]}"
+    return np.load(dst)
+
+
+def test_dsp_named_op_types_dispatch_and_match_the_dsp_restatement(res_dsp):
+    res = res_dsp
+    assert int(res["launches"]) >= 3 * 6 * int(res["n_dsp"]), "DSP-named ops did not run on the B200 backend"
+    """SURVEY.md section 8 a11: OpType_NITI_DSP_{CONV, DECONV, TRANSPOSEGRADIENT_CONV, PARALLEL_GRADIENTCONV,
+    GRADIENT_SPLITBatchCONV, GRADIENTCONV}_Int8, created through the reference's express API with the operand forms its
+    grad rule emits, run on the B200 plug-in and equal the oracle's restatement of the Hexagon requantisation
+    (parity of that restatement is unpinned: the DSP path itself needs a Snapdragon cDSP)."""
+    for i in range(int(res["n_dsp"])):
+        for kind in (0, 1):
+            assert int(res[f"dsp_conv{kind}_{i}"]) == 1, (kind, i)
+        for kind in (2, 3, 4, 5):
+            assert int(res[f"dsp_dw{kind}_{i}"]) == 1, (kind, i)

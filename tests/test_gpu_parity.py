@@ -211,6 +211,60 @@ def test_fused_single_phase_ops_vs_oracle(nb, run, oracle, cfg):
         assert np.array_equal(dxg, oracle.relu_grad(x, odx))
 
 
+@pytest.mark.parametrize("mag", [3, 64, 129, 5000, 1 << 15, 1 << 22, (1 << 30) + 12345])
+@pytest.mark.parametrize("div", [1, 16, 32])
+def test_rescale_dsp_vs_oracle(nb, oracle, mag, div):
+    """niti_rescale_dsp (the DSP-named op types' round-half-up requantisation) against the
+    oracle's restatement of niti_op_supernode_new.c:4614-4634 + quantize.c:337-400, ragged length, exponent output"""
+    import torch
+    rng = np.random.default_rng(mag % 1000 + div)
+    n = 16 * 517 + 11
+    a = rng.integers(-mag, mag + 1, size=n).astype(np.int32)
+    a[5] = mag; a[n - 1] = -mag
+    want, shift = oracle.rescale_dsp(a, div)
+    acc = torch.from_numpy(a).cuda()
+    mx = torch.zeros(1, dtype=torch.int32, device="cuda:0")
+    out = torch.zeros(n, dtype=torch.int8, device="cuda:0")
+    ex = torch.tensor([-5], dtype=torch.int8, device="cuda:0"); ew = torch.tensor([-9], dtype=torch.int8, device="cuda:0")
+    ey = torch.zeros(1, dtype=torch.int8, device="cuda:0")
+    nb.absmax(acc, n, mx)
+    nb.rescale_dsp(acc, n, mx, out, div, ex, ew, ey)
+    torch.cuda.synchronize()
+    assert int(mx.item()) == mag
+    assert np.array_equal(out.cpu().numpy(), want)
+    assert int(ey.item()) == -14 + shift
+
+
+@pytest.mark.parametrize("cfg", [(2, 16, 8, 8, 32, 3, 1, 1), (4, 64, 8, 8, 128, 3, 1, 1), (3, 8, 6, 6, 12, 3, 1, 0)])
+def test_dsp_conv_ops_vs_oracle(nb, run, oracle, cfg):
+    """the contractions behind OpType_NITI_DSP_CONV / _DECONV / _*GRADIENT*CONV with the DSP rounding: tcgen05 / SIMT
+    accumulators + niti_rescale_dsp == oracle accumulators + restated DSP requantisation (/32 for TRANSPOSEGRADIENT)"""
+    import torch
+    from tests.gpu_util import dev, nhwc, to_desc
+    n, c, h, w, oc, k, st, p = cfg
+    s = shape(n, c, h, w, oc, k, stride=st, pad=p)
+    rng = np.random.default_rng(hash(cfg) % (2 ** 31))
+    x = _rand(rng, (n, c, h, w)); wt = _rand(rng, (oc, c, k, k), -64, 64)
+    dy = _rand(rng, (n, oc, s.oh, s.ow), -50, 50)
+    for kind, div in (("fwd", 1), ("dw", 32), ("dw", 16)):
+        if kind == "fwd":
+            oacc, _ = oracle.conv_fwd_acc(s, x, wt)
+            acc = torch.empty((n, s.oh, s.ow, oc), dtype=torch.int32, device="cuda:0")
+            mx = torch.zeros(1, dtype=torch.int32, device="cuda:0")
+            nb.conv_fwd_acc(to_desc(s), dev(nhwc(x)), dev(nhwc(wt)), acc, mx)
+            want, _ = oracle.rescale_dsp(nhwc(oacc), div)
+        else:
+            oacc, _ = oracle.conv_dw_acc(s, x, dy)
+            acc = torch.empty((oc, k, k, c), dtype=torch.int32, device="cuda:0")
+            mx = torch.zeros(1, dtype=torch.int32, device="cuda:0")
+            nb.conv_dw_acc(to_desc(s), dev(nhwc(x)), dev(nhwc(dy)), acc, mx)
+            want, _ = oracle.rescale_dsp(nhwc(oacc), div)
+        out = torch.zeros(acc.numel(), dtype=torch.int8, device="cuda:0")
+        nb.rescale_dsp(acc, acc.numel(), mx, out, div)
+        torch.cuda.synchronize()
+        assert np.array_equal(out.cpu().numpy().reshape(want.shape), want), (kind, div)
+
+
 def test_matmul_nt(nb, run, oracle):
     rng = np.random.default_rng(5)
     for (e, h, l) in [(64, 500, 832), (25, 52, 4096), (7, 12, 33)]:

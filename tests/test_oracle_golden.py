@@ -81,3 +81,45 @@ def test_ragged_and_empty(oracle):
     assert oracle.sgd_update(np.zeros((0,), np.int8), np.zeros((0,), np.int8)).size == 0
     out, inc = oracle.rescale_act(np.zeros((0,), np.int32))
     assert out.size == 0 and inc == 0
+
+
+def _dsp_requant_numpy(acc, post_div):
+    """independent restatement of the DSP requantisation (niti_op_supernode_new.c:4614-4634, quantize.c:337-400,
+    NITI_DSPConv_Int8.cpp:447-452) in numpy, for checking oracle/niti_oracle.c niti_o_rescale_dsp"""
+    a = acc.astype(np.int64)
+    m = int(np.abs(a).max()) if a.size else 0
+    cl = m - 1 if m < 4 else int(m - 1).bit_length()          # quantize.h:260-265 ceiling_log2
+    shift = max(cl - 7, 0)
+    q = np.floor_divide(a + (1 << (shift - 1)), 1 << shift) if shift > 0 else a
+    q = np.clip(q, -128, 127)
+    if post_div > 1:
+        q = np.sign(q) * (np.abs(q) // post_div)               # C division truncates toward zero
+    return q.astype(np.int8), shift
+
+
+def test_dsp_requant_known_answers_and_restatement(oracle):
+    """SURVEY.md section 8 a11 — the DSP path's rounding.  No cDSP here, so this rule is pinned only by the reference's
+    source (parity unpinned): hand-worked answers + an independent numpy restatement."""
+    acc = np.array([1000, -1000, 511, -513, 4, -4, 3, 0, 996, -996], dtype=np.int32)
+    out, shift = oracle.rescale_dsp(acc, 1)
+    assert shift == 3                                          # ceiling_log2(1000) = 10
+    assert out.tolist() == [125, -125, 64, -64, 1, 0, 0, 0, 125, -124]      # round half up: 0.5 -> 1, -0.5 -> 0
+    out16, _ = oracle.rescale_dsp(acc, 16)
+    assert out16.tolist() == [7, -7, 4, -4, 0, 0, 0, 0, 7, -7]
+    # powers of two sit on the ceil(log2) boundary: 1024 -> shift 3 -> 128 saturates to 127; -1024 -> -128 survives
+    out, shift = oracle.rescale_dsp(np.array([1024, -1024], dtype=np.int32), 1)
+    assert shift == 3 and out.tolist() == [127, -128]
+    # small accumulators (the reference's `1 << shift` with a negative count is undefined): kept as they are
+    out, shift = oracle.rescale_dsp(np.array([64, -37, 5], dtype=np.int32), 1)
+    assert shift == 0 and out.tolist() == [64, -37, 5]
+    for v, want in [(0, -1), (1, 0), (2, 1), (3, 2), (4, 2), (5, 3), (128, 7), (129, 8), (1 << 20, 20), ((1 << 20) + 1, 21)]:
+        assert oracle.lib.niti_o_dsp_ceiling_log2(v) == want
+    rng = np.random.default_rng(11)
+    for mag in (3, 100, 129, 5000, 1 << 15, 1 << 22, (1 << 30) + 12345):
+        for div in (1, 16, 32):
+            a = rng.integers(-mag, mag + 1, size=1003).astype(np.int32)
+            got, s1 = oracle.rescale_dsp(a, div)
+            want, s2 = _dsp_requant_numpy(a, div)
+            assert s1 == s2 and np.array_equal(got, want), (mag, div)
+    out, shift = oracle.rescale_dsp(np.zeros(0, dtype=np.int32), 1)
+    assert out.size == 0 and shift == 0
