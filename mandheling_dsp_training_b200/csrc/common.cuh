@@ -14,6 +14,7 @@ struct niti_ctx {
     int sm_count;
     int path;                 // NITI_PATH_*
     int auto_tma2;            // AUTO prefers the CTA-pair kernels where eligible
+    int pdl;                  // programmatic dependent launch on the step's kernel chain (NITI_B200_PDL: bit mask of NITI_PDL_* kernel classes, default NITI_PDL_FUSED — measured best)
     int64_t launches;
     const char* last_path;
     char err[256];
@@ -34,6 +35,32 @@ __device__ __forceinline__ void niti_trace(unsigned long long* trace, int slot) 
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
         trace[(size_t)blockIdx.x * 8 + slot] = t;
     }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Programmatic dependent launch.  A training step is a chain of ~45 short launches, each a partial wave; with the
+// attribute below a kernel's CTAs are placed and run their prologue (barrier init, TMEM allocation, tensor-map fetch)
+// while the previous kernel of the stream drains, and block in niti_pdl_wait() until that kernel has completed and its
+// writes are visible.  Contract for every kernel launched through niti_launch(): no global memory access before
+// niti_pdl_wait().  niti_pdl_trigger() lets the NEXT kernel of the stream start being placed.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void niti_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void niti_pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+enum { NITI_PDL_FUSED = 1, NITI_PDL_STEM = 2, NITI_PDL_UPDATE = 4, NITI_PDL_ELEMENTWISE = 8 };
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t niti_launch(const niti_ctx* ctx, int cls, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                               Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; // cls: NITI_PDL_* kernel class bit.  Data parallel (peer exchange connected): off — CTAs placed ahead of time would sit on
+    // the SMs reserved for the concurrent NCCL all-reduce (dp.cu).
+    cfg.numAttrs = (ctx && (ctx->pdl & cls) && ctx->dp.world <= 1) ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
 int  niti_fail(niti_ctx* ctx, int code, const char* what, cudaError_t e = cudaSuccess);

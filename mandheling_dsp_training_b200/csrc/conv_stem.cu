@@ -80,6 +80,8 @@ stem_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
     __syncthreads();
     tc::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    niti_pdl_trigger();
+    niti_pdl_wait();                                         // programmatic dependent launch: see common.cuh
     const int my_tiles = (p.m_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
     if (warp == 0) {
@@ -291,6 +293,7 @@ int stem_conv_fwd_fused(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x,
         configured = smem;
     }
     const int grid = p.m_tiles < ctx->sm_count ? p.m_tiles : ctx->sm_count;
-    stem_fwd_kernel<<<grid, kStemThreads, smem, st>>>(ma, mb, p);
+    cudaError_t lerr = niti_launch(ctx, NITI_PDL_STEM, stem_fwd_kernel, dim3(grid), dim3(kStemThreads), (size_t)smem, st, ma, mb, p);
+    if (lerr != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "launch stem_fwd", lerr);
     return niti_check_launch(ctx, "stem_fwd");
 }

@@ -521,6 +521,7 @@ igemm_fused_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t rank = cluster_ctarank();
     const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+    niti_pdl_trigger();                                      // the next launch of the stream may start placing its CTAs
     if (tid == 64) niti_trace(e.trace, 0);
 
     if (tid == 0) {
@@ -534,6 +535,7 @@ igemm_fused_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
     cluster_sync_all();
     tc::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    niti_pdl_wait();                                         // prologue done; operands of the previous launch are now visible
 
     if (warp == 0) {
         if (lane == 0) {
@@ -717,13 +719,19 @@ template <int BN, int BKC>
 int launch_fused(niti_ctx* ctx, const CUtensorMap& a, const CUtensorMap& b, const Tma2Params& p, const FusedEpi& e, int pairs,
                  cudaStream_t st) {
     using C = CfgF<BN, BKC>;
+    // One CTA per SM, enforced through the shared-memory request: every CTA allocates all 512 TMEM columns and then
+    // waits at a grid barrier, so two CTAs of this launch sharing an SM (possible for the BKC = 64 configurations, < 114 KB,
+    // once programmatic dependent launch places CTAs on partly occupied SMs) would deadlock — the second blocks in
+    // tcgen05.alloc while the first waits for it at the barrier.
+    constexpr size_t kSmemReq = C::SMEM > 120 * 1024 ? (size_t)C::SMEM : (size_t)120 * 1024;
     static bool configured = false;
     if (!configured) {
-        cudaError_t err = cudaFuncSetAttribute(igemm_fused_kernel<BN, BKC>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        cudaError_t err = cudaFuncSetAttribute(igemm_fused_kernel<BN, BKC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemReq);
         if (err != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "cudaFuncSetAttribute(igemm_fused)", err);
         configured = true;
     }
-    igemm_fused_kernel<BN, BKC><<<dim3(2 * pairs), kFusedThreads, C::SMEM, st>>>(a, b, p, e);
+    cudaError_t lerr = niti_launch(ctx, NITI_PDL_FUSED, igemm_fused_kernel<BN, BKC>, dim3(2 * pairs), dim3(kFusedThreads), kSmemReq, st, a, b, p, e);
+    if (lerr != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "launch igemm_fused", lerr);
     return niti_check_launch(ctx, "igemm_fused");
 }
 

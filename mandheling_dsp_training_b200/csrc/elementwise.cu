@@ -125,6 +125,7 @@ __device__ __forceinline__ uint4 vmax4x4(uint4 a, uint4 b) {
 
 __global__ void __launch_bounds__(kThreads) maxpool_vec_kernel(const uint4* __restrict__ x, int n, int h, int w, int c16,
                                                                int k, int s, int oh, int ow, uint4* __restrict__ y) {
+    niti_pdl_trigger(); niti_pdl_wait();                     // programmatic dependent launch: see common.cuh
     const size_t total = (size_t)n * oh * ow * c16;
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
         int cv = (int)(i % c16); size_t p = i / c16;
@@ -147,6 +148,7 @@ __global__ void __launch_bounds__(kThreads) maxpool_vec_kernel(const uint4* __re
 __global__ void __launch_bounds__(kThreads) maxpool_grad_vec_kernel(const uint4* __restrict__ x, const uint4* __restrict__ y,
                                                                     const uint4* __restrict__ dy, int n, int h, int w, int c16,
                                                                     int k, int oh, int ow, uint4* __restrict__ dx, int gate_relu) {
+    niti_pdl_trigger(); niti_pdl_wait();                     // programmatic dependent launch: see common.cuh
     const size_t total = (size_t)n * oh * ow * c16;
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
         int cv = (int)(i % c16); size_t p = i / c16;
@@ -173,6 +175,7 @@ __global__ void __launch_bounds__(kThreads) maxpool_grad_vec_kernel(const uint4*
 // integer softmax cross-entropy gradient; one thread per sample (batch is small, classes ~10)
 __global__ void loss_grad_kernel(const int8_t* __restrict__ logits, const int8_t* __restrict__ ascale_p,
                                  const int32_t* __restrict__ labels, int batch, int classes, int8_t* __restrict__ grad) {
+    niti_pdl_trigger(); niti_pdl_wait();                     // programmatic dependent launch: see common.cuh
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= batch) return;
     const int a = (int)*ascale_p;
@@ -275,8 +278,10 @@ extern "C" int niti_maxpool(niti_ctx* ctx, const int8_t* x, int n, int h, int w,
     if (!ctx || !x || !y || n <= 0 || h < k || w < k || c <= 0 || k <= 0 || s <= 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_maxpool");
     int oh = (h - k) / s + 1, ow = (w - k) / s + 1;
     if (c % 16 == 0 && aligned16(x) && aligned16(y)) {
-        maxpool_vec_kernel<<<grid_for(ctx, (size_t)n * oh * ow * (c / 16)), kThreads, 0, (cudaStream_t)st>>>(
-            reinterpret_cast<const uint4*>(x), n, h, w, c / 16, k, s, oh, ow, reinterpret_cast<uint4*>(y));
+        cudaError_t le = niti_launch(ctx, NITI_PDL_ELEMENTWISE, maxpool_vec_kernel, dim3(grid_for(ctx, (size_t)n * oh * ow * (c / 16))), dim3(kThreads), 0,
+                                     (cudaStream_t)st, reinterpret_cast<const uint4*>(x), n, h, w, c / 16, k, s, oh, ow,
+                                     reinterpret_cast<uint4*>(y));
+        if (le != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "launch maxpool_vec", le);
         return niti_check_launch(ctx, "maxpool_vec");
     }
     maxpool_kernel<<<grid_for(ctx, (size_t)n * oh * ow * c), kThreads, 0, (cudaStream_t)st>>>(x, n, h, w, c, k, s, oh, ow, y);
@@ -292,9 +297,11 @@ extern "C" int niti_maxpool_grad_gated(niti_ctx* ctx, const int8_t* x, const int
             cudaError_t e = cudaMemsetAsync(dx, 0, (size_t)n * h * w * c, (cudaStream_t)st);
             if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "maxpool_grad memset", e);
         }
-        maxpool_grad_vec_kernel<<<grid_for(ctx, (size_t)n * oh * ow * (c / 16)), kThreads, 0, (cudaStream_t)st>>>(
-            reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(y), reinterpret_cast<const uint4*>(dy),
-            n, h, w, c / 16, k, oh, ow, reinterpret_cast<uint4*>(dx), gate_relu);
+        cudaError_t le = niti_launch(ctx, NITI_PDL_ELEMENTWISE, maxpool_grad_vec_kernel, dim3(grid_for(ctx, (size_t)n * oh * ow * (c / 16))), dim3(kThreads), 0,
+                                     (cudaStream_t)st, reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(y),
+                                     reinterpret_cast<const uint4*>(dy), n, h, w, c / 16, k, oh, ow, reinterpret_cast<uint4*>(dx),
+                                     gate_relu);
+        if (le != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "launch maxpool_grad_vec", le);
         return niti_check_launch(ctx, "maxpool_grad_vec");
     }
     maxpool_grad_kernel<<<grid_for(ctx, (size_t)n * h * w * c), kThreads, 0, (cudaStream_t)st>>>(x, y, dy, n, h, w, c, k, s, oh, ow, dx, gate_relu);
@@ -307,7 +314,9 @@ extern "C" int niti_maxpool_grad(niti_ctx* ctx, const int8_t* x, const int8_t* y
 extern "C" int niti_loss_grad(niti_ctx* ctx, const int8_t* logits, const int8_t* ascale, const int32_t* labels,
                               int batch, int classes, int8_t* grad, niti_stream st) {
     if (!ctx || !logits || !ascale || !labels || !grad || batch <= 0 || classes <= 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_loss_grad");
-    loss_grad_kernel<<<(batch + 63) / 64, 64, 0, (cudaStream_t)st>>>(logits, ascale, labels, batch, classes, grad);
+    cudaError_t le = niti_launch(ctx, NITI_PDL_ELEMENTWISE, loss_grad_kernel, dim3((batch + 63) / 64), dim3(64), 0, (cudaStream_t)st, logits, ascale, labels,
+                                 batch, classes, grad);
+    if (le != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "launch loss_grad", le);
     return niti_check_launch(ctx, "loss_grad");
 }
 extern "C" int niti_nchw_to_nhwc(niti_ctx* ctx, const int8_t* src, int n, int c, int h, int w, int8_t* dst, niti_stream st) {

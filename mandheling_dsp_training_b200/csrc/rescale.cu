@@ -193,6 +193,7 @@ rescale_split_kernel(const int32_t* __restrict__ acc, size_t per, int slices, co
 }
 
 __global__ void zero_u32_kernel(uint32_t* p, int count) {
+    niti_pdl_trigger(); niti_pdl_wait();                     // programmatic dependent launch: see common.cuh
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < count) p[i] = 0u;
 }
@@ -211,7 +212,8 @@ bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) ==
 
 extern "C" int niti_zero_u32(niti_ctx* ctx, uint32_t* p, int count, niti_stream st) {
     if (!ctx || !p || count <= 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_zero_u32");
-    zero_u32_kernel<<<(count + 63) / 64, 64, 0, (cudaStream_t)st>>>(p, count);
+    cudaError_t le = niti_launch(ctx, NITI_PDL_ELEMENTWISE, zero_u32_kernel, dim3((count + 63) / 64), dim3(64), 0, (cudaStream_t)st, p, count);
+    if (le != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "launch zero_u32", le);
     return niti_check_launch(ctx, "zero_u32");
 }
 

@@ -55,6 +55,8 @@ update_batched_kernel(const __grid_constant__ UpdSegs S, uint32_t* sync) {
     __shared__ uint32_t red[kUpdThreads / 32];
     __shared__ uint32_t tbuf[kUpdThreads / 32][32 * 9];          // per warp: 32 rows x 36 bytes (padded) transpose tile
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    niti_pdl_trigger();
+    niti_pdl_wait();                                         // programmatic dependent launch: see common.cuh
 
     // ---------------- phase 1: max|acc| per segment ----------------
     const uint32_t nchunks = S.chunk_begin[S.n];
@@ -206,7 +208,8 @@ extern "C" int niti_update_batched(niti_ctx* ctx, const niti_update_seg* segs, i
         }
         S.chunk_begin[S.n] = chunks; S.tile_begin[S.n] = tiles;
         const int grid = ctx->sm_count * blocks_per_sm;            // all CTAs co-resident: the grid barrier needs it
-        update_batched_kernel<<<grid, kUpdThreads, 0, (cudaStream_t)st>>>(S, ctx->ws_u32 + 40);
+        cudaError_t lerr = niti_launch(ctx, NITI_PDL_UPDATE, update_batched_kernel, dim3(grid), dim3(kUpdThreads), 0, (cudaStream_t)st, S, ctx->ws_u32 + 40);
+        if (lerr != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "launch update_batched", lerr);
         int rc = niti_check_launch(ctx, "update_batched");
         if (rc) return rc;
     }
