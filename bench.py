@@ -224,9 +224,11 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: there is no CPU fallback (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     if world > 1:
-        # the dW all-reduce runs beside the persistent contraction kernels: keep NCCL to a few CTAs (the library leaves
-        # NITI_B200_DP_RESERVE_SMS = 8 SMs free for it, csrc/dp.cu); measured 2xB200: 0.873 -> 0.802 ms/step
-        os.environ.setdefault("NCCL_MAX_CTAS", "8")
+        # the dW all-reduce runs beside the contraction kernels: the library leaves NITI_B200_DP_RESERVE_SMS = 16 SMs free
+        # for it (csrc/dp.cu) and NCCL is capped at the same 16 CTAs (never more CTAs than free SMs: 4xB200 with
+        # reserve 8 / 16 CTAs collapsed to 51.7 ms per step).  Measured 2xB200, ms/step: (reserve, max CTAs) = (8,8) 0.810,
+        # (8,16) 0.727, (16,16) 0.726, (8,32) 0.779, (24,32) 0.817, (4,4) 1.011; reserve 0 starves NCCL (41 ms)
+        os.environ.setdefault("NCCL_MAX_CTAS", "16")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     spec_key, dbatch, desc_text = WORKLOADS[args.workload]
     batch = args.batch or dbatch

@@ -59,7 +59,7 @@ inline cudaError_t niti_launch(const niti_ctx* ctx, int cls, void (*kernel)(KArg
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; // cls: NITI_PDL_* kernel class bit.  Data parallel (peer exchange connected): off — CTAs placed ahead of time would sit on
     // the SMs reserved for the concurrent NCCL all-reduce (dp.cu).
-    cfg.numAttrs = (ctx && (ctx->pdl & cls) && ctx->dp.world <= 1) ? 1 : 0;
+    cfg.numAttrs = (ctx && (ctx->pdl & cls) && (ctx->dp.world <= 1 || (ctx->pdl & 256))) ? 1 : 0;   // bit 8: allow with DP (experiments)
     return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 

@@ -44,7 +44,10 @@ extern "C" int niti_dp_connect(niti_ctx* ctx, int rank, int world, const unsigne
     // contraction kernels otherwise occupy every SM (1 CTA/SM, ~200 KB smem) and the collective cannot start until one exits
     if (world > 1) {
         const char* env = getenv("NITI_B200_DP_RESERVE_SMS");
-        const int reserve = env ? atoi(env) : 8;
+        // Keep reserve >= NCCL's CTA cap (bench.py sets NCCL_MAX_CTAS=16): with fewer free SMs than NCCL CTAs the
+        // collective's CTAs wait for SMs held by contraction kernels that are themselves spinning on a peer (max exchange,
+        // grid barrier) — measured 4xB200 with reserve 8 / 16 NCCL CTAs: 51.7 ms per step instead of 1.0.
+        const int reserve = env ? atoi(env) : 16;
         if (reserve >= 0 && reserve < ctx->sm_count / 2) ctx->sm_count -= reserve;
         ctx->sm_count &= ~1;                              // CTA pairs
     }
