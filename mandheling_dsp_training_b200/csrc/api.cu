@@ -138,7 +138,7 @@ int niti_ctx_create(int device, niti_ctx** out) {
     const char* a2 = getenv("NITI_B200_AUTO_TMA2");
     ctx->auto_tma2 = a2 ? atoi(a2) : 1;
     const char* pdl = getenv("NITI_B200_PDL");
-    ctx->pdl = pdl ? atoi(pdl) : 1;
+    ctx->pdl = pdl ? atoi(pdl) : (1 | 512);      // fused kernels, trigger at the exponent barrier
     ctx->last_path = "none";
     if (prop.major != 10) {
         snprintf(ctx->err, sizeof(ctx->err), "device is sm_%d%d; this library is built for sm_100a only", prop.major, prop.minor);

@@ -14,7 +14,7 @@ struct niti_ctx {
     int sm_count;
     int path;                 // NITI_PATH_*
     int auto_tma2;            // AUTO prefers the CTA-pair kernels where eligible
-    int pdl;                  // programmatic dependent launch on the step's kernel chain (NITI_B200_PDL: bit mask of NITI_PDL_* kernel classes, default NITI_PDL_FUSED — measured best)
+    int pdl;                  // programmatic dependent launch on the step's kernel chain (NITI_B200_PDL: bit mask of NITI_PDL_* kernel classes, default NITI_PDL_FUSED | NITI_PDL_TRIGGER_LATE — measured best)
     int64_t launches;
     const char* last_path;
     char err[256];
@@ -47,7 +47,9 @@ __device__ __forceinline__ void niti_trace(unsigned long long* trace, int slot) 
 __device__ __forceinline__ void niti_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void niti_pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
-enum { NITI_PDL_FUSED = 1, NITI_PDL_STEM = 2, NITI_PDL_UPDATE = 4, NITI_PDL_ELEMENTWISE = 8 };
+enum { NITI_PDL_FUSED = 1, NITI_PDL_STEM = 2, NITI_PDL_UPDATE = 4, NITI_PDL_ELEMENTWISE = 8,
+       NITI_PDL_WITH_DP = 256,        // keep it on when the peer exchange is connected (experiments)
+       NITI_PDL_TRIGGER_LATE = 512 }; // fused kernels release the next launch at their exponent barrier instead of at entry
 
 template <typename... KArgs, typename... Args>
 inline cudaError_t niti_launch(const niti_ctx* ctx, int cls, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,

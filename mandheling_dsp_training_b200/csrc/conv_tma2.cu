@@ -483,6 +483,7 @@ struct FusedEpi {
     uint32_t* sync;                  // {arrival counter, exit counter}
     DpView dp; int dp_slot;
     unsigned long long* trace;
+    int trigger_late;                // PDL: let the next launch start placing CTAs at the exponent barrier, not at entry
 };
 
 template <int BN, int BKC> struct CfgF {
@@ -521,7 +522,7 @@ igemm_fused_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t rank = cluster_ctarank();
     const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
-    niti_pdl_trigger();                                      // the next launch of the stream may start placing its CTAs
+    if (!e.trigger_late) niti_pdl_trigger();                 // the next launch of the stream may start placing its CTAs
     if (tid == 64) niti_trace(e.trace, 0);
 
     if (tid == 0) {
@@ -644,6 +645,7 @@ igemm_fused_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
                 mx = warp_max_u32(mx);
                 if (lane == 0 && mx) atomicMax(p.maxabs, mx);
                 asm volatile("bar.sync 1, 512;" ::: "memory");
+                if (e.trigger_late) niti_pdl_trigger();
                 if (etid == 0) {
                     niti_trace(e.trace, 3);
                     grid_barrier(e.sync, gridDim.x);
@@ -772,7 +774,7 @@ int fused_conv_fwd(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, cons
     p.lower_h = -d->pad; p.lower_w = -d->pad; p.flip = 0;
     p.cchunks = d->c / bkc; p.num_kb = d->kh * d->kw * p.cchunks;
     FusedEpi e{};
-    e.y = y; e.gate = nullptr; e.exp_a = ex; e.exp_b = ew; e.exp_out = ey; e.relu = relu; e.dp = ctx->dp; e.dp_slot = dp_slot; e.trace = ctx->trace;
+    e.y = y; e.gate = nullptr; e.exp_a = ex; e.exp_b = ew; e.exp_out = ey; e.relu = relu; e.dp = ctx->dp; e.dp_slot = dp_slot; e.trace = ctx->trace; e.trigger_late = (ctx->pdl & 512) ? 1 : 0;
     CUtensorMap ma;
     if (!make_im2col2(&ma, x, d->n, d->h, d->w, d->c, -d->pad, -d->pad, d->pad - (d->kh - 1) * d->dil, d->pad - (d->kw - 1) * d->dil, d->stride, bkc))
         return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncodeIm2col(x) failed");
@@ -793,7 +795,7 @@ int fused_conv_dx(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* dy, cons
     p.lower_h = -pph; p.lower_w = -ppw; p.flip = 1;
     p.cchunks = d->oc / bkc; p.num_kb = d->kh * d->kw * p.cchunks;
     FusedEpi e{};
-    e.y = dx; e.gate = gate; e.relu = 0; e.dp = ctx->dp; e.dp_slot = dp_slot; e.trace = ctx->trace;
+    e.y = dx; e.gate = gate; e.relu = 0; e.dp = ctx->dp; e.dp_slot = dp_slot; e.trace = ctx->trace; e.trigger_late = (ctx->pdl & 512) ? 1 : 0;
     CUtensorMap ma;
     if (!make_im2col2(&ma, dy, d->n, oh, ow, d->oc, -pph, -ppw, d->h - oh - pph, d->w - ow - ppw, 1, bkc))
         return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncodeIm2col(dy) failed");

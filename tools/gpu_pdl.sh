@@ -1,5 +1,5 @@
 mkdir -p gpurun_out
-for pdl in 0 1 9 15; do
+for pdl in 1 513 521 527 1; do
 NITI_B200_PDL=$pdl timeout 60 python bench.py --no-cpu-baseline --steps 50 > gpurun_out/bench_pdl$pdl.json 2> gpurun_out/bench_pdl$pdl.err; echo bench pdl=$pdl rc=$?; tail -2 gpurun_out/bench_pdl$pdl.err
 python -c "
 import json
