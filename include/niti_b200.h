@@ -57,7 +57,7 @@ int         niti_set_path(niti_ctx* ctx, int path);
 int         niti_version(void);
 /* kernels launched through this context since creation (bench.py's gpu_launches evidence) */
 int64_t     niti_launch_count(niti_ctx* ctx);
-/* name of the kernel family the last conv/matmul call used: "tma", "tc" or "simt" */
+/* name of the kernel family the last conv/matmul call used: "simt", "tc", "tma", "tma2", "fused" or "stem" */
 const char* niti_last_path(niti_ctx* ctx);
 
 /* ---- phase 1: int32 accumulators + running max|acc| ---------------------------------------
@@ -181,6 +181,12 @@ int niti_conv_dx_fused(niti_ctx*, const niti_conv_desc*, const int8_t* dy, const
 int niti_conv_dx(niti_ctx*, const niti_conv_desc*, const int8_t* dy, const int8_t* w, int8_t* dx, niti_stream);
 int niti_conv_dw(niti_ctx*, const niti_conv_desc*, const int8_t* x, const int8_t* dy, int8_t* dw, niti_stream);
 int niti_matmul_nt(niti_ctx*, int e, int h, int l, const int8_t* a, const int8_t* b, int8_t* c, niti_stream);
+/* NITI_GradientSplitConv_Int8::onExecute (NITI_GradientSplitConv_Int8.cpp:195-386) as one call: dW contraction, then the
+ * output channels cut into `slices` groups, each rescaled with its own exponent (PSTO(acc_s, b_s - 3)) and aligned to the
+ * largest one (niti_rescale_grad_split).  niti_split_count restates the reference's slice rule (.cpp:209-222; host side,
+ * oc = output channels, oh/ow = spatial size of dY); oc % slices == 0 and slices <= 32. */
+int niti_split_count(int oc, int oh, int ow);
+int niti_conv_dw_split(niti_ctx*, const niti_conv_desc*, const int8_t* x, const int8_t* dy, int slices, int8_t* dw, niti_stream);
 
 /* ---- element-wise ops of the training step, NHWC ---------------------- */
 int niti_relu(niti_ctx*, const int8_t* x, int8_t* y, size_t n, niti_stream);                 /* NITI_CPURelu_Int8.cpp:47-53 */

@@ -305,6 +305,32 @@ int niti_conv_dw(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, const 
     return niti_rescale_grad(ctx, acc, n, ctx->ws_u32, 2, dw, nullptr, st);
 }
 
+// slice count of NITI_GradientSplitConv_Int8 (NITI_GradientSplitConv_Int8.cpp:209-222): OC is only rounded up to a multiple
+// of 32 when OC % 32 != 0 (otherwise the reference's align32 is 0 and nothing is split)
+int niti_split_count(int oc, int oh, int ow) {
+    if (oc <= 0 || oh <= 0 || ow <= 0) return 0;
+    int align32 = oc % 32;
+    if (align32 != 0) align32 = (oc / 32 + 1) * 32;
+    const int high = 8192 / ow / oh;
+    int real = oc;
+    while (align32 > high) { align32 /= 2; real /= 2; }
+    return real > 0 ? oc / real : 0;
+}
+
+int niti_conv_dw_split(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, const int8_t* dy, int slices, int8_t* dw,
+                       niti_stream st) {
+    if (!ctx || !desc_ok(d) || !dw || slices <= 0 || slices > 32 || d->oc % slices != 0)
+        return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_dw_split: bad argument (1 <= slices <= 32, oc % slices == 0)");
+    const size_t n = (size_t)d->oc * d->kh * d->kw * d->c, per = n / slices;
+    if (per % 4 != 0) return niti_fail(ctx, NITI_ERR_UNSUPPORTED, "niti_conv_dw_split: slice size must be a multiple of 4 words");
+    int32_t* acc; int rc = niti_ws_acc(ctx, n * 4, &acc); if (rc) return rc;
+    if ((rc = niti_zero_u32(ctx, ctx->ws_u32, 32, st))) return rc;
+    if ((rc = niti_conv_dw_acc(ctx, d, x, dy, acc, nullptr, st))) return rc;
+    for (int s = 0; s < slices; ++s)                           // an OC slice is contiguous in [oc][kh][kw][c]
+        if ((rc = niti_absmax(ctx, acc + (size_t)s * per, per, ctx->ws_u32 + s, st))) return rc;
+    return niti_rescale_grad_split(ctx, acc, per, slices, ctx->ws_u32, 3, dw, st);
+}
+
 int niti_matmul_nt(niti_ctx* ctx, int e, int h, int l, const int8_t* a, const int8_t* b, int8_t* c, niti_stream st) {
     if (!ctx || e <= 0 || h <= 0 || l <= 0 || !c) return niti_fail(ctx, NITI_ERR_ARG, "niti_matmul_nt: bad argument");
     size_t n = (size_t)e * h;

@@ -73,6 +73,9 @@ _SIGS = {
     "niti_conv_dx": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P]),
     "niti_conv_dw": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P]),
     "niti_matmul_nt": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P, _P, _P]),
+    "niti_rescale_grad_split": (C.c_int, [_P, _P, C.c_size_t, C.c_int, _P, C.c_int, _P, _P]),
+    "niti_split_count": (C.c_int, [C.c_int, C.c_int, C.c_int]),
+    "niti_conv_dw_split": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, C.c_int, _P, _P]),
     "niti_relu": (C.c_int, [_P, _P, _P, C.c_size_t, _P]),
     "niti_relu_grad": (C.c_int, [_P, _P, _P, _P, C.c_size_t, _P]),
     "niti_maxpool": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
@@ -245,6 +248,17 @@ class NitiB200:
     def rescale_grad(self, acc, n, maxabs, sub, dw_out=None, w_inout=None, stream=None):
         self._ck(self.lib.niti_rescale_grad(self.h, _ptr(acc), n, _ptr(maxabs), sub, _ptr(dw_out), _ptr(w_inout),
                                             self._stream(stream)))
+
+    def rescale_grad_split(self, acc, n_per_slice, slices, maxabs, sub, out, stream=None):
+        """maxabs: `slices` uint32 slots holding max|acc_s|; out = per-slice rule B + alignment (NITI_GradientSplitConv_Int8)"""
+        self._ck(self.lib.niti_rescale_grad_split(self.h, _ptr(acc), n_per_slice, int(slices), _ptr(maxabs), int(sub), _ptr(out),
+                                                  self._stream(stream)))
+
+    def split_count(self, oc, oh, ow):
+        return self.lib.niti_split_count(int(oc), int(oh), int(ow))
+
+    def conv_dw_split(self, d, x, dy, slices, dw, stream=None):
+        self._ck(self.lib.niti_conv_dw_split(self.h, C.byref(d), _ptr(x), _ptr(dy), int(slices), _ptr(dw), self._stream(stream)))
 
     def sgd_update(self, w, dw, n, stream=None):
         self._ck(self.lib.niti_sgd_update(self.h, _ptr(w), _ptr(dw), n, self._stream(stream)))

@@ -525,6 +525,21 @@ public:
                 return new B200NitiDspGradientConv(backend, conv->common(), 16, true);
             case OpType_NITI_DSP_GRADIENTCONV_Int8:
             case OpType_NITI_DSP_PARALLEL_GRADIENTCONV_Int8:
+            // OpType_NITI_DSP_MATMUL_GRADIENT_Int8 — the op BASELINE.json's north star names.  Operand contract read off the
+            // execution and its size computer: shape rule NITI_DSPGradientCONVSizeComputer, the SAME one as DSP_GRADIENTCONV
+            // (source/shape/ShapeNITI_Conv_Int8.cpp:146-236, registered :528); inputs[0] = x NHWC [N,H,W,C], inputs[1] = dY
+            // NHWC [N,OH,OW,OC] (NITI_DSPMatmulGradientConv_Int8.cpp:110-126), kernelX/Y = OW/OH, zero-padded by padX (:153);
+            // the hexagon graph is pad -> im2col -> transpose {3,1,2,0} -> [C*KH*KW, N*OH*OW] x dY as [N*OH*OW, OC]
+            // (QuantizedMatMul_8x8to32) -> requantise -> transpose to [KH,KW,C,OC], then the int8 result is divided by 16
+            // (:548-550).  That is the dW contraction with the DSP rounding and post-division 16.
+            case OpType_NITI_DSP_MATMUL_GRADIENT_Int8:
+            // OpType_NITI_DSP_MATMUL_Int8 — same size computer (ShapeNITI_Conv_Int8.cpp:532), same operands, same /16
+            // (NITI_DSPMatmul_Int8.cpp:297-302).  The reference execution is unfinished: its graph is the bare
+            // QuantizedMatMul_8x8to32 of scratch tensors matmulA [C*KH*KW, OH*OW*N] x matmulB [OH*OW*N, OC] (:72-87,193-262)
+            // that are never filled from the inputs, and outputs[0] is never written by the graph.  What IS defined — the
+            // shape rule, the matmul dimensions (exactly the im2col form of the dW contraction) and the /16 — is what
+            // MATMUL_GRADIENT computes, so both op types share this execution.
+            case OpType_NITI_DSP_MATMUL_Int8:
                 if (inputs.size() < 2) return nullptr;
                 return new B200NitiDspGradientConv(backend, conv->common(), 16, false);
             default:
@@ -563,6 +578,10 @@ REGISTER_B200_OP_CREATOR(DspDwCreator, OpType_NITI_DSP_GRADIENTCONV_Int8);
 REGISTER_B200_OP_CREATOR(DspDwTransposeCreator, OpType_NITI_DSP_TRANSPOSEGRADIENT_CONV_Int8);
 REGISTER_B200_OP_CREATOR(DspDwParallelCreator, OpType_NITI_DSP_PARALLEL_GRADIENTCONV_Int8);
 REGISTER_B200_OP_CREATOR(DspDwSplitBatchCreator, OpType_NITI_DSP_GRADIENT_SPLITBatchCONV_Int8);
+typedef ConvCreator DspMatmulGradientCreator;
+typedef ConvCreator DspMatmulCreator;
+REGISTER_B200_OP_CREATOR(DspMatmulGradientCreator, OpType_NITI_DSP_MATMUL_GRADIENT_Int8);
+REGISTER_B200_OP_CREATOR(DspMatmulCreator, OpType_NITI_DSP_MATMUL_Int8);
 
 } // namespace
 } // namespace B200

@@ -87,6 +87,45 @@ void niti_o_rescale_grad(const int32_t* acc, long n, int sub, int8_t* out) {
     free(tmp);
 }
 
+/* ---- NITI_GradientSplitConv_Int8 ----------------------------------------------------------
+ * Slice count, NITI_GradientSplitConv_Int8.cpp:209-222: `oc` = weight->batch() (output channels of dyT [OC,N,OH,OW]),
+ * oh/ow = weight->height()/width().  Note the reference only rounds OC up to a multiple of 32 when OC % 32 != 0; with
+ * OC % 32 == 0 its `align32` is 0, the loop never runs and the op degenerates to one slice. */
+int niti_o_split_count(int oc, int oh, int ow) {
+    int align32 = oc % 32;
+    if (align32 != 0) align32 = (oc / 32 + 1) * 32;
+    int high = 8192 / ow / oh;
+    int real = oc;
+    while (align32 > high) { align32 /= 2; real /= 2; }
+    return real > 0 ? oc / real : 0;       /* real == 0 divides by zero in the reference */
+}
+/* Per-slice rule + alignment, NITI_GradientSplitConv_Int8.cpp:318-362: acc holds `slices` equal contiguous slices (one per
+ * group of output channels); scale[s] = RangeEstimate(acc_s); out_s = scale[s]==0 ? 0 : (int8)PSTO(acc_s, scale[s]-3);
+ * then every slice with scale[s] < max scale is integer-divided (C truncation, int8 operand promoted to int) by
+ * 1 << (max - scale[s]). */
+void niti_o_rescale_grad_split(const int32_t* acc, long n_per_slice, int slices, int8_t* out) {
+    int* scale = (int*)malloc(sizeof(int) * (size_t)(slices > 0 ? slices : 1));
+    int32_t* tmp = (int32_t*)malloc(sizeof(int32_t) * (size_t)(n_per_slice > 0 ? n_per_slice : 1));
+    for (int s = 0; s < slices; ++s) {
+        const int32_t* a = acc + (long)s * n_per_slice;
+        int8_t* o = out + (long)s * n_per_slice;
+        scale[s] = niti_o_range_estimate(a, n_per_slice);
+        if (scale[s] == 0) { memset(o, 0, (size_t)n_per_slice); continue; }
+        niti_o_psto_shift(a, scale[s] - 3, tmp, n_per_slice);
+        for (long i = 0; i < n_per_slice; ++i) o[i] = (int8_t)tmp[i];
+    }
+    int mx = scale[0];
+    for (int s = 1; s < slices; ++s) if (mx < scale[s]) mx = scale[s];
+    for (int s = 0; s < slices; ++s) {
+        if (mx > scale[s]) {
+            int8_t* o = out + (long)s * n_per_slice;
+            const int32_t div = shl1(mx - scale[s]);
+            for (long i = 0; i < n_per_slice; ++i) o[i] = (int8_t)((int32_t)o[i] / div);
+        }
+    }
+    free(tmp); free(scale);
+}
+
 /* ---- DSP-named op types: requantisation of the Hexagon path.  PARITY UNPINNED: the code
  * below restates the reference's sources, but the reference's DSP path only runs on a Snapdragon cDSP, so no output of
  * it could be produced here to check the restatement against.

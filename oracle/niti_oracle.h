@@ -54,6 +54,10 @@ int  niti_o_rescale_act(const int32_t* acc, long n, int8_t* out);
 /* rule B (dW): b==0 -> zeros, else PSTO(b - sub) with sub = 2 (GradientConv) or 3 (Matmul). */
 void niti_o_rescale_grad(const int32_t* acc, long n, int sub, int8_t* out);
 
+/* NITI_GradientSplitConv_Int8.cpp:209-222 (slice count) and :318-362 (per-slice rule B with sub = 3 + post-alignment) */
+int  niti_o_split_count(int oc, int oh, int ow);
+void niti_o_rescale_grad_split(const int32_t* acc, long n_per_slice, int slices, int8_t* out);
+
 /* DSP-named op types: round-half-up requantisation of the Hexagon path (niti_op_supernode_new.c:4614-4634,
  * quantize.c:337-400); returns the shift (exponent increment).  post_div: 1, 16 or 32.  PARITY UNPINNED (no cDSP). */
 int  niti_o_dsp_ceiling_log2(uint32_t v);

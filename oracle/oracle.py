@@ -75,6 +75,10 @@ class Oracle:
         L.niti_o_dsp_ceiling_log2.argtypes = [C.c_uint32]
         L.niti_o_rescale_grad.restype = None
         L.niti_o_rescale_grad.argtypes = [_i32p, C.c_long, C.c_int, _i8p]
+        L.niti_o_split_count.restype = C.c_int
+        L.niti_o_split_count.argtypes = [C.c_int, C.c_int, C.c_int]
+        L.niti_o_rescale_grad_split.restype = None
+        L.niti_o_rescale_grad_split.argtypes = [_i32p, C.c_long, C.c_int, _i8p]
         L.niti_o_range_estimate.restype = C.c_int
         L.niti_o_range_estimate.argtypes = [_i32p, C.c_long]
         L.niti_o_psto_shift.restype = None
@@ -140,6 +144,34 @@ class Oracle:
         self.lib.niti_o_rescale_grad(a.reshape(-1), a.size, sub, out.reshape(-1))
         return out
 
+    def split_count(self, oc, oh, ow):
+        """slice count of NITI_GradientSplitConv_Int8 (.cpp:209-222)"""
+        return self.lib.niti_o_split_count(int(oc), int(oh), int(ow))
+
+    def rescale_grad_split(self, acc, slices):
+        """acc: int32, `slices` equal contiguous slices along axis 0 -> int8 (per-slice PSTO(b_s - 3) + alignment)"""
+        a = _c(acc, np.int32)
+        assert a.size % slices == 0
+        out = np.empty(a.shape, np.int8)
+        self.lib.niti_o_rescale_grad_split(a.reshape(-1), a.size // slices, int(slices), out.reshape(-1))
+        return out
+
+    def conv_dw_split(self, s, x, dy):
+        """NITI_GradientSplitConv_Int8: dW [oc,c,kh,kw] with the output channels cut in split_count slices"""
+        acc, _ = self.conv_dw_acc(s, x, dy)
+        k = self.split_count(s.oc, s.oh, s.ow)
+        return self.rescale_grad_split(acc, k), k
+
+    @staticmethod
+    def matmul_unpack_a(raw, e, l):
+        """A as NITI_Matmul_Int8 addresses its input buffer: [l/4][e][4] blocks (NITI_Matmul_Int8.cpp:186-196) -> [e, l]"""
+        return np.ascontiguousarray(np.asarray(raw, np.int8).reshape(l // 4, e, 4).transpose(1, 0, 2).reshape(e, l))
+
+    @staticmethod
+    def matmul_pack_c(c, e, h):
+        """C [e, h] -> the [h/4][e][4] blocks NITI_Matmul_Int8 writes its output buffer in"""
+        return np.ascontiguousarray(np.asarray(c, np.int8).reshape(e, h // 4, 4).transpose(1, 0, 2)).reshape(-1)
+
     # ---- whole ops
     def conv_fwd(self, s, x, w, ex, ew):
         acc, _ = self.conv_fwd_acc(s, x, w)
@@ -200,6 +232,13 @@ class Reference:
         return os.path.exists(os.path.join(_REF_DIR, "libniti_ref_driver.so"))
 
     def __init__(self, threads=4, workdir=None):
+        # The reference build exports libstdc++ symbols of its own (default visibility, Makefile.ref) and is loaded
+        # RTLD_GLOBAL so plug-ins can resolve MNN core symbols; a torch imported AFTER it would bind to those copies and
+        # abort in std::locale.  Load torch first when it is there.
+        try:
+            import torch  # noqa: F401
+        except ImportError:
+            pass
         self.lib = L = C.CDLL(os.path.join(_REF_DIR, "libniti_ref_driver.so"), mode=C.RTLD_GLOBAL)  # plug-ins resolve MNN core symbols against it
         workdir = workdir or os.path.join(_REF_DIR, "_cwd")
         os.makedirs(workdir, exist_ok=True)
@@ -236,6 +275,26 @@ class Reference:
         rc = L.ref_conv_bwd(self._sp(s), _c(x), _c(w), _c(dy), ex, ew, dx, dw)
         assert rc == 0, rc
         return dx, dw
+
+    def matmul_raw(self, a_raw, b, e, l, h):
+        """OpType_NITI_MatMul_Int8 (transposeB) on RAW buffers: a_raw e*l bytes, b [h, l]; returns the raw e*h output bytes"""
+        f = self.lib.ref_matmul
+        f.restype = C.c_int
+        f.argtypes = [C.c_int, C.c_int, C.c_int, _i8p, _i8p, _i8p]
+        out = np.empty(e * h, np.int8)
+        rc = f(e, l, h, _c(a_raw).reshape(-1), _c(b).reshape(-1), out)
+        assert rc == 0, rc
+        return out
+
+    def grad_conv(self, s, x, dy, split=False):
+        """dW [oc,c,kh,kw] through OpType_NITI_GradientCONV_Int8 / OpType_NITI_GradientSplitCONV_Int8 (stride 1)"""
+        f = self.lib.ref_grad_conv
+        f.restype = C.c_int
+        f.argtypes = [C.c_int, C.POINTER(C.c_int), _i8p, _i8p, _i8p]
+        dw = np.empty((s.oc, s.c, s.kh, s.kw), np.int8)
+        rc = f(int(bool(split)), self._sp(s), _c(x), _c(dy), dw)
+        assert rc == 0, rc
+        return dw
 
     def sgd_update(self, w, dw):
         out = np.empty_like(_c(w))

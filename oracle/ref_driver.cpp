@@ -160,14 +160,16 @@ int ref_loss_grad(const int8_t* logits, int ascale, const int* onehot, int b, in
 // Convolution2DCommon and NHWC operands, exactly the form grad/NITI_DSPConv_Int8_Grad.cpp:36-222 and
 // express/NeuralNetWorkOp.cpp:2031-2100 emit.  On the reference CPU backend these executions need the Hexagon FastRPC
 // library (not runnable here); tests/test_gpu_mnn_backend.py runs them on the B200 plug-in only.
-// kind: 0 DSP_CONV, 1 DSP_DECONV, 2 TRANSPOSEGRADIENT_CONV, 3 PARALLEL_GRADIENTCONV, 4 GRADIENT_SPLITBatchCONV, 5 DSP_GRADIENTCONV
+// kind: 0 DSP_CONV, 1 DSP_DECONV, 2 TRANSPOSEGRADIENT_CONV, 3 PARALLEL_GRADIENTCONV, 4 GRADIENT_SPLITBatchCONV, 5 DSP_GRADIENTCONV,
+//       6 DSP_MATMUL_GRADIENT (NITI_DSPMatmulGradientConv_Int8.cpp:105-553), 7 DSP_MATMUL (NITI_DSPMatmul_Int8.cpp:142-305)
 // geo = {kernelY, kernelX, stride, pad, inputCount, outputCount}; returns the exponent output, odims = output dims.
 int ref_dsp_op(int kind, const int* geo, const int8_t* a, const int* adims, const int8_t* b, const int* bdims, int e0, int e1,
                int8_t* out, int* odims) {
     static const OpType types[] = {OpType_NITI_DSP_CONV_Int8, OpType_NITI_DSP_DECONV_Int8,
                                    OpType_NITI_DSP_TRANSPOSEGRADIENT_CONV_Int8, OpType_NITI_DSP_PARALLEL_GRADIENTCONV_Int8,
-                                   OpType_NITI_DSP_GRADIENT_SPLITBatchCONV_Int8, OpType_NITI_DSP_GRADIENTCONV_Int8};
-    if (kind < 0 || kind > 5) return -1000;
+                                   OpType_NITI_DSP_GRADIENT_SPLITBatchCONV_Int8, OpType_NITI_DSP_GRADIENTCONV_Int8,
+                                   OpType_NITI_DSP_MATMUL_GRADIENT_Int8, OpType_NITI_DSP_MATMUL_Int8};
+    if (kind < 0 || kind > 7) return -1000;
     std::unique_ptr<OpT> op(new OpT);
     op->type = types[kind];
     op->main.type = OpParameter_NITI_CONV_Int8;
@@ -194,6 +196,65 @@ int ref_dsp_op(int kind, const int* geo, const int8_t* a, const int* adims, cons
     ::memcpy(out, ptr, info->size);
     auto ep = e->readMap<int8_t>();
     return ep ? (int)ep[0] : -1003;
+}
+
+// OpType_NITI_MatMul_Int8 exactly as source/geometry/NITI_GeometryConv2DBackPropFilter_Int8.cpp:78-126 emits it:
+// MatMul parameter with transposeB = true, inputs {A [e, l], B [h, l]} as 2-d int8 tensors, one output C [e, h].
+// The buffers cross this boundary RAW (the execution reads A and writes C through its own packed [channel/4][batch][4]
+// addressing, NITI_Matmul_Int8.cpp:186-208; tests restate that addressing).
+int ref_matmul(int e, int l, int h, const int8_t* a, const int8_t* b, int8_t* c) {
+    std::unique_ptr<OpT> op(new OpT);
+    op->type = OpType_NITI_MatMul_Int8;
+    op->main.type = OpParameter_MatMul;
+    op->main.value = new MatMulT;
+    op->main.AsMatMul()->transposeA = false;
+    op->main.AsMatMul()->transposeB = true;
+    auto av = constI8(a, {e, l});
+    auto bv = constI8(b, {h, l});
+    auto expr = Expr::create(std::move(op), {av, bv}, 1);
+    auto y = Variable::create(expr, 0);
+    auto info = y->getInfo();
+    if (!info || info->dim.size() != 2 || info->dim[0] != e || info->dim[1] != h) return -1;
+    auto ptr = y->readMap<int8_t>();
+    if (!ptr) return -2;
+    ::memcpy(c, ptr, (size_t)e * h);
+    return 0;
+}
+
+// dW through OpType_NITI_GradientCONV_Int8 (split = 0) or OpType_NITI_GradientSplitCONV_Int8 (split = 1) with the operand
+// forms of the reference's own grad rule, stride-1 branch (tools/train/source/grad/NITI_Conv_Int8_Grad.cpp:167-190):
+// {xT [C,N,H,W] NC4HW4, dyT [OC,N,OH,OW] NCHW, ascale, wscale}, kernelX/Y = OW/OH, inputCount = N, outputCount = OC;
+// result [C,OC,KH,KW] -> NCHW -> transpose {1,0,2,3} = dw [OC,C,KH,KW].  The split op type has no producer in the tree
+// (SURVEY.md 8 a5); this is the only way to execute NITI_GradientSplitConv_Int8.cpp:195-386.
+int ref_grad_conv(int split, const int* shp, const int8_t* x, const int8_t* dy, int8_t* dw) {
+    Shape s; ::memcpy(&s, shp, sizeof(s));
+    if (s.stride != 1 || s.dil != 1) return -1;
+    const int oh = s.h + 2 * s.pad - s.kh + 1, ow = s.w + 2 * s.pad - s.kw + 1;
+    std::unique_ptr<OpT> op(new OpT);
+    op->type = split ? OpType_NITI_GradientSplitCONV_Int8 : OpType_NITI_GradientCONV_Int8;
+    op->main.type = OpParameter_NITI_CONV_Int8;
+    auto conv = new NITI_CONV_Int8T;
+    conv->common.reset(new Convolution2DCommonT);
+    conv->common->kernelX = ow; conv->common->kernelY = oh;
+    conv->common->strideX = conv->common->strideY = 1;
+    conv->common->dilateX = conv->common->dilateY = 1;
+    conv->common->padX = conv->common->padY = s.pad;
+    conv->common->padMode = PadMode_CAFFE;
+    conv->common->group = 1;
+    conv->common->inputCount = s.n; conv->common->outputCount = s.oc;
+    op->main.value = conv;
+    auto xv  = constI8(x, {s.n, s.c, s.h, s.w});
+    auto dyv = constI8(dy, {s.n, s.oc, oh, ow});
+    auto xT  = _Convert(_NITI_Transpose_INT8(xv, {1, 0, 2, 3}), NC4HW4);
+    auto dyT = _NITI_Transpose_INT8(dyv, {1, 0, 2, 3});
+    auto expr = Expr::create(std::move(op), {xT, dyT, _Scalar<int8_t>(-7), _Scalar<int8_t>(-7)}, 2);
+    auto ret = Variable::create(expr, 0);
+    auto out = _NITI_Transpose_INT8(_Convert(ret, NCHW), {1, 0, 2, 3});
+    auto info = out->getInfo();
+    if (!info || info->dim.size() != 4) return -2;
+    if (info->dim[0] != s.oc || info->dim[1] != s.c || info->dim[2] != s.kh || info->dim[3] != s.kw) return -3;
+    copyOut(out, dw);
+    return 0;
 }
 
 int ref_use_backend(int forwardType, const char* plugin, int threads) {

@@ -27,3 +27,15 @@ def golden_conv():
 def golden_ew():
     import numpy as np
     return np.load(os.path.join(ROOT, "tests", "golden", "elementwise_cases.npz"))
+
+
+@pytest.fixture(scope="session")
+def golden_mm():
+    import numpy as np
+    return np.load(os.path.join(ROOT, "tests", "golden", "matmul_cases.npz"))
+
+
+@pytest.fixture(scope="session")
+def golden_split():
+    import numpy as np
+    return np.load(os.path.join(ROOT, "tests", "golden", "split_cases.npz"))

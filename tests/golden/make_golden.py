@@ -86,6 +86,44 @@ def main():
         ew[f"loss_grad.{a}.logits"], ew[f"loss_grad.{a}.labels"] = lg, lab
         ew[f"loss_grad.{a}.grad"] = ref.loss_grad(lg, a, lab)
     np.savez_compressed(os.path.join(OUT, "elementwise_cases.npz"), **ew)
+
+    # ---- OpType_NITI_MatMul_Int8 (a4) and OpType_NITI_GradientSplitCONV_Int8 (a5): neither has a producer the demo
+    # reaches, so the driver creates the ops directly (ref_matmul / ref_grad_conv in oracle/ref_driver.cpp)
+    mm = {}
+    rng = np.random.default_rng(11)
+    for i, (e, l, h, amax, bmax) in enumerate([(36, 64, 8, 127, 60), (100, 128, 12, 127, 127), (108, 256, 20, 90, 40),
+                                               (64, 832, 500, 127, 127), (16, 16, 4, 2, 1), (8, 4, 4, 1, 1)]):
+        a_raw = rng.integers(-amax, amax + 1, size=e * l, dtype=np.int8)
+        b = rng.integers(-bmax, bmax + 1, size=(h, l), dtype=np.int8)
+        if i == 5:
+            a_raw[:] = 0                                  # b == 0 -> zeros (Q2)
+        mm[f"mm{i}.dims"] = np.array([e, l, h], np.int32)
+        mm[f"mm{i}.a_raw"], mm[f"mm{i}.b"] = a_raw, b
+        mm[f"mm{i}.c_raw"] = ref.matmul_raw(a_raw, b, e, l, h)
+        assert orc.matmul_nt_acc(orc.matmul_unpack_a(a_raw, e, l), b)[1] < 2 ** 24
+    np.savez_compressed(os.path.join(OUT, "matmul_cases.npz"), **mm)
+
+    sp = {}
+    rng = np.random.default_rng(13)
+    # (n, c, h, oc, k, pad, dy_absmax): slice counts 2, 4, 1 (OC % 32 == 0 never splits), 2 with a zero slice
+    for i, (n, c, hh, oc, k, pad, dymax) in enumerate([(4, 8, 16, 48, 3, 1, 50), (2, 4, 20, 48, 3, 1, 40),
+                                                       (2, 4, 20, 96, 3, 1, 40), (2, 4, 18, 40, 3, 0, 20)]):
+        s = shape(n, c, hh, hh, oc, k, stride=1, pad=pad)
+        x = rng.integers(-127, 128, size=(n, c, hh, hh), dtype=np.int8)
+        dy = rng.integers(-dymax, dymax + 1, size=(n, oc, s.oh, s.ow), dtype=np.int8)
+        slices = orc.split_count(oc, s.oh, s.ow)
+        per = oc // slices
+        for sl in range(slices):
+            dy[:, sl * per:(sl + 1) * per] //= (1 << (sl % 4))     # slices of different magnitude -> alignment divides
+        if i == 3:
+            dy[:, per:] = 0                                        # one slice with b_s == 0
+        sp[f"sp{i}.shape"] = np.array([getattr(s, f) for f, _ in s._fields_], np.int32)
+        sp[f"sp{i}.x"], sp[f"sp{i}.dy"] = x, dy
+        sp[f"sp{i}.slices"] = np.int32(slices)
+        sp[f"sp{i}.dw"] = ref.grad_conv(s, x, dy, split=True)
+        sp[f"sp{i}.dw_unsplit"] = ref.grad_conv(s, x, dy, split=False)
+        assert orc.conv_dw_acc(s, x, dy)[1] < 2 ** 24
+    np.savez_compressed(os.path.join(OUT, "split_cases.npz"), **sp)
     print("wrote", os.listdir(OUT))
 
 

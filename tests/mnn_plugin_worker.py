@@ -24,6 +24,10 @@ LENET = [("conv", 20, 5, 1, 0), ("relu",), ("pool", 2, 2), ("conv", 52, 5, 1, 0)
          ("flatten",), ("conv", 500, 1, 1, 0), ("relu",), ("conv", 12, 1, 1, 0)]      # demo/mnistTrain.cpp:131-181
 
 
+MATMUL_CASES = [(36, 64, 8), (100, 128, 12), (64, 832, 500), (52, 100, 16)]           # (e, l, h)
+SPLIT_CASES = [(4, 8, 16, 48, 3, 1), (2, 4, 20, 48, 3, 1), (2, 8, 12, 64, 3, 1)]      # (n, c, h, oc, k, pad)
+
+
 def xavier_int8(rng, oc, c, k):
     w = rng.normal(0.0, np.sqrt(2.0 / ((c + oc) * k * k)), size=(oc, c, k, k)).astype(np.float32)
     r = float(np.abs(w).max())
@@ -42,6 +46,21 @@ def evaluate(ref, tag, out, steps, batch):
         dx, dw = ref.conv_bwd(s, x, wt, dy)
         out[f"{tag}_fwd{i}_y"], out[f"{tag}_fwd{i}_e"] = y, np.int32(e)
         out[f"{tag}_bwd{i}_dx"], out[f"{tag}_bwd{i}_dw"] = dx, dw
+    # a4: OpType_NITI_MatMul_Int8 (raw buffers, the execution's own packed addressing) and
+    # a5: OpType_NITI_GradientSplitCONV_Int8 (slice counts 2, 4, 1), created directly (ref_driver.cpp)
+    for i, (e, l, h) in enumerate(MATMUL_CASES):
+        rng = np.random.default_rng(200 + i)
+        a_raw = rng.integers(-127, 128, size=e * l, dtype=np.int8)
+        b = rng.integers(-90, 91, size=(h, l), dtype=np.int8)
+        out[f"{tag}_matmul{i}"] = ref.matmul_raw(a_raw, b, e, l, h)
+    for i, (n, c, hh, oc, k, p) in enumerate(SPLIT_CASES):
+        s = shape(n, c, hh, hh, oc, k, stride=1, pad=p)
+        rng = np.random.default_rng(300 + i)
+        x = rng.integers(-127, 128, size=(n, c, hh, hh), dtype=np.int8)
+        dy = rng.integers(-50, 51, size=(n, oc, s.oh, s.ow), dtype=np.int8)
+        dy[:, oc // 2:] //= 4
+        out[f"{tag}_split{i}"] = ref.grad_conv(s, x, dy, split=True)
+        out[f"{tag}_nosplit{i}"] = ref.grad_conv(s, x, dy, split=False)
     rng = np.random.default_rng(7)
     a = rng.integers(-127, 128, size=(4, 8, 8, 8), dtype=np.int8)
     g = rng.integers(-127, 128, size=(4, 8, 8, 8), dtype=np.int8)
@@ -89,7 +108,8 @@ def evaluate_dsp(ref, out):
                 bad.append(("conv", kind, i, y.shape, e, shift))
         dacc, _ = orc.conv_dw_acc(s, x, dy)                   # [oc, c, kh, kw]
         xT = np.ascontiguousarray(x_nhwc.transpose(3, 1, 2, 0))
-        for kind, div, xin in ((2, 32, xT), (3, 16, x_nhwc), (4, 16, xT), (5, 16, x_nhwc)):
+        # 6 = DSP_MATMUL_GRADIENT (the north star's op), 7 = DSP_MATMUL: operands as DSP_GRADIENTCONV (same size computer)
+        for kind, div, xin in ((2, 32, xT), (3, 16, x_nhwc), (4, 16, xT), (5, 16, x_nhwc), (6, 16, x_nhwc), (7, 16, x_nhwc)):
             wantw, shiftw = orc.rescale_dsp(dacc, div)
             dw, e = ref.dsp_op(kind, (s.oh, s.ow, 1, p, n, oc), xin, dy_nhwc, 0, 0, out_elems=wantw.size)
             ok = dw.shape == (k, k, c, oc) and np.array_equal(dw, wantw.transpose(2, 3, 1, 0)) and e == shiftw
@@ -104,7 +124,7 @@ def main():
     dst = os.path.abspath(sys.argv[1])          # Reference() changes the cwd (DSP.txt / parallel.txt live there)
     steps = int(sys.argv[2]) if len(sys.argv) > 2 else 3
     batch = int(sys.argv[3]) if len(sys.argv) > 3 else 64
-    out = {"n_conv": np.int32(len(CONV_CASES))}
+    out = {"n_conv": np.int32(len(CONV_CASES)), "n_matmul": np.int32(len(MATMUL_CASES)), "n_split": np.int32(len(SPLIT_CASES))}
     ref = Reference(threads=4)
     if len(sys.argv) > 4 and sys.argv[4] == "dsp":          # DSP-named op types only (own process: no CPU leg exists)
         ref.use_backend(MNN_FORWARD_USER_0, PLUGIN)

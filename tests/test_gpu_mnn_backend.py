@@ -41,6 +41,17 @@ def test_conv_ops_identical(res):
             assert np.array_equal(res["cpu_" + k], res["b200_" + k]), k
 
 
+def test_matmul_and_gradient_split_conv_identical(res):
+    """a4 / a5 through the plug-in: OpType_NITI_MatMul_Int8 (B200NitiMatMul, packed [l/4][e][4] gathers) and
+    OpType_NITI_GradientSplitCONV_Int8 (per-slice exponents + alignment) equal the reference CPU executions byte for byte"""
+    for i in range(int(res["n_matmul"])):
+        assert np.array_equal(res[f"cpu_matmul{i}"], res[f"b200_matmul{i}"]), ("matmul", i)
+    for i in range(int(res["n_split"])):
+        assert np.array_equal(res[f"cpu_split{i}"], res[f"b200_split{i}"]), ("split", i)
+        assert np.array_equal(res[f"cpu_nosplit{i}"], res[f"b200_nosplit{i}"]), ("nosplit", i)
+    assert any(not np.array_equal(res[f"cpu_split{i}"], res[f"cpu_nosplit{i}"]) for i in range(int(res["n_split"])))
+
+
 def test_elementwise_ops_identical(res):
     for k in ("relu", "relu_grad", "maxpool"):
         assert np.array_equal(res["cpu_" + k], res["b200_" + k]), k
@@ -65,13 +76,13 @@ def res_dsp(tmp_path_factory):
 
 def test_dsp_named_op_types_dispatch_and_match_the_dsp_restatement(res_dsp):
     res = res_dsp
-    assert int(res["launches"]) >= 3 * 6 * int(res["n_dsp"]), "DSP-named ops did not run on the B200 backend"
+    assert int(res["launches"]) >= 3 * 8 * int(res["n_dsp"]), "DSP-named ops did not run on the B200 backend"
     """SURVEY.md section 8 a11: OpType_NITI_DSP_{CONV, DECONV, TRANSPOSEGRADIENT_CONV, PARALLEL_GRADIENTCONV,
-    GRADIENT_SPLITBatchCONV, GRADIENTCONV}_Int8, created through the reference's express API with the operand forms its
+    GRADIENT_SPLITBatchCONV, GRADIENTCONV, MATMUL_GRADIENT, MATMUL}_Int8, created through the reference's express API with the operand forms its
     grad rule emits, run on the B200 plug-in and equal the oracle's restatement of the Hexagon requantisation
     (parity of that restatement is unpinned: the DSP path itself needs a Snapdragon cDSP)."""
     for i in range(int(res["n_dsp"])):
         for kind in (0, 1):
             assert int(res[f"dsp_conv{kind}_{i}"]) == 1, (kind, i)
-        for kind in (2, 3, 4, 5):
+        for kind in (2, 3, 4, 5, 6, 7):         # 6 = DSP_MATMUL_GRADIENT (north-star op), 7 = DSP_MATMUL
             assert int(res[f"dsp_dw{kind}_{i}"]) == 1, (kind, i)

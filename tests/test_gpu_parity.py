@@ -272,6 +272,58 @@ def test_matmul_nt(nb, run, oracle):
         assert np.array_equal(run.matmul_nt(a, b), oracle.matmul_nt(a, b)[0])
 
 
+@pytest.mark.parametrize("i", range(6))
+def test_matmul_golden_reference_vectors(nb, run, oracle, golden_mm, i):
+    """a4: niti_matmul_nt against outputs of the reference's NITI_Matmul_Int8 execution (tests/golden/make_golden.py);
+    A / C cross the reference boundary in its [channel/4][batch][4] addressing, restated by matmul_unpack_a / pack_c"""
+    g = golden_mm
+    e, l, h = (int(v) for v in g[f"mm{i}.dims"])
+    a = oracle.matmul_unpack_a(g[f"mm{i}.a_raw"], e, l)
+    c = run.matmul_nt(a, g[f"mm{i}.b"])
+    assert np.array_equal(oracle.matmul_pack_c(c, e, h), g[f"mm{i}.c_raw"])
+    assert np.array_equal(c, oracle.matmul_nt(a, g[f"mm{i}.b"])[0])
+
+
+@pytest.mark.parametrize("i", range(4))
+def test_gradient_split_conv_golden_reference_vectors(nb, oracle, golden_split, i):
+    """a5: niti_conv_dw_split (contraction + per-slice exponents + alignment, NITI_GradientSplitConv_Int8.cpp:318-362)
+    against outputs of the reference execution"""
+    import torch
+    from tests.gpu_util import to_desc, dev, nhwc, nchw
+    g = golden_split
+    s = ConvShape(*[int(v) for v in g[f"sp{i}.shape"]])
+    slices = int(g[f"sp{i}.slices"])
+    assert nb.split_count(s.oc, s.oh, s.ow) == slices == oracle.split_count(s.oc, s.oh, s.ow)
+    dw = torch.empty((s.oc, s.kh, s.kw, s.c), dtype=torch.int8, device="cuda:0")
+    nb.conv_dw_split(to_desc(s), dev(nhwc(g[f"sp{i}.x"])), dev(nhwc(g[f"sp{i}.dy"])), slices, dw)
+    torch.cuda.synchronize()
+    assert np.array_equal(nchw(dw.cpu().numpy()), g[f"sp{i}.dw"])
+
+
+@pytest.mark.parametrize("slices", [1, 2, 3, 8, 32])
+@pytest.mark.parametrize("mags", [(0, 1, 5), (100, 1 << 12, 1 << 20), (3, 3, 3), ((1 << 30) + 7, 2, 0)])
+def test_rescale_grad_split_vs_oracle(nb, oracle, slices, mags):
+    """the split rule alone, over magnitudes that put slices up to 30 bits apart (1 << 31 divisor wraps like the x86 build)"""
+    import torch
+    rng = np.random.default_rng(slices * 7 + len(mags))
+    per = 1000
+    acc = np.zeros((slices, per), np.int32)
+    for sl in range(slices):
+        m = mags[sl % len(mags)]
+        if m:
+            acc[sl] = rng.integers(-m, m + 1, size=per)
+            acc[sl, 0] = m
+    want = oracle.rescale_grad_split(acc, slices)
+    a = torch.from_numpy(acc.reshape(-1)).cuda()
+    mx = torch.zeros(slices, dtype=torch.int32, device="cuda:0")
+    for sl in range(slices):
+        nb.absmax(a[sl * per:(sl + 1) * per], per, mx[sl:sl + 1])
+    out = torch.empty(slices * per, dtype=torch.int8, device="cuda:0")
+    nb.rescale_grad_split(a, per, slices, mx, 3, out)
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy().reshape(slices, per), want)
+
+
 # ------------------------------------------------------------------ rescale / update kernels
 @pytest.mark.parametrize("n", [0, 1, 15, 16, 17, 4096, 100003])
 @pytest.mark.parametrize("mag", [0, 1, 3, 100, 128, 129, 255, 256, 257, 1 << 14, (1 << 23) + 7, (1 << 30) + 5])

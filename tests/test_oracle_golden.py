@@ -123,3 +123,34 @@ def test_dsp_requant_known_answers_and_restatement(oracle):
             assert s1 == s2 and np.array_equal(got, want), (mag, div)
     out, shift = oracle.rescale_dsp(np.zeros(0, dtype=np.int32), 1)
     assert out.size == 0 and shift == 0
+
+
+# ---- a4: OpType_NITI_MatMul_Int8, pinned by reference outputs (tests/golden/make_golden.py, ref_matmul) -------------
+@pytest.mark.parametrize("i", range(6))
+def test_matmul_matches_reference(oracle, golden_mm, i):
+    g = golden_mm
+    e, l, h = (int(v) for v in g[f"mm{i}.dims"])
+    a = oracle.matmul_unpack_a(g[f"mm{i}.a_raw"], e, l)         # the execution's own [l/4][e][4] addressing of A
+    c, acc = oracle.matmul_nt(a, g[f"mm{i}.b"])
+    assert np.array_equal(oracle.matmul_pack_c(c, e, h), g[f"mm{i}.c_raw"])
+    if i == 5:
+        assert not c.any()                                       # b == 0 -> zeros (Q2)
+
+
+# ---- a5: OpType_NITI_GradientSplitCONV_Int8 (per-slice exponents + alignment) ----------------------------------------
+@pytest.mark.parametrize("i", range(4))
+def test_gradient_split_conv_matches_reference(oracle, golden_split, i):
+    g = golden_split
+    s = ConvShape(*[int(v) for v in g[f"sp{i}.shape"]])
+    slices = int(g[f"sp{i}.slices"])
+    assert oracle.split_count(s.oc, s.oh, s.ow) == slices
+    dw, k = oracle.conv_dw_split(s, g[f"sp{i}.x"], g[f"sp{i}.dy"])
+    assert k == slices and np.array_equal(dw, g[f"sp{i}.dw"])
+    assert np.array_equal(oracle.conv_dw(s, g[f"sp{i}.x"], g[f"sp{i}.dy"])[0], g[f"sp{i}.dw_unsplit"])
+
+
+def test_split_cases_cover_the_rule(golden_split):
+    counts = sorted(int(golden_split[f"sp{i}.slices"]) for i in range(4))
+    assert counts == [1, 2, 2, 4]
+    # the alignment really divides somewhere, and a zero slice exists
+    assert any(not np.array_equal(golden_split[f"sp{i}.dw"], golden_split[f"sp{i}.dw_unsplit"]) for i in range(4))

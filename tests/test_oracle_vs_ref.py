@@ -66,3 +66,28 @@ def test_live_reference_training_steps(oracle, ref):
     for a, (b, _) in zip(out["weights"], w2):
         assert np.array_equal(a, b)
     assert np.all(np.isfinite(out["loss"]))
+
+
+@pytest.mark.parametrize("dims", [(36, 64, 8), (52, 100, 16), (25 * 4, 36, 20)])
+def test_live_reference_matmul(oracle, ref, dims):
+    """OpType_NITI_MatMul_Int8 as NITI_GeometryConv2DBackPropFilter_Int8.cpp:78-126 emits it (transposeB), created with
+    Expr::create in ref_driver.cpp; A / C are addressed as [channel/4][batch][4] blocks by the execution itself."""
+    e, l, h = dims
+    rng = np.random.default_rng(e)
+    a_raw = rng.integers(-127, 128, size=e * l, dtype=np.int8)
+    b = rng.integers(-90, 91, size=(h, l), dtype=np.int8)
+    c, _ = oracle.matmul_nt(oracle.matmul_unpack_a(a_raw, e, l), b)
+    assert np.array_equal(oracle.matmul_pack_c(c, e, h), ref.matmul_raw(a_raw, b, e, l, h))
+
+
+@pytest.mark.parametrize("cfg", [(4, 8, 16, 48, 3, 1), (2, 4, 20, 48, 3, 1), (2, 8, 12, 24, 3, 1)])
+def test_live_reference_gradient_split_conv(oracle, ref, cfg):
+    n, c, hh, oc, k, pad = cfg
+    s = shape(n, c, hh, hh, oc, k, stride=1, pad=pad)
+    rng = np.random.default_rng(oc + hh)
+    x = rng.integers(-127, 128, size=(n, c, hh, hh), dtype=np.int8)
+    dy = rng.integers(-50, 51, size=(n, oc, s.oh, s.ow), dtype=np.int8)
+    dy[:, oc // 2:] //= 4
+    dw, slices = oracle.conv_dw_split(s, x, dy)
+    assert np.array_equal(dw, ref.grad_conv(s, x, dy, split=True))
+    assert np.array_equal(oracle.conv_dw(s, x, dy)[0], ref.grad_conv(s, x, dy, split=False))
