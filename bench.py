@@ -52,7 +52,8 @@ def reference_step_fn(workload, batch):
     built (kind "reference"), else the C oracle port (kind "port", 1 core)."""
     import numpy as np
     from oracle.oracle import Oracle, Reference, shape
-    from mandheling_dsp_training_b200.step import SPECS, niti_xavier_int8, oracle_step
+    from mandheling_dsp_training_b200.step import SPECS, niti_xavier_int8
+    from oracle.step_twin import oracle_step
     spec_fn, chw = SPECS[WORKLOADS[workload][0]]
     spec = spec_fn()
     rng = np.random.default_rng(0)

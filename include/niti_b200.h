@@ -14,8 +14,18 @@
  *   accumulators            : int32, same index order as the int8 tensor they rescale into
  *   exponents               : int8 scalars in device memory (quirk Q7: carried beside each tensor)
  *   max-abs                 : uint32 scalar in device memory (input of the shared-exponent step)
- * Everything is asynchronous on the given stream and CUDA-graph capturable: no host sync, no
- * allocation, no host-visible scalar on the path.
+ * Everything is asynchronous on the given stream and CUDA-graph capturable: no host sync and no
+ * host-visible scalar on the path.  Allocation: the phase-1/phase-2 and fused entry points allocate nothing; the whole-op
+ * conveniences that take no scratch pointer (niti_conv_fwd/dx/dw, niti_matmul_nt, niti_conv_dw_split, a NULL `acc`, a
+ * NULL `wt`) grow a context workspace with cudaMalloc on first use — call them once eagerly before capturing (under
+ * capture the growth fails with NITI_ERR_CUDA rather than corrupting the graph), and re-capture after a call that grew it.
+ *
+ * Concurrency rule: the persistent kernels behind niti_conv_fwd_fused, niti_conv_dx_fused, niti_conv_fwd/dx[_acc] (split-K),
+ * niti_conv_dw[_acc] and niti_update_batched hold a grid-wide barrier whose counters belong to the context.  At most ONE
+ * such call of a context may be in flight at a time: issue them on one stream, or order streams with events.  (A second
+ * one running concurrently could share SMs with the first and neither barrier would ever fill; the spin is bounded and a
+ * barrier that gives up sets a sticky flag, niti_sync_error.)  niti_conv_dw_accumulate holds no barrier and may run beside
+ * them — that is how a training step overlaps dW with the dX chain.
  *
  * There is NO CPU fallback: every entry point fails with NITI_ERR_CUDA when no device is usable.
  */
@@ -119,12 +129,20 @@ int niti_rescale_act_dp(niti_ctx*, const int32_t* acc, size_t n, const uint32_t*
  *   niti_dp_alloc    allocates this rank's exchange buffer and returns its 64-byte CUDA IPC handle
  *   niti_dp_connect  maps every rank's buffer (handles = world x 64 bytes, rank-ordered, gathered by the host)
  *   niti_dp_step_begin bumps the device-side step epoch; call once at the start of every step (graph-capturable)
- *   niti_dp_error    *out != 0 when a peer never answered (its process died): results since then are invalid */
+ *   niti_dp_error    *out != 0 when a peer did not answer within the spin budget (NITI_B200_DP_TIMEOUT_MS, default 60000):
+ *                    results since the last clean poll are invalid.  Hosts poll it at their sync points. */
 int niti_dp_alloc(niti_ctx*, unsigned char handle_out[64]);
 int niti_dp_connect(niti_ctx*, int rank, int world, const unsigned char* handles);
 int niti_dp_close(niti_ctx*);
 int niti_dp_step_begin(niti_ctx*, niti_stream);
 int niti_dp_error(niti_ctx*, int* out);
+/* SMs the library leaves free for the collective kernels running beside the contractions once niti_dp_connect was called
+ * with world > 1 (NITI_B200_DP_RESERVE_SMS, default 16).  The collective library must be capped at no more CTAs than this
+ * (NCCL_MAX_CTAS): with more, its CTAs wait for SMs held by kernels that are themselves waiting on a peer. */
+int niti_dp_reserved_sms(niti_ctx*);
+/* *out != 0 when a grid-wide barrier of one of this context's persistent kernels gave up (see the concurrency rule at the
+ * top): every result since the last clean poll is invalid.  Synchronises with the device. */
+int niti_sync_error(niti_ctx*, int* out);
 /* rule B — dW / matmul (NITI_GradientConv_Int8.cpp:274-296 sub=2; NITI_Matmul_Int8.cpp:216-228 sub=3):
  *   b==0: zeros; else PSTO(b-sub).  dw_out optional; when w_inout is given the int8 SGD step
  *   w <- clip127(w - dw) (optimizer/NITI_SGD.hpp:49-52, BinaryUtils.hpp:276-299) is fused. */

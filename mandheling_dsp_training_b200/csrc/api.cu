@@ -68,6 +68,21 @@ int niti_fail(niti_ctx* ctx, int code, const char* what, cudaError_t e) {
     return code;
 }
 
+int niti_func_smem(niti_ctx* ctx, const void* fn, int bytes, const char* what) {
+    for (int i = 0; i < ctx->n_smem_cfg; ++i)
+        if (ctx->smem_cfg[i].fn == fn) {
+            if (ctx->smem_cfg[i].bytes >= bytes) return NITI_OK;
+            cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+            if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, what, e);
+            ctx->smem_cfg[i].bytes = bytes;
+            return NITI_OK;
+        }
+    cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, what, e);
+    if (ctx->n_smem_cfg < 64) { ctx->smem_cfg[ctx->n_smem_cfg].fn = fn; ctx->smem_cfg[ctx->n_smem_cfg].bytes = bytes; ctx->n_smem_cfg++; }
+    return NITI_OK;
+}
+
 int niti_check_launch(niti_ctx* ctx, const char* what) {
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, what, e);
@@ -129,6 +144,7 @@ int niti_ctx_create(int device, niti_ctx** out) {
     memset(ctx, 0, sizeof(*ctx));
     ctx->device = device;
     ctx->sm_count = prop.multiProcessorCount;
+    ctx->sm_total = prop.multiProcessorCount;
     ctx->path = NITI_PATH_AUTO;
     const char* env = getenv("NITI_B200_PATH");
     if (env && !strcmp(env, "simt")) ctx->path = NITI_PATH_SIMT;
@@ -393,6 +409,15 @@ int niti_stream_sync(niti_ctx* ctx, niti_stream st) {
     if (!ctx) return NITI_ERR_ARG;
     cudaError_t e = cudaStreamSynchronize((cudaStream_t)st);
     return e == cudaSuccess ? NITI_OK : niti_fail(ctx, NITI_ERR_CUDA, "niti_stream_sync", e);
+}
+
+int niti_sync_error(niti_ctx* ctx, int* out) {
+    if (!ctx || !out) return niti_fail(ctx, NITI_ERR_ARG, "niti_sync_error");
+    uint32_t v = 0;
+    cudaError_t e = cudaMemcpy(&v, ctx->ws_u32 + 63, sizeof(v), cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "niti_sync_error", e);
+    *out = (int)v;
+    return NITI_OK;
 }
 
 int niti_debug_trace(niti_ctx* ctx, unsigned long long* device_buf) {

@@ -11,7 +11,8 @@
 
 struct niti_ctx {
     int device;
-    int sm_count;
+    int sm_count;             // SMs the persistent kernels size their grids for (device SMs minus the data-parallel reserve)
+    int sm_total;             // SMs of the device
     int path;                 // NITI_PATH_*
     int auto_tma2;            // AUTO prefers the CTA-pair kernels where eligible
     int pdl;                  // programmatic dependent launch on the step's kernel chain (NITI_B200_PDL: bit mask of NITI_PDL_* kernel classes, default NITI_PDL_FUSED | NITI_PDL_TRIGGER_LATE — measured best)
@@ -25,6 +26,10 @@ struct niti_ctx {
     // data-parallel scalar exchange over peer memory (dp.cuh); world <= 1 when not connected
     DpBuffer* dp_buf;
     DpView dp;
+    int dp_reserve;           // SMs left to the concurrent collective (dp.cu)
+    // kernels whose dynamic shared memory limit was raised on THIS device (function attributes are per device)
+    struct { const void* fn; int bytes; } smem_cfg[64];
+    int n_smem_cfg;
     // optional phase trace (niti_debug_trace): kernels that support it write %globaltimer stamps [block][8] here
     unsigned long long* trace;
 };
@@ -65,7 +70,34 @@ inline cudaError_t niti_launch(const niti_ctx* ctx, int cls, void (*kernel)(KArg
     return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Grid-wide barrier of the persistent kernels (every CTA resident: grid <= SM count, one CTA per SM by shared-memory
+// size).  One thread per CTA.  The counters live in ctx->ws_u32 (64 words, 256-byte aligned); word 63 of that block is the
+// context's sticky sync-error flag: a barrier that is not released within ~20 s (another barrier-holding kernel of the same
+// context running concurrently on a second stream, SMs taken by another process) sets it and falls through instead of
+// hanging the device.  Hosts read it with niti_sync_error.  RULE (niti_b200.h): at most one barrier-holding call of a
+// context in flight at a time.
+// ---------------------------------------------------------------------------------------------
+constexpr long long kGridBarrierTimeoutCycles = 40000000000LL;
+__device__ __forceinline__ uint32_t* niti_sync_error_word(uint32_t* counter) {
+    return reinterpret_cast<uint32_t*>(reinterpret_cast<uintptr_t>(counter) & ~(uintptr_t)255) + 63;
+}
+__device__ __forceinline__ void niti_grid_barrier(uint32_t* counter, uint32_t target) {
+    __threadfence();
+    atomicAdd(counter, 1u);
+    if (*reinterpret_cast<volatile uint32_t*>(counter) < target) {
+        const long long t0 = clock64();
+        while (*reinterpret_cast<volatile uint32_t*>(counter) < target) {
+            __nanosleep(32);
+            if (clock64() - t0 > kGridBarrierTimeoutCycles) { atomicExch(niti_sync_error_word(counter), 1u); break; }
+        }
+    }
+    __threadfence();
+}
+
 int  niti_fail(niti_ctx* ctx, int code, const char* what, cudaError_t e = cudaSuccess);
+// raise a kernel's dynamic shared-memory limit once per context (= per device)
+int  niti_func_smem(niti_ctx* ctx, const void* fn, int bytes, const char* what);
 int  niti_check_launch(niti_ctx* ctx, const char* what);
 int  niti_ws_acc(niti_ctx* ctx, size_t bytes, int32_t** out);
 int  niti_ws_i8(niti_ctx* ctx, size_t bytes, int8_t** out);

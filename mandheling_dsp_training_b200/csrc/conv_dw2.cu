@@ -236,12 +236,7 @@ template <int BKC, int G>
 int launch_dw2(niti_ctx* ctx, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& d, const Dw2Params& p, int grid,
                cudaStream_t st) {
     using C = DwCfg<BKC, G>;
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(dw2_kernel<BKC, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
-        if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "cudaFuncSetAttribute(dw2)", e);
-        configured = true;
-    }
+    if (int rc_cfg = niti_func_smem(ctx, (const void*)dw2_kernel<BKC, G>, C::SMEM, "cudaFuncSetAttribute(dw2)")) return rc_cfg;
     dw2_kernel<BKC, G><<<grid, kDwThreads, C::SMEM, st>>>(a, b, d, p);
     return niti_check_launch(ctx, "dw2");
 }

@@ -198,31 +198,7 @@ stem_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
                 asm volatile("bar.sync 1, 512;" ::: "memory");
                 if (etid == 0) {
                     tmax::grid_barrier(p.sync, gridDim.x);
-                    uint32_t m = __ldcg(p.maxabs);
-                    if (p.dp.world > 1) {
-                        DpBuffer* mine = p.dp.peer[p.dp.rank];
-                        const uint32_t epoch = *reinterpret_cast<volatile uint32_t*>(&mine->epoch);
-                        if (blockIdx.x == 0) {
-                            const unsigned long long w = ((unsigned long long)epoch << 32) | (unsigned long long)m;
-                            for (int r = 0; r < p.dp.world; ++r) {
-                                unsigned long long* dst = &p.dp.peer[r]->word[p.dp_slot][p.dp.rank];
-                                asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(dst), "l"(w) : "memory");
-                            }
-                        }
-                        const long long t0 = clock64();
-                        for (int r = 0; r < p.dp.world; ++r) {
-                            if (r == p.dp.rank) continue;
-                            const unsigned long long* src = &mine->word[p.dp_slot][r];
-                            unsigned long long w;
-                            for (;;) {
-                                asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(w) : "l"(src) : "memory");
-                                if ((uint32_t)(w >> 32) == epoch) break;
-                                if (clock64() - t0 > 4000000000LL) { mine->error = 1u; w = 0; break; }
-                                __nanosleep(100);
-                            }
-                            m = max(m, (uint32_t)w);
-                        }
-                    }
+                    const uint32_t m = dp_exchange_max(p.dp, p.dp_slot, __ldcg(p.maxabs), blockIdx.x == 0);
                     *bcast = m;
                 }
                 asm volatile("bar.sync 1, 512;" ::: "memory");
@@ -286,12 +262,7 @@ int stem_conv_fwd_fused(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x,
     if (!tmax::make_tiled_u8(&mb, w, (uint64_t)d->oc, (uint64_t)p.taps * 16, (uint32_t)d->oc, 16, 0))
         return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncodeTiled(w, stem) failed");
     const int smem = kStemStages * kTapsPerBlock * 2048 + ((p.taps_p * d->oc * 16 + 127) & ~127) + 512 + 1024;
-    static int configured = 0;
-    if (configured < smem) {
-        cudaError_t e = cudaFuncSetAttribute(stem_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "cudaFuncSetAttribute(stem_fwd)", e);
-        configured = smem;
-    }
+    if (int rc_cfg = niti_func_smem(ctx, (const void*)stem_fwd_kernel, (int)(smem), "cudaFuncSetAttribute(stem_fwd)")) return rc_cfg;
     const int grid = p.m_tiles < ctx->sm_count ? p.m_tiles : ctx->sm_count;
     cudaError_t lerr = niti_launch(ctx, NITI_PDL_STEM, stem_fwd_kernel, dim3(grid), dim3(kStemThreads), (size_t)smem, st, ma, mb, p);
     if (lerr != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "launch stem_fwd", lerr);

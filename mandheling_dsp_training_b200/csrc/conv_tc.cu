@@ -351,12 +351,7 @@ __global__ void __launch_bounds__(kThreads) probe_kernel(int iters) {
 
 template <int BN>
 int launch_kmajor(niti_ctx* ctx, const TcParams& p, cudaStream_t st) {
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(igemm_kmajor_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<BN>());
-        if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "cudaFuncSetAttribute(igemm_kmajor)", e);
-        configured = true;
-    }
+    if (int rc_cfg = niti_func_smem(ctx, (const void*)igemm_kmajor_kernel<BN>, (int)(smem_bytes<BN>()), "cudaFuncSetAttribute(igemm_kmajor)")) return rc_cfg;
     dim3 grid((unsigned)((p.M + BM - 1) / BM), (unsigned)((p.Ncols + BN - 1) / BN));
     igemm_kmajor_kernel<BN><<<grid, kThreads, smem_bytes<BN>(), st>>>(p);
     return niti_check_launch(ctx, "igemm_kmajor");
@@ -414,12 +409,7 @@ int tc_conv_dx_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* dy, con
 int tc_conv_dw_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, const int8_t* dy, int32_t* acc,
                    uint32_t* maxabs, cudaStream_t st) {
     constexpr int BN = 128;
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(dw_mnmajor_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<BN>());
-        if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "cudaFuncSetAttribute(dw_mnmajor)", e);
-        configured = true;
-    }
+    if (int rc_cfg = niti_func_smem(ctx, (const void*)dw_mnmajor_kernel<BN>, (int)(smem_bytes<BN>()), "cudaFuncSetAttribute(dw_mnmajor)")) return rc_cfg;
     const int oh = conv_out_h(d), ow = conv_out_w(d);
     TcParams p{};
     p.A = dy; p.B = x; p.acc = acc; p.maxabs = nullptr;
@@ -453,16 +443,17 @@ int tc_probe_i8_peak(niti_ctx* ctx, int iters, double* tops) {
     cudaError_t e = cudaFuncSetAttribute(probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "probe attr", e);
     cudaEvent_t t0, t1; cudaEventCreate(&t0); cudaEventCreate(&t1);
-    probe_kernel<<<ctx->sm_count, kThreads, smem>>>(iters / 4 + 1);      // warm-up
+    // every SM of the device, whatever the data-parallel reserve: the roofline denominator must not depend on N
+    probe_kernel<<<ctx->sm_total, kThreads, smem>>>(iters / 4 + 1);      // warm-up
     cudaEventRecord(t0);
-    probe_kernel<<<ctx->sm_count, kThreads, smem>>>(iters);
+    probe_kernel<<<ctx->sm_total, kThreads, smem>>>(iters);
     cudaEventRecord(t1);
     e = cudaEventSynchronize(t1);
     if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "probe run", e);
     float ms = 0; cudaEventElapsedTime(&ms, t0, t1);
     cudaEventDestroy(t0); cudaEventDestroy(t1);
     ctx->launches += 2;
-    double ops = 2.0 * 128 * 256 * 128 * (double)iters * ctx->sm_count;
+    double ops = 2.0 * 128 * 256 * 128 * (double)iters * ctx->sm_total;
     *tops = ops / (ms * 1e-3) / 1e12;
     return NITI_OK;
 }

@@ -281,12 +281,7 @@ bool make_im2col(CUtensorMap* m, const void* base, int n, int h, int w, int c, i
 template <int BN, int BKC, int MODE>
 int launch(niti_ctx* ctx, const CUtensorMap& a, const CUtensorMap& b, const TmaParams& p, dim3 grid, cudaStream_t st) {
     using C = Cfg<BN, BKC, MODE>;
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(igemm_tma_kernel<BN, BKC, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
-        if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "cudaFuncSetAttribute(igemm_tma)", e);
-        configured = true;
-    }
+    if (int rc_cfg = niti_func_smem(ctx, (const void*)igemm_tma_kernel<BN, BKC, MODE>, C::SMEM, "cudaFuncSetAttribute(igemm_tma)")) return rc_cfg;
     igemm_tma_kernel<BN, BKC, MODE><<<grid, kThreads, C::SMEM, st>>>(a, b, p);
     return niti_check_launch(ctx, "igemm_tma");
 }

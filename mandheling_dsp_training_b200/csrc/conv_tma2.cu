@@ -114,13 +114,7 @@ __device__ __forceinline__ uint64_t make_desc2(uint32_t addr, uint32_t lbo, uint
 
 __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async;" ::: "memory"); }
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }      // the 4 epilogue warps
-// Grid-wide barrier for the persistent grid (every CTA is resident: grid <= SM count, 1 CTA/SM).  One thread per CTA.
-__device__ __forceinline__ void grid_barrier(uint32_t* counter, uint32_t target) {
-    __threadfence();
-    atomicAdd(counter, 1u);
-    while (*reinterpret_cast<volatile uint32_t*>(counter) < target) { __nanosleep(32); }
-    __threadfence();
-}
+__device__ __forceinline__ void grid_barrier(uint32_t* counter, uint32_t target) { niti_grid_barrier(counter, target); }   // common.cuh
 
 template <int BN, int BKC> struct Cfg2 {
     static constexpr int A_BYTES = 128 * BKC;               // this CTA's 128 im2col rows
@@ -377,12 +371,7 @@ bool make_im2col2(CUtensorMap* m, const void* base, int n, int h, int w, int c, 
 template <int BN, int BKC>
 int launch2(niti_ctx* ctx, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& d, const Tma2Params& p, int pairs, cudaStream_t st) {
     using C = Cfg2<BN, BKC>;
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(igemm_tma2_kernel<BN, BKC>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
-        if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "cudaFuncSetAttribute(igemm_tma2)", e);
-        configured = true;
-    }
+    if (int rc = niti_func_smem(ctx, (const void*)igemm_tma2_kernel<BN, BKC>, C::SMEM, "cudaFuncSetAttribute(igemm_tma2)")) return rc;
     igemm_tma2_kernel<BN, BKC><<<dim3(2 * pairs), kThreads2, C::SMEM, st>>>(a, b, d, p);
     return niti_check_launch(ctx, "igemm_tma2");
 }
@@ -650,31 +639,7 @@ igemm_fused_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
                     niti_trace(e.trace, 3);
                     grid_barrier(e.sync, gridDim.x);
                     niti_trace(e.trace, 4);
-                    uint32_t m = __ldcg(p.maxabs);
-                    if (e.dp.world > 1) {
-                        DpBuffer* mine = e.dp.peer[e.dp.rank];
-                        const uint32_t epoch = *reinterpret_cast<volatile uint32_t*>(&mine->epoch);
-                        if (blockIdx.x == 0) {
-                            const unsigned long long w = ((unsigned long long)epoch << 32) | (unsigned long long)m;
-                            for (int r = 0; r < e.dp.world; ++r) {
-                                unsigned long long* dst = &e.dp.peer[r]->word[e.dp_slot][e.dp.rank];
-                                asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(dst), "l"(w) : "memory");
-                            }
-                        }
-                        const long long t0 = clock64();
-                        for (int r = 0; r < e.dp.world; ++r) {
-                            if (r == e.dp.rank) continue;
-                            const unsigned long long* src = &mine->word[e.dp_slot][r];
-                            unsigned long long w;
-                            for (;;) {
-                                asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(w) : "l"(src) : "memory");
-                                if ((uint32_t)(w >> 32) == epoch) break;
-                                if (clock64() - t0 > 4000000000LL) { mine->error = 1u; w = 0; break; }
-                                __nanosleep(100);
-                            }
-                            m = max(m, (uint32_t)w);
-                        }
-                    }
+                    const uint32_t m = dp_exchange_max(e.dp, e.dp_slot, __ldcg(p.maxabs), blockIdx.x == 0);
                     *bcast = m;
                 }
                 asm volatile("bar.sync 1, 512;" ::: "memory");
@@ -726,12 +691,7 @@ int launch_fused(niti_ctx* ctx, const CUtensorMap& a, const CUtensorMap& b, cons
     // once programmatic dependent launch places CTAs on partly occupied SMs) would deadlock — the second blocks in
     // tcgen05.alloc while the first waits for it at the barrier.
     constexpr size_t kSmemReq = C::SMEM > 120 * 1024 ? (size_t)C::SMEM : (size_t)120 * 1024;
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t err = cudaFuncSetAttribute(igemm_fused_kernel<BN, BKC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemReq);
-        if (err != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "cudaFuncSetAttribute(igemm_fused)", err);
-        configured = true;
-    }
+    if (int rc = niti_func_smem(ctx, (const void*)igemm_fused_kernel<BN, BKC>, (int)kSmemReq, "cudaFuncSetAttribute(igemm_fused)")) return rc;
     cudaError_t lerr = niti_launch(ctx, NITI_PDL_FUSED, igemm_fused_kernel<BN, BKC>, dim3(2 * pairs), dim3(kFusedThreads), kSmemReq, st, a, b, p, e);
     if (lerr != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "launch igemm_fused", lerr);
     return niti_check_launch(ctx, "igemm_fused");

@@ -30,6 +30,15 @@ extern "C" int niti_dp_connect(niti_ctx* ctx, int rank, int world, const unsigne
         return niti_fail(ctx, NITI_ERR_ARG, "niti_dp_connect: bad argument (call niti_dp_alloc first; world <= 8)");
     DpView v{};
     v.world = world; v.rank = rank;
+    {   // spin budget of one exchange: generous, because ordinary first-step skew between ranks (lazy module load, NCCL
+        // communicator set-up, workspace growth on one rank) is seconds; a dead peer still surfaces through niti_dp_error
+        const char* t = getenv("NITI_B200_DP_TIMEOUT_MS");
+        const double ms = t ? atof(t) : 60000.0;
+        int khz = 0; cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, ctx->device);
+        if (khz <= 0) khz = 2000000;
+        v.timeout_cycles = (long long)(ms * (double)khz);
+        if (v.timeout_cycles < 1000) v.timeout_cycles = 1000;
+    }
     for (int r = 0; r < world; ++r) {
         if (r == rank) { v.peer[r] = ctx->dp_buf; continue; }
         cudaIpcMemHandle_t h;
@@ -48,8 +57,10 @@ extern "C" int niti_dp_connect(niti_ctx* ctx, int rank, int world, const unsigne
         // collective's CTAs wait for SMs held by contraction kernels that are themselves spinning on a peer (max exchange,
         // grid barrier) — measured 4xB200 with reserve 8 / 16 NCCL CTAs: 51.7 ms per step instead of 1.0.
         const int reserve = env ? atoi(env) : 16;
-        if (reserve >= 0 && reserve < ctx->sm_count / 2) ctx->sm_count -= reserve;
+        ctx->sm_count = ctx->sm_total;                    // recomputed from the device's SM count: connecting twice reserves once
+        if (reserve >= 0 && reserve < ctx->sm_total / 2) ctx->sm_count -= reserve;
         ctx->sm_count &= ~1;                              // CTA pairs
+        ctx->dp_reserve = ctx->sm_total - ctx->sm_count;
     }
     return NITI_OK;
 }
@@ -59,6 +70,8 @@ extern "C" int niti_dp_close(niti_ctx* ctx) {
     for (int r = 0; r < ctx->dp.world; ++r)
         if (r != ctx->dp.rank && ctx->dp.peer[r]) cudaIpcCloseMemHandle(ctx->dp.peer[r]);
     ctx->dp = DpView{};
+    ctx->sm_count = ctx->sm_total;
+    ctx->dp_reserve = 0;
     return NITI_OK;
 }
 
@@ -67,6 +80,9 @@ extern "C" int niti_dp_step_begin(niti_ctx* ctx, niti_stream st) {
     dp_step_begin_kernel<<<1, 1, 0, (cudaStream_t)st>>>(ctx->dp_buf);
     return niti_check_launch(ctx, "dp_step_begin");
 }
+
+// SMs left free for the collective kernels that run beside the contractions (0 when not connected)
+extern "C" int niti_dp_reserved_sms(niti_ctx* ctx) { return ctx ? ctx->dp_reserve : 0; }
 
 extern "C" int niti_dp_error(niti_ctx* ctx, int* out) {
     if (!ctx || !out || !ctx->dp_buf) return niti_fail(ctx, NITI_ERR_ARG, "niti_dp_error");

@@ -27,36 +27,47 @@ struct DpBuffer {
 struct DpView {                                       // passed by value to kernels
     DpBuffer* peer[kDpMaxWorld];                      // peer[r] = rank r's buffer as mapped in this process
     int world, rank;
+    long long timeout_cycles;                         // spin budget per exchange (niti_dp_connect: NITI_B200_DP_TIMEOUT_MS, default 60 s)
 };
+
+// The exchange itself, run by ONE thread of the launch's publishing CTA (`publish`) and by one thread of every CTA that
+// needs the result: store (epoch << 32 | local) into every rank's buffer, then spin on the local copy of each peer's word
+// until it carries this step's epoch.  Returns the max over ranks.  A peer that never answers within timeout_cycles
+// (its process died, or it is stuck behind something that waits for us) sets DpBuffer.error — sticky, read by
+// niti_dp_error; hosts poll it at their sync points and must treat everything since the last clean poll as invalid.
+__device__ __forceinline__ uint32_t dp_exchange_max(const DpView& v, int slot, uint32_t local, bool publish) {
+    if (v.world <= 1) return local;
+    DpBuffer* mine = v.peer[v.rank];
+    const uint32_t epoch = *reinterpret_cast<volatile uint32_t*>(&mine->epoch);
+    if (publish) {
+        const unsigned long long w = ((unsigned long long)epoch << 32) | (unsigned long long)local;
+        for (int r = 0; r < v.world; ++r) {
+            unsigned long long* dst = &v.peer[r]->word[slot][v.rank];
+            asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(dst), "l"(w) : "memory");
+        }
+    }
+    uint32_t m = local;
+    const long long t0 = clock64();
+    for (int r = 0; r < v.world; ++r) {
+        if (r == v.rank) continue;
+        const unsigned long long* src = &mine->word[slot][r];
+        unsigned long long w;
+        for (;;) {
+            asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(w) : "l"(src) : "memory");
+            if ((uint32_t)(w >> 32) == epoch) break;
+            if (clock64() - t0 > v.timeout_cycles) { mine->error = 1u; w = 0; break; }
+            __nanosleep(100);
+        }
+        m = max(m, (uint32_t)w);
+    }
+    return m;
+}
 
 // returns max over ranks of `local`; must be called by ALL threads of the block (uses one __shared__ word).
 // Block 0 publishes.  world <= 1: returns local.
 __device__ __forceinline__ uint32_t dp_allreduce_max(const DpView& v, int slot, uint32_t local, uint32_t* sh) {
     if (v.world <= 1) return local;
-    DpBuffer* mine = v.peer[v.rank];
-    const uint32_t epoch = *reinterpret_cast<volatile uint32_t*>(&mine->epoch);
-    if (blockIdx.x == 0 && (int)threadIdx.x < v.world) {
-        const unsigned long long w = ((unsigned long long)epoch << 32) | (unsigned long long)local;
-        unsigned long long* dst = &v.peer[threadIdx.x]->word[slot][v.rank];
-        asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(dst), "l"(w) : "memory");
-    }
-    if (threadIdx.x == 0) {
-        uint32_t m = local;
-        const long long t0 = clock64();
-        for (int r = 0; r < v.world; ++r) {
-            if (r == v.rank) continue;
-            const unsigned long long* src = &mine->word[slot][r];
-            unsigned long long w;
-            for (;;) {
-                asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(w) : "l"(src) : "memory");
-                if ((uint32_t)(w >> 32) == epoch) break;
-                if (clock64() - t0 > 4000000000LL) { mine->error = 1u; w = 0; break; }     // ~2 s: peer is gone
-                __nanosleep(100);
-            }
-            m = max(m, (uint32_t)w);
-        }
-        *sh = m;
-    }
+    if (threadIdx.x == 0) *sh = dp_exchange_max(v, slot, local, blockIdx.x == 0);
     __syncthreads();
     return *sh;
 }

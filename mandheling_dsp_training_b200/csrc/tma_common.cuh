@@ -57,12 +57,8 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t addr, uint32_t lbo, uint3
 }
 
 // Grid-wide barrier for a persistent grid whose CTAs are all resident (grid <= SM count at 1 CTA/SM).  One thread per CTA.
-__device__ __forceinline__ void grid_barrier(uint32_t* counter, uint32_t target) {
-    __threadfence();
-    atomicAdd(counter, 1u);
-    while (*reinterpret_cast<volatile uint32_t*>(counter) < target) { __nanosleep(32); }
-    __threadfence();
-}
+// (common.cuh niti_grid_barrier: bounded spin, sets the context's sync-error flag instead of hanging.)
+__device__ __forceinline__ void grid_barrier(uint32_t* counter, uint32_t target) { niti_grid_barrier(counter, target); }
 
 // ---- host: tensor-map encoders --------------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,

@@ -26,12 +26,7 @@ struct UpdSegs {
     int n;
 };
 
-__device__ __forceinline__ void grid_barrier_upd(uint32_t* counter, uint32_t target) {
-    __threadfence();
-    atomicAdd(counter, 1u);
-    while (*reinterpret_cast<volatile uint32_t*>(counter) < target) { __nanosleep(64); }
-    __threadfence();
-}
+__device__ __forceinline__ void grid_barrier_upd(uint32_t* counter, uint32_t target) { niti_grid_barrier(counter, target); }
 
 __device__ __forceinline__ uint32_t pack4u(int32_t a, int32_t b, int32_t c, int32_t d) {
     return (uint32_t)(a & 0xff) | ((uint32_t)(b & 0xff) << 8) | ((uint32_t)(c & 0xff) << 16) | ((uint32_t)(d & 0xff) << 24);
@@ -182,8 +177,8 @@ update_batched_kernel(const __grid_constant__ UpdSegs S, uint32_t* sync) {
 
 extern "C" int niti_update_batched(niti_ctx* ctx, const niti_update_seg* segs, int nseg, niti_stream st) {
     if (!ctx || !segs || nseg <= 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_update_batched: bad argument");
-    static int blocks_per_sm = 0;
-    if (blocks_per_sm == 0) {
+    int blocks_per_sm = 0;                                    // occupancy is a per-device property: no process-wide cache
+    {
         int occ = 0;
         cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, update_batched_kernel, kUpdThreads, 0);
         if (e != cudaSuccess || occ < 1) return niti_fail(ctx, NITI_ERR_CUDA, "niti_update_batched: occupancy query", e);

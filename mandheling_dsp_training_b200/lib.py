@@ -66,6 +66,8 @@ _SIGS = {
     "niti_dp_close": (C.c_int, [_P]),
     "niti_dp_step_begin": (C.c_int, [_P, _P]),
     "niti_dp_error": (C.c_int, [_P, C.POINTER(C.c_int)]),
+    "niti_dp_reserved_sms": (C.c_int, [_P]),
+    "niti_sync_error": (C.c_int, [_P, C.POINTER(C.c_int)]),
     "niti_sgd_update": (C.c_int, [_P, _P, _P, C.c_size_t, _P]),
     "niti_conv_fwd": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, _P]),
     "niti_conv_fwd_fused": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, C.c_int, _P, _P, C.c_int, _P]),
@@ -111,6 +113,16 @@ def _ptr(t):
     if isinstance(t, int):
         return t
     return t.data_ptr()
+
+
+def dp_env(reserve_sms=16):
+    """Environment a data-parallel job needs BEFORE torch.distributed.init_process_group("nccl"): caps NCCL at the SMs the
+    library leaves free for it (csrc/dp.cu).  Values already set are respected if they satisfy the rule."""
+    os.environ.setdefault("NITI_B200_DP_RESERVE_SMS", str(int(reserve_sms)))
+    res = int(os.environ["NITI_B200_DP_RESERVE_SMS"])
+    cap = os.environ.get("NCCL_MAX_CTAS")
+    if cap is None or not cap.isdigit() or int(cap) > res:
+        os.environ["NCCL_MAX_CTAS"] = str(res)
 
 
 class NitiB200:
@@ -223,8 +235,17 @@ class NitiB200:
 
     # ---- data-parallel scalar exchange over peer memory
     def dp_connect(self, dist):
-        """gather every rank's IPC handle through torch.distributed and map the peers' exchange buffers"""
+        """gather every rank's IPC handle through torch.distributed and map the peers' exchange buffers.
+        Enforces the SM-reserve rule of csrc/dp.cu: the collective library's CTA cap (NCCL_MAX_CTAS) must be set and must
+        not exceed the SMs the library leaves free, otherwise NCCL CTAs wait for SMs held by kernels spinning on a peer."""
         import torch
+        reserve = int(os.environ.get("NITI_B200_DP_RESERVE_SMS", "16"))
+        if dist.get_backend() == "nccl" and dist.get_world_size() > 1:
+            cap = os.environ.get("NCCL_MAX_CTAS")
+            if cap is None or not cap.isdigit() or int(cap) > reserve or int(cap) < 1:
+                raise NitiError(f"data parallel needs NCCL_MAX_CTAS set (before the process group is created) to at most "
+                                f"NITI_B200_DP_RESERVE_SMS = {reserve}; found {cap!r}.  Use lib.dp_env() before "
+                                "init_process_group.")
         h = (C.c_ubyte * 64)()
         self._ck(self.lib.niti_dp_alloc(self.h, C.cast(h, _P)))
         world, rank = dist.get_world_size(), dist.get_rank()
@@ -236,6 +257,21 @@ class NitiB200:
         self._ck(self.lib.niti_dp_connect(self.h, rank, world, C.cast(buf, _P)))
         dist.barrier()
         self.dp_connected = True
+
+    def dp_reserved_sms(self):
+        return self.lib.niti_dp_reserved_sms(self.h)
+
+    def sync_error(self):
+        v = C.c_int(0)
+        self._ck(self.lib.niti_sync_error(self.h, C.byref(v)))
+        return v.value
+
+    def check_errors(self):
+        """poll the sticky device-side error flags (synchronises): raises when a peer exchange or a grid barrier gave up"""
+        if getattr(self, "dp_connected", False) and self.dp_error():
+            raise NitiError("data-parallel max|acc| exchange timed out: a peer did not answer; replicas may have diverged")
+        if self.sync_error():
+            raise NitiError("a grid-wide barrier timed out (two barrier-holding calls of one context in flight?)")
 
     def dp_step_begin(self, stream=None):
         self._ck(self.lib.niti_dp_step_begin(self.h, self._stream(stream)))

@@ -358,6 +358,13 @@ class NitiNet:
         self.forward()
         self.backward_and_update()
 
+    def check(self):
+        """Host sync point: poll the device-side error flags (a peer exchange or a grid barrier that gave up) and raise.
+        Synchronises the device.  Data-parallel callers run it after warm-up and at the end of every timed / logged
+        region: a timed-out exchange means the replicas no longer share exponents."""
+        torch.cuda.synchronize(self.dev)
+        self.nb.check_errors()
+
     def capture(self):
         """CUDA-graph the step.  Returns a callable that replays it.  Data-parallel: the NCCL all-reduces are captured
         into the graph with the kernels (every rank must capture and replay in lock-step)."""
@@ -366,7 +373,7 @@ class NitiNet:
         with torch.cuda.stream(s):
             self.step()                                   # warm-up: workspaces grow here, not under capture
         torch.cuda.current_stream(self.dev).wait_stream(s)
-        torch.cuda.synchronize(self.dev)
+        self.check()
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):
             self.step()
@@ -375,52 +382,3 @@ class NitiNet:
     def algorithmic_ops(self):
         """2*M*N*K (unpadded) of every contraction of one step: fwd + dW per conv, dX for all but the first"""
         return sum(2 * L.ops + (L.ops if L.index > 0 else 0.0) for L in self.convs)
-
-
-# ---- CPU twin on the oracle (tests / cpu_baseline only) ------------------------------------------------
-def oracle_step(orc, spec, x_nchw, ascale, labels, weights, shape_fn):
-    """Same step on the CPU oracle; `weights` list of (OIHW int8, wscale) is updated in place.
-    Returns (logits, exponent).  Lives here so tests and bench share one definition; it is only ever
-    called from tests/, smoke() and bench.py's cpu_baseline / reference legs."""
-    acts = []
-    cur, e = x_nchw, int(ascale)
-    wi = 0
-    trace = []
-    for item in spec:
-        kind = item[0]
-        if kind == "conv":
-            _, oc, k, st, pad = item
-            n, c, h, w = cur.shape
-            s = shape_fn(n, c, h, w, oc, k, stride=st, pad=pad)
-            W, ew = weights[wi]
-            y, ey, _ = orc.conv_fwd(s, cur, W, e, ew)
-            trace.append(("conv", s, cur, wi)); wi += 1
-            cur, e = y, ey
-        elif kind == "relu":
-            trace.append(("relu", cur)); cur = orc.relu(cur)
-        elif kind == "pool":
-            y = orc.maxpool(cur, item[1], item[2])
-            trace.append(("pool", cur, y, item[1], item[2])); cur = y
-        elif kind == "flatten":
-            trace.append(("flatten", cur.shape)); cur = np.ascontiguousarray(cur.reshape(cur.shape[0], -1, 1, 1))
-    logits, e_logits = cur, e
-    g = orc.loss_grad(np.ascontiguousarray(logits.reshape(logits.shape[0], -1)), e_logits, labels)
-    g = g.reshape(logits.shape)
-    new_w = {}
-    for t in reversed(trace):
-        if t[0] == "conv":
-            _, s, xin, i = t
-            W, ew = weights[i]
-            dw, _ = orc.conv_dw(s, xin, g)
-            new_w[i] = orc.sgd_update(W, dw)
-            if i > 0:
-                g, _ = orc.conv_dx(s, g, W)
-        elif t[0] == "relu":
-            g = orc.relu_grad(t[1], g)
-        elif t[0] == "pool":
-            g = orc.maxpool_grad(t[1], t[2], g, t[3], t[4])
-        elif t[0] == "flatten":
-            g = np.ascontiguousarray(g.reshape(t[1]))
-    for i, W in new_w.items():
-        weights[i] = (W, weights[i][1])
-    return logits, e_logits

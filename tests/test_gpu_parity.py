@@ -494,3 +494,52 @@ def test_full_size_vgg_layer_properties(nb):
     nb.set_path(0)
     assert torch.equal(p0 + p1, dwa)
     assert torch.equal(neg, -acc)
+
+
+@pytest.mark.parametrize("shape_", [(256, 256, 8, 256), (256, 512, 2, 512), (256, 64, 16, 128), (256, 512, 4, 512)])
+def test_full_size_product_kernels_vs_pinned_simt_and_oracle_rescale(nb, oracle, shape_):
+    """The three kernels bench.py times — igemm_fused_kernel (fwd + dX, incl. several resident tiles per CTA pair),
+    the two-phase PATH_TMA2 route and dw2_kernel (niti_conv_dw_accumulate) — at the FULL VGG-11 batch-256 layer sizes.
+    Oracle leg: the SIMT kernel's int32 accumulators (itself pinned against the CPU oracle element for element at small
+    sizes, test_accumulators_and_outputs_vs_oracle) rescaled by the CPU oracle (niti_o_rescale_act)."""
+    import torch
+    from tests.gpu_util import PATH_SIMT, PATH_TMA2
+    from mandheling_dsp_training_b200.lib import desc
+    n, c, hw, oc = shape_
+    torch.manual_seed(hw)
+    d = desc(n, c, hw, hw, oc, 3, pad=1)
+    i8 = dict(dtype=torch.int8, device="cuda"); i32 = dict(dtype=torch.int32, device="cuda")
+    x = torch.randint(0, 128, (n, hw, hw, c), **i8)                      # post-ReLU activations
+    w = torch.randint(-30, 31, (oc, 3, 3, c), **i8)
+    dy = torch.randint(-40, 41, (n, hw, hw, oc), **i8)
+    gate = torch.randint(-5, 6, (n, hw, hw, c), **i8)
+    wt = w.permute(3, 1, 2, 0).contiguous()
+    ref = {}
+    for path in (PATH_SIMT, PATH_TMA2):
+        nb.set_path(path)
+        acc = torch.empty((n, hw, hw, oc), **i32); dxa = torch.empty((n, hw, hw, c), **i32); dwa = torch.empty((oc, 3, 3, c), **i32)
+        nb.conv_fwd_acc(d, x, w, acc); nb.conv_dx_acc(d, dy, w, dxa); nb.conv_dw_acc(d, x, dy, dwa)
+        torch.cuda.synchronize()
+        ref[path] = (acc, dxa, dwa)
+    nb.set_path(0)
+    for a, b in zip(ref[PATH_SIMT], ref[PATH_TMA2]):
+        assert torch.equal(a, b)
+    acc, dxa, dwa = ref[PATH_SIMT]
+    # fused forward (+ReLU) and fused dX (+ReLU-grad gate): single launch, accumulators never leave tensor memory
+    y = torch.empty((n, hw, hw, oc), **i8); ey = torch.zeros(1, **i8); mx = torch.zeros(2, **i32)
+    ex = torch.full((1,), -7, **i8); ew = torch.full((1,), -9, **i8)
+    nb.conv_fwd_fused(d, x, w, ex, ew, y, ey, True, None, mx[0:1])
+    assert nb.last_path == "fused"
+    dx = torch.empty((n, hw, hw, c), **i8)
+    nb.conv_dx_fused(d, dy, w, wt, dx, gate, None, mx[1:2])
+    assert nb.last_path == "fused"
+    dw2 = torch.zeros((oc, 3, 3, c), **i32)
+    nb.conv_dw_accumulate(d, x, dy, dw2)
+    torch.cuda.synchronize()
+    want_y, inc = oracle.rescale_act(acc.cpu().numpy())
+    assert np.array_equal(y.cpu().numpy(), np.maximum(want_y, 0))
+    assert int(ey.item()) == -16 + inc and int(mx[0].item()) == int(acc.abs().max().item())
+    want_dx, _ = oracle.rescale_act(dxa.cpu().numpy())
+    want_dx = np.where(gate.cpu().numpy() > 0, want_dx, 0).astype(np.int8)
+    assert np.array_equal(dx.cpu().numpy(), want_dx)
+    assert torch.equal(dw2, dwa)

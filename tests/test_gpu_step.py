@@ -5,7 +5,8 @@ import pytest
 import torch
 
 from oracle.oracle import shape
-from mandheling_dsp_training_b200.step import NitiNet, oracle_step, lenet_spec
+from mandheling_dsp_training_b200.step import NitiNet, lenet_spec
+from oracle.step_twin import oracle_step
 
 pytestmark = pytest.mark.gpu
 

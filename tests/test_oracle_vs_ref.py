@@ -55,7 +55,7 @@ def test_live_reference_training_steps(oracle, ref):
     """Whole training steps of the reference's NITIInt8 MNIST model (demo/mnistTrain.cpp:131-182) through its own
     Module / OpGrad / NITI_SGD code with injected weights, against oracle_step: logits, exponents and every
     updated weight tensor identical after 3 steps (the full-loop pin of SURVEY.md section 8c(2))."""
-    from mandheling_dsp_training_b200.step import oracle_step
+    from oracle.step_twin import oracle_step
     spec, ws, x, lab = _lenet_case(3, 8)
     out = ref.net_train(spec, x, -7, lab, ws, tclasses=10)
     w2 = [(w.copy(), e) for w, e in ws]

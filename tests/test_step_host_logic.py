@@ -9,7 +9,8 @@ import torch.distributed as dist
 import torch.multiprocessing as mp
 
 from oracle.oracle import Oracle, shape
-from mandheling_dsp_training_b200.step import NitiNet, oracle_step, lenet_spec, niti_xavier_int8
+from mandheling_dsp_training_b200.step import NitiNet, lenet_spec, niti_xavier_int8
+from oracle.step_twin import oracle_step
 from tests.fake_backend import OracleBackend
 
 SMALL = [("conv", 8, 3, 1, 1), ("relu",), ("pool", 2, 2), ("conv", 16, 3, 1, 1), ("relu",), ("pool", 2, 2),
