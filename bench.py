@@ -38,7 +38,12 @@ def parse():
     ap.add_argument("--workload", default="vgg11", choices=sorted(WORKLOADS))
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (default: the workload's)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--ref-batch", type=int, default=4, help="bounded sample size for the CPU reference")
+    ap.add_argument("--ref-batch", type=int, default=0, help="override the reference arm's batch (default: same config as our arm; sets config.reduced)")
+    ap.add_argument("--ref-budget", type=float, default=170.0, help="seconds of timed reference steps (reference arm)")
+    ap.add_argument("--cpu-sample", type=int, default=32, help="samples per step of the bounded cpu_baseline leg of the default run")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: the workload's batch PER GPU; strong: the workload's batch is the GLOBAL batch, split over the GPUs")
+    ap.add_argument("--no-dp-check", action="store_true", help="skip the data-parallel correctness witness (world > 1)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying a CUDA graph")
     return ap.parse_args()
@@ -47,22 +52,15 @@ def parse():
 # ----------------------------------------------------------------------------------------------------
 # CPU reference leg (cpu_baseline and --impl reference).  The only place bench.py touches oracle/.
 # ----------------------------------------------------------------------------------------------------
-def reference_step_fn(workload, batch):
-    """Returns (step_callable, kind, cores, note).  Uses the unmodified reference when oracle/_ref was
-    built (kind "reference"), else the C oracle port (kind "port", 1 core)."""
+def _walk_weights(workload):
     import numpy as np
-    from oracle.oracle import Oracle, Reference, shape
     from mandheling_dsp_training_b200.step import SPECS, niti_xavier_int8
-    from oracle.step_twin import oracle_step
     spec_fn, chw = SPECS[WORKLOADS[workload][0]]
     spec = spec_fn()
-    rng = np.random.default_rng(0)
-    x = rng.integers(-127, 128, size=(batch,) + chw, dtype=np.int8)
-    labels = rng.integers(0, 10, size=batch).astype(np.int32)
     wrng = np.random.default_rng(1)
     ws, c = [], chw[0]
     h, w_ = chw[1], chw[2]
-    for it in spec:                                     # walk shapes to size the weights
+    for it in spec:
         if it[0] == "conv":
             ws.append(niti_xavier_int8(wrng, it[1], c, it[2], it[2]))
             c = it[1]; h = (h + 2 * it[4] - it[2]) // it[3] + 1; w_ = (w_ + 2 * it[4] - it[2]) // it[3] + 1
@@ -70,46 +68,36 @@ def reference_step_fn(workload, batch):
             h = (h - it[1]) // it[2] + 1; w_ = (w_ - it[1]) // it[2] + 1
         elif it[0] == "flatten":
             c, h, w_ = c * h * w_, 1, 1
+    return spec, chw, ws
+
+
+def reference_step_fn(workload, batch):
+    """Returns (step_callable, kind, cores, note).  With oracle/_ref built (kind "reference") a step is one iteration of
+    the UNMODIFIED reference's own training loop — its Module forward, _NITI_LOSS_SUM, OpGrad over the whole graph and
+    NITI_SGD::step (ref_net_train in oracle/ref_driver.cpp = demo/MnistUtils.cpp:79-147 with injected data and weights) —
+    on its CPU backend with every host thread MNN will take.  Otherwise the C oracle port (kind "port", 1 core)."""
+    import numpy as np
+    from oracle.oracle import Oracle, Reference, shape
+    from oracle.step_twin import oracle_step
+    spec, chw, ws = _walk_weights(workload)
+    rng = np.random.default_rng(0)
+    x = rng.integers(-127, 128, size=(batch,) + chw, dtype=np.int8)
+    labels = rng.integers(0, 10, size=batch).astype(np.int32)
     if Reference.available():
         cores = min(os.cpu_count() or 1, 32)            # MNN caps its pool at 32 threads (CPUBackend.cpp:29)
         ref = Reference(threads=cores)
-        state = [(w.copy(), e) for w, e in ws]
+        state = {"ws": [(w.copy(), e) for w, e in ws]}
+        classes = [it for it in spec if it[0] == "conv"][-1][1]
 
         def step():
-            cur, e, trace, wi = x, -7, [], 0
-            for it in spec:
-                if it[0] == "conv":
-                    n, c_, hh, ww = cur.shape
-                    s_ = shape(n, c_, hh, ww, it[1], it[2], stride=it[3], pad=it[4])
-                    W, ew = state[wi]
-                    y, e2 = ref.conv_fwd(s_, cur, W, e, ew)
-                    trace.append(("conv", s_, cur, wi)); wi += 1; cur, e = y, e2
-                elif it[0] == "relu":
-                    trace.append(("relu", cur)); cur = ref.relu(cur)
-                elif it[0] == "pool":
-                    trace.append(("pool", cur, it[1], it[2])); cur = ref.maxpool(cur, it[1], it[2])
-                elif it[0] == "flatten":
-                    trace.append(("flatten", cur.shape)); cur = np.ascontiguousarray(cur.reshape(cur.shape[0], -1, 1, 1))
-            g = ref.loss_grad(np.ascontiguousarray(cur.reshape(cur.shape[0], -1)), e, labels).reshape(cur.shape)
-            for t in reversed(trace):
-                if t[0] == "conv":
-                    _, s_, xin, i = t
-                    W, ew = state[i]
-                    dx_, dw_ = ref.conv_bwd(s_, xin, W, g)
-                    state[i] = (ref.sgd_update(W, dw_), ew)
-                    if i > 0:
-                        g = dx_
-                elif t[0] == "relu":
-                    g = ref.relu_grad(t[1], g)
-                elif t[0] == "pool":
-                    g = ref.maxpool_grad(t[1], g, t[2], t[3])
-                elif t[0] == "flatten":
-                    g = np.ascontiguousarray(g.reshape(t[1]))
-        return step, "reference", cores, f"unmodified reference ops (oracle/_ref) on {batch} samples, {cores} threads"
+            out = ref.net_train(spec, x[None], -7, labels[None], state["ws"], tclasses=classes)
+            state["ws"] = [(w, e) for w, (_, e) in zip(out["weights"], state["ws"])]
+        return step, "reference", cores, (f"unmodified reference training loop (Module forward + OpGrad + NITI_SGD, oracle/_ref) "
+                                          f"on its CPU backend, batch {batch}, {cores} threads")
     orc = Oracle()
     state = [(w.copy(), e) for w, e in ws]
     return (lambda: oracle_step(orc, spec, x, -7, labels, state, shape)), "port", 1, \
-        f"C oracle port on {batch} samples, 1 thread (oracle/_ref not built)"
+        f"C oracle port, batch {batch}, 1 thread (oracle/_ref not built)"
 
 
 class _QuietStdout:
@@ -127,28 +115,46 @@ class _QuietStdout:
         os.close(self.null); os.close(self.saved)
 
 
-def time_reference(workload, batch, steps, warmup, budget_s=45.0):
+def time_reference(workload, batch, steps, warmup, budget_s=45.0, warm_batch=None):
+    """Times up to `steps` reference steps of `batch` samples (stops once budget_s is spent, at least one step).
+    Warm-up: `warmup` steps at warm_batch samples (default: the timed batch)."""
     with _QuietStdout():
         step, kind, cores, note = reference_step_fn(workload, batch)
-        for _ in range(max(0, warmup)):
-            step()
+        if warmup > 0:
+            wstep = step if not warm_batch or warm_batch == batch else reference_step_fn(workload, warm_batch)[0]
+            for _ in range(warmup):
+                wstep()
         t0 = time.perf_counter(); done = 0
         while done < steps and (time.perf_counter() - t0 < budget_s or done == 0):
             step(); done += 1
         dt = time.perf_counter() - t0
     return {"value": batch * done / dt, "unit": "samples/s", "cores": cores, "kind": kind,
-            "sample": f"{note}; {done} steps in {dt:.1f}s"}, dt / done
+            "sample": f"{note}; {done} steps in {dt:.1f}s"}, dt / done, done
 
 
 def run_reference_arm(args):
+    """The reference arm: the reference's own CPU implementation on this box's host cores, SAME config as our arm (the
+    workload's batch) unless --ref-batch overrides it (then `reduced` is set).  A batch-256 VGG-11 step is about a minute
+    of CPU time, so the timed region is as many whole steps as fit `--ref-budget` seconds (steps_done), after one warm-up
+    step on 16 samples (pages the code in; a full-size warm-up would double the run)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    cb, ms = time_reference(args.workload, args.ref_batch, args.steps, args.warmup, budget_s=150.0)
+    batch = args.ref_batch or (args.batch or WORKLOADS[args.workload][1])
+    reduced = batch != (args.batch or WORKLOADS[args.workload][1])
+    cb, s_per_step, done = time_reference(args.workload, batch, args.steps, 1, budget_s=args.ref_budget, warm_batch=min(16, batch))
+    scaling = {}
+    for b in (4, 16, 64):                               # how the CPU path scales with batch (threads over the batch)
+        if b < batch:
+            r, _, _ = time_reference(args.workload, b, 1, 0, budget_s=1.0)
+            scaling[str(b)] = round(r["value"], 3)
+    scaling[str(batch)] = round(cb["value"], 3)
     line = {"impl": "reference", "metric": "int8_train_samples_per_sec", "value": cb["value"], "unit": "samples/s",
-            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms * 1e3,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
-            "config": {"workload": WORKLOADS[args.workload][2], "sample_batch": args.ref_batch},
+            "n_gpus": args.gpus, "steps": args.steps, "steps_done": done, "warmup": args.warmup, "ms_per_step": s_per_step * 1e3,
+            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+            "config": {"workload": WORKLOADS[args.workload][2], "per_gpu_batch": batch, "global_batch": batch,
+                       "reduced": reduced, "ref_batch_scaling": scaling,
+                       "note": "one host runs the whole batch; value does not grow with --gpus"},
             "cpu_baseline": cb,
             "e2e": {"value": cb["value"], "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
@@ -229,10 +235,15 @@ def main():
         # for it (csrc/dp.cu) and NCCL is capped at the same 16 CTAs (never more CTAs than free SMs: 4xB200 with
         # reserve 8 / 16 CTAs collapsed to 51.7 ms per step).  Measured 2xB200, ms/step: (reserve, max CTAs) = (8,8) 0.810,
         # (8,16) 0.727, (16,16) 0.726, (8,32) 0.779, (24,32) 0.817, (4,4) 1.011; reserve 0 starves NCCL (41 ms)
-        os.environ.setdefault("NCCL_MAX_CTAS", "16")
+        from mandheling_dsp_training_b200 import lib as _lib
+        _lib.dp_env()                                        # NCCL_MAX_CTAS <= NITI_B200_DP_RESERVE_SMS, enforced by dp_connect
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     spec_key, dbatch, desc_text = WORKLOADS[args.workload]
     batch = args.batch or dbatch
+    if args.scaling == "strong":                             # the workload's batch is the GLOBAL batch
+        if batch % world:
+            raise SystemExit(f"--scaling strong: global batch {batch} is not divisible by {world} GPUs")
+        batch //= world
     spec_fn, chw = SPECS[spec_key]
     nb = NitiB200(local)
     net = NitiNet(nb, spec_fn(), batch, chw, device=local, dist=dist if world > 1 else None)
@@ -282,6 +293,7 @@ def main():
     barrier()
     sampler.active = False
     step_ms = [a.elapsed_time(b) for a, b in ev]
+    net.check()                                              # sticky device-side error flags (peer exchange / grid barrier)
     launches_timed = launches_per_step * args.steps         # graph replays launch the captured kernels
     del launches0
     total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device="cuda")
@@ -321,10 +333,44 @@ def main():
     t1.record()
     barrier()
     sampler.active = False
+    net.check()
     e2e_ms = torch.tensor([t0.elapsed_time(t1)], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
     e2e_value = batch * world * args.steps / (float(e2e_ms.item()) * 1e-3)
+
+    # ---- data-parallel correctness witness: 3 steps from re-initialised weights on a fixed global batch; every rank's
+    # weights must be identical, and equal to ONE GPU stepping the whole global batch (rank 0 runs that on a second,
+    # unconnected context; layers whose tiles exceed tensor memory at that batch take the two-phase route by themselves)
+    dp_check = None
+    if world > 1 and not args.no_dp_check:
+        crng = np.random.default_rng(4242)
+        gx = torch.from_numpy(crng.integers(-127, 128, size=(3, batch * world, chw[1], chw[2], chw[0]), dtype=np.int8))
+        gl = torch.from_numpy(crng.integers(0, 10, size=(3, batch * world)).astype(np.int32))
+        net.init_weights(seed=1)
+        for i in range(3):
+            net.set_input(gx[i, rank * batch:(rank + 1) * batch].cuda(), -7, gl[i, rank * batch:(rank + 1) * batch].cuda())
+            net.step()                                       # eager: the captured graph and the eager path must agree anyway
+        net.check()
+        mine = torch.cat([L.w.reshape(-1) for L in net.convs] + [net.e_logits.reshape(-1)])
+        allw = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allw, mine)
+        same_ranks = all(torch.equal(allw[0], t) for t in allw[1:])
+        equals_1gpu = None
+        if rank == 0:
+            nb1 = NitiB200(local)
+            net1 = NitiNet(nb1, spec_fn(), batch * world, chw, device=local)
+            net1.init_weights(seed=1)
+            for i in range(3):
+                net1.set_input(gx[i].cuda(), -7, gl[i].cuda())
+                net1.step()
+            net1.check()
+            one = torch.cat([L.w.reshape(-1) for L in net1.convs] + [net1.e_logits.reshape(-1)])
+            equals_1gpu = bool(torch.equal(one, mine)) and bool(torch.equal(net1.logits[:batch], net.logits))
+            del net1, nb1
+        dp_check = {"weights_equal_across_ranks": bool(same_ranks), "equals_1gpu_global_batch": equals_1gpu, "steps": 3,
+                    "global_batch": batch * world}
+        dist.barrier()
 
     clocks = sampler.summary()         # sampled over warm-up + all timed regions
     if world > 1:
@@ -364,7 +410,8 @@ def main():
     cpu_baseline = None
     if world == 1 and not args.no_cpu_baseline:
         try:
-            cpu_baseline, _ = time_reference(args.workload, args.ref_batch, 3, 1, budget_s=25.0)
+            cpu_baseline, _, _ = time_reference(args.workload, args.cpu_sample, 2, 1, budget_s=20.0, warm_batch=min(8, args.cpu_sample))
+            cpu_baseline["sample"] += f" (bounded sample: {args.cpu_sample}-sample steps of the same net; the same-config number is the --impl reference arm)"
         except Exception as ex:      # pragma: no cover
             cpu_baseline = {"value": None, "unit": "samples/s", "cores": 0, "kind": "unavailable", "sample": str(ex)}
 
@@ -372,7 +419,7 @@ def main():
     line = {
         "metric": "int8_train_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": world,
         "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": total_ms / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8", "data": "synthetic",
+        "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "int8", "data": "synthetic",
         "config": {"workload": desc_text, "per_gpu_batch": batch, "global_batch": batch * world,
                    "parallelism": f"dp{world}", "launch": "cuda_graph" if use_graph else "eager",
                    "dp_exchange": ("max|acc|: in-kernel NVLink peer-memory exchange; dW: bucketed NCCL all-reduce(SUM) overlapped with backward"
@@ -386,6 +433,7 @@ def main():
         "clocks": clocks,
         "roofline": roofline,
         "cpu_baseline": cpu_baseline,
+        "dp_check": dp_check,
         "tensor_frac_of_step": (net.algorithmic_ops() / (total_ms / args.steps * 1e-3) / 1e12 / peak_tops) if peak_tops else None,
     }
     print(json.dumps(line), flush=True)
