@@ -196,6 +196,45 @@ int niti_conv_fwd_fused(niti_ctx*, const niti_conv_desc*, const int8_t* x, const
  * (caller scratch of n*h*w*c words or NULL).  wt: transposed weights as in niti_conv_dx_acc_wt (NULL: per-call transpose). */
 int niti_conv_dx_fused(niti_ctx*, const niti_conv_desc*, const int8_t* dy, const int8_t* w, const int8_t* wt, int8_t* dx,
                        const int8_t* gate, int32_t* acc, uint32_t* maxabs, int dp_slot, niti_stream);
+/* niti_conv_fwd_fused with the 2x2 stride-2 max pool that follows the ReLU (NITI_Maxpool_Int8.cpp:24-70) folded into the store:
+ * y [n,oh,ow,oc] is still written (backward needs it), y_pool [n,oh/2,ow/2,oc] is the pooled tensor.  One launch when the
+ * fused kernel takes the shape and ow is 2, 4, 8 or 16 with oh even; otherwise niti_conv_fwd_fused + niti_maxpool. */
+int niti_conv_fwd_fused_pool(niti_ctx*, const niti_conv_desc*, const int8_t* x, const int8_t* w, const int8_t* ex,
+                             const int8_t* ew, int8_t* y, int8_t* ey, int relu, int8_t* y_pool, int32_t* acc, uint32_t* maxabs,
+                             int dp_slot, niti_stream);
+/* niti_conv_dx_fused whose result is the gradient w.r.t. a 2x2/2 max-POOLED tensor, with the pool's gradient
+ * (NITI_CPUPoolGrad_Int8.cpp:36-72: the first window element equal to the maximum takes it) and, when gate_relu != 0, the
+ * ReLU gradient of the layer before the pool folded into the store: pool_x [n,2h,2w,c] is the pre-pool forward tensor,
+ * dx_prepool [n,2h,2w,c] receives the gradient w.r.t. it.  dx_pooled [n,h,w,c] is scratch for the unfused route (shapes the
+ * fused kernel does not take) and may be NULL when the caller knows the fused kernel applies. */
+int niti_conv_dx_fused_poolgrad(niti_ctx*, const niti_conv_desc*, const int8_t* dy, const int8_t* w, const int8_t* wt,
+                                int8_t* dx_prepool, const int8_t* pool_x, int gate_relu, int8_t* dx_pooled, int32_t* acc,
+                                uint32_t* maxabs, int dp_slot, niti_stream);
+
+/* ---- chains: several fused ops behind ONE persistent launch ----------------------------------------------------------
+ * The reference runs a training step as a serial loop over ops (express/Executor.cpp:333-359).  A chain is a list of
+ * forward (or dX) ops of which each consumes what the previous one stored; niti_chain_run executes them in one launch that
+ * keeps tensor memory, barriers and CTAs alive across layers (csrc/conv_chain.cu).  Results are identical to calling the
+ * ops one by one.  Every op must be within the fused kernel's contract (niti_chain_create returns NITI_ERR_UNSUPPORTED
+ * otherwise and the caller issues the ops individually).  Pointers are captured at creation. */
+typedef struct {
+    niti_conv_desc d;
+    int32_t op;                      /* 0 forward (NITI_Conv_Int8), 1 dX (NITI_DeConv_Int8)                         */
+    const int8_t* in;                /* forward: x [n,h,w,c]; dX: dy [n,oh,ow,oc]                                    */
+    const int8_t* w;                 /* forward: w [oc,kh,kw,c]; dX: the transposed weights wt [c,kh,kw,oc]           */
+    const int8_t* ex; const int8_t* ew; int8_t* ey;   /* forward: exponents in / out (dX: NULL)                      */
+    int8_t* out;                     /* forward: y; dX: dx (with pool_x: the gradient w.r.t. the pre-pool tensor)     */
+    int32_t relu;                    /* forward: fold NITI_CPURelu_Int8 into the store                               */
+    const int8_t* gate;              /* dX: fold NITI_CPUReluGrad_Int8 (tensor of out's shape), or NULL               */
+    int8_t* out_pool;                /* forward: also write the 2x2/2 max-pooled tensor, or NULL                      */
+    const int8_t* pool_x; int32_t pool_gate;   /* dX: fold the max-pool gradient (+ ReLU gate) as in niti_conv_dx_fused_poolgrad */
+    uint32_t* maxabs; int32_t dp_slot;         /* zeroed slot -> this rank's max|acc|; exchange slot (niti_rescale_act_dp) */
+} niti_chain_op;
+typedef struct niti_chain niti_chain;
+int niti_chain_op_eligible(niti_ctx*, const niti_chain_op* op);      /* 1 when the fused kernel takes this op (shape + pooling geometry) */
+int niti_chain_create(niti_ctx*, const niti_chain_op* ops, int n, niti_chain** out);
+int niti_chain_run(niti_ctx*, niti_chain*, niti_stream);
+int niti_chain_destroy(niti_ctx*, niti_chain*);
 int niti_conv_dx(niti_ctx*, const niti_conv_desc*, const int8_t* dy, const int8_t* w, int8_t* dx, niti_stream);
 int niti_conv_dw(niti_ctx*, const niti_conv_desc*, const int8_t* x, const int8_t* dy, int8_t* dw, niti_stream);
 int niti_matmul_nt(niti_ctx*, int e, int h, int l, const int8_t* a, const int8_t* b, int8_t* c, niti_stream);
@@ -217,6 +256,10 @@ int niti_maxpool_grad_gated(niti_ctx*, const int8_t* x, const int8_t* y, const i
                             int k, int s, int8_t* dx, int gate_relu, niti_stream);
 int niti_loss_grad(niti_ctx*, const int8_t* logits, const int8_t* ascale, const int32_t* labels,
                    int batch, int classes, int8_t* grad, niti_stream);                        /* NITI_CPULossGrad_Int8.cpp:82-201 */
+/* same, for logit / gradient rows of `stride` bytes of which the first `classes` are real (output channels zero-padded
+ * to the tensor cores' granule); the padding columns of grad are written as 0 */
+int niti_loss_grad_strided(niti_ctx*, const int8_t* logits, const int8_t* ascale, const int32_t* labels,
+                           int batch, int classes, int stride, int8_t* grad, niti_stream);
 
 /* ---- layout conversion at the boundary ----------------------------------------------------- */
 int niti_nchw_to_nhwc(niti_ctx*, const int8_t* src, int n, int c, int h, int w, int8_t* dst, niti_stream);

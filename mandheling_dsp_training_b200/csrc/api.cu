@@ -46,6 +46,10 @@ int fused_conv_fwd(niti_ctx*, const niti_conv_desc*, const int8_t*, const int8_t
                    int, uint32_t*, int, cudaStream_t);
 int fused_conv_dx(niti_ctx*, const niti_conv_desc*, const int8_t*, const int8_t*, int8_t*, const int8_t*, uint32_t*, int, cudaStream_t);
 
+// conv_chain.cu: the layer-walking fused kernel; a chain of one op is the single-op fused entry point
+int chain_run_single(niti_ctx*, const niti_chain_op*, cudaStream_t);
+bool chain_op_eligible(niti_ctx*, const niti_chain_op*);
+
 // kernel family selection: TMA-fed tcgen05 > cp.async-fed tcgen05 > SIMT, subject to shape eligibility
 // and the context's forced path.  Returns 0 simt, 1 tc (cp.async), 2 tma, 3 tma2 (CTA pair), -1 unsupported under the
 // forced path.
@@ -153,6 +157,8 @@ int niti_ctx_create(int device, niti_ctx** out) {
     if (env && !strcmp(env, "tma2")) ctx->path = NITI_PATH_TMA2;
     const char* a2 = getenv("NITI_B200_AUTO_TMA2");
     ctx->auto_tma2 = a2 ? atoi(a2) : 1;
+    const char* uc = getenv("NITI_B200_CHAIN");           // 0: the round-1 per-shape templates (igemm_fused_kernel) for A/B runs
+    ctx->use_chain = uc ? atoi(uc) : 1;
     const char* pdl = getenv("NITI_B200_PDL");
     ctx->pdl = pdl ? atoi(pdl) : (1 | 512);      // fused kernels, trigger at the exponent barrier
     ctx->last_path = "none";
@@ -277,9 +283,15 @@ int niti_conv_fwd_fused(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x,
         ctx->last_path = "stem";
         return stem_conv_fwd_fused(ctx, d, x, w, ex, ew, y, ey, relu, maxabs, dp_slot, (cudaStream_t)st);
     }
-    if ((ctx->path == NITI_PATH_AUTO || ctx->path == NITI_PATH_TMA2) && ctx->auto_tma2 && fused_fwd_eligible(ctx, d)) {
-        ctx->last_path = "fused";
-        return fused_conv_fwd(ctx, d, x, w, ex, ew, y, ey, relu, maxabs, dp_slot, (cudaStream_t)st);
+    if ((ctx->path == NITI_PATH_AUTO || ctx->path == NITI_PATH_TMA2) && ctx->auto_tma2) {
+        niti_chain_op op{};
+        op.d = *d; op.op = 0; op.in = x; op.w = w; op.ex = ex; op.ew = ew; op.ey = ey; op.out = y; op.relu = relu;
+        op.maxabs = maxabs; op.dp_slot = dp_slot;
+        if (ctx->use_chain && chain_op_eligible(ctx, &op)) { ctx->last_path = "fused"; return chain_run_single(ctx, &op, (cudaStream_t)st); }
+        if (fused_fwd_eligible(ctx, d)) {
+            ctx->last_path = "fused";
+            return fused_conv_fwd(ctx, d, x, w, ex, ew, y, ey, relu, maxabs, dp_slot, (cudaStream_t)st);
+        }
     }
     const size_t n = (size_t)d->n * conv_out_h(d) * conv_out_w(d) * d->oc;
     int rc;
@@ -292,15 +304,56 @@ int niti_conv_dx_fused(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* dy,
                        const int8_t* gate, int32_t* acc, uint32_t* maxabs, int dp_slot, niti_stream st) {
     if (!ctx || !desc_ok(d) || !dy || !w || !dx || !maxabs) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_dx_fused: bad argument");
     if (dp_slot < 0 || dp_slot >= kDpSlots) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_dx_fused: slot out of range");
-    if (wt && (ctx->path == NITI_PATH_AUTO || ctx->path == NITI_PATH_TMA2) && ctx->auto_tma2 && fused_dx_eligible(ctx, d)) {
-        ctx->last_path = "fused";
-        return fused_conv_dx(ctx, d, dy, wt, dx, gate, maxabs, dp_slot, (cudaStream_t)st);
+    if (wt && (ctx->path == NITI_PATH_AUTO || ctx->path == NITI_PATH_TMA2) && ctx->auto_tma2) {
+        niti_chain_op op{};
+        op.d = *d; op.op = 1; op.in = dy; op.w = wt; op.out = dx; op.gate = gate; op.maxabs = maxabs; op.dp_slot = dp_slot;
+        if (ctx->use_chain && chain_op_eligible(ctx, &op)) { ctx->last_path = "fused"; return chain_run_single(ctx, &op, (cudaStream_t)st); }
+        if (fused_dx_eligible(ctx, d)) {
+            ctx->last_path = "fused";
+            return fused_conv_dx(ctx, d, dy, wt, dx, gate, maxabs, dp_slot, (cudaStream_t)st);
+        }
     }
     const size_t n = (size_t)d->n * d->h * d->w * d->c;
     int rc;
     if (!acc && (rc = niti_ws_acc(ctx, n * 4, &acc))) return rc;
     if ((rc = niti_conv_dx_acc_wt(ctx, d, dy, w, wt, acc, maxabs, st))) return rc;
     return niti_rescale_act_dp(ctx, acc, n, maxabs, dx, nullptr, nullptr, nullptr, 0, gate, dp_slot, st);
+}
+
+int niti_conv_fwd_fused_pool(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, const int8_t* w, const int8_t* ex,
+                             const int8_t* ew, int8_t* y, int8_t* ey, int relu, int8_t* y_pool, int32_t* acc, uint32_t* maxabs,
+                             int dp_slot, niti_stream st) {
+    if (!ctx || !desc_ok(d) || !x || !w || !y || !y_pool || !maxabs) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_fwd_fused_pool: bad argument");
+    if (dp_slot < 0 || dp_slot >= kDpSlots) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_fwd_fused_pool: slot out of range");
+    const int oh = conv_out_h(d), ow = conv_out_w(d);
+    if (oh < 2 || ow < 2) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_fwd_fused_pool: output smaller than the pool window");
+    if ((ctx->path == NITI_PATH_AUTO || ctx->path == NITI_PATH_TMA2) && ctx->auto_tma2 && ctx->use_chain) {
+        niti_chain_op op{};
+        op.d = *d; op.op = 0; op.in = x; op.w = w; op.ex = ex; op.ew = ew; op.ey = ey; op.out = y; op.relu = relu; op.out_pool = y_pool;
+        op.maxabs = maxabs; op.dp_slot = dp_slot;
+        if (chain_op_eligible(ctx, &op)) { ctx->last_path = "fused"; return chain_run_single(ctx, &op, (cudaStream_t)st); }
+    }
+    int rc = niti_conv_fwd_fused(ctx, d, x, w, ex, ew, y, ey, relu, acc, maxabs, dp_slot, st);
+    if (rc) return rc;
+    return niti_maxpool(ctx, y, d->n, oh, ow, d->oc, 2, 2, y_pool, st);
+}
+
+int niti_conv_dx_fused_poolgrad(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* dy, const int8_t* w, const int8_t* wt,
+                                int8_t* dx_prepool, const int8_t* pool_x, int gate_relu, int8_t* dx_pooled, int32_t* acc,
+                                uint32_t* maxabs, int dp_slot, niti_stream st) {
+    if (!ctx || !desc_ok(d) || !dy || !w || !dx_prepool || !pool_x || !maxabs) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_dx_fused_poolgrad: bad argument");
+    if (dp_slot < 0 || dp_slot >= kDpSlots) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_dx_fused_poolgrad: slot out of range");
+    if (wt && (ctx->path == NITI_PATH_AUTO || ctx->path == NITI_PATH_TMA2) && ctx->auto_tma2 && ctx->use_chain) {
+        niti_chain_op op{};
+        op.d = *d; op.op = 1; op.in = dy; op.w = wt; op.out = dx_prepool; op.pool_x = pool_x; op.pool_gate = gate_relu;
+        op.maxabs = maxabs; op.dp_slot = dp_slot;
+        if (chain_op_eligible(ctx, &op)) { ctx->last_path = "fused"; return chain_run_single(ctx, &op, (cudaStream_t)st); }
+    }
+    if (!dx_pooled) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_dx_fused_poolgrad: shape needs the unfused route and dx_pooled is NULL");
+    int rc = niti_conv_dx_fused(ctx, d, dy, w, wt, dx_pooled, nullptr, acc, maxabs, dp_slot, st);
+    if (rc) return rc;
+    // pool_y is recomputed by the gradient kernel from pool_x; it needs the pooled forward tensor: take the window maximum
+    return niti_maxpool_grad_from_x(ctx, pool_x, dx_pooled, d->n, 2 * d->h, 2 * d->w, d->c, dx_prepool, gate_relu, st);
 }
 
 int niti_conv_dx(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* dy, const int8_t* w, int8_t* dx, niti_stream st) {

@@ -15,6 +15,7 @@ struct niti_ctx {
     int sm_total;             // SMs of the device
     int path;                 // NITI_PATH_*
     int auto_tma2;            // AUTO prefers the CTA-pair kernels where eligible
+    int use_chain;            // fused ops run in the layer-walking kernel (conv_chain.cu); 0 = round-1 templates
     int pdl;                  // programmatic dependent launch on the step's kernel chain (NITI_B200_PDL: bit mask of NITI_PDL_* kernel classes, default NITI_PDL_FUSED | NITI_PDL_TRIGGER_LATE — measured best)
     int64_t launches;
     const char* last_path;
@@ -99,6 +100,9 @@ int  niti_fail(niti_ctx* ctx, int code, const char* what, cudaError_t e = cudaSu
 // raise a kernel's dynamic shared-memory limit once per context (= per device)
 int  niti_func_smem(niti_ctx* ctx, const void* fn, int bytes, const char* what);
 int  niti_check_launch(niti_ctx* ctx, const char* what);
+// 2x2/2 max-pool gradient that takes the window maximum from x itself (elementwise.cu)
+int  niti_maxpool_grad_from_x(niti_ctx* ctx, const int8_t* x, const int8_t* dy, int n, int h, int w, int c, int8_t* dx, int gate_relu,
+                              niti_stream st);
 int  niti_ws_acc(niti_ctx* ctx, size_t bytes, int32_t** out);
 int  niti_ws_i8(niti_ctx* ctx, size_t bytes, int8_t** out);
 

@@ -1,0 +1,499 @@
+// conv_chain.cu — the layer-walking fused NITI op: one persistent launch runs a CHAIN of forward (or dX) convolutions.
+//
+// Per layer (= one reference op, NITI_Conv_Int8.cpp:162-310 / NITI_DeConv_Int8.cpp:187-332, plus the element-wise ops the
+// reference runs around it):
+//     contraction (TMA im2col -> tcgen05.mma.cta_group::2 kind::i8, int32 in tensor memory)
+//  -> max|acc| straight from tensor memory -> grid barrier (+ NVLink peer exchange when data-parallel, dp.cuh)
+//  -> shared exponent -> PSTO -> int8, with the neighbouring element-wise ops folded into the store:
+//        forward : ReLU (NITI_CPURelu_Int8) and the 2x2/2 max pool that follows it (NITI_Maxpool_Int8.cpp:24-70)
+//        dX      : ReLU-grad gate (NITI_CPUReluGrad_Int8) or max-pool gradient + gate (NITI_CPUPoolGrad_Int8.cpp:36-72)
+//  -> grid barrier -> next layer (its operand is what this layer just stored).
+// The reference executes these as separate ops in a serial per-op loop (express/Executor.cpp:333-359); round 1 ran one
+// launch per op (igemm_fused_kernel<BN,BKC>, conv_tma2.cu) and measured 7-14 us of launch + prologue + drain per op on top
+// of 9-24 us in the kernel (profiles/phase_r2_vgg_before.txt).  Here tile shape and pipeline depth are run-time per layer,
+// tensor memory is allocated once, the mbarrier ring is re-used across layers with per-stage phase bits, and a chain of one
+// layer is the single-op entry point (niti_conv_fwd_fused / niti_conv_dx_fused).
+#include "pair_ptx.cuh"
+#include "tma_common.cuh"
+#include <new>
+#include <vector>
+
+bool tma2_fwd_eligible(const niti_conv_desc*);
+bool tma2_dx_eligible(const niti_conv_desc*);
+
+namespace {
+
+constexpr int kChainThreads = 576;   // warp 0: TMA producer, warp 1: MMA issuer + TMEM owner, warps 2-17: epilogue
+constexpr int kChainMaxTiles = 8;    // resident accumulator tiles per CTA pair (512 TMEM columns / 64)
+constexpr int kChainMaxStages = 8;
+constexpr int kChainSmem = 232448;   // all of it: one CTA per SM is a requirement (512 TMEM columns + grid barriers)
+constexpr int kChainStageArea = ((kChainSmem - 1024 - 512) / 1024) * 1024;
+
+struct alignas(128) ChainLayer {
+    CUtensorMap mapA;                 // activations (forward: x, dX: dy), im2col mode, box {bkc, 128 pixels}
+    CUtensorMap mapB;                 // weights [Ncols][K] K-major, box {bkc, bn/2}
+    int M, Ncols;                     // output extents: pixels x channels
+    int out_h, out_w;                 // pixel space enumerated by the im2col rows
+    int kh, kw, dil, stride, lower_h, lower_w, flip;
+    int cchunks, num_kb;              // channel chunks per tap; K blocks per tile
+    int n_tiles, items, pairs;        // items = m_tiles * n_tiles, distributed over `pairs` CTA pairs
+    int bn, bkc, stages;
+    int8_t* y; const int8_t* gate;
+    const int8_t* exp_a; const int8_t* exp_b; int8_t* exp_out;
+    uint32_t* maxabs;
+    int relu, dp_slot;
+    int8_t* y_pool; int pool;         // forward: 2x2/2 max pool of y fused into the store (out_w in {2,4,8,16}, out_h even)
+    const int8_t* pg_x; int pg_gate;  // dX: the result is the gradient w.r.t. a pooled tensor; pg_x = the pre-pool forward
+                                      // tensor [n][2*out_h][2*out_w][Ncols]; y receives the gradient w.r.t. it
+};
+
+struct ChainArgs {
+    const ChainLayer* table;          // device array, or nullptr: use the by-value layer
+    int nlayers;
+    uint32_t* sync;                   // {arrival counter, exit counter}
+    DpView dp;
+    unsigned long long* trace;        // [layer][block][8] globaltimer stamps, or nullptr
+    int trigger_late;
+};
+
+__device__ __forceinline__ void chain_trace(unsigned long long* trace, int layer, int slot) {
+    if (trace != nullptr) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        trace[((size_t)layer * gridDim.x + blockIdx.x) * 8 + slot] = t;
+    }
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ uint32_t pack4c(int32_t a, int32_t b, int32_t c, int32_t d) {
+    return (uint32_t)(a & 0xff) | ((uint32_t)(b & 0xff) << 8) | ((uint32_t)(c & 0xff) << 16) | ((uint32_t)(d & 0xff) << 24);
+}
+__device__ __forceinline__ uint4 ldg_u4(const int8_t* p) { return *reinterpret_cast<const uint4*>(p); }
+__device__ __forceinline__ uint4 vmax4(uint4 a, uint4 b) {
+    return make_uint4(__vmaxs4(a.x, b.x), __vmaxs4(a.y, b.y), __vmaxs4(a.z, b.z), __vmaxs4(a.w, b.w));
+}
+__device__ __forceinline__ uint4 vand4(uint4 a, uint4 b) { return make_uint4(a.x & b.x, a.y & b.y, a.z & b.z, a.w & b.w); }
+__device__ __forceinline__ uint4 vandn4(uint4 a, uint4 b) { return make_uint4(a.x & ~b.x, a.y & ~b.y, a.z & ~b.z, a.w & ~b.w); }
+__device__ __forceinline__ uint4 vor4(uint4 a, uint4 b) { return make_uint4(a.x | b.x, a.y | b.y, a.z | b.z, a.w | b.w); }
+__device__ __forceinline__ uint4 vge4(uint4 a, uint4 b) {
+    return make_uint4(__vcmpges4(a.x, b.x), __vcmpges4(a.y, b.y), __vcmpges4(a.z, b.z), __vcmpges4(a.w, b.w));
+}
+__device__ __forceinline__ uint4 vgt0(uint4 a) {
+    return make_uint4(__vcmpgts4(a.x, 0u), __vcmpgts4(a.y, 0u), __vcmpgts4(a.z, 0u), __vcmpgts4(a.w, 0u));
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kChainThreads, 1)
+chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
+    extern __shared__ uint8_t smem_raw_chain[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw_chain) + 1023) & ~(uintptr_t)1023);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kChainStageArea);            // used in the leader only
+    uint64_t* empty_bar = full_bar + kChainMaxStages;                                    // per CTA
+    uint64_t* tfull_bar = empty_bar + kChainMaxStages;                                   // per CTA, one per resident tile
+    uint64_t* layer_bar = tfull_bar + kChainMaxTiles;                                    // per CTA: the next layer's operand is in memory
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(layer_bar + 1);
+    uint32_t* bcast = tmem_slot + 1;
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t rank = cluster_ctarank();
+    const int pair = blockIdx.x >> 1;
+    if (!a.trigger_late) niti_pdl_trigger();                 // the next launch of the stream may start placing its CTAs
+    if (tid == 64) chain_trace(a.trace, 0, 0);
+
+    if (tid == 0) {
+        for (int s = 0; s < kChainMaxStages; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], 1); }
+        for (int t = 0; t < kChainMaxTiles; ++t) tc::mbar_init(&tfull_bar[t], 1);
+        tc::mbar_init(layer_bar, 1);
+        tc::fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc2<512>(tmem_slot);
+    tc::tc_fence_before();
+    cluster_sync_all();
+    tc::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    niti_pdl_wait();                                         // prologue done; everything the previous launch wrote is visible
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ------------------------------ TMA producer (both CTAs) ------------------------------
+            uint32_t pphase = 0;                             // per-stage phase bits of empty_bar
+            for (int l = 0; l < a.nlayers; ++l) {
+                const ChainLayer& L = a.table ? a.table[l] : single;
+                prefetch_tmap2(&L.mapA); prefetch_tmap2(&L.mapB);
+                if (l > 0) {
+                    tc::mbar_wait(layer_bar, (uint32_t)(l - 1) & 1u);       // previous layer stored everywhere (grid barrier passed)
+                    tmax::fence_proxy_async_all();                          // generic-proxy stores -> async-proxy (TMA) reads
+                }
+                if (pair >= L.pairs) continue;
+                const uint32_t a_bytes = 128u * (uint32_t)L.bkc, stage = a_bytes + (uint32_t)(L.bn / 2) * (uint32_t)L.bkc;
+                int s = 0;
+                for (int item = pair; item < L.items; item += L.pairs) {
+                    const int n_t = item % L.n_tiles; const int m_t = item / L.n_tiles;
+                    int m0 = m_t * 256 + (int)rank * 128;
+                    if (m0 >= L.M) m0 = 0;                   // fully out-of-range half: load valid rows, results are masked
+                    const int nrow0 = n_t * L.bn + (int)rank * (L.bn / 2);
+                    const int q = m0 % L.out_w; const int t = m0 / L.out_w;
+                    const int pp = t % L.out_h; const int bn_ = t / L.out_h;
+                    const int bw = q * L.stride + L.lower_w, bh = pp * L.stride + L.lower_h;
+                    for (int kb = 0; kb < L.num_kb; ++kb) {
+                        tc::mbar_wait(&empty_bar[s], ((pphase >> s) & 1u) ^ 1u);
+                        pphase ^= 1u << s;
+                        const uint32_t a_dst = tc::smem_u32(smem) + (uint32_t)s * stage;
+                        if (rank == 0) mbar_expect_tx(&full_bar[s], 2u * stage);
+                        const int tp = kb / L.cchunks, cc = kb - tp * L.cchunks;
+                        int ky = tp / L.kw, kx = tp - ky * L.kw;
+                        if (L.flip) { ky = L.kh - 1 - ky; kx = L.kw - 1 - kx; }
+                        tma2_load_im2col(&L.mapA, a_dst, &full_bar[s], cc * L.bkc, bw, bh, bn_, (uint16_t)(kx * L.dil), (uint16_t)(ky * L.dil));
+                        tma2_load_2d(&L.mapB, a_dst + a_bytes, &full_bar[s], kb * L.bkc, nrow0);
+                        if (++s == L.stages) s = 0;
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && rank == 0) {
+            // ------------------------------ MMA issuer (leader CTA only) ------------------------------
+            uint32_t cphase = 0;                             // per-stage phase bits of full_bar
+            for (int l = 0; l < a.nlayers; ++l) {
+                const ChainLayer& L = a.table ? a.table[l] : single;
+                if (pair >= L.pairs) continue;
+                const uint32_t idesc = tc::make_idesc_i8(256, L.bn, 0, 0);
+                const uint32_t lay = (L.bkc == 128) ? 2u : 4u;
+                const uint32_t a_bytes = 128u * (uint32_t)L.bkc, stage = a_bytes + (uint32_t)(L.bn / 2) * (uint32_t)L.bkc;
+                const uint32_t sbo = 8u * (uint32_t)L.bkc;
+                const int ksteps = L.bkc / 32;
+                int s = 0; uint32_t tile_iter = 0;
+                for (int item = pair; item < L.items; item += L.pairs, ++tile_iter) {
+                    const uint32_t d_tmem = tmem_base + tile_iter * (uint32_t)L.bn;       // every tile keeps its own columns
+                    for (int kb = 0; kb < L.num_kb; ++kb) {
+                        tc::mbar_wait(&full_bar[s], (cphase >> s) & 1u);
+                        cphase ^= 1u << s;
+                        tc::tc_fence_after();
+                        const uint32_t a_base = tc::smem_u32(smem) + (uint32_t)s * stage;
+                        const uint32_t b_base = a_base + a_bytes;
+                        for (int kk = 0; kk < ksteps; ++kk) {
+                            const uint64_t ad = make_desc2(a_base + kk * 32, 16, sbo, lay);
+                            const uint64_t bd = make_desc2(b_base + kk * 32, 16, sbo, lay);
+                            umma2_i8(d_tmem, ad, bd, idesc, (uint32_t)((kb != 0) || (kk != 0)));
+                        }
+                        umma2_commit_mc(&empty_bar[s], 3);   // frees this stage in both CTAs
+                        if (++s == L.stages) s = 0;
+                    }
+                    umma2_commit_mc(&tfull_bar[tile_iter], 3);
+                }
+            }
+        }
+    } else {
+        // ------------------------------ epilogue (warps 2..17, both CTAs) ------------------------------
+        const int quarter = warp & 3;                        // TMEM lane quarter this warp may read
+        const int group = (warp - 2) >> 2;                   // four warps share a quarter: every 4th 16-column chunk each
+        const int etid = tid - 64;
+        uint32_t tphase = 0;                                 // per-tile phase bits of tfull_bar
+        uint32_t nbar = 0;                                   // grid barriers passed so far
+        if (etid == 0) chain_trace(a.trace, 0, 1);
+        for (int l = 0; l < a.nlayers; ++l) {
+            const ChainLayer& L = a.table ? a.table[l] : single;
+            const bool active = pair < L.pairs;
+            int shift = 0, kind = 0;
+            uint32_t mx = 0;
+            const int hw = L.out_h * L.out_w;
+            for (int pass = 0; pass < 2; ++pass) {
+                uint32_t tile_iter = 0;
+                if (active)
+                for (int item = pair; item < L.items; item += L.pairs, ++tile_iter) {
+                    const int n_t = item % L.n_tiles; const int m_t = item / L.n_tiles;
+                    const int row0 = m_t * 256 + (int)rank * 128 + quarter * 32;
+                    const int row = row0 + lane;
+                    const int n0 = n_t * L.bn;
+                    if (pass == 0) {
+                        tc::mbar_wait(&tfull_bar[tile_iter], (tphase >> tile_iter) & 1u);
+                        tc::tc_fence_after();
+                        if (etid == 0 && tile_iter == 0) chain_trace(a.trace, l, 2);
+                    }
+                    if (row0 >= L.M) continue;               // warp-uniform
+                    const bool row_ok = row < L.M;
+                    // pixel coordinates of this row (pool / pool-gradient addressing)
+                    int img = 0, py = 0, px = 0;
+                    if (pass == 1 && (L.pool || L.pg_x != nullptr)) { img = row / hw; const int r = row - img * hw; py = r / L.out_w; px = r - py * L.out_w; }
+#pragma unroll 1
+                    for (int c0 = group * 16; c0 < L.bn; c0 += 64) {
+                        if (n0 + c0 >= L.Ncols) break;       // warp-uniform (Ncols % 16 == 0)
+                        uint32_t v[16];
+                        tmem_ld16(tmem_base + ((uint32_t)(quarter * 32) << 16) + tile_iter * (uint32_t)L.bn + (uint32_t)c0, v);
+                        tc::tmem_ld_wait();
+                        if (pass == 0) {
+                            if (row_ok) {
+#pragma unroll
+                                for (int q = 0; q < 16; ++q) mx = max(mx, niti_abs_u32((int32_t)v[q]));
+                            }
+                            continue;
+                        }
+                        uint32_t o[4];
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            int32_t r[4];
+#pragma unroll
+                            for (int k = 0; k < 4; ++k) {
+                                const int32_t x = (int32_t)v[4 * q + k];
+                                r[k] = kind == 0 ? niti_psto_fast(x, shift) : x;      // kind 0 has shift >= 2; kind 1: raw cast (Q3)
+                            }
+                            o[q] = pack4c(r[0], r[1], r[2], r[3]);
+                        }
+                        if (L.relu) { o[0] = __vmaxs4(o[0], 0u); o[1] = __vmaxs4(o[1], 0u); o[2] = __vmaxs4(o[2], 0u); o[3] = __vmaxs4(o[3], 0u); }
+                        const int col = n0 + c0;
+                        if (L.pg_x == nullptr) {
+                            const size_t off = (size_t)row * L.Ncols + col;
+                            if (row_ok) {
+                                if (L.gate != nullptr) {     // NITI_CPUReluGrad: pass where the forward value was > 0
+                                    const uint4 g = vgt0(ldg_u4(L.gate + off));
+                                    o[0] &= g.x; o[1] &= g.y; o[2] &= g.z; o[3] &= g.w;
+                                }
+                                *reinterpret_cast<uint4*>(L.y + off) = make_uint4(o[0], o[1], o[2], o[3]);
+                            }
+                            if (L.pool) {
+                                // 2x2/2 max pool across lanes: lane bit 0 = x parity, lane bit log2(out_w) = y parity
+                                uint32_t m[4];
+#pragma unroll
+                                for (int q = 0; q < 4; ++q) {
+                                    m[q] = __vmaxs4(o[q], __shfl_xor_sync(0xffffffffu, o[q], 1));
+                                    m[q] = __vmaxs4(m[q], __shfl_xor_sync(0xffffffffu, m[q], L.out_w));
+                                }
+                                if (row_ok && !(px & 1) && !(py & 1)) {
+                                    const size_t po = (((size_t)img * (L.out_h >> 1) + (py >> 1)) * (L.out_w >> 1) + (px >> 1)) * L.Ncols + col;
+                                    *reinterpret_cast<uint4*>(L.y_pool + po) = make_uint4(m[0], m[1], m[2], m[3]);
+                                }
+                            }
+                        } else if (row_ok) {
+                            // max-pool gradient (+ ReLU-grad gate): this row is one pooled pixel; route its gradient to the
+                            // first window element (row-major) that equals the window maximum, zero elsewhere
+                            const int w2 = L.out_w * 2;
+                            const size_t b00 = (((size_t)img * (L.out_h * 2) + 2 * py) * w2 + 2 * px) * L.Ncols + col;
+                            const size_t b10 = b00 + (size_t)w2 * L.Ncols;
+                            const uint4 x00 = ldg_u4(L.pg_x + b00), x01 = ldg_u4(L.pg_x + b00 + L.Ncols);
+                            const uint4 x10 = ldg_u4(L.pg_x + b10), x11 = ldg_u4(L.pg_x + b10 + L.Ncols);
+                            const uint4 mxv = vmax4(vmax4(x00, x01), vmax4(x10, x11));
+                            const uint4 g = make_uint4(o[0], o[1], o[2], o[3]);
+                            uint4 e0 = vge4(x00, mxv), done = e0;
+                            uint4 e1 = vandn4(vge4(x01, mxv), done); done = vor4(done, e1);
+                            uint4 e2 = vandn4(vge4(x10, mxv), done); done = vor4(done, e2);
+                            uint4 e3 = vandn4(vge4(x11, mxv), done);
+                            if (L.pg_gate) { e0 = vand4(e0, vgt0(x00)); e1 = vand4(e1, vgt0(x01)); e2 = vand4(e2, vgt0(x10)); e3 = vand4(e3, vgt0(x11)); }
+                            *reinterpret_cast<uint4*>(L.y + b00) = vand4(g, e0);
+                            *reinterpret_cast<uint4*>(L.y + b00 + L.Ncols) = vand4(g, e1);
+                            *reinterpret_cast<uint4*>(L.y + b10) = vand4(g, e2);
+                            *reinterpret_cast<uint4*>(L.y + b10 + L.Ncols) = vand4(g, e3);
+                        }
+                    }
+                }
+                if (pass == 0) {
+                    // ---- global max|acc|: warp max -> atomicMax -> grid barrier -> (data parallel: peer exchange) ----
+                    mx = warp_max_u32(mx);
+                    if (lane == 0 && mx) atomicMax(L.maxabs, mx);
+                    asm volatile("bar.sync 1, 512;" ::: "memory");
+                    if (a.trigger_late && l == a.nlayers - 1) niti_pdl_trigger();
+                    if (etid == 0) {
+                        chain_trace(a.trace, l, 3);
+                        ++nbar; niti_grid_barrier(a.sync, nbar * gridDim.x);
+                        chain_trace(a.trace, l, 4);
+                        *bcast = dp_exchange_max(a.dp, L.dp_slot, __ldcg(L.maxabs), blockIdx.x == 0);
+                    }
+                    asm volatile("bar.sync 1, 512;" ::: "memory");
+                    const int b = niti_bitwidth(*bcast);
+                    const int s = b - 7;
+                    if (s > 1) { shift = s; kind = 0; } else if (s == 1) { shift = 2; kind = 0; } else { shift = 0; kind = 1; }
+                    if (blockIdx.x == 0 && etid == 0 && L.exp_out != nullptr)
+                        *L.exp_out = (int8_t)((L.exp_a ? (int)*L.exp_a : 0) + (L.exp_b ? (int)*L.exp_b : 0) + (kind == 1 ? 0 : shift));
+                }
+            }
+            // this pair's tiles of the layer are drained: flip their phase bits
+            if (active) {
+                const int mine = (L.items - pair + L.pairs - 1) / L.pairs;
+                tphase ^= (1u << mine) - 1u;
+            }
+            tc::tc_fence_before();
+            asm volatile("bar.sync 1, 512;" ::: "memory");   // every epilogue warp of this CTA has stored (and read TMEM)
+            if (etid == 0) {
+                chain_trace(a.trace, l, 5);
+                if (l + 1 < a.nlayers) {
+                    ++nbar; niti_grid_barrier(a.sync, nbar * gridDim.x);          // the layer's output is complete everywhere
+                    tc::mbar_arrive(layer_bar);                                    // release this CTA's producer
+                    chain_trace(a.trace, l, 6);
+                }
+            }
+        }
+        if (etid == 0) {                                     // last CTA out re-arms the grid barrier for the next launch
+            __threadfence();
+            if (atomicAdd(a.sync + 1, 1u) == gridDim.x - 1) { a.sync[0] = 0u; a.sync[1] = 0u; __threadfence(); }
+        }
+    }
+    __syncwarp();
+    tc::tc_fence_before();
+    cluster_sync_all();
+    if (warp == 1) tmem_dealloc2<512>(tmem_base);
+    if (tid == 64) chain_trace(a.trace, a.nlayers - 1, 7);
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+// tile shape + residency plan: the largest BN that still gives >= ~2/3 of the CTA pairs a tile; every pair must be able to
+// keep all its tiles in its 512 TMEM columns
+bool chain_plan(int max_pairs, int M, int Ncols, int* bn_out, int* pairs_out, int* items_out) {
+    const long m_tiles = (M + 255) / 256;
+    int bn = 64;
+    for (int cand : {256, 128}) {
+        if (Ncols > cand / 2 && m_tiles * ((Ncols + cand - 1) / cand) >= (2 * max_pairs) / 3) { bn = cand; break; }
+    }
+    if (Ncols <= 64) bn = 64; else if (Ncols <= 128 && bn > 128) bn = 128;
+    const long items = m_tiles * ((Ncols + bn - 1) / bn);
+    const int pairs = (int)(items < max_pairs ? items : max_pairs);
+    const long per_pair = (items + pairs - 1) / pairs;
+    if (per_pair * bn > 512 || per_pair > kChainMaxTiles) return false;
+    *bn_out = bn; *pairs_out = pairs; *items_out = (int)items;
+    return true;
+}
+
+bool pool_geometry_ok(int out_h, int out_w) {
+    return (out_w == 2 || out_w == 4 || out_w == 8 || out_w == 16) && out_h % 2 == 0 && (out_h * out_w) % 2 == 0;
+}
+
+}  // namespace
+
+// One op of a chain as the C ABI describes it (niti_b200.h niti_chain_op), lowered to the kernel's layer record.
+// Returns NITI_OK, or NITI_ERR_UNSUPPORTED when the op cannot run in the fused kernel (caller falls back).
+int chain_lower(niti_ctx* ctx, const niti_chain_op* op, ChainLayer* L) {
+    if (!tmax::driver_ok()) return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncode* entry points unavailable");
+    const niti_conv_desc* d = &op->d;
+    const int oh = conv_out_h(d), ow = conv_out_w(d);
+    const int max_pairs = ctx->sm_count / 2;
+    *L = ChainLayer{};
+    int bn, pairs, items;
+    if (op->op == 0) {
+        if (!tma2_fwd_eligible(d) || d->oc % 16 != 0) return NITI_ERR_UNSUPPORTED;
+        L->M = d->n * oh * ow; L->Ncols = d->oc;
+        if (!chain_plan(max_pairs, L->M, L->Ncols, &bn, &pairs, &items)) return NITI_ERR_UNSUPPORTED;
+        L->bkc = d->c % 128 == 0 ? 128 : 64;
+        L->out_h = oh; L->out_w = ow; L->kh = d->kh; L->kw = d->kw; L->dil = d->dil; L->stride = d->stride;
+        L->lower_h = -d->pad; L->lower_w = -d->pad; L->flip = 0;
+        L->cchunks = d->c / L->bkc; L->num_kb = d->kh * d->kw * L->cchunks;
+        if (!tmax::make_im2col_u8(&L->mapA, op->in, d->n, d->h, d->w, d->c, -d->pad, -d->pad, d->pad - (d->kh - 1) * d->dil,
+                                  d->pad - (d->kw - 1) * d->dil, d->stride, L->bkc, 128, L->bkc))
+            return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncodeIm2col(x) failed");
+        if (!tmax::make_tiled_u8(&L->mapB, op->w, (uint64_t)d->oc, (uint64_t)d->kh * d->kw * d->c, (uint32_t)(bn / 2), (uint32_t)L->bkc, L->bkc))
+            return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncodeTiled(w) failed");
+        if (op->out_pool != nullptr) {
+            if (!pool_geometry_ok(oh, ow)) return NITI_ERR_UNSUPPORTED;
+            L->pool = 1; L->y_pool = op->out_pool;
+        }
+        L->relu = op->relu; L->exp_a = op->ex; L->exp_b = op->ew; L->exp_out = op->ey;
+    } else {
+        if (!tma2_dx_eligible(d) || d->c % 16 != 0) return NITI_ERR_UNSUPPORTED;
+        const int pph = (d->kh - 1) * d->dil - d->pad, ppw = (d->kw - 1) * d->dil - d->pad;   // padding of the equivalent forward conv
+        L->M = d->n * d->h * d->w; L->Ncols = d->c;
+        if (!chain_plan(max_pairs, L->M, L->Ncols, &bn, &pairs, &items)) return NITI_ERR_UNSUPPORTED;
+        L->bkc = d->oc % 128 == 0 ? 128 : 64;
+        L->out_h = d->h; L->out_w = d->w; L->kh = d->kh; L->kw = d->kw; L->dil = d->dil; L->stride = 1;
+        L->lower_h = -pph; L->lower_w = -ppw; L->flip = 1;
+        L->cchunks = d->oc / L->bkc; L->num_kb = d->kh * d->kw * L->cchunks;
+        if (!tmax::make_im2col_u8(&L->mapA, op->in, d->n, oh, ow, d->oc, -pph, -ppw, d->h - oh - pph, d->w - ow - ppw, 1, L->bkc, 128, L->bkc))
+            return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncodeIm2col(dy) failed");
+        if (!tmax::make_tiled_u8(&L->mapB, op->w, (uint64_t)d->c, (uint64_t)d->kh * d->kw * d->oc, (uint32_t)(bn / 2), (uint32_t)L->bkc, L->bkc))
+            return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncodeTiled(wt) failed");
+        L->gate = op->gate;
+        if (op->pool_x != nullptr) { L->pg_x = op->pool_x; L->pg_gate = op->pool_gate; L->gate = nullptr; }
+    }
+    L->n_tiles = (L->Ncols + bn - 1) / bn; L->items = items; L->pairs = pairs; L->bn = bn;
+    const int stage = 128 * L->bkc + (bn / 2) * L->bkc;
+    L->stages = kChainStageArea / stage > kChainMaxStages ? kChainMaxStages : kChainStageArea / stage;
+    L->y = op->out; L->maxabs = op->maxabs; L->dp_slot = op->dp_slot;
+    return NITI_OK;
+}
+
+struct niti_chain {
+    ChainLayer* table;                // device
+    int nlayers, grid;
+    std::vector<ChainLayer> host;
+};
+
+static int chain_launch(niti_ctx* ctx, const ChainLayer* single, const ChainLayer* table, int nlayers, int grid, cudaStream_t st) {
+    if (int rc = niti_func_smem(ctx, (const void*)chain_kernel, kChainSmem, "cudaFuncSetAttribute(chain_kernel)")) return rc;
+    ChainArgs a{};
+    a.table = table; a.nlayers = nlayers; a.sync = ctx->ws_u32 + 52; a.dp = ctx->dp; a.trace = ctx->trace;
+    a.trigger_late = (ctx->pdl & NITI_PDL_TRIGGER_LATE) ? 1 : 0;
+    static const ChainLayer zero{};
+    cudaError_t e = niti_launch(ctx, NITI_PDL_FUSED, chain_kernel, dim3(grid), dim3(kChainThreads), (size_t)kChainSmem, st,
+                                single ? *single : zero, a);
+    if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "launch chain_kernel", e);
+    return niti_check_launch(ctx, "chain_kernel");
+}
+
+// single op through the chain kernel (the fused forward / dX entry points of api.cu)
+int chain_run_single(niti_ctx* ctx, const niti_chain_op* op, cudaStream_t st) {
+    ChainLayer L;
+    int rc = chain_lower(ctx, op, &L);
+    if (rc != NITI_OK) return rc;
+    return chain_launch(ctx, &L, nullptr, 1, 2 * L.pairs, st);
+}
+
+bool chain_op_eligible(niti_ctx* ctx, const niti_chain_op* op) {
+    const niti_conv_desc* d = &op->d;
+    const int max_pairs = ctx->sm_count / 2;
+    int bn, pairs, items;
+    if (op->op == 0) {
+        if (!tma2_fwd_eligible(d) || d->oc % 16 != 0) return false;
+        if (!chain_plan(max_pairs, d->n * conv_out_h(d) * conv_out_w(d), d->oc, &bn, &pairs, &items)) return false;
+        return op->out_pool == nullptr || pool_geometry_ok(conv_out_h(d), conv_out_w(d));
+    }
+    if (!tma2_dx_eligible(d) || d->c % 16 != 0) return false;
+    return chain_plan(max_pairs, d->n * d->h * d->w, d->c, &bn, &pairs, &items);
+}
+
+extern "C" int niti_chain_op_eligible(niti_ctx* ctx, const niti_chain_op* op) {
+    if (!ctx || !op) return 0;
+    if (!(ctx->path == NITI_PATH_AUTO || ctx->path == NITI_PATH_TMA2) || !ctx->auto_tma2 || !ctx->use_chain) return 0;
+    return chain_op_eligible(ctx, op) ? 1 : 0;
+}
+
+extern "C" int niti_chain_create(niti_ctx* ctx, const niti_chain_op* ops, int n, niti_chain** out) {
+    if (!ctx || !ops || n <= 0 || !out) return niti_fail(ctx, NITI_ERR_ARG, "niti_chain_create: bad argument");
+    *out = nullptr;
+    niti_chain* c = new (std::nothrow) niti_chain();
+    if (!c) return niti_fail(ctx, NITI_ERR_CUDA, "niti_chain_create: out of host memory");
+    c->host.resize(n);
+    int max_pairs = 0;
+    for (int i = 0; i < n; ++i) {
+        if (!ops[i].in || !ops[i].w || !ops[i].out || !ops[i].maxabs || ops[i].dp_slot < 0 || ops[i].dp_slot >= kDpSlots) {
+            delete c; return niti_fail(ctx, NITI_ERR_ARG, "niti_chain_create: op with a null operand or a slot out of range");
+        }
+        int rc = chain_lower(ctx, &ops[i], &c->host[i]);
+        if (rc != NITI_OK) {
+            delete c;
+            return rc == NITI_ERR_UNSUPPORTED ? niti_fail(ctx, rc, "niti_chain_create: an op is outside the fused kernel's contract") : rc;
+        }
+        if (c->host[i].pairs > max_pairs) max_pairs = c->host[i].pairs;
+    }
+    c->nlayers = n; c->grid = 2 * max_pairs;
+    cudaError_t e = cudaMalloc(&c->table, sizeof(ChainLayer) * (size_t)n);
+    if (e != cudaSuccess) { delete c; return niti_fail(ctx, NITI_ERR_CUDA, "niti_chain_create: cudaMalloc", e); }
+    e = cudaMemcpy(c->table, c->host.data(), sizeof(ChainLayer) * (size_t)n, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) { cudaFree(c->table); delete c; return niti_fail(ctx, NITI_ERR_CUDA, "niti_chain_create: upload", e); }
+    *out = c;
+    return NITI_OK;
+}
+
+extern "C" int niti_chain_run(niti_ctx* ctx, niti_chain* c, niti_stream st) {
+    if (!ctx || !c || !c->table) return niti_fail(ctx, NITI_ERR_ARG, "niti_chain_run: bad argument");
+    ctx->last_path = "chain";
+    return chain_launch(ctx, nullptr, c->table, c->nlayers, c->grid, (cudaStream_t)st);
+}
+
+extern "C" int niti_chain_destroy(niti_ctx* ctx, niti_chain* c) {
+    if (!c) return NITI_ERR_ARG;
+    if (c->table) cudaFree(c->table);
+    delete c;
+    return NITI_OK;
+}

@@ -154,7 +154,19 @@ __global__ void __launch_bounds__(kThreads) maxpool_grad_vec_kernel(const uint4*
         int cv = (int)(i % c16); size_t p = i / c16;
         int ox = (int)(p % ow); p /= ow;
         int oy = (int)(p % oh); int b = (int)(p / oh);
-        const uint4 m = y[i], g = dy[i];
+        const uint4 g = dy[i];
+        uint4 m;
+        if (y != nullptr) m = y[i];
+        else {                                               // window maximum taken from x itself
+            m = make_uint4(0x80808080u, 0x80808080u, 0x80808080u, 0x80808080u);
+            for (int ky = 0; ky < k; ++ky) {
+                int iy = oy * k + ky; if (iy >= h) break;
+                for (int kx = 0; kx < k; ++kx) {
+                    int ix = ox * k + kx; if (ix >= w) break;
+                    m = vmax4x4(m, x[(((size_t)b * h + iy) * w + ix) * c16 + cv]);
+                }
+            }
+        }
         uint4 done = make_uint4(0u, 0u, 0u, 0u);
         for (int ky = 0; ky < k; ++ky) {
             int iy = oy * k + ky; if (iy >= h) break;
@@ -172,15 +184,17 @@ __global__ void __launch_bounds__(kThreads) maxpool_grad_vec_kernel(const uint4*
     }
 }
 
-// integer softmax cross-entropy gradient; one thread per sample (batch is small, classes ~10)
+// integer softmax cross-entropy gradient; one thread per sample (batch is small, classes ~10).  Rows are `stride` bytes
+// apart, the first `classes` entries are real, grad's padding columns are written as 0.  ev(j) and the 64-bit division are
+// evaluated once per class (kept in a local array for classes <= 32, recomputed beyond that).
 __global__ void loss_grad_kernel(const int8_t* __restrict__ logits, const int8_t* __restrict__ ascale_p,
-                                 const int32_t* __restrict__ labels, int batch, int classes, int8_t* __restrict__ grad) {
+                                 const int32_t* __restrict__ labels, int batch, int classes, int stride, int8_t* __restrict__ grad) {
     niti_pdl_trigger(); niti_pdl_wait();                     // programmatic dependent launch: see common.cuh
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= batch) return;
     const int a = (int)*ascale_p;
-    const int8_t* row = logits + (size_t)i * classes;
-    int8_t* out = grad + (size_t)i * classes;
+    const int8_t* row = logits + (size_t)i * stride;
+    int8_t* out = grad + (size_t)i * stride;
     long long sum = 0;
     long long mx = 0;
     if (a > -7) {
@@ -202,15 +216,22 @@ __global__ void loss_grad_kernel(const int8_t* __restrict__ logits, const int8_t
         long long t = row[j];
         return base + t * shiftbase + t * t;
     };
-    for (int j = 0; j < classes; ++j) sum += ev(j);
+    constexpr int kKeep = 32;
+    long long e[kKeep];
+    for (int j = 0; j < classes; ++j) { const long long v = ev(j); if (j < kKeep) e[j] = v; sum += v; }
     long long gsum = 0;
-    for (int j = 0; j < classes; ++j) gsum += (ev(j) * (1 << 11)) / sum;
+    for (int j = 0; j < classes; ++j) {
+        const long long g = ((j < kKeep ? e[j] : ev(j)) * (1 << 11)) / sum;
+        if (j < kKeep) e[j] = g;
+        gsum += g;
+    }
     const int tgt = labels[i];
     for (int j = 0; j < classes; ++j) {
-        long long g = (ev(j) * (1 << 11)) / sum;
+        long long g = j < kKeep ? e[j] : (ev(j) * (1 << 11)) / sum;
         if (j == tgt) g -= gsum;
         out[j] = (int8_t)niti_psto((int32_t)g, 4);
     }
+    for (int j = classes; j < stride; ++j) out[j] = 0;
 }
 
 // generic 4-d permutation of int8 tensors through index arithmetic (boundary only; small tensors)
@@ -311,13 +332,29 @@ extern "C" int niti_maxpool_grad(niti_ctx* ctx, const int8_t* x, const int8_t* y
                                  int k, int s, int8_t* dx, niti_stream st) {
     return niti_maxpool_grad_gated(ctx, x, y, dy, n, h, w, c, k, s, dx, 0, st);
 }
-extern "C" int niti_loss_grad(niti_ctx* ctx, const int8_t* logits, const int8_t* ascale, const int32_t* labels,
-                              int batch, int classes, int8_t* grad, niti_stream st) {
-    if (!ctx || !logits || !ascale || !labels || !grad || batch <= 0 || classes <= 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_loss_grad");
-    cudaError_t le = niti_launch(ctx, NITI_PDL_ELEMENTWISE, loss_grad_kernel, dim3((batch + 63) / 64), dim3(64), 0, (cudaStream_t)st, logits, ascale, labels,
-                                 batch, classes, grad);
+extern "C" int niti_loss_grad_strided(niti_ctx* ctx, const int8_t* logits, const int8_t* ascale, const int32_t* labels,
+                                      int batch, int classes, int stride, int8_t* grad, niti_stream st) {
+    if (!ctx || !logits || !ascale || !labels || !grad || batch <= 0 || classes <= 0 || stride < classes)
+        return niti_fail(ctx, NITI_ERR_ARG, "niti_loss_grad");
+    cudaError_t le = niti_launch(ctx, NITI_PDL_ELEMENTWISE, loss_grad_kernel, dim3((batch + 31) / 32), dim3(32), 0, (cudaStream_t)st, logits, ascale, labels,
+                                 batch, classes, stride, grad);
     if (le != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "launch loss_grad", le);
     return niti_check_launch(ctx, "loss_grad");
+}
+extern "C" int niti_loss_grad(niti_ctx* ctx, const int8_t* logits, const int8_t* ascale, const int32_t* labels,
+                              int batch, int classes, int8_t* grad, niti_stream st) {
+    return niti_loss_grad_strided(ctx, logits, ascale, labels, batch, classes, classes, grad, st);
+}
+int niti_maxpool_grad_from_x(niti_ctx* ctx, const int8_t* x, const int8_t* dy, int n, int h, int w, int c, int8_t* dx, int gate_relu,
+                             niti_stream st) {
+    if (!ctx || !x || !dy || !dx || n <= 0 || h < 2 || w < 2 || (h & 1) || (w & 1) || c % 16 != 0 || !aligned16(x) || !aligned16(dy) || !aligned16(dx))
+        return niti_fail(ctx, NITI_ERR_UNSUPPORTED, "max-pool gradient from x: needs even h, w and c % 16 == 0");
+    const int oh = h / 2, ow = w / 2;
+    cudaError_t le = niti_launch(ctx, NITI_PDL_ELEMENTWISE, maxpool_grad_vec_kernel, dim3(grid_for(ctx, (size_t)n * oh * ow * (c / 16))), dim3(kThreads), 0,
+                                 (cudaStream_t)st, reinterpret_cast<const uint4*>(x), (const uint4*)nullptr,
+                                 reinterpret_cast<const uint4*>(dy), n, h, w, c / 16, 2, oh, ow, reinterpret_cast<uint4*>(dx), gate_relu);
+    if (le != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "launch maxpool_grad_vec", le);
+    return niti_check_launch(ctx, "maxpool_grad_vec");
 }
 extern "C" int niti_nchw_to_nhwc(niti_ctx* ctx, const int8_t* src, int n, int c, int h, int w, int8_t* dst, niti_stream st) {
     if (!ctx || !src || !dst || n <= 0 || c <= 0 || h <= 0 || w <= 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_nchw_to_nhwc");

@@ -39,6 +39,13 @@ class UpdateSeg(C.Structure):
                 ("oc", C.c_int32), ("taps", C.c_int32), ("c", C.c_int32), ("sub", C.c_int32)]
 
 
+class ChainOp(C.Structure):
+    """niti_chain_op: one forward / dX op of a chain (include/niti_b200.h)"""
+    _fields_ = [("d", ConvDesc), ("op", C.c_int32), ("inp", _P), ("w", _P), ("ex", _P), ("ew", _P), ("ey", _P), ("out", _P),
+                ("relu", C.c_int32), ("gate", _P), ("out_pool", _P), ("pool_x", _P), ("pool_gate", C.c_int32),
+                ("maxabs", _P), ("dp_slot", C.c_int32)]
+
+
 _SIGS = {
     "niti_ctx_create": (C.c_int, [C.c_int, C.POINTER(_P)]),
     "niti_ctx_destroy": (C.c_int, [_P]),
@@ -72,6 +79,13 @@ _SIGS = {
     "niti_conv_fwd": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, _P]),
     "niti_conv_fwd_fused": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, C.c_int, _P, _P, C.c_int, _P]),
     "niti_conv_dx_fused": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, _P, C.c_int, _P]),
+    "niti_conv_fwd_fused_pool": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, C.c_int, _P, _P, _P, C.c_int, _P]),
+    "niti_conv_dx_fused_poolgrad": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P, C.c_int, _P, _P, _P, C.c_int, _P]),
+    "niti_chain_op_eligible": (C.c_int, [_P, C.POINTER(ChainOp)]),
+    "niti_chain_create": (C.c_int, [_P, _P, C.c_int, C.POINTER(_P)]),
+    "niti_chain_run": (C.c_int, [_P, _P, _P]),
+    "niti_chain_destroy": (C.c_int, [_P, _P]),
+    "niti_loss_grad_strided": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, _P, _P]),
     "niti_conv_dx": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P]),
     "niti_conv_dw": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P]),
     "niti_matmul_nt": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P, _P, _P]),
@@ -311,6 +325,43 @@ class NitiB200:
         self._ck(self.lib.niti_conv_dx_fused(self.h, C.byref(d), _ptr(dy), _ptr(w), _ptr(wt), _ptr(dx), _ptr(gate), _ptr(acc),
                                              _ptr(maxabs), int(dp_slot), self._stream(stream)))
 
+    def conv_fwd_fused_pool(self, d, x, w, ex, ew, y, ey, relu, y_pool, acc, maxabs, dp_slot=0, stream=None):
+        """forward op + ReLU + the 2x2/2 max pool behind it: writes y and y_pool"""
+        self._ck(self.lib.niti_conv_fwd_fused_pool(self.h, C.byref(d), _ptr(x), _ptr(w), _ptr(ex), _ptr(ew), _ptr(y), _ptr(ey),
+                                                   int(bool(relu)), _ptr(y_pool), _ptr(acc), _ptr(maxabs), int(dp_slot),
+                                                   self._stream(stream)))
+
+    def conv_dx_fused_poolgrad(self, d, dy, w, wt, dx_prepool, pool_x, gate_relu, dx_pooled, acc, maxabs, dp_slot=0, stream=None):
+        """dX op + max-pool gradient (+ ReLU gate) of the pool in front of this conv: writes the gradient w.r.t. pool_x"""
+        self._ck(self.lib.niti_conv_dx_fused_poolgrad(self.h, C.byref(d), _ptr(dy), _ptr(w), _ptr(wt), _ptr(dx_prepool), _ptr(pool_x),
+                                                      int(bool(gate_relu)), _ptr(dx_pooled), _ptr(acc), _ptr(maxabs), int(dp_slot),
+                                                      self._stream(stream)))
+
+    # ---- chains (several fused ops in one persistent launch)
+    @staticmethod
+    def chain_op(d, op, inp, w, out, maxabs, dp_slot, ex=None, ew=None, ey=None, relu=False, gate=None, out_pool=None,
+                 pool_x=None, pool_gate=False):
+        o = ChainOp()
+        o.d = d; o.op = int(op); o.inp = _ptr(inp); o.w = _ptr(w); o.ex = _ptr(ex); o.ew = _ptr(ew); o.ey = _ptr(ey)
+        o.out = _ptr(out); o.relu = int(bool(relu)); o.gate = _ptr(gate); o.out_pool = _ptr(out_pool)
+        o.pool_x = _ptr(pool_x); o.pool_gate = int(bool(pool_gate)); o.maxabs = _ptr(maxabs); o.dp_slot = int(dp_slot)
+        return o
+
+    def chain_op_eligible(self, op):
+        return bool(self.lib.niti_chain_op_eligible(self.h, C.byref(op)))
+
+    def chain_create(self, ops):
+        arr = (ChainOp * len(ops))(*ops)
+        h = _P()
+        self._ck(self.lib.niti_chain_create(self.h, C.cast(arr, _P), len(ops), C.byref(h)))
+        return h
+
+    def chain_run(self, chain, stream=None):
+        self._ck(self.lib.niti_chain_run(self.h, chain, self._stream(stream)))
+
+    def chain_destroy(self, chain):
+        self.lib.niti_chain_destroy(self.h, chain)
+
     def conv_dx(self, d, dy, w, dx, stream=None):
         self._ck(self.lib.niti_conv_dx(self.h, C.byref(d), _ptr(dy), _ptr(w), _ptr(dx), self._stream(stream)))
 
@@ -336,6 +387,10 @@ class NitiB200:
     def maxpool_grad_gated(self, x, y, dy, n, h, w, c, k, s, dx, gate_relu, stream=None):
         self._ck(self.lib.niti_maxpool_grad_gated(self.h, _ptr(x), _ptr(y), _ptr(dy), n, h, w, c, k, s, _ptr(dx),
                                                   int(bool(gate_relu)), self._stream(stream)))
+
+    def loss_grad_strided(self, logits, ascale, labels, batch, classes, stride, grad, stream=None):
+        self._ck(self.lib.niti_loss_grad_strided(self.h, _ptr(logits), _ptr(ascale), _ptr(labels), batch, classes, stride, _ptr(grad),
+                                                 self._stream(stream)))
 
     def loss_grad(self, logits, ascale, labels, batch, classes, grad, stream=None):
         self._ck(self.lib.niti_loss_grad(self.h, _ptr(logits), _ptr(ascale), _ptr(labels), batch, classes, _ptr(grad), self._stream(stream)))

@@ -97,22 +97,24 @@ def fuse_spec(spec):
 
 class NitiNet:
     """Device-resident int8 training step.  `fuse=False` keeps one kernel per reference op (the literal
-    op sequence); `fuse=True` (default) folds ReLU / ReLU-grad into neighbouring stores.  Both are
-    bit-identical (tests/test_gpu_step.py)."""
+    op sequence); `fuse=True` (default) folds ReLU / ReLU-grad / max-pool / max-pool-grad into neighbouring stores and runs
+    consecutive forward convolutions as one persistent chain launch.  Both are bit-identical (tests/test_gpu_step.py)."""
 
-    def __init__(self, nb: NitiB200, spec, batch, in_chw, device=0, dist=None, fuse=True, pad_c=16):
+    def __init__(self, nb: NitiB200, spec, batch, in_chw, device=0, dist=None, fuse=True, pad_c=16, chain=True):
         self.nb, self.batch = nb, batch
         self.dev = device if isinstance(device, torch.device) else torch.device("cuda", device)
         self.dist = dist if (dist is not None and dist.is_initialized() and dist.get_world_size() > 1) else None
         self.timer = None                      # optional callable(kind, ops, fn) used by bench.py
         c, h, w = in_chw
         self.in_c = c
-        # Zero-pad the input channels of the first conv to a multiple of 16 so it runs on tcgen05.
-        # Exact: padded activations are 0, padded weights start at 0 and their dW is 0, so they stay 0,
-        # and neither max|acc| nor any real element changes.
-        first_conv_c = c
+        # Zero-pad channel counts to the tensor cores' granule (16): the input channels of the first conv (1 / 3 -> 16) and,
+        # where the backend can address padded logit rows, every conv's output channels (12 classes -> 16).
+        # Exact: padded activations are 0, padded weights start at 0 and their dW is 0 (a zero activation column on one
+        # side, a zero dY column on the other), so they stay 0, and neither max|acc| nor any real element changes.
+        c_real = c
         if pad_c and c % pad_c != 0:
             c = (c + pad_c - 1) // pad_c * pad_c
+        pad_oc = pad_c if (fuse and pad_c and hasattr(nb, "loss_grad_strided")) else 0
         i8 = dict(dtype=torch.int8, device=self.dev)
         i32 = dict(dtype=torch.int32, device=self.dev)
         self.x_in = torch.zeros((batch, h, w, c), **i8)
@@ -123,27 +125,30 @@ class NitiNet:
         dw_total = 0
         for item in (fuse_spec(spec) if fuse else [it + ((False,) if it[0] == "conv" else ()) for it in spec]):
             kind = item[0]
-            L = _Op(); L.kind = kind; L.relu = False
+            L = _Op(); L.kind = kind; L.relu = False; L.alias = False
+            L.fwd_fused = L.bwd_fused = False              # pool ops: done inside the neighbouring conv launches
+            L.pool_op = None                                # conv ops: the pool folded into the forward store
             if kind == "conv":
                 _, oc, k, st, pad, relu = item
-                L.d = make_desc(batch, c, h, w, oc, k, stride=st, pad=pad)
-                L.c_real = first_conv_c if not self.convs else c
+                oc_p = (oc + pad_oc - 1) // pad_oc * pad_oc if pad_oc else oc
+                L.d = make_desc(batch, c, h, w, oc_p, k, stride=st, pad=pad)
+                L.c_real, L.oc_real = c_real, oc
                 L.relu = relu
                 L.x, L.ex = cur, cur_e
-                L.w = torch.zeros((oc, k, k, c), **i8)
+                L.w = torch.zeros((oc_p, k, k, c), **i8)
                 # transposed copy [c][kh][kw][oc]: the K-major B operand of the tensor-core dX kernels, kept in sync
                 # by the batched update (no per-step transposes); the first conv has no dX
-                L.wt = torch.zeros((c, k, k, oc), **i8) if (fuse and self.convs) else None
+                L.wt = torch.zeros((c, k, k, oc_p), **i8) if (fuse and self.convs) else None
                 L.ew = torch.zeros(1, **i8)
-                L.y = torch.zeros((batch, L.d.oh, L.d.ow, oc), **i8)
+                L.y = torch.zeros((batch, L.d.oh, L.d.ow, oc_p), **i8)
                 L.ey = torch.zeros(1, **i8)
                 L.n_y, L.n_x, L.n_w = L.y.numel(), cur.numel(), L.w.numel()
-                L.ops = 2.0 * L.n_y * L.c_real * k * k
+                L.ops = 2.0 * batch * L.d.oh * L.d.ow * oc * L.c_real * k * k          # algorithmic: unpadded
                 L.dw_off = dw_total
                 dw_total += (L.n_w + 63) // 64 * 64
                 L.index = len(self.convs)
                 self.convs.append(L)
-                cur, cur_e, c, h, w = L.y, L.ey, oc, L.d.oh, L.d.ow
+                cur, cur_e, c, c_real, h, w = L.y, L.ey, oc_p, oc, L.d.oh, L.d.ow
             elif kind == "relu":
                 L.x = cur; L.y = torch.zeros_like(cur); cur = L.y
             elif kind == "pool":
@@ -153,14 +158,18 @@ class NitiNet:
                 L.x = cur; L.y = torch.zeros((batch, oh, ow, c), **i8)
                 cur, h, w = L.y, oh, ow
             elif kind == "flatten":
-                # the reference flattens in NCHW order (_Convert(NCHW) + _Reshape, mnistTrain.cpp:170-171)
+                # the reference flattens in NCHW order (_Convert(NCHW) + _Reshape, mnistTrain.cpp:170-171); with h*w == 1
+                # that is the same bytes as NHWC, so the op is an alias (no copy, and the gradient is written in place)
                 L.geom = (batch, c, h, w)
-                L.x = cur; L.y = torch.zeros((batch, 1, 1, c * h * w), **i8)
-                cur, c, h, w = L.y, c * h * w, 1, 1
+                L.x = cur
+                L.alias = bool(fuse) and h * w == 1
+                L.y = cur.view(batch, 1, 1, c) if L.alias else torch.zeros((batch, 1, 1, c * h * w), **i8)
+                cur, c, c_real, h, w = L.y, c * h * w, c_real * h * w, 1, 1
             self.ops.append(L)
-        self.logits, self.e_logits, self.classes = cur, cur_e, c
-        for L in self.ops:                                   # one gradient tensor per op output
-            L.dy = torch.zeros_like(L.y)
+        self.logits_buf, self.e_logits, self.classes = cur, cur_e, c_real
+        self.logits = cur[..., :c_real]                      # real classes (the buffer's rows may be padded to 16)
+        for i, L in enumerate(self.ops):                     # one gradient tensor per op output
+            L.dy = self.ops[i - 1].dy.view_as(L.y) if L.alias else torch.zeros_like(L.y)
         self.acc = torch.zeros(max(max(L.n_y, L.n_x) for L in self.convs), **i32)   # fwd / dX accumulators
         self.dw_acc = torch.zeros(dw_total, **i32)                                   # one bucket: all dW accumulators
         self.maxabs = torch.zeros(4 * len(self.convs) + 4, **i32)                    # one slot per reduction
@@ -194,11 +203,68 @@ class NitiNet:
         # point (niti_conv_dw_accumulate) and the gradient bucket cleared once per step (done beside forward).
         self.overlap_dw = bool(fuse) and hasattr(nb, "conv_dw_accumulate") and self.dev.type == "cuda"
         self.side = torch.cuda.Stream(self.dev) if self.overlap_dw else None
+        self._plan_fusions(chain)
+
+    def _plan_fusions(self, chain):
+        """Decide which pools fold into the conv before them (forward store) and into the dX of the conv after them
+        (max-pool gradient + ReLU gate), and group consecutive fused-eligible forward convs into chain launches."""
+        nb, nconv = self.nb, len(self.convs)
+        self._fwd_plan = [("op", i) for i in range(len(self.ops))]
+        for i, L in enumerate(self.ops):
+            # the op that really produced this op's input (alias flattens are views): its folded ReLU gates our dX
+            j = i - 1
+            while j >= 0 and self.ops[j].alias:
+                j -= 1
+            L.src = self.ops[j] if j >= 0 else None
+            L.pg = None
+        if not (self.fused_ops and hasattr(nb, "conv_fwd_fused_pool")):
+            return
+
+        def pool_2x2(P):
+            n, h, w, c = P.geom
+            return P.kind == "pool" and P.k == 2 and P.s == 2 and h % 2 == 0 and w % 2 == 0 and c % 16 == 0
+        for i, L in enumerate(self.ops):
+            nxt = self.ops[i + 1] if i + 1 < len(self.ops) else None
+            if L.kind == "conv" and L.relu and nxt is not None and pool_2x2(nxt):
+                L.pool_op = nxt; nxt.fwd_fused = True
+            if L.kind == "conv" and L.index > 0:
+                # a 2x2/2 pool in front of this conv folds its gradient into this conv's dX launch
+                P = L.src
+                if P is not None and pool_2x2(P) and P.src is not None and L.wt is not None:
+                    src = P.src                                # the op whose output was pooled
+                    L.pg = (P, src.dy, bool(src.relu))         # pool op, gradient target, ReLU gate of the pooled tensor
+                    P.bwd_fused = True
+        # forward chains
+        if not (chain and hasattr(nb, "chain_create")):
+            return
+        plan, run = [], []
+
+        def flush():
+            if len(run) >= 2:
+                plan.append(("chain", nb.chain_create([self._chain_op(self.ops[i]) for i in run]), list(run)))
+            else:
+                plan.extend(("op", i) for i in run)
+            run.clear()
+        for i, L in enumerate(self.ops):
+            if L.kind == "conv" and nb.chain_op_eligible(self._chain_op(L)):
+                run.append(i)
+            elif (L.kind == "pool" and L.fwd_fused) or L.alias:
+                if not run:
+                    plan.append(("op", i))                    # nothing to launch, kept for symmetry
+            else:
+                flush(); plan.append(("op", i))
+        flush()
+        self._fwd_plan = plan
+
+    def _chain_op(self, L):
+        P = L.pool_op
+        return self.nb.chain_op(L.d, 0, L.x, L.w, L.y, self.maxabs[L.index: L.index + 1], L.index, ex=L.ex, ew=L.ew, ey=L.ey,
+                                relu=L.relu, out_pool=P.y if P is not None else None)
 
     # ---- parameters -------------------------------------------------------------------------------
     def init_weights(self, seed=1):
         rng = np.random.default_rng(seed)
-        ws = [niti_xavier_int8(rng, L.d.oc, L.c_real, L.d.kh, L.d.kw) for L in self.convs]
+        ws = [niti_xavier_int8(rng, L.oc_real, L.c_real, L.d.kh, L.d.kw) for L in self.convs]
         self.load_weights(ws)
         return ws
 
@@ -206,13 +272,13 @@ class NitiNet:
         """ws: list of (OIHW int8 numpy, wscale)"""
         for L, (w, e) in zip(self.convs, ws):
             L.w.zero_()
-            L.w[..., :L.c_real].copy_(torch.from_numpy(np.ascontiguousarray(np.transpose(w, (0, 2, 3, 1)))))
+            L.w[:L.oc_real, ..., :L.c_real].copy_(torch.from_numpy(np.ascontiguousarray(np.transpose(w, (0, 2, 3, 1)))))
             if L.wt is not None:
                 L.wt.copy_(L.w.permute(3, 1, 2, 0))
             L.ew.fill_(int(e))
 
     def weights_oihw(self):
-        return [np.ascontiguousarray(np.transpose(L.w[..., :L.c_real].cpu().numpy(), (0, 3, 1, 2))) for L in self.convs]
+        return [np.ascontiguousarray(np.transpose(L.w[:L.oc_real, ..., :L.c_real].cpu().numpy(), (0, 3, 1, 2))) for L in self.convs]
 
     def set_input(self, x_nhwc, ascale, labels, non_blocking=True):
         """host (pinned) or device tensors -> the step's input buffers (the e2e H2D leg)"""
@@ -267,23 +333,37 @@ class NitiNet:
         if self.overlap_dw:
             with self._beside():
                 self.dw_acc.zero_()
-        for L in self.ops:
+        for unit in self._fwd_plan:
+            if unit[0] == "chain":
+                # consecutive fused forward convs (+ ReLU + pool) in ONE persistent launch (csrc/conv_chain.cu)
+                layers = [self.ops[i] for i in unit[2]]
+                self._timed("fwd", sum(L.ops for L in layers), lambda: nb.chain_run(unit[1]))
+                continue
+            L = self.ops[unit[1]]
             if L.kind == "conv":
                 slot = self.maxabs[L.index: L.index + 1]
                 if self.fused_ops:
-                    # whole op (conv + exponent + rescale + ReLU) behind one call: one launch for stem layers
-                    # (conv_stem.cu) and whenever the output tiles fit in tensor memory (conv_tma2.cu, fused kernel)
-                    self._timed("fwd", L.ops, lambda: nb.conv_fwd_fused(L.d, L.x, L.w, L.ex, L.ew, L.y, L.ey, L.relu,
-                                                                       self.acc, slot, dp_slot=L.index))
+                    # whole op (conv + exponent + rescale + ReLU [+ max pool]) behind one call: one launch for stem layers
+                    # (conv_stem.cu) and whenever the output tiles fit in tensor memory (conv_chain.cu)
+                    if L.pool_op is not None:
+                        self._timed("fwd", L.ops, lambda: nb.conv_fwd_fused_pool(L.d, L.x, L.w, L.ex, L.ew, L.y, L.ey, L.relu,
+                                                                                L.pool_op.y, self.acc, slot, dp_slot=L.index))
+                    else:
+                        self._timed("fwd", L.ops, lambda: nb.conv_fwd_fused(L.d, L.x, L.w, L.ex, L.ew, L.y, L.ey, L.relu,
+                                                                           self.acc, slot, dp_slot=L.index))
                     continue
                 self._timed("fwd", L.ops, lambda: nb.conv_fwd_acc(L.d, L.x, L.w, self.acc, slot))
                 self._rescale(L.n_y, L.index, L.y, L.ex, L.ew, L.ey, relu=L.relu)
             elif L.kind == "relu":
                 nb.relu(L.x, L.y, L.x.numel())
             elif L.kind == "pool":
+                if L.fwd_fused:
+                    continue
                 n, h, w, c = L.geom
                 nb.maxpool(L.x, n, h, w, c, L.k, L.s, L.y)
             elif L.kind == "flatten":
+                if L.alias:
+                    continue
                 n, c, h, w = L.geom
                 if h * w == 1:
                     L.y.copy_(L.x.view_as(L.y))
@@ -294,7 +374,11 @@ class NitiNet:
         nb = self.nb
         nconv = len(self.convs)
         last = self.ops[-1]
-        nb.loss_grad(self.logits, self.e_logits, self.labels, self.batch, self.classes, last.dy)
+        stride = self.logits_buf.shape[-1]
+        if stride != self.classes:
+            nb.loss_grad_strided(self.logits_buf, self.e_logits, self.labels, self.batch, self.classes, stride, last.dy)
+        else:
+            nb.loss_grad(self.logits_buf, self.e_logits, self.labels, self.batch, self.classes, last.dy)
         if last.relu:
             nb.relu_grad(last.y, last.dy, last.dy, last.y.numel())
         for idx in range(len(self.ops) - 1, -1, -1):
@@ -302,7 +386,7 @@ class NitiNet:
             dy = L.dy
             prev = self.ops[idx - 1] if idx > 0 else None
             dx = prev.dy if prev is not None else None       # gradient w.r.t. this op's input
-            gate = prev is not None and prev.relu            # input came through a folded ReLU
+            gate = L.src is not None and L.src.relu          # input came through a folded ReLU
             if L.kind == "conv":
                 acc_dw = self.dw_acc[L.dw_off: L.dw_off + L.n_w]
                 with self._beside():
@@ -316,8 +400,14 @@ class NitiNet:
                 if dx is not None:
                     slot = self.maxabs[nconv + L.index: nconv + L.index + 1]
                     if self.fused_ops:
-                        self._timed("dx", L.ops, lambda: nb.conv_dx_fused(L.d, dy, L.w, L.wt, dx, L.x if gate else None,
-                                                                          self.acc, slot, dp_slot=nconv + L.index))
+                        pg = getattr(L, "pg", None)
+                        if pg is not None:
+                            # dX + the max-pool gradient (+ ReLU gate) of the pool in front of this conv, one launch
+                            self._timed("dx", L.ops, lambda: nb.conv_dx_fused_poolgrad(L.d, dy, L.w, L.wt, pg[1], pg[0].x, pg[2], pg[0].dy,
+                                                                                       self.acc, slot, dp_slot=nconv + L.index))
+                        else:
+                            self._timed("dx", L.ops, lambda: nb.conv_dx_fused(L.d, dy, L.w, L.wt, dx, L.x if gate else None,
+                                                                              self.acc, slot, dp_slot=nconv + L.index))
                         continue
                     if L.wt is not None:
                         self._timed("dx", L.ops, lambda: nb.conv_dx_acc_wt(L.d, dy, L.w, L.wt, self.acc, slot))
@@ -329,9 +419,13 @@ class NitiNet:
                 if gate:
                     nb.relu_grad(L.x, dx, dx, L.x.numel())
             elif L.kind == "pool":
+                if L.bwd_fused and self.fused_ops:
+                    continue                                   # done by the dX launch of the conv behind this pool
                 n, h, w, c = L.geom
                 nb.maxpool_grad_gated(L.x, L.y, dy, n, h, w, c, L.k, L.s, dx, gate)
             elif L.kind == "flatten":
+                if L.alias:
+                    continue                                   # L.dy is a view of the producer's gradient tensor
                 n, c, h, w = L.geom
                 if h * w == 1:
                     dx.copy_(dy.view_as(dx))

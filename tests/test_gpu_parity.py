@@ -543,3 +543,107 @@ def test_full_size_product_kernels_vs_pinned_simt_and_oracle_rescale(nb, oracle,
     want_dx = np.where(gate.cpu().numpy() > 0, want_dx, 0).astype(np.int8)
     assert np.array_equal(dx.cpu().numpy(), want_dx)
     assert torch.equal(dw2, dwa)
+
+
+# ------------------------------------------------------------------ pool / pool-gradient folded into the fused ops, chains
+POOL_SHAPES = [(8, 64, 16, 128), (16, 64, 8, 64), (4, 128, 4, 256), (32, 64, 2, 64), (2, 64, 12, 64)]   # (n, c, hw, oc); 12: unfused route
+
+
+@pytest.mark.parametrize("cfg", POOL_SHAPES)
+def test_conv_fwd_fused_pool_vs_oracle(nb, oracle, cfg):
+    """NITI_Conv_Int8 + NITI_CPURelu_Int8 + NITI_Maxpool_Int8 (2x2/2) behind one call: y and y_pool against the oracle's
+    op-by-op sequence"""
+    import torch
+    from tests.gpu_util import to_desc, dev, nhwc, nchw
+    n, c, hw, oc = cfg
+    s = shape(n, c, hw, hw, oc, 3, stride=1, pad=1)
+    rng = np.random.default_rng(hw * oc)
+    x = _rand(rng, (n, c, hw, hw)); w = _rand(rng, (oc, c, 3, 3), -40, 40)
+    want_y, want_e, _ = oracle.conv_fwd(s, x, w, -7, -6)
+    want_y = oracle.relu(want_y); want_p = oracle.maxpool(want_y, 2, 2)
+    i8 = dict(dtype=torch.int8, device="cuda:0")
+    y = torch.empty((n, hw, hw, oc), **i8); yp = torch.empty((n, hw // 2, hw // 2, oc), **i8)
+    ey = torch.zeros(1, **i8); mx = torch.zeros(1, dtype=torch.int32, device="cuda:0")
+    acc = torch.empty(y.numel(), dtype=torch.int32, device="cuda:0")
+    nb.conv_fwd_fused_pool(to_desc(s), dev(nhwc(x)), dev(nhwc(w)), torch.full((1,), -7, **i8), torch.full((1,), -6, **i8), y, ey, True, yp, acc, mx)
+    torch.cuda.synchronize()
+    assert np.array_equal(nchw(y.cpu().numpy()), want_y)
+    assert np.array_equal(nchw(yp.cpu().numpy()), want_p)
+    assert int(ey.item()) == want_e
+
+
+@pytest.mark.parametrize("cfg", POOL_SHAPES)
+@pytest.mark.parametrize("gate", [True, False])
+def test_conv_dx_fused_poolgrad_vs_oracle(nb, oracle, cfg, gate):
+    """NITI_DeConv_Int8 + NITI_CPUPoolGrad_Int8 (+ NITI_CPUReluGrad_Int8) behind one call.  The pre-pool tensor has many
+    ties (values in [-3, 3]) so the 'first maximum in row-major order takes the gradient' rule is exercised."""
+    import torch
+    from tests.gpu_util import to_desc, dev, nhwc, nchw
+    n, c, hw, oc = cfg                                  # the conv's input is the POOLED tensor [n, c, hw, hw]
+    s = shape(n, c, hw, hw, oc, 3, stride=1, pad=1)
+    rng = np.random.default_rng(hw * oc + 1)
+    dy = _rand(rng, (n, oc, hw, hw), -50, 50); w = _rand(rng, (oc, c, 3, 3), -40, 40)
+    xpre = _rand(rng, (n, c, 2 * hw, 2 * hw), -3, 3)
+    dxp, _ = oracle.conv_dx(s, dy, w)
+    want = oracle.maxpool_grad(xpre, oracle.maxpool(xpre, 2, 2), dxp, 2, 2)
+    if gate:
+        want = oracle.relu_grad(xpre, want)
+    i8 = dict(dtype=torch.int8, device="cuda:0")
+    wd = dev(nhwc(w)); wt = wd.permute(3, 1, 2, 0).contiguous()
+    out = torch.full((n, 2 * hw, 2 * hw, c), 77, **i8)
+    scratch = torch.empty((n, hw, hw, c), **i8)
+    mx = torch.zeros(1, dtype=torch.int32, device="cuda:0")
+    acc = torch.empty(scratch.numel(), dtype=torch.int32, device="cuda:0")
+    nb.conv_dx_fused_poolgrad(to_desc(s), dev(nhwc(dy)), wd, wt, out, dev(nhwc(xpre)), gate, scratch, acc, mx)
+    torch.cuda.synchronize()
+    assert np.array_equal(nchw(out.cpu().numpy()), want)
+
+
+def test_chain_of_forward_ops_equals_the_ops_one_by_one(nb, oracle):
+    """niti_chain_run: three forward convs (+ ReLU, + pools) in one persistent launch against the oracle's op sequence;
+    layers differ in tile shape (BN 128 / 64), K-block (64 / 128 channels) and pipeline depth, one pair idles in layer 3."""
+    import torch
+    from tests.gpu_util import to_desc, dev, nhwc, nchw
+    n = 8
+    rng = np.random.default_rng(42)
+    x = _rand(rng, (n, 64, 16, 16))
+    ws = [_rand(rng, (128, 64, 3, 3), -40, 40), _rand(rng, (128, 128, 3, 3), -30, 30), _rand(rng, (64, 128, 1, 1), -50, 50)]
+    shapes = [shape(n, 64, 16, 16, 128, 3, pad=1), shape(n, 128, 8, 8, 128, 3, pad=1), shape(n, 128, 8, 8, 64, 1, pad=0)]
+    pools = [True, False, True]
+    # oracle
+    cur, e = x, -7
+    want = []
+    for s, w, p in zip(shapes, ws, pools):
+        y, e, _ = oracle.conv_fwd(s, cur, w, e, -8)
+        y = oracle.relu(y)
+        yp = oracle.maxpool(y, 2, 2) if p else None
+        want.append((y, yp, e))
+        cur = yp if p else y
+    # device
+    i8 = dict(dtype=torch.int8, device="cuda:0")
+    xin = dev(nhwc(x)); ex = torch.full((1,), -7, **i8); ew = torch.full((1,), -8, **i8)
+    mx = torch.zeros(4, dtype=torch.int32, device="cuda:0")
+    ops, outs, keep = [], [], []
+    cur_t, cur_e = xin, ex
+    for i, (s, w, p) in enumerate(zip(shapes, ws, pools)):
+        d = to_desc(s)
+        wd = dev(nhwc(w)); keep.append(wd)
+        y = torch.empty((n, d.oh, d.ow, s.oc), **i8)
+        yp = torch.empty((n, d.oh // 2, d.ow // 2, s.oc), **i8) if p else None
+        ey = torch.zeros(1, **i8)
+        op = nb.chain_op(d, 0, cur_t, wd, y, mx[i:i + 1], i, ex=cur_e, ew=ew, ey=ey, relu=True, out_pool=yp)
+        assert nb.chain_op_eligible(op)
+        ops.append(op); outs.append((y, yp, ey))
+        cur_t, cur_e = (yp if p else y), ey
+    ch = nb.chain_create(ops)
+    for rep in range(2):                                 # run twice: barrier re-arm + phase bits across launches
+        mx.zero_()
+        nb.chain_run(ch)
+    torch.cuda.synchronize()
+    nb.chain_destroy(ch)
+    for (y, yp, ey), (wy, wyp, we) in zip(outs, want):
+        assert np.array_equal(nchw(y.cpu().numpy()), wy)
+        if wyp is not None:
+            assert np.array_equal(nchw(yp.cpu().numpy()), wyp)
+        assert int(ey.item()) == we
+    assert nb.sync_error() == 0

@@ -30,8 +30,16 @@ RGB_NET = [("conv", 32, 3, 1, 1), ("relu",), ("conv", 32, 3, 1, 1), ("relu",), (
            ("conv", 64, 1, 1, 0), ("relu",), ("conv", 12, 1, 1, 0)]
 
 
+# VGG-shaped: stem + a forward chain of 6 fused convs with pools folded in (16 -> 8 -> 4 -> 2 -> 1) + alias flatten + padded classes
+VGG_NET = [("conv", 64, 3, 1, 1), ("relu",), ("pool", 2, 2), ("conv", 128, 3, 1, 1), ("relu",), ("pool", 2, 2),
+           ("conv", 128, 3, 1, 1), ("relu",), ("conv", 256, 3, 1, 1), ("relu",), ("pool", 2, 2),
+           ("conv", 256, 3, 1, 1), ("relu",), ("pool", 2, 2), ("flatten",),
+           ("conv", 256, 1, 1, 0), ("relu",), ("conv", 12, 1, 1, 0)]
+
+
 @pytest.mark.parametrize("fuse", [True, False])
-@pytest.mark.parametrize("spec,chw,batch", [(lenet_spec(), (1, 28, 28), 8), (TC_NET, (16, 8, 8), 8), (RGB_NET, (3, 8, 8), 8)])
+@pytest.mark.parametrize("spec,chw,batch", [(lenet_spec(), (1, 28, 28), 8), (TC_NET, (16, 8, 8), 8), (RGB_NET, (3, 8, 8), 8),
+                                            (VGG_NET, (3, 16, 16), 8)])
 def test_training_steps_bit_exact_vs_oracle(nb, oracle, spec, chw, batch, fuse):
     net = NitiNet(nb, spec, batch, chw, fuse=fuse)
     ws = [(w.copy(), e) for w, e in net.init_weights(seed=1)]
@@ -49,8 +57,19 @@ def test_training_steps_bit_exact_vs_oracle(nb, oracle, spec, chw, batch, fuse):
             assert np.array_equal(a, b), (it, i)
 
 
-def test_cuda_graph_replay_equals_eager(nb):
-    spec, chw, batch = TC_NET, (16, 8, 8), 16
+def test_vgg_shaped_net_uses_a_forward_chain_and_folded_pools(nb):
+    net = NitiNet(nb, VGG_NET, 8, (3, 16, 16))
+    kinds = [u[0] for u in net._fwd_plan]
+    assert "chain" in kinds, kinds
+    chain = [u for u in net._fwd_plan if u[0] == "chain"][0]
+    assert len(chain[2]) >= 5
+    assert sum(1 for L in net.ops if L.kind == "pool" and L.fwd_fused) >= 3
+    assert sum(1 for L in net.ops if L.kind == "pool" and L.bwd_fused) >= 3
+    assert net.logits_buf.shape[-1] == 16 and net.logits.shape[-1] == 12
+
+
+@pytest.mark.parametrize("spec,chw,batch", [(TC_NET, (16, 8, 8), 16), (VGG_NET, (3, 16, 16), 8)])
+def test_cuda_graph_replay_equals_eager(nb, spec, chw, batch):
     x, labels = _data(batch, chw, 0)
     xin = torch.from_numpy(np.ascontiguousarray(np.transpose(x, (0, 2, 3, 1))))
     a = NitiNet(nb, spec, batch, chw); a.init_weights(seed=3)

@@ -28,7 +28,7 @@ def main():
     for _ in range(3):
         net.step()
     torch.cuda.synchronize()
-    trace = torch.zeros(160 * 8, dtype=torch.int64, device="cuda")
+    trace = torch.zeros(24 * 160 * 8, dtype=torch.int64, device="cuda")    # [layer][block][8], chains walk up to 24 layers
     nb.debug_trace(trace)
     rows = []
     convs = iter([])
@@ -39,29 +39,49 @@ def main():
         torch.cuda.synchronize()
         a.record(); fn(); b.record()
         torch.cuda.synchronize()
-        t = trace.cpu().numpy().reshape(-1, 8)
-        t = t[t[:, 0] > 0]
-        rows.append((kind, nb.last_path, ops, a.elapsed_time(b) * 1e3, t.copy()))
+        rows.append((kind, nb.last_path, ops, a.elapsed_time(b) * 1e3, trace.cpu().numpy().copy()))
     net.timer = timer
     net.step()
     torch.cuda.synchronize()
     nb.debug_trace(None)
-    names = ["set-up", "first tile (K loop)", "max pass", "grid barrier", "rescale+store", "exit"]
+    # stamps (csrc/conv_chain.cu): per launch [0][block][0] entry, [0][block][1] set-up done, [last][block][7] exit; per layer
+    # 2 first tile accumulated, 3 max pass done, 4 exponent barrier (+ peer exchange) passed, 5 rescale + store done,
+    # 6 layer barrier passed (not after the last layer)
+    names = ["K loop (first tile)", "max pass", "exponent barrier", "rescale+store", "layer barrier"]
     print(f"# phase trace, {wl} batch {batch}, one eager step (every launch synchronised: cold pipeline, no PDL overlap)")
-    print(f"# columns: kind path GOP | event us | CTAs | first-entry..last-exit us | median us per phase: " + " | ".join(names))
+    print("# per launch: kind path GOP | event us | in-kernel span us (first entry .. last exit) | set-up us")
+    print("#   per layer: CTAs | median us per phase: " + " | ".join(names))
     tot = {}
-    for kind, path, ops, ev_us, t in rows:
-        if len(t) == 0:
+    for kind, path, ops, ev_us, raw in rows:
+        grids = [g for g in (148, 146, 144, 132, 130, 128) if False]
+        t_all = raw.reshape(-1)
+        if not (t_all > 0).any():
             print(f"{kind:4s} {path:6s} {ops / 1e9:7.2f} | {ev_us:7.1f} | (no trace: kernel family without phase stamps)")
             continue
-        span = (t[:, 6].max() - t[:, 0].min()) / 1e3
-        d = np.diff(t[:, :7], axis=1) / 1e3
-        med = np.median(d, axis=0)
-        print(f"{kind:4s} {path:6s} {ops / 1e9:7.2f} | {ev_us:7.1f} | {len(t):3d} | {span:7.1f} | " + " | ".join(f"{v:6.1f}" for v in med))
-        for n_, v in zip(names, med):
-            tot[n_] = tot.get(n_, 0.0) + float(v)
-        tot["launch overhead (event - span)"] = tot.get("launch overhead (event - span)", 0.0) + max(0.0, ev_us - span)
-    print("# sum over traced launches, us:", {k: round(v, 1) for k, v in tot.items()})
+        # the grid size is whatever makes entry stamps [0][b][0] contiguous: count blocks with an entry stamp
+        entry = raw.reshape(-1, 8)[:, 0]
+        grid = int((entry[:160] > 0).sum())
+        t = raw[: (raw.size // (grid * 8)) * grid * 8].reshape(-1, grid, 8)
+        nl = int((t[:, :, 3] > 0).any(axis=1).sum())
+        t0, t1 = t[0, :, 0].min(), t[nl - 1, :, 7].max()
+        setup = float(np.median(t[0, :, 1] - t[0, :, 0])) / 1e3
+        print(f"{kind:4s} {path:6s} {ops / 1e9:7.2f} | {ev_us:7.1f} | {(t1 - t0) / 1e3:7.1f} | {setup:5.1f}")
+        tot["launch overhead (event - span)"] = tot.get("launch overhead (event - span)", 0.0) + max(0.0, ev_us - (t1 - t0) / 1e3)
+        tot["set-up"] = tot.get("set-up", 0.0) + setup
+        prev_end = t[0, :, 1].astype(np.float64)
+        for l in range(nl):
+            act = t[l, :, 2] > 0
+            k = np.where(act, t[l, :, 2] - prev_end, np.nan)
+            ph = [np.nanmedian(k) / 1e3 if act.any() else 0.0,
+                  float(np.median((t[l, :, 3] - np.where(act, t[l, :, 2], prev_end)))) / 1e3,
+                  float(np.median(t[l, :, 4] - t[l, :, 3])) / 1e3,
+                  float(np.median(t[l, :, 5] - t[l, :, 4])) / 1e3,
+                  float(np.median(t[l, :, 6] - t[l, :, 5])) / 1e3 if l + 1 < nl else 0.0]
+            print(f"     layer {l:2d}: {int(act.sum()):3d} | " + " | ".join(f"{v:6.1f}" for v in ph))
+            for n_, v in zip(names, ph):
+                tot[n_] = tot.get(n_, 0.0) + float(v)
+            prev_end = (t[l, :, 6] if l + 1 < nl else t[l, :, 5]).astype(np.float64)
+    print("# sum over traced launches, us:", {k: round(float(v), 1) for k, v in tot.items()})
 
 
 if __name__ == "__main__":
