@@ -294,6 +294,12 @@ int niti_conv_fwd_host(niti_ctx*, const niti_conv_desc*, const int8_t* x_nhwc, c
  * device_buf[block * 8 + phase] (phases: 0 entry, 1 set-up done, 2 first tile accumulated, 3 max pass done, 4 grid barrier
  * passed, 5 rescale + store done, 6 exit); device_buf must hold 8 words per CTA of the largest grid.  NULL disables. */
 int niti_debug_trace(niti_ctx*, unsigned long long* device_buf);
+/* launch timeline for kernel development: while device_buf != NULL every instrumented launch issued through this context
+ * takes the next record {first CTA entry, last CTA exit} (%globaltimer ns; the caller presets records to {~0, 0}) — records are
+ * assigned at launch time, so a captured CUDA graph keeps writing the same records on every replay.  capacity in records. */
+int niti_debug_timeline(niti_ctx*, unsigned long long* device_buf, int capacity);
+int niti_debug_timeline_count(niti_ctx*);
+const char* niti_debug_timeline_name(niti_ctx*, int i);
 /* dense tcgen05 kind::i8 issue-rate probe (no global traffic): returns achieved TOPS */
 int niti_probe_i8_peak(niti_ctx*, int iters, double* tops_out);
 

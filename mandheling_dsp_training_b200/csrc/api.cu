@@ -479,6 +479,14 @@ int niti_debug_trace(niti_ctx* ctx, unsigned long long* device_buf) {
     return NITI_OK;
 }
 
+int niti_debug_timeline(niti_ctx* ctx, unsigned long long* device_buf, int capacity) {
+    if (!ctx) return NITI_ERR_ARG;
+    ctx->tl = device_buf; ctx->tl_cap = device_buf ? capacity : 0; ctx->tl_n = 0;
+    return NITI_OK;
+}
+int niti_debug_timeline_count(niti_ctx* ctx) { return ctx ? ctx->tl_n : 0; }
+const char* niti_debug_timeline_name(niti_ctx* ctx, int i) { return (ctx && i >= 0 && i < ctx->tl_n) ? ctx->tl_name[i] : ""; }
+
 int niti_probe_i8_peak(niti_ctx* ctx, int iters, double* tops_out) {
     if (!ctx || !tops_out || iters <= 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_probe_i8_peak");
     return tc_probe_i8_peak(ctx, iters, tops_out);

@@ -53,6 +53,7 @@ struct ChainArgs {
     uint32_t* sync;                   // {arrival counter, exit counter}
     DpView dp;
     unsigned long long* trace;        // [layer][block][8] globaltimer stamps, or nullptr
+    unsigned long long* tl;           // launch timeline record, or nullptr
     int trigger_late;
 };
 
@@ -87,6 +88,9 @@ __device__ __forceinline__ uint4 vgt0(uint4 a) {
     return make_uint4(__vcmpgts4(a.x, 0u), __vcmpgts4(a.y, 0u), __vcmpgts4(a.z, 0u), __vcmpgts4(a.w, 0u));
 }
 
+// kTable: walk a.table[0..nlayers) in global memory; otherwise the one layer passed by value (its tensor maps are then read
+// straight from the kernel-parameter bank instead of through a generic pointer that may point either way)
+template <bool kTable>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kChainThreads, 1)
 chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
     extern __shared__ uint8_t smem_raw_chain[];
@@ -97,18 +101,27 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
     uint64_t* layer_bar = tfull_bar + kChainMaxTiles;                                    // per CTA: the next layer's operand is in memory
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(layer_bar + 1);
     uint32_t* bcast = tmem_slot + 1;
+    uint32_t* cta_max = tmem_slot + 2;                                                   // this CTA's max|acc| of the current layer
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t rank = cluster_ctarank();
     const int pair = blockIdx.x >> 1;
+    if (tid == 0) *cta_max = 0u;
     if (!a.trigger_late) niti_pdl_trigger();                 // the next launch of the stream may start placing its CTAs
     if (tid == 64) chain_trace(a.trace, 0, 0);
+    niti_tl_enter(a.tl);
 
     if (tid == 0) {
         for (int s = 0; s < kChainMaxStages; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], 1); }
         for (int t = 0; t < kChainMaxTiles; ++t) tc::mbar_init(&tfull_bar[t], 1);
         tc::mbar_init(layer_bar, 1);
         tc::fence_barrier_init();
+    }
+    // tensor maps of every layer are fetched now, behind the set-up, not in front of each layer's first load (a cold
+    // descriptor fetch cost 1.5-2.3 us per layer on the critical path: profiles/phase_r2_vgg_chain_v1.txt)
+    if (tid >= 32 && tid < 32 + 2 * a.nlayers && tid < 64) {
+        const ChainLayer& Lp = kTable ? a.table[(tid - 32) >> 1] : single;
+        prefetch_tmap2(((tid - 32) & 1) ? &Lp.mapB : &Lp.mapA);
     }
     if (warp == 1) tmem_alloc2<512>(tmem_slot);
     tc::tc_fence_before();
@@ -117,73 +130,96 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
     const uint32_t tmem_base = *tmem_slot;
     niti_pdl_wait();                                         // prologue done; everything the previous launch wrote is visible
 
+    // Both issuing roles run their loops with the WHOLE warp (all values warp-uniform) and only the instruction that must
+    // come from one thread sits under elect.sync.  Written as `if (lane == 0) { loop }` the compiler cannot prove that the
+    // operands of UTMALDG / UTCIMMA are uniform and wraps every one of them in an ELECT / R2UR.BROADCAST / BRA.U.ANY loop:
+    // ~120 dependent single-thread instructions per K block, which — not TMA or the tensor pipe — set the 330 ns per K block
+    // measured in round 1 (profiles/phase_r2_vgg_before.txt: same time per block for 20 KB and 24 KB stages, 64 or 128 CTAs).
     if (warp == 0) {
-        if (lane == 0) {
-            // ------------------------------ TMA producer (both CTAs) ------------------------------
-            uint32_t pphase = 0;                             // per-stage phase bits of empty_bar
-            for (int l = 0; l < a.nlayers; ++l) {
-                const ChainLayer& L = a.table ? a.table[l] : single;
-                prefetch_tmap2(&L.mapA); prefetch_tmap2(&L.mapB);
-                if (l > 0) {
-                    tc::mbar_wait(layer_bar, (uint32_t)(l - 1) & 1u);       // previous layer stored everywhere (grid barrier passed)
-                    tmax::fence_proxy_async_all();                          // generic-proxy stores -> async-proxy (TMA) reads
-                }
-                if (pair >= L.pairs) continue;
-                const uint32_t a_bytes = 128u * (uint32_t)L.bkc, stage = a_bytes + (uint32_t)(L.bn / 2) * (uint32_t)L.bkc;
-                int s = 0;
-                for (int item = pair; item < L.items; item += L.pairs) {
-                    const int n_t = item % L.n_tiles; const int m_t = item / L.n_tiles;
-                    int m0 = m_t * 256 + (int)rank * 128;
-                    if (m0 >= L.M) m0 = 0;                   // fully out-of-range half: load valid rows, results are masked
-                    const int nrow0 = n_t * L.bn + (int)rank * (L.bn / 2);
-                    const int q = m0 % L.out_w; const int t = m0 / L.out_w;
-                    const int pp = t % L.out_h; const int bn_ = t / L.out_h;
-                    const int bw = q * L.stride + L.lower_w, bh = pp * L.stride + L.lower_h;
-                    for (int kb = 0; kb < L.num_kb; ++kb) {
-                        tc::mbar_wait(&empty_bar[s], ((pphase >> s) & 1u) ^ 1u);
-                        pphase ^= 1u << s;
-                        const uint32_t a_dst = tc::smem_u32(smem) + (uint32_t)s * stage;
+        // ------------------------------ TMA producer (both CTAs) ------------------------------
+        uint32_t pphase = 0;                             // per-stage phase bits of empty_bar
+        for (int l = 0; l < a.nlayers; ++l) {
+            const ChainLayer& L = kTable ? a.table[l] : single;
+            if (l > 0) {
+                tc::mbar_wait(layer_bar, (uint32_t)(l - 1) & 1u);       // previous layer stored everywhere (grid barrier passed)
+                tmax::fence_proxy_async_all();                          // generic-proxy stores -> async-proxy (TMA) reads
+            }
+            // the layer record is read ONCE into registers: every asm below clobbers memory, so fields left in the
+            // (global or param) record would be re-loaded on each use — measured +25 % on the K loop
+            const int Lpairs = L.pairs, Litems = L.items, Lntiles = L.n_tiles, LM = L.M, Lbn = L.bn, Lbkc = L.bkc;
+            const int Low = L.out_w, Loh = L.out_h, Lstride = L.stride, Llw = L.lower_w, Llh = L.lower_h, Lnumkb = L.num_kb;
+            const int Lcch = L.cchunks, Lkw = L.kw, Lkh = L.kh, Lflip = L.flip, Ldil = L.dil, Lstages = L.stages;
+            if (pair >= Lpairs) continue;
+            const uint32_t a_bytes = 128u * (uint32_t)Lbkc, stage = a_bytes + (uint32_t)(Lbn / 2) * (uint32_t)Lbkc;
+            // tap walk without divisions: forward runs (ky, kx) up from (0, 0), dX (flipped kernel) down from (kh-1, kw-1)
+            const int kx_first = Lflip ? (Lkw - 1) * Ldil : 0, kx_last = Lflip ? 0 : (Lkw - 1) * Ldil;
+            const int kstep = Lflip ? -Ldil : Ldil;
+            const int ky_first = Lflip ? (Lkh - 1) * Ldil : 0;
+            int s = 0;
+            for (int item = pair; item < Litems; item += Lpairs) {
+                const int n_t = item % Lntiles; const int m_t = item / Lntiles;
+                int m0 = m_t * 256 + (int)rank * 128;
+                if (m0 >= LM) m0 = 0;                    // fully out-of-range half: load valid rows, results are masked
+                const int nrow0 = n_t * Lbn + (int)rank * (Lbn / 2);
+                const int q = m0 % Low; const int t = m0 / Low;
+                const int pp = t % Loh; const int bn_ = t / Loh;
+                const int bw = q * Lstride + Llw, bh = pp * Lstride + Llh;
+                int cc = 0, kx = kx_first, ky = ky_first, kcol = 0;      // channel chunk, tap offsets, K coordinate of block kb
+                for (int kb = 0; kb < Lnumkb; ++kb) {
+                    tc::mbar_wait(&empty_bar[s], ((pphase >> s) & 1u) ^ 1u);
+                    pphase ^= 1u << s;
+                    const uint32_t a_dst = tc::smem_u32(smem) + (uint32_t)s * stage;
+                    if (elect_one()) {
                         if (rank == 0) mbar_expect_tx(&full_bar[s], 2u * stage);
-                        const int tp = kb / L.cchunks, cc = kb - tp * L.cchunks;
-                        int ky = tp / L.kw, kx = tp - ky * L.kw;
-                        if (L.flip) { ky = L.kh - 1 - ky; kx = L.kw - 1 - kx; }
-                        tma2_load_im2col(&L.mapA, a_dst, &full_bar[s], cc * L.bkc, bw, bh, bn_, (uint16_t)(kx * L.dil), (uint16_t)(ky * L.dil));
-                        tma2_load_2d(&L.mapB, a_dst + a_bytes, &full_bar[s], kb * L.bkc, nrow0);
-                        if (++s == L.stages) s = 0;
+                        tma2_load_im2col(&L.mapA, a_dst, &full_bar[s], cc, bw, bh, bn_, (uint16_t)kx, (uint16_t)ky);
+                        tma2_load_2d(&L.mapB, a_dst + a_bytes, &full_bar[s], kcol, nrow0);
+                    }
+                    if (++s == Lstages) s = 0;
+                    kcol += Lbkc; cc += Lbkc;
+                    if (cc == Lcch * Lbkc) {
+                        cc = 0;
+                        if (kx == kx_last) { kx = kx_first; ky += kstep; } else kx += kstep;
                     }
                 }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0 && rank == 0) {
+        if (rank == 0) {
             // ------------------------------ MMA issuer (leader CTA only) ------------------------------
             uint32_t cphase = 0;                             // per-stage phase bits of full_bar
             for (int l = 0; l < a.nlayers; ++l) {
-                const ChainLayer& L = a.table ? a.table[l] : single;
-                if (pair >= L.pairs) continue;
-                const uint32_t idesc = tc::make_idesc_i8(256, L.bn, 0, 0);
-                const uint32_t lay = (L.bkc == 128) ? 2u : 4u;
-                const uint32_t a_bytes = 128u * (uint32_t)L.bkc, stage = a_bytes + (uint32_t)(L.bn / 2) * (uint32_t)L.bkc;
-                const uint32_t sbo = 8u * (uint32_t)L.bkc;
-                const int ksteps = L.bkc / 32;
+                const ChainLayer& L = kTable ? a.table[l] : single;
+                const int Lpairs = L.pairs, Litems = L.items, Lbn = L.bn, Lbkc = L.bkc, Lnumkb = L.num_kb, Lstages = L.stages;
+                if (pair >= Lpairs) continue;
+                const uint32_t idesc = tc::make_idesc_i8(256, Lbn, 0, 0);
+                const uint32_t a_bytes = 128u * (uint32_t)Lbkc, stage = a_bytes + (uint32_t)(Lbn / 2) * (uint32_t)Lbkc;
+                // shared-memory descriptor = layer constant | (address >> 4): K-major, LBO 16 B, SBO 8 rows, swizzle of the row
+                const uint64_t dconst = make_desc2(0u, 16, 8u * (uint32_t)Lbkc, (Lbkc == 128) ? 2u : 4u);
                 int s = 0; uint32_t tile_iter = 0;
-                for (int item = pair; item < L.items; item += L.pairs, ++tile_iter) {
-                    const uint32_t d_tmem = tmem_base + tile_iter * (uint32_t)L.bn;       // every tile keeps its own columns
-                    for (int kb = 0; kb < L.num_kb; ++kb) {
+                for (int item = pair; item < Litems; item += Lpairs, ++tile_iter) {
+                    const uint32_t d_tmem = tmem_base + tile_iter * (uint32_t)Lbn;        // every tile keeps its own columns
+                    for (int kb = 0; kb < Lnumkb; ++kb) {
                         tc::mbar_wait(&full_bar[s], (cphase >> s) & 1u);
                         cphase ^= 1u << s;
                         tc::tc_fence_after();
                         const uint32_t a_base = tc::smem_u32(smem) + (uint32_t)s * stage;
-                        const uint32_t b_base = a_base + a_bytes;
-                        for (int kk = 0; kk < ksteps; ++kk) {
-                            const uint64_t ad = make_desc2(a_base + kk * 32, 16, sbo, lay);
-                            const uint64_t bd = make_desc2(b_base + kk * 32, 16, sbo, lay);
-                            umma2_i8(d_tmem, ad, bd, idesc, (uint32_t)((kb != 0) || (kk != 0)));
+                        const uint64_t ad = dconst | (uint64_t)(a_base >> 4);
+                        const uint64_t bd = dconst | (uint64_t)((a_base + a_bytes) >> 4);
+                        if (elect_one()) {
+                            if (Lbkc == 128) {
+                                umma2_i8(d_tmem, ad, bd, idesc, (uint32_t)(kb != 0));
+                                umma2_i8(d_tmem, ad + 2, bd + 2, idesc, 1u);
+                                umma2_i8(d_tmem, ad + 4, bd + 4, idesc, 1u);
+                                umma2_i8(d_tmem, ad + 6, bd + 6, idesc, 1u);
+                            } else {
+                                umma2_i8(d_tmem, ad, bd, idesc, (uint32_t)(kb != 0));
+                                umma2_i8(d_tmem, ad + 2, bd + 2, idesc, 1u);
+                            }
+                            umma2_commit_mc(&empty_bar[s], 3);   // frees this stage in both CTAs
+                            if (kb == Lnumkb - 1) umma2_commit_mc(&tfull_bar[tile_iter], 3);
                         }
-                        umma2_commit_mc(&empty_bar[s], 3);   // frees this stage in both CTAs
-                        if (++s == L.stages) s = 0;
+                        if (++s == Lstages) s = 0;
                     }
-                    umma2_commit_mc(&tfull_bar[tile_iter], 3);
                 }
             }
         }
@@ -196,34 +232,54 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
         uint32_t nbar = 0;                                   // grid barriers passed so far
         if (etid == 0) chain_trace(a.trace, 0, 1);
         for (int l = 0; l < a.nlayers; ++l) {
-            const ChainLayer& L = a.table ? a.table[l] : single;
-            const bool active = pair < L.pairs;
+            const ChainLayer& L = kTable ? a.table[l] : single;
+            // layer record -> registers (see the producer)
+            const int eM = L.M, eN = L.Ncols, eoh = L.out_h, eow = L.out_w, ent = L.n_tiles, eitems = L.items, epairs = L.pairs;
+            const int ebn = L.bn, erelu = L.relu, epool = L.pool, epgg = L.pg_gate, edps = L.dp_slot;
+            int8_t* const ey = L.y; const int8_t* const egate = L.gate; int8_t* const eyp = L.y_pool; const int8_t* const epgx = L.pg_x;
+            uint32_t* const emax = L.maxabs; const int8_t* const eea = L.exp_a; const int8_t* const eeb = L.exp_b; int8_t* const eeo = L.exp_out;
+            const bool active = pair < epairs;
             int shift = 0, kind = 0;
             uint32_t mx = 0;
-            const int hw = L.out_h * L.out_w;
+            const int hw = eoh * eow;
             for (int pass = 0; pass < 2; ++pass) {
                 uint32_t tile_iter = 0;
                 if (active)
-                for (int item = pair; item < L.items; item += L.pairs, ++tile_iter) {
-                    const int n_t = item % L.n_tiles; const int m_t = item / L.n_tiles;
+                for (int item = pair; item < eitems; item += epairs, ++tile_iter) {
+                    const int n_t = item % ent; const int m_t = item / ent;
                     const int row0 = m_t * 256 + (int)rank * 128 + quarter * 32;
                     const int row = row0 + lane;
-                    const int n0 = n_t * L.bn;
+                    const int n0 = n_t * ebn;
                     if (pass == 0) {
                         tc::mbar_wait(&tfull_bar[tile_iter], (tphase >> tile_iter) & 1u);
                         tc::tc_fence_after();
                         if (etid == 0 && tile_iter == 0) chain_trace(a.trace, l, 2);
                     }
-                    if (row0 >= L.M) continue;               // warp-uniform
-                    const bool row_ok = row < L.M;
+                    if (row0 >= eM) continue;               // warp-uniform
+                    const bool row_ok = row < eM;
                     // pixel coordinates of this row (pool / pool-gradient addressing)
                     int img = 0, py = 0, px = 0;
-                    if (pass == 1 && (L.pool || L.pg_x != nullptr)) { img = row / hw; const int r = row - img * hw; py = r / L.out_w; px = r - py * L.out_w; }
+                    if (pass == 1 && (epool || epgx != nullptr)) { img = row / hw; const int r = row - img * hw; py = r / eow; px = r - py * eow; }
 #pragma unroll 1
-                    for (int c0 = group * 16; c0 < L.bn; c0 += 64) {
-                        if (n0 + c0 >= L.Ncols) break;       // warp-uniform (Ncols % 16 == 0)
+                    for (int c0 = group * 16; c0 < ebn; c0 += 64) {
+                        if (n0 + c0 >= eN) break;       // warp-uniform (Ncols % 16 == 0)
+                        // pass 1: the global loads the store needs are issued before the tensor-memory read so the latencies overlap
+                        const int col = n0 + c0;
+                        uint4 x00, x01, x10, x11, gv;
+                        size_t b00 = 0, b10 = 0;
+                        if (pass == 1 && row_ok) {
+                            if (epgx != nullptr) {
+                                const int w2 = eow * 2;
+                                b00 = (((size_t)img * (eoh * 2) + 2 * py) * w2 + 2 * px) * eN + col;
+                                b10 = b00 + (size_t)w2 * eN;
+                                x00 = ldg_u4(epgx + b00); x01 = ldg_u4(epgx + b00 + eN);
+                                x10 = ldg_u4(epgx + b10); x11 = ldg_u4(epgx + b10 + eN);
+                            } else if (egate != nullptr) {
+                                gv = ldg_u4(egate + (size_t)row * eN + col);
+                            }
+                        }
                         uint32_t v[16];
-                        tmem_ld16(tmem_base + ((uint32_t)(quarter * 32) << 16) + tile_iter * (uint32_t)L.bn + (uint32_t)c0, v);
+                        tmem_ld16(tmem_base + ((uint32_t)(quarter * 32) << 16) + tile_iter * (uint32_t)ebn + (uint32_t)c0, v);
                         tc::tmem_ld_wait();
                         if (pass == 0) {
                             if (row_ok) {
@@ -243,75 +299,72 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
                             }
                             o[q] = pack4c(r[0], r[1], r[2], r[3]);
                         }
-                        if (L.relu) { o[0] = __vmaxs4(o[0], 0u); o[1] = __vmaxs4(o[1], 0u); o[2] = __vmaxs4(o[2], 0u); o[3] = __vmaxs4(o[3], 0u); }
-                        const int col = n0 + c0;
-                        if (L.pg_x == nullptr) {
-                            const size_t off = (size_t)row * L.Ncols + col;
+                        if (erelu) { o[0] = __vmaxs4(o[0], 0u); o[1] = __vmaxs4(o[1], 0u); o[2] = __vmaxs4(o[2], 0u); o[3] = __vmaxs4(o[3], 0u); }
+                        if (epgx == nullptr) {
+                            const size_t off = (size_t)row * eN + col;
                             if (row_ok) {
-                                if (L.gate != nullptr) {     // NITI_CPUReluGrad: pass where the forward value was > 0
-                                    const uint4 g = vgt0(ldg_u4(L.gate + off));
+                                if (egate != nullptr) {     // NITI_CPUReluGrad: pass where the forward value was > 0
+                                    const uint4 g = vgt0(gv);
                                     o[0] &= g.x; o[1] &= g.y; o[2] &= g.z; o[3] &= g.w;
                                 }
-                                *reinterpret_cast<uint4*>(L.y + off) = make_uint4(o[0], o[1], o[2], o[3]);
+                                *reinterpret_cast<uint4*>(ey + off) = make_uint4(o[0], o[1], o[2], o[3]);
                             }
-                            if (L.pool) {
+                            if (epool) {
                                 // 2x2/2 max pool across lanes: lane bit 0 = x parity, lane bit log2(out_w) = y parity
                                 uint32_t m[4];
 #pragma unroll
                                 for (int q = 0; q < 4; ++q) {
                                     m[q] = __vmaxs4(o[q], __shfl_xor_sync(0xffffffffu, o[q], 1));
-                                    m[q] = __vmaxs4(m[q], __shfl_xor_sync(0xffffffffu, m[q], L.out_w));
+                                    m[q] = __vmaxs4(m[q], __shfl_xor_sync(0xffffffffu, m[q], eow));
                                 }
                                 if (row_ok && !(px & 1) && !(py & 1)) {
-                                    const size_t po = (((size_t)img * (L.out_h >> 1) + (py >> 1)) * (L.out_w >> 1) + (px >> 1)) * L.Ncols + col;
-                                    *reinterpret_cast<uint4*>(L.y_pool + po) = make_uint4(m[0], m[1], m[2], m[3]);
+                                    const size_t po = (((size_t)img * (eoh >> 1) + (py >> 1)) * (eow >> 1) + (px >> 1)) * eN + col;
+                                    *reinterpret_cast<uint4*>(eyp + po) = make_uint4(m[0], m[1], m[2], m[3]);
                                 }
                             }
                         } else if (row_ok) {
                             // max-pool gradient (+ ReLU-grad gate): this row is one pooled pixel; route its gradient to the
                             // first window element (row-major) that equals the window maximum, zero elsewhere
-                            const int w2 = L.out_w * 2;
-                            const size_t b00 = (((size_t)img * (L.out_h * 2) + 2 * py) * w2 + 2 * px) * L.Ncols + col;
-                            const size_t b10 = b00 + (size_t)w2 * L.Ncols;
-                            const uint4 x00 = ldg_u4(L.pg_x + b00), x01 = ldg_u4(L.pg_x + b00 + L.Ncols);
-                            const uint4 x10 = ldg_u4(L.pg_x + b10), x11 = ldg_u4(L.pg_x + b10 + L.Ncols);
                             const uint4 mxv = vmax4(vmax4(x00, x01), vmax4(x10, x11));
                             const uint4 g = make_uint4(o[0], o[1], o[2], o[3]);
                             uint4 e0 = vge4(x00, mxv), done = e0;
                             uint4 e1 = vandn4(vge4(x01, mxv), done); done = vor4(done, e1);
                             uint4 e2 = vandn4(vge4(x10, mxv), done); done = vor4(done, e2);
                             uint4 e3 = vandn4(vge4(x11, mxv), done);
-                            if (L.pg_gate) { e0 = vand4(e0, vgt0(x00)); e1 = vand4(e1, vgt0(x01)); e2 = vand4(e2, vgt0(x10)); e3 = vand4(e3, vgt0(x11)); }
-                            *reinterpret_cast<uint4*>(L.y + b00) = vand4(g, e0);
-                            *reinterpret_cast<uint4*>(L.y + b00 + L.Ncols) = vand4(g, e1);
-                            *reinterpret_cast<uint4*>(L.y + b10) = vand4(g, e2);
-                            *reinterpret_cast<uint4*>(L.y + b10 + L.Ncols) = vand4(g, e3);
+                            if (epgg) { e0 = vand4(e0, vgt0(x00)); e1 = vand4(e1, vgt0(x01)); e2 = vand4(e2, vgt0(x10)); e3 = vand4(e3, vgt0(x11)); }
+                            *reinterpret_cast<uint4*>(ey + b00) = vand4(g, e0);
+                            *reinterpret_cast<uint4*>(ey + b00 + eN) = vand4(g, e1);
+                            *reinterpret_cast<uint4*>(ey + b10) = vand4(g, e2);
+                            *reinterpret_cast<uint4*>(ey + b10 + eN) = vand4(g, e3);
                         }
                     }
                 }
                 if (pass == 0) {
                     // ---- global max|acc|: warp max -> atomicMax -> grid barrier -> (data parallel: peer exchange) ----
+                    // one global atomic per CTA, not per warp: 16 x 148 atomics on one word serialise in L2 for microseconds
                     mx = warp_max_u32(mx);
-                    if (lane == 0 && mx) atomicMax(L.maxabs, mx);
+                    if (lane == 0 && mx) atomicMax(cta_max, mx);
                     asm volatile("bar.sync 1, 512;" ::: "memory");
                     if (a.trigger_late && l == a.nlayers - 1) niti_pdl_trigger();
                     if (etid == 0) {
+                        const uint32_t cm = *cta_max; *cta_max = 0u;
+                        if (cm) atomicMax(emax, cm);
                         chain_trace(a.trace, l, 3);
                         ++nbar; niti_grid_barrier(a.sync, nbar * gridDim.x);
                         chain_trace(a.trace, l, 4);
-                        *bcast = dp_exchange_max(a.dp, L.dp_slot, __ldcg(L.maxabs), blockIdx.x == 0);
+                        *bcast = dp_exchange_max(a.dp, edps, __ldcg(emax), blockIdx.x == 0);
                     }
                     asm volatile("bar.sync 1, 512;" ::: "memory");
                     const int b = niti_bitwidth(*bcast);
                     const int s = b - 7;
                     if (s > 1) { shift = s; kind = 0; } else if (s == 1) { shift = 2; kind = 0; } else { shift = 0; kind = 1; }
-                    if (blockIdx.x == 0 && etid == 0 && L.exp_out != nullptr)
-                        *L.exp_out = (int8_t)((L.exp_a ? (int)*L.exp_a : 0) + (L.exp_b ? (int)*L.exp_b : 0) + (kind == 1 ? 0 : shift));
+                    if (blockIdx.x == 0 && etid == 0 && eeo != nullptr)
+                        *eeo = (int8_t)((eea ? (int)*eea : 0) + (eeb ? (int)*eeb : 0) + (kind == 1 ? 0 : shift));
                 }
             }
             // this pair's tiles of the layer are drained: flip their phase bits
             if (active) {
-                const int mine = (L.items - pair + L.pairs - 1) / L.pairs;
+                const int mine = (eitems - pair + epairs - 1) / epairs;
                 tphase ^= (1u << mine) - 1u;
             }
             tc::tc_fence_before();
@@ -335,6 +388,7 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
     cluster_sync_all();
     if (warp == 1) tmem_dealloc2<512>(tmem_base);
     if (tid == 64) chain_trace(a.trace, a.nlayers - 1, 7);
+    niti_tl_exit(a.tl);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -420,13 +474,15 @@ struct niti_chain {
 };
 
 static int chain_launch(niti_ctx* ctx, const ChainLayer* single, const ChainLayer* table, int nlayers, int grid, cudaStream_t st) {
-    if (int rc = niti_func_smem(ctx, (const void*)chain_kernel, kChainSmem, "cudaFuncSetAttribute(chain_kernel)")) return rc;
+    if (int rc = niti_func_smem(ctx, table ? (const void*)chain_kernel<true> : (const void*)chain_kernel<false>, kChainSmem,
+                                "cudaFuncSetAttribute(chain_kernel)")) return rc;
     ChainArgs a{};
     a.table = table; a.nlayers = nlayers; a.sync = ctx->ws_u32 + 52; a.dp = ctx->dp; a.trace = ctx->trace;
+    a.tl = niti_tl_next(ctx, nlayers > 1 ? "chain" : (single && single->flip ? "dx_fused" : "fwd_fused"));
     a.trigger_late = (ctx->pdl & NITI_PDL_TRIGGER_LATE) ? 1 : 0;
     static const ChainLayer zero{};
-    cudaError_t e = niti_launch(ctx, NITI_PDL_FUSED, chain_kernel, dim3(grid), dim3(kChainThreads), (size_t)kChainSmem, st,
-                                single ? *single : zero, a);
+    cudaError_t e = table ? niti_launch(ctx, NITI_PDL_FUSED, chain_kernel<true>, dim3(grid), dim3(kChainThreads), (size_t)kChainSmem, st, zero, a)
+                          : niti_launch(ctx, NITI_PDL_FUSED, chain_kernel<false>, dim3(grid), dim3(kChainThreads), (size_t)kChainSmem, st, *single, a);
     if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "launch chain_kernel", e);
     return niti_check_launch(ctx, "chain_kernel");
 }

@@ -26,6 +26,7 @@ struct Dw2Params {
     int accumulate;                   // acc += dW into a caller-zeroed buffer: no in-kernel clear, no grid barrier
     int32_t* acc; size_t nout;
     uint32_t* sync;                   // {arrival counter, exit counter}
+    unsigned long long* tl;
 };
 
 template <int BKC, int G> struct DwCfg {
@@ -71,6 +72,7 @@ dw2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 1);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    niti_tl_enter(p.tl);
 
     if (tid == 0) {
         for (int s = 0; s < C::STAGES; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], 1); }
@@ -224,6 +226,7 @@ dw2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
     tc::tc_fence_before();
     __syncthreads();
     if (warp == 1) tc::tmem_dealloc<C::TMEM_COLS>(tmem_base);
+    niti_tl_exit(p.tl);
 }
 
 } // namespace
@@ -266,7 +269,7 @@ int dw2_conv_dw_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, con
     p.splits = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;
     p.items = (int)(tiles * p.splits);
     p.acc = acc; p.nout = (size_t)d->oc * d->kh * d->kw * d->c; p.sync = ctx->ws_u32 + 44;
-    p.accumulate = accumulate;
+    p.accumulate = accumulate; p.tl = niti_tl_next(ctx, "dw2");
     CUtensorMap ma, mb, md;
     if (!tmax::make_tiled_u8(&ma, dy, (uint64_t)p.npix, (uint64_t)d->oc, 128, 128, 128))
         return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncodeTiled(dy) failed");

@@ -32,6 +32,7 @@ struct StemParams {
     int relu;
     uint32_t* sync;                   // {arrival counter, exit counter}
     DpView dp; int dp_slot;
+    unsigned long long* tl;
 };
 
 __device__ __forceinline__ uint32_t pack4s(int32_t a, int32_t b, int32_t c, int32_t d) {
@@ -62,6 +63,7 @@ stem_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
     uint32_t* bcast = tmem_slot + 1;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    niti_tl_enter(p.tl);
     const int accw = p.oc <= 32 ? 32 : (p.oc <= 64 ? 64 : (p.oc <= 128 ? 128 : 256));   // columns per accumulator stage
 
     if (tid == 0) {
@@ -219,6 +221,7 @@ stem_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
     tc::tc_fence_before();
     __syncthreads();
     if (warp == 1) tc::tmem_dealloc<512>(tmem_base);
+    niti_tl_exit(p.tl);
 }
 
 } // namespace
@@ -250,7 +253,7 @@ int stem_conv_fwd_fused(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x,
     p.m_tiles = (p.M + 127) / 128;
     p.y = y; p.maxabs = maxabs; p.exp_a = ex; p.exp_b = ew; p.exp_out = ey; p.relu = relu;
     p.sync = ctx->ws_u32 + 48;
-    p.dp = ctx->dp; p.dp_slot = dp_slot;
+    p.dp = ctx->dp; p.dp_slot = dp_slot; p.tl = niti_tl_next(ctx, "stem_fwd");
     CUtensorMap ma, mb;
     p.rows_mode = tmax::rows16_ok(d->c, d->stride, d->dil, oh, ow) ? 1 : 0;
     if (p.rows_mode) {

@@ -124,8 +124,9 @@ __device__ __forceinline__ uint4 vmax4x4(uint4 a, uint4 b) {
 }
 
 __global__ void __launch_bounds__(kThreads) maxpool_vec_kernel(const uint4* __restrict__ x, int n, int h, int w, int c16,
-                                                               int k, int s, int oh, int ow, uint4* __restrict__ y) {
+                                                               int k, int s, int oh, int ow, uint4* __restrict__ y, unsigned long long* tl) {
     niti_pdl_trigger(); niti_pdl_wait();                     // programmatic dependent launch: see common.cuh
+    niti_tl_enter(tl);
     const size_t total = (size_t)n * oh * ow * c16;
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
         int cv = (int)(i % c16); size_t p = i / c16;
@@ -141,14 +142,17 @@ __global__ void __launch_bounds__(kThreads) maxpool_vec_kernel(const uint4* __re
         }
         y[i] = m;
     }
+    niti_tl_exit(tl);
 }
 
 // non-overlapping windows (k == s): one thread owns a whole window x 16 channels, so the "first element
 // >= max in row-major order wins" rule is a running mask and every dx word is written exactly once.
 __global__ void __launch_bounds__(kThreads) maxpool_grad_vec_kernel(const uint4* __restrict__ x, const uint4* __restrict__ y,
                                                                     const uint4* __restrict__ dy, int n, int h, int w, int c16,
-                                                                    int k, int oh, int ow, uint4* __restrict__ dx, int gate_relu) {
+                                                                    int k, int oh, int ow, uint4* __restrict__ dx, int gate_relu,
+                                                                    unsigned long long* tl) {
     niti_pdl_trigger(); niti_pdl_wait();                     // programmatic dependent launch: see common.cuh
+    niti_tl_enter(tl);
     const size_t total = (size_t)n * oh * ow * c16;
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
         int cv = (int)(i % c16); size_t p = i / c16;
@@ -182,14 +186,17 @@ __global__ void __launch_bounds__(kThreads) maxpool_grad_vec_kernel(const uint4*
             }
         }
     }
+    niti_tl_exit(tl);
 }
 
 // integer softmax cross-entropy gradient; one thread per sample (batch is small, classes ~10).  Rows are `stride` bytes
 // apart, the first `classes` entries are real, grad's padding columns are written as 0.  ev(j) and the 64-bit division are
 // evaluated once per class (kept in a local array for classes <= 32, recomputed beyond that).
 __global__ void loss_grad_kernel(const int8_t* __restrict__ logits, const int8_t* __restrict__ ascale_p,
-                                 const int32_t* __restrict__ labels, int batch, int classes, int stride, int8_t* __restrict__ grad) {
+                                 const int32_t* __restrict__ labels, int batch, int classes, int stride, int8_t* __restrict__ grad,
+                                 unsigned long long* tl) {
     niti_pdl_trigger(); niti_pdl_wait();                     // programmatic dependent launch: see common.cuh
+    niti_tl_enter(tl);
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= batch) return;
     const int a = (int)*ascale_p;
@@ -232,6 +239,7 @@ __global__ void loss_grad_kernel(const int8_t* __restrict__ logits, const int8_t
         out[j] = (int8_t)niti_psto((int32_t)g, 4);
     }
     for (int j = classes; j < stride; ++j) out[j] = 0;
+    niti_tl_exit(tl);
 }
 
 // generic 4-d permutation of int8 tensors through index arithmetic (boundary only; small tensors)
@@ -301,7 +309,7 @@ extern "C" int niti_maxpool(niti_ctx* ctx, const int8_t* x, int n, int h, int w,
     if (c % 16 == 0 && aligned16(x) && aligned16(y)) {
         cudaError_t le = niti_launch(ctx, NITI_PDL_ELEMENTWISE, maxpool_vec_kernel, dim3(grid_for(ctx, (size_t)n * oh * ow * (c / 16))), dim3(kThreads), 0,
                                      (cudaStream_t)st, reinterpret_cast<const uint4*>(x), n, h, w, c / 16, k, s, oh, ow,
-                                     reinterpret_cast<uint4*>(y));
+                                     reinterpret_cast<uint4*>(y), niti_tl_next(ctx, "maxpool"));
         if (le != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "launch maxpool_vec", le);
         return niti_check_launch(ctx, "maxpool_vec");
     }
@@ -321,7 +329,7 @@ extern "C" int niti_maxpool_grad_gated(niti_ctx* ctx, const int8_t* x, const int
         cudaError_t le = niti_launch(ctx, NITI_PDL_ELEMENTWISE, maxpool_grad_vec_kernel, dim3(grid_for(ctx, (size_t)n * oh * ow * (c / 16))), dim3(kThreads), 0,
                                      (cudaStream_t)st, reinterpret_cast<const uint4*>(x), reinterpret_cast<const uint4*>(y),
                                      reinterpret_cast<const uint4*>(dy), n, h, w, c / 16, k, oh, ow, reinterpret_cast<uint4*>(dx),
-                                     gate_relu);
+                                     gate_relu, niti_tl_next(ctx, "maxpool_grad"));
         if (le != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "launch maxpool_grad_vec", le);
         return niti_check_launch(ctx, "maxpool_grad_vec");
     }
@@ -337,7 +345,7 @@ extern "C" int niti_loss_grad_strided(niti_ctx* ctx, const int8_t* logits, const
     if (!ctx || !logits || !ascale || !labels || !grad || batch <= 0 || classes <= 0 || stride < classes)
         return niti_fail(ctx, NITI_ERR_ARG, "niti_loss_grad");
     cudaError_t le = niti_launch(ctx, NITI_PDL_ELEMENTWISE, loss_grad_kernel, dim3((batch + 31) / 32), dim3(32), 0, (cudaStream_t)st, logits, ascale, labels,
-                                 batch, classes, stride, grad);
+                                 batch, classes, stride, grad, niti_tl_next(ctx, "loss_grad"));
     if (le != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "launch loss_grad", le);
     return niti_check_launch(ctx, "loss_grad");
 }
@@ -352,7 +360,8 @@ int niti_maxpool_grad_from_x(niti_ctx* ctx, const int8_t* x, const int8_t* dy, i
     const int oh = h / 2, ow = w / 2;
     cudaError_t le = niti_launch(ctx, NITI_PDL_ELEMENTWISE, maxpool_grad_vec_kernel, dim3(grid_for(ctx, (size_t)n * oh * ow * (c / 16))), dim3(kThreads), 0,
                                  (cudaStream_t)st, reinterpret_cast<const uint4*>(x), (const uint4*)nullptr,
-                                 reinterpret_cast<const uint4*>(dy), n, h, w, c / 16, 2, oh, ow, reinterpret_cast<uint4*>(dx), gate_relu);
+                                 reinterpret_cast<const uint4*>(dy), n, h, w, c / 16, 2, oh, ow, reinterpret_cast<uint4*>(dx), gate_relu,
+                                 niti_tl_next(ctx, "maxpool_grad"));
     if (le != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "launch maxpool_grad_vec", le);
     return niti_check_launch(ctx, "maxpool_grad_vec");
 }

@@ -46,12 +46,12 @@ __device__ __forceinline__ int32_t upd_one(int32_t acc, int32_t w, int b, int sh
 }
 
 __global__ void __launch_bounds__(kUpdThreads)
-update_batched_kernel(const __grid_constant__ UpdSegs S, uint32_t* sync) {
+update_batched_kernel(const __grid_constant__ UpdSegs S, uint32_t* sync, unsigned long long* tl) {
     __shared__ uint32_t red[kUpdThreads / 32];
-    __shared__ uint32_t tbuf[kUpdThreads / 32][32 * 9];          // per warp: 32 rows x 36 bytes (padded) transpose tile
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     niti_pdl_trigger();
     niti_pdl_wait();                                         // programmatic dependent launch: see common.cuh
+    niti_tl_enter(tl);
 
     // ---------------- phase 1: max|acc| per segment ----------------
     const uint32_t nchunks = S.chunk_begin[S.n];
@@ -87,81 +87,65 @@ update_batched_kernel(const __grid_constant__ UpdSegs S, uint32_t* sync) {
     __syncthreads();
 
     // ---------------- phase 2: rule B + SGD (+ transposed copy), one 32x32 tile per warp ----------------
+    // Lanes run along the COLUMNS of the [oc][taps*c] weight matrix: every row of the tile is one coalesced 128-byte read
+    // of the int32 accumulators and one 32-byte read / write of the weights.  After 32 rows lane j holds column c0+j of the
+    // updated tile, i.e. 32 consecutive bytes of row (c0+j) of the transposed copy wt = [c][taps][oc] — written as two
+    // 16-byte stores, no shared-memory transpose.
     const uint32_t ntiles = S.tile_begin[S.n];
     const uint32_t nwarps = gridDim.x * (kUpdThreads / 32);
-    uint32_t* tb = tbuf[warp];
     for (uint32_t u = blockIdx.x * (kUpdThreads / 32) + warp; u < ntiles; u += nwarps) {
         const int si = find_seg(S.tile_begin, S.n, u);
         const niti_update_seg& sg = S.s[si];
-        const int cols = sg.taps * sg.c;
+        const int cols = sg.taps * sg.c, oc = sg.oc;
         const int ctiles = (cols + 31) >> 5;
         const uint32_t t = u - S.tile_begin[si];
         const int r0 = (int)(t / ctiles) << 5, c0 = (int)(t % ctiles) << 5;
         const int b = niti_bitwidth(__ldcg(sg.maxabs));
         const int shift = b - sg.sub;
-        const int row = r0 + lane;
-        const bool full = (r0 + 32 <= sg.oc) && (c0 + 32 <= cols) && ((cols & 31) == 0);
-        uint32_t o[8];
-        if (full) {
-            const size_t base = (size_t)row * cols + c0;
-            const int4* av = reinterpret_cast<const int4*>(sg.acc + base);
-            const uint4* wv = reinterpret_cast<const uint4*>(sg.w + base);
-            const uint4 w0 = wv[0], w1 = wv[1];
-            const uint32_t wi[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+        const int col = c0 + lane;
+        const bool col_ok = col < cols;
+        const int rows = min(32, oc - r0);
+        const int32_t* ap = sg.acc + (size_t)r0 * cols + col;
+        int8_t* wp = sg.w + (size_t)r0 * cols + col;
+        uint32_t q[8];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const int4 a = __ldcg(av + j);
-                const uint32_t ww = wi[j];
-                o[j] = pack4u(upd_one(a.x, (int32_t)(int8_t)(ww & 0xff), b, shift),
-                              upd_one(a.y, (int32_t)(int8_t)((ww >> 8) & 0xff), b, shift),
-                              upd_one(a.z, (int32_t)(int8_t)((ww >> 16) & 0xff), b, shift),
-                              upd_one(a.w, (int32_t)(int8_t)((ww >> 24) & 0xff), b, shift));
-            }
-            uint4* wo = reinterpret_cast<uint4*>(sg.w + base);
-            wo[0] = make_uint4(o[0], o[1], o[2], o[3]);
-            wo[1] = make_uint4(o[4], o[5], o[6], o[7]);
-        } else {
+        for (int j = 0; j < 8; ++j) q[j] = 0u;
+        if (rows == 32) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                int32_t r[4] = {0, 0, 0, 0};
+            for (int r = 0; r < 32; r += 8) {
+                int32_t av[8], wv[8];
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const int col = c0 + j * 4 + k;
-                    if (row < sg.oc && col < cols) {
-                        const size_t idx = (size_t)row * cols + col;
-                        r[k] = upd_one(sg.acc[idx], (int32_t)sg.w[idx], b, shift);
-                        sg.w[idx] = (int8_t)r[k];
-                    }
+                for (int k = 0; k < 8; ++k) {                  // eight independent rows in flight
+                    av[k] = col_ok ? __ldcg(ap + (size_t)(r + k) * cols) : 0;
+                    wv[k] = col_ok ? (int32_t)wp[(size_t)(r + k) * cols] : 0;
                 }
-                o[j] = pack4u(r[0], r[1], r[2], r[3]);
+                uint32_t lo = 0, hi = 0;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const int32_t nv = upd_one(av[k], wv[k], b, shift);
+                    if (col_ok) wp[(size_t)(r + k) * cols] = (int8_t)nv;
+                    if (k < 4) lo |= (uint32_t)(nv & 0xff) << (8 * k); else hi |= (uint32_t)(nv & 0xff) << (8 * (k - 4));
+                }
+                q[r >> 2] = lo; q[(r >> 2) + 1] = hi;
+            }
+        } else {
+            for (int r = 0; r < rows; ++r) {
+                if (col_ok) {
+                    const int32_t nv = upd_one(__ldcg(ap + (size_t)r * cols), (int32_t)wp[(size_t)r * cols], b, shift);
+                    wp[(size_t)r * cols] = (int8_t)nv;
+                    q[r >> 2] |= (uint32_t)(nv & 0xff) << (8 * (r & 3));
+                }
             }
         }
-        if (sg.wt != nullptr) {                                   // warp-uniform
-            // transpose the 32x32 byte tile through shared memory: lane r wrote row r, lane j reads column j
-            __syncwarp();
-#pragma unroll
-            for (int j = 0; j < 8; ++j) tb[lane * 9 + j] = o[j];
-            __syncwarp();
-            const uint8_t* tbb = reinterpret_cast<const uint8_t*>(tb);
-            uint32_t q[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                uint32_t x = 0;
-#pragma unroll
-                for (int k = 0; k < 4; ++k) x |= (uint32_t)tbb[(j * 4 + k) * 36 + lane] << (8 * k);
-                q[j] = x;
-            }
-            const int col = c0 + lane;                             // this lane's column of W = row of Wt
-            if (col < cols) {
-                const int tap = col / sg.c, ci = col - tap * sg.c;
-                int8_t* dst = sg.wt + ((size_t)ci * sg.taps + tap) * sg.oc + r0;
-                if (full && (sg.oc & 31) == 0) {
-                    uint4* d4 = reinterpret_cast<uint4*>(dst);
-                    d4[0] = make_uint4(q[0], q[1], q[2], q[3]);
-                    d4[1] = make_uint4(q[4], q[5], q[6], q[7]);
-                } else {
-                    for (int k = 0; k < 32 && r0 + k < sg.oc; ++k) dst[k] = (int8_t)((q[k >> 2] >> (8 * (k & 3))) & 0xff);
-                }
+        if (sg.wt != nullptr && col_ok) {
+            const int tap = col / sg.c, ci = col - tap * sg.c;
+            int8_t* dst = sg.wt + ((size_t)ci * sg.taps + tap) * oc + r0;
+            if (rows == 32 && (oc & 15) == 0) {
+                uint4* d4 = reinterpret_cast<uint4*>(dst);
+                d4[0] = make_uint4(q[0], q[1], q[2], q[3]);
+                d4[1] = make_uint4(q[4], q[5], q[6], q[7]);
+            } else {
+                for (int k = 0; k < rows; ++k) dst[k] = (int8_t)((q[k >> 2] >> (8 * (k & 3))) & 0xff);
             }
         }
     }
@@ -171,6 +155,7 @@ update_batched_kernel(const __grid_constant__ UpdSegs S, uint32_t* sync) {
     if (tid == 0) {
         if (atomicAdd(sync + 1, 1u) == gridDim.x - 1) { sync[0] = 0u; sync[1] = 0u; __threadfence(); }
     }
+    niti_tl_exit(tl);
 }
 
 } // namespace
@@ -203,7 +188,7 @@ extern "C" int niti_update_batched(niti_ctx* ctx, const niti_update_seg* segs, i
         }
         S.chunk_begin[S.n] = chunks; S.tile_begin[S.n] = tiles;
         const int grid = ctx->sm_count * blocks_per_sm;            // all CTAs co-resident: the grid barrier needs it
-        cudaError_t lerr = niti_launch(ctx, NITI_PDL_UPDATE, update_batched_kernel, dim3(grid), dim3(kUpdThreads), 0, (cudaStream_t)st, S, ctx->ws_u32 + 40);
+        cudaError_t lerr = niti_launch(ctx, NITI_PDL_UPDATE, update_batched_kernel, dim3(grid), dim3(kUpdThreads), 0, (cudaStream_t)st, S, ctx->ws_u32 + 40, niti_tl_next(ctx, "update_batched"));
         if (lerr != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "launch update_batched", lerr);
         int rc = niti_check_launch(ctx, "update_batched");
         if (rc) return rc;

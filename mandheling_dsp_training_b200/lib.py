@@ -104,6 +104,9 @@ _SIGS = {
     "niti_nhwc_to_nc4hw4": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
     "niti_conv_fwd_host": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, C.c_int8, C.c_int8, _P, _P]),
     "niti_debug_trace": (C.c_int, [_P, _P]),
+    "niti_debug_timeline": (C.c_int, [_P, _P, C.c_int]),
+    "niti_debug_timeline_count": (C.c_int, [_P]),
+    "niti_debug_timeline_name": (C.c_char_p, [_P, C.c_int]),
     "niti_probe_i8_peak": (C.c_int, [_P, C.c_int, C.POINTER(C.c_double)]),
 }
 EXPORTED_SYMBOLS = tuple(_SIGS)
@@ -417,6 +420,12 @@ class NitiB200:
 
     def debug_trace(self, buf):
         self._ck(self.lib.niti_debug_trace(self.h, _ptr(buf)))
+
+    def debug_timeline(self, buf, capacity=0):
+        self._ck(self.lib.niti_debug_timeline(self.h, _ptr(buf), int(capacity)))
+
+    def timeline_names(self):
+        return [self.lib.niti_debug_timeline_name(self.h, i).decode() for i in range(self.lib.niti_debug_timeline_count(self.h))]
 
     def probe_i8_peak(self, iters=2000):
         t = C.c_double(0)

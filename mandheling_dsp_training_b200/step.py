@@ -221,8 +221,10 @@ class NitiNet:
             return
 
         def pool_2x2(P):
+            if P.kind != "pool":
+                return False
             n, h, w, c = P.geom
-            return P.kind == "pool" and P.k == 2 and P.s == 2 and h % 2 == 0 and w % 2 == 0 and c % 16 == 0
+            return P.k == 2 and P.s == 2 and h % 2 == 0 and w % 2 == 0 and c % 16 == 0
         for i, L in enumerate(self.ops):
             nxt = self.ops[i + 1] if i + 1 < len(self.ops) else None
             if L.kind == "conv" and L.relu and nxt is not None and pool_2x2(nxt):

@@ -8,6 +8,7 @@ timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/${tag}_pytest.log 
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${tag}_smoke.log 2>&1; echo smoke rc=$?; tail -1 gpurun_out/${tag}_smoke.log
 timeout 400 python bench.py --no-cpu-baseline > gpurun_out/${tag}_bench_vgg.json 2> gpurun_out/${tag}_bench_vgg.err; echo bench rc=$?
 python tools/phase_trace.py vgg11 256 > gpurun_out/${tag}_phase_vgg.txt 2>&1; echo phase rc=$?
+python tools/timeline.py vgg11 256 > gpurun_out/${tag}_timeline_vgg.txt 2>&1; echo timeline rc=$?
 python - <<PY
 import json
 try:
@@ -17,4 +18,4 @@ try:
 except Exception as e:
     print("bench unreadable", e)
 PY
-tail -25 gpurun_out/${tag}_phase_vgg.txt
+head -60 gpurun_out/${tag}_timeline_vgg.txt
