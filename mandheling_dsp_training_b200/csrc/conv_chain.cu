@@ -169,7 +169,7 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
                     tc::mbar_wait(&empty_bar[s], ((pphase >> s) & 1u) ^ 1u);
                     pphase ^= 1u << s;
                     const uint32_t a_dst = tc::smem_u32(smem) + (uint32_t)s * stage;
-                    if (elect_one()) {
+                    if (tc::elect_one()) {
                         if (rank == 0) mbar_expect_tx(&full_bar[s], 2u * stage);
                         tma2_load_im2col(&L.mapA, a_dst, &full_bar[s], cc, bw, bh, bn_, (uint16_t)kx, (uint16_t)ky);
                         tma2_load_2d(&L.mapB, a_dst + a_bytes, &full_bar[s], kcol, nrow0);
@@ -205,7 +205,7 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
                         const uint32_t a_base = tc::smem_u32(smem) + (uint32_t)s * stage;
                         const uint64_t ad = dconst | (uint64_t)(a_base >> 4);
                         const uint64_t bd = dconst | (uint64_t)((a_base + a_bytes) >> 4);
-                        if (elect_one()) {
+                        if (tc::elect_one()) {
                             if (Lbkc == 128) {
                                 umma2_i8(d_tmem, ad, bd, idesc, (uint32_t)(kb != 0));
                                 umma2_i8(d_tmem, ad + 2, bd + 2, idesc, 1u);

@@ -86,23 +86,27 @@ dw2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
     tc::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
+    // Both issuing roles run with the whole warp on warp-uniform values; only the issue itself sits under elect.sync, so the
+    // compiler feeds UTMALDG / UTCIMMA from uniform registers instead of wrapping each one in an ELECT / R2UR.BROADCAST loop
+    // (12 MMAs + 4 loads per K block here; see conv_chain.cu).
     if (warp == 0) {
-        if (lane == 0) {
-            // ------------------------------ TMA producer ------------------------------
-            uint32_t n = 0;
-            for (int item = blockIdx.x; item < p.items; item += gridDim.x) {
-                const DwItem it = decode_item<G>(p, item);
-                for (int kb = it.kb0; kb < it.kb1; ++kb, ++n) {
-                    const int s = n % C::STAGES; const uint32_t ph = (n / C::STAGES) & 1u;
-                    tc::mbar_wait(&empty_bar[s], ph ^ 1u);
-                    const uint32_t a_dst = tc::smem_u32(smem + s * C::STAGE);
+        // ------------------------------ TMA producer ------------------------------
+        uint32_t n = 0;
+        for (int item = blockIdx.x; item < p.items; item += gridDim.x) {
+            const DwItem it = decode_item<G>(p, item);
+            const int ky0 = it.tap0 / p.kw, kx0 = it.tap0 - ky0 * p.kw;
+            for (int kb = it.kb0; kb < it.kb1; ++kb, ++n) {
+                const int s = n % C::STAGES; const uint32_t ph = (n / C::STAGES) & 1u;
+                tc::mbar_wait(&empty_bar[s], ph ^ 1u);
+                const uint32_t a_dst = tc::smem_u32(smem + s * C::STAGE);
+                const int pix0 = kb * 128;
+                const int q = pix0 % p.out_w; const int t = pix0 / p.out_w;
+                const int pp = t % p.out_h; const int nn = t / p.out_h;
+                if (tc::elect_one()) {
                     tmax::mbar_expect_tx(&full_bar[s], (uint32_t)(C::A_BYTES + it.ng * C::B_BYTES));
-                    const int pix0 = kb * 128;
-                    const int q = pix0 % p.out_w; const int t = pix0 / p.out_w;
-                    const int pp = t % p.out_h; const int nn = t / p.out_h;
                     tmax::load_2d(&mapA, a_dst, &full_bar[s], it.ot * 128, pix0);
+                    int kx = kx0, ky = ky0;
                     for (int g = 0; g < it.ng; ++g) {
-                        const int tap = it.tap0 + g, ky = tap / p.kw, kx = tap - ky * p.kw;
                         if (BKC == 16 && p.rows_mode)
                             tmax::load_3d(&mapB, a_dst + C::A_BYTES + g * C::B_BYTES, &full_bar[s], (kx + p.lower_w) * 2,
                                           pp + ky + p.lower_h, nn);
@@ -110,50 +114,53 @@ dw2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUt
                             tmax::load_im2col(&mapB, a_dst + C::A_BYTES + g * C::B_BYTES, &full_bar[s], it.ct * BKC,
                                               q * p.stride + p.lower_w, pp * p.stride + p.lower_h, nn,
                                               (uint16_t)(kx * p.dil), (uint16_t)(ky * p.dil));
+                        if (++kx == p.kw) { kx = 0; ++ky; }
                     }
                 }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // ------------------------------ MMA issuer ------------------------------
-            constexpr uint32_t idesc = tc::make_idesc_i8(128, BKC, 1, 1);
-            constexpr uint32_t lay = (BKC == 128) ? 2u : (BKC == 64 ? 4u : 0u);
-            uint32_t n = 0, tile_iter = 0;
-            for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++tile_iter) {
-                const DwItem it = decode_item<G>(p, item);
-                tc::mbar_wait(tempty_bar, (tile_iter & 1u) ^ 1u);          // epilogue drained the previous item
+        // ------------------------------ MMA issuer ------------------------------
+        constexpr uint32_t idesc = tc::make_idesc_i8(128, BKC, 1, 1);
+        constexpr uint32_t lay = (BKC == 128) ? 2u : (BKC == 64 ? 4u : 0u);
+        // shared-memory descriptors = constant | (address >> 4)
+        const uint64_t adc = tmax::make_desc(0u, 128 * 128, 1024, 2u);
+        const uint64_t bdc = BKC == 16 ? tmax::make_desc(0u, 128, 2048, 0u) : tmax::make_desc(0u, 128 * BKC, 8 * BKC, lay);
+        uint32_t n = 0, tile_iter = 0;
+        for (int item = blockIdx.x; item < p.items; item += gridDim.x, ++tile_iter) {
+            const DwItem it = decode_item<G>(p, item);
+            tc::mbar_wait(tempty_bar, (tile_iter & 1u) ^ 1u);          // epilogue drained the previous item
+            tc::tc_fence_after();
+            const uint32_t idesc_n = tc::make_idesc_i8(128, it.ng * 16, 1, 1);
+            for (int kb = it.kb0; kb < it.kb1; ++kb, ++n) {
+                const int s = n % C::STAGES; const uint32_t ph = (n / C::STAGES) & 1u;
+                tc::mbar_wait(&full_bar[s], ph);
                 tc::tc_fence_after();
-                for (int kb = it.kb0; kb < it.kb1; ++kb, ++n) {
-                    const int s = n % C::STAGES; const uint32_t ph = (n / C::STAGES) & 1u;
-                    tc::mbar_wait(&full_bar[s], ph);
-                    tc::tc_fence_after();
-                    const uint32_t a_base = tc::smem_u32(smem + s * C::STAGE);
+                const uint32_t a_base = tc::smem_u32(smem + s * C::STAGE);
+                const uint64_t ad0 = adc | (uint64_t)(a_base >> 4);
+                const uint64_t bd0 = bdc | (uint64_t)((a_base + C::A_BYTES) >> 4);
+                const uint32_t acc_on = (uint32_t)(kb != it.kb0);
+                if (tc::elect_one()) {
                     if (BKC == 16) {
                         // stem layers (<= 16 input channels): the ng tap tiles [128 pixels][16 B] sit back to back, i.e. one
                         // MN-major un-swizzled B operand of N = ng*16 columns: 16-byte column chunks SBO = 2048 B apart,
                         // 8-pixel K groups LBO = 128 B apart -> ONE MMA per K32 covers every tap of the group
-                        const uint32_t idesc_n = tc::make_idesc_i8(128, it.ng * 16, 1, 1);
-                        const uint32_t b_base = a_base + C::A_BYTES;
 #pragma unroll
-                        for (int kk = 0; kk < 4; ++kk) {
-                            const uint64_t ad = tmax::make_desc(a_base + kk * 32 * 128, 128 * 128, 1024, 2u);
-                            const uint64_t bd = tmax::make_desc(b_base + kk * 32 * 16, 128, 2048, 0u);
-                            tc::umma_i8(tmem_base, ad, bd, idesc_n, (uint32_t)((kb != it.kb0) || (kk != 0)));
-                        }
-                    } else
-                    for (int g = 0; g < it.ng; ++g) {
-                        const uint32_t b_base = a_base + C::A_BYTES + g * C::B_BYTES;
+                        for (int kk = 0; kk < 4; ++kk)
+                            tc::umma_i8(tmem_base, ad0 + (uint64_t)(kk * ((32 * 128) >> 4)), bd0 + (uint64_t)(kk * ((32 * 16) >> 4)), idesc_n,
+                                        kk == 0 ? acc_on : 1u);
+                    } else {
+                        for (int g = 0; g < it.ng; ++g) {
+                            const uint64_t bdg = bd0 + (uint64_t)(g * (C::B_BYTES >> 4));
 #pragma unroll
-                        for (int kk = 0; kk < 4; ++kk) {                     // 128 pixels = 4 x K32
-                            const uint64_t ad = tmax::make_desc(a_base + kk * 32 * 128, 128 * 128, 1024, 2u);
-                            const uint64_t bd = tmax::make_desc(b_base + kk * 32 * BKC, 128 * BKC, 8 * BKC, lay);
-                            tc::umma_i8(tmem_base + g * BKC, ad, bd, idesc, (uint32_t)((kb != it.kb0) || (kk != 0)));
+                            for (int kk = 0; kk < 4; ++kk)                     // 128 pixels = 4 x K32
+                                tc::umma_i8(tmem_base + g * BKC, ad0 + (uint64_t)(kk * ((32 * 128) >> 4)), bdg + (uint64_t)(kk * ((32 * BKC) >> 4)),
+                                            idesc, kk == 0 ? acc_on : 1u);
                         }
                     }
                     tc::umma_commit(&empty_bar[s]);
+                    if (kb == it.kb1 - 1) tc::umma_commit(tfull_bar);
                 }
-                tc::umma_commit(tfull_bar);
             }
         }
     } else {

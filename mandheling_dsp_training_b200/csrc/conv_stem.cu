@@ -86,63 +86,71 @@ stem_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
     niti_pdl_wait();                                         // programmatic dependent launch: see common.cuh
     const int my_tiles = (p.m_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
+    // issue loops: whole warp on uniform values, single-thread instructions under elect.sync (see conv_chain.cu)
     if (warp == 0) {
-        if (lane == 0) {
-            // ------------------------------ TMA producer ------------------------------
+        // ------------------------------ TMA producer ------------------------------
+        if (tc::elect_one()) {
             tmax::mbar_expect_tx(w_bar, (uint32_t)(p.taps * p.oc * 16));
             for (int t = 0; t < p.taps; ++t) tmax::load_2d(&mapB, tc::smem_u32(bsm + t * p.oc * 16), w_bar, t * 16, 0);
-            uint32_t n = 0;
-            for (int pass = 0; pass < 2; ++pass)
-                for (int i = 0; i < my_tiles; ++i) {
-                    const int m0 = ((int)blockIdx.x + i * (int)gridDim.x) * 128;
-                    const int q = m0 % p.out_w; const int t = m0 / p.out_w;
-                    const int pp = t % p.out_h; const int bn = t / p.out_h;
-                    const int bw = q * p.stride + p.lower_w, bh = pp * p.stride + p.lower_h;
-                    for (int kb = 0; kb < p.num_kb; ++kb, ++n) {
-                        const int s = n % kStemStages; const uint32_t ph = (n / kStemStages) & 1u;
-                        tc::mbar_wait(&empty_bar[s], ph ^ 1u);
-                        const int tap0 = kb * kTapsPerBlock, nt = min(kTapsPerBlock, p.taps - tap0);
+        }
+        uint32_t n = 0;
+        for (int pass = 0; pass < 2; ++pass)
+            for (int i = 0; i < my_tiles; ++i) {
+                const int m0 = ((int)blockIdx.x + i * (int)gridDim.x) * 128;
+                const int q = m0 % p.out_w; const int t = m0 / p.out_w;
+                const int pp = t % p.out_h; const int bn = t / p.out_h;
+                const int bw = q * p.stride + p.lower_w, bh = pp * p.stride + p.lower_h;
+                int kx = 0, ky = 0;
+                for (int kb = 0; kb < p.num_kb; ++kb, ++n) {
+                    const int s = n % kStemStages; const uint32_t ph = (n / kStemStages) & 1u;
+                    tc::mbar_wait(&empty_bar[s], ph ^ 1u);
+                    const int tap0 = kb * kTapsPerBlock, nt = min(kTapsPerBlock, p.taps - tap0);
+                    const uint32_t a_dst = tc::smem_u32(smem + s * STAGE);
+                    if (tc::elect_one()) {
                         tmax::mbar_expect_tx(&full_bar[s], (uint32_t)(nt * 2048));
-                        const uint32_t a_dst = tc::smem_u32(smem + s * STAGE);
+                        int kxx = kx, kyy = ky;
                         for (int g = 0; g < nt; ++g) {
-                            const int tap = tap0 + g, ky = tap / p.kw, kx = tap - ky * p.kw;
-                            if (p.rows_mode) tmax::load_3d(&mapA, a_dst + g * 2048, &full_bar[s], (kx + p.lower_w) * 2, pp + ky + p.lower_h, bn);
+                            if (p.rows_mode) tmax::load_3d(&mapA, a_dst + g * 2048, &full_bar[s], (kxx + p.lower_w) * 2, pp + kyy + p.lower_h, bn);
                             else tmax::load_im2col(&mapA, a_dst + g * 2048, &full_bar[s], 0, bw, bh, bn,
-                                                   (uint16_t)(kx * p.dil), (uint16_t)(ky * p.dil));
+                                                   (uint16_t)(kxx * p.dil), (uint16_t)(kyy * p.dil));
+                            if (++kxx == p.kw) { kxx = 0; ++kyy; }
                         }
                     }
+                    for (int g = 0; g < nt; ++g) if (++kx == p.kw) { kx = 0; ++ky; }
                 }
-        }
+            }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // ------------------------------ MMA issuer ------------------------------
-            const uint32_t idesc = tc::make_idesc_i8(128, p.oc, 0, 0);
-            const uint32_t b_lbo = (uint32_t)p.oc * 16u;
-            tc::mbar_wait(w_bar, 0);
-            tc::tc_fence_after();
-            uint32_t n = 0, tile_iter = 0;
-            for (int pass = 0; pass < 2; ++pass)
-                for (int i = 0; i < my_tiles; ++i, ++tile_iter) {
-                    const uint32_t a = tile_iter & 1u, aph = (tile_iter >> 1) & 1u;
-                    tc::mbar_wait(&tempty_bar[a], aph ^ 1u);
+        // ------------------------------ MMA issuer ------------------------------
+        const uint32_t idesc = tc::make_idesc_i8(128, p.oc, 0, 0);
+        const uint32_t b_lbo = (uint32_t)p.oc * 16u;
+        const uint64_t adc = tmax::make_desc(0u, 2048, 128, 0u);
+        const uint64_t bdc = tmax::make_desc(0u, b_lbo, 128, 0u);
+        tc::mbar_wait(w_bar, 0);
+        tc::tc_fence_after();
+        uint32_t n = 0, tile_iter = 0;
+        for (int pass = 0; pass < 2; ++pass)
+            for (int i = 0; i < my_tiles; ++i, ++tile_iter) {
+                const uint32_t a = tile_iter & 1u, aph = (tile_iter >> 1) & 1u;
+                tc::mbar_wait(&tempty_bar[a], aph ^ 1u);
+                tc::tc_fence_after();
+                const uint32_t d_tmem = tmem_base + a * accw;
+                for (int kb = 0; kb < p.num_kb; ++kb, ++n) {
+                    const int s = n % kStemStages; const uint32_t ph = (n / kStemStages) & 1u;
+                    tc::mbar_wait(&full_bar[s], ph);
                     tc::tc_fence_after();
-                    const uint32_t d_tmem = tmem_base + a * accw;
-                    for (int kb = 0; kb < p.num_kb; ++kb, ++n) {
-                        const int s = n % kStemStages; const uint32_t ph = (n / kStemStages) & 1u;
-                        tc::mbar_wait(&full_bar[s], ph);
-                        tc::tc_fence_after();
-                        const uint32_t a_base = tc::smem_u32(smem + s * STAGE);
-                        const int tap0 = kb * kTapsPerBlock, ntp = min(kTapsPerBlock, p.taps_p - tap0);     // even
-                        for (int j = 0; j < ntp / 2; ++j) {
-                            const uint64_t ad = tmax::make_desc(a_base + j * 4096, 2048, 128, 0u);
-                            const uint64_t bd = tmax::make_desc(tc::smem_u32(bsm) + (uint32_t)(tap0 + 2 * j) * b_lbo, b_lbo, 128, 0u);
-                            tc::umma_i8(d_tmem, ad, bd, idesc, (uint32_t)((kb | j) != 0));
-                        }
+                    const uint32_t a_base = tc::smem_u32(smem + s * STAGE);
+                    const int tap0 = kb * kTapsPerBlock, ntp = min(kTapsPerBlock, p.taps_p - tap0);     // even
+                    const uint64_t ad0 = adc | (uint64_t)(a_base >> 4);
+                    const uint64_t bd0 = bdc | (uint64_t)((tc::smem_u32(bsm) + (uint32_t)tap0 * b_lbo) >> 4);
+                    if (tc::elect_one()) {
+                        for (int j = 0; j < ntp / 2; ++j)
+                            tc::umma_i8(d_tmem, ad0 + (uint64_t)(j * (4096 >> 4)), bd0 + (uint64_t)(j * ((2u * b_lbo) >> 4)), idesc,
+                                        (uint32_t)((kb | j) != 0));
                         tc::umma_commit(&empty_bar[s]);
+                        if (kb == p.num_kb - 1) tc::umma_commit(&tfull_bar[a]);
                     }
-                    tc::umma_commit(&tfull_bar[a]);
                 }
-        }
+            }
     } else {
         // ------------------------------ epilogue (warps 2..17) ------------------------------
         // 16 warps: the rescale arithmetic (~15 integer instructions per output) needs the issue slots of a full SM, one

@@ -83,39 +83,48 @@ igemm_tma2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
     tc::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
+    // issue loops: whole warp on uniform values, single-thread instructions under elect.sync (see conv_chain.cu)
     if (warp == 0) {
-        if (lane == 0) {
-            // ------------------------------ TMA producer (both CTAs) ------------------------------
-            uint32_t it = 0;
-            for (int item = pair; item < p.items; item += num_pairs) {
-                const int n_t = item % p.n_tiles; const int rest = item / p.n_tiles;
-                const int sp = rest % p.splits;   const int m_t = rest / p.splits;
-                int m0 = m_t * 256 + (int)rank * 128;
-                if (m0 >= p.M) m0 = 0;            // fully out-of-range half: load valid rows, results are clipped / masked
-                const int nrow0 = n_t * BN + (int)rank * (BN / 2);
-                const int q = m0 % p.out_w; const int t = m0 / p.out_w;
-                const int pp = t % p.out_h; const int bn = t / p.out_h;
-                const int bw = q * p.stride + p.lower_w, bh = pp * p.stride + p.lower_h;
-                const int kb0 = sp * p.kb_per_split, kb1 = min(p.num_kb, kb0 + p.kb_per_split);
-                for (int kb = kb0; kb < kb1; ++kb, ++it) {
-                    const int s = it % C::STAGES; const uint32_t ph = (it / C::STAGES) & 1u;
-                    tc::mbar_wait(&empty_bar[s], ph ^ 1u);
-                    const uint32_t a_dst = tc::smem_u32(smem + s * C::STAGE);
-                    const uint32_t b_dst = a_dst + C::A_BYTES;
+        // ------------------------------ TMA producer (both CTAs) ------------------------------
+        uint32_t it = 0;
+        const int kx_first = p.flip ? (p.kw - 1) * p.dil : 0, kx_last = p.flip ? 0 : (p.kw - 1) * p.dil;
+        const int kstep = p.flip ? -p.dil : p.dil;
+        for (int item = pair; item < p.items; item += num_pairs) {
+            const int n_t = item % p.n_tiles; const int rest = item / p.n_tiles;
+            const int sp = rest % p.splits;   const int m_t = rest / p.splits;
+            int m0 = m_t * 256 + (int)rank * 128;
+            if (m0 >= p.M) m0 = 0;            // fully out-of-range half: load valid rows, results are clipped / masked
+            const int nrow0 = n_t * BN + (int)rank * (BN / 2);
+            const int q = m0 % p.out_w; const int t = m0 / p.out_w;
+            const int pp = t % p.out_h; const int bn = t / p.out_h;
+            const int bw = q * p.stride + p.lower_w, bh = pp * p.stride + p.lower_h;
+            const int kb0 = sp * p.kb_per_split, kb1 = min(p.num_kb, kb0 + p.kb_per_split);
+            // tap / channel-chunk walk without per-block divisions
+            const int tp0 = kb0 / p.cchunks; int cc = kb0 - tp0 * p.cchunks;
+            int ky = tp0 / p.kw, kx = tp0 - ky * p.kw;
+            if (p.flip) { ky = p.kh - 1 - ky; kx = p.kw - 1 - kx; }
+            ky *= p.dil; kx *= p.dil;
+            for (int kb = kb0; kb < kb1; ++kb, ++it) {
+                const int s = it % C::STAGES; const uint32_t ph = (it / C::STAGES) & 1u;
+                tc::mbar_wait(&empty_bar[s], ph ^ 1u);
+                const uint32_t a_dst = tc::smem_u32(smem + s * C::STAGE);
+                if (tc::elect_one()) {
                     if (rank == 0) mbar_expect_tx(&full_bar[s], 2u * (uint32_t)C::STAGE);
-                    const int tp = kb / p.cchunks, cc = kb - tp * p.cchunks;
-                    int ky = tp / p.kw, kx = tp - ky * p.kw;
-                    if (p.flip) { ky = p.kh - 1 - ky; kx = p.kw - 1 - kx; }
-                    tma2_load_im2col(&mapA, a_dst, &full_bar[s], cc * BKC, bw, bh, bn, (uint16_t)(kx * p.dil), (uint16_t)(ky * p.dil));
-                    tma2_load_2d(&mapB, b_dst, &full_bar[s], kb * BKC, nrow0);
+                    tma2_load_im2col(&mapA, a_dst, &full_bar[s], cc * BKC, bw, bh, bn, (uint16_t)kx, (uint16_t)ky);
+                    tma2_load_2d(&mapB, a_dst + C::A_BYTES, &full_bar[s], kb * BKC, nrow0);
+                }
+                if (++cc == p.cchunks) {
+                    cc = 0;
+                    if (kx == kx_last) { kx = kx_first; ky += kstep; } else kx += kstep;
                 }
             }
         }
     } else if (warp == 1) {
-        if (lane == 0 && rank == 0) {
+        if (rank == 0) {
             // ------------------------------ MMA issuer (leader CTA only) ------------------------------
             constexpr uint32_t idesc = tc::make_idesc_i8(256, BN, 0, 0);
             constexpr uint32_t lay = (BKC == 128) ? 2u : 4u;
+            const uint64_t dconst = make_desc2(0u, 16, 8 * BKC, lay);
             uint32_t it = 0, tile_iter = 0;
             for (int item = pair; item < p.items; item += num_pairs, ++tile_iter) {
                 const int rest = item / p.n_tiles; const int sp = rest % p.splits;
@@ -129,16 +138,16 @@ igemm_tma2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
                     tc::mbar_wait(&full_bar[s], ph);
                     tc::tc_fence_after();
                     const uint32_t a_base = tc::smem_u32(smem + s * C::STAGE);
-                    const uint32_t b_base = a_base + C::A_BYTES;
+                    const uint64_t ad = dconst | (uint64_t)(a_base >> 4);
+                    const uint64_t bd = dconst | (uint64_t)((a_base + C::A_BYTES) >> 4);
+                    if (tc::elect_one()) {
 #pragma unroll
-                    for (int kk = 0; kk < BKC / 32; ++kk) {
-                        const uint64_t ad = make_desc2(a_base + kk * 32, 16, 8 * BKC, lay);
-                        const uint64_t bd = make_desc2(b_base + kk * 32, 16, 8 * BKC, lay);
-                        umma2_i8(d_tmem, ad, bd, idesc, (uint32_t)((kb != kb0) || (kk != 0)));
+                        for (int kk = 0; kk < BKC / 32; ++kk)
+                            umma2_i8(d_tmem, ad + 2 * kk, bd + 2 * kk, idesc, (uint32_t)((kb != kb0) || (kk != 0)));
+                        umma2_commit_mc(&empty_bar[s], 3);       // frees this stage in both CTAs
+                        if (kb == kb1 - 1) umma2_commit_mc(&tfull_bar[a], 3);   // accumulator stage complete, both CTAs
                     }
-                    umma2_commit_mc(&empty_bar[s], 3);       // frees this stage in both CTAs
                 }
-                umma2_commit_mc(&tfull_bar[a], 3);           // accumulator stage complete, both CTAs
             }
         }
     } else {

@@ -72,12 +72,6 @@ template <int N> __device__ __forceinline__ void bulk_wait() { asm volatile("cp.
 __device__ __forceinline__ void prefetch_tmap2(const CUtensorMap* map) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
 }
-// one lane of the (converged) warp; the compiler recognises the ELECT predicate as a single-thread region
-__device__ __forceinline__ bool elect_one() {
-    uint32_t pred;
-    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
-    return pred != 0;
-}
 __device__ __forceinline__ uint64_t make_desc2(uint32_t addr, uint32_t lbo, uint32_t sbo, uint32_t layout) {
     uint64_t d = 0;
     d |= (uint64_t)((addr >> 4) & 0x3FFF);
