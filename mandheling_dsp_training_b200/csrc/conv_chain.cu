@@ -74,6 +74,7 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
 __device__ __forceinline__ uint32_t pack4c(int32_t a, int32_t b, int32_t c, int32_t d) {
     return (uint32_t)(a & 0xff) | ((uint32_t)(b & 0xff) << 8) | ((uint32_t)(c & 0xff) << 16) | ((uint32_t)(d & 0xff) << 24);
 }
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ uint4 ldg_u4(const int8_t* p) { return *reinterpret_cast<const uint4*>(p); }
 __device__ __forceinline__ uint4 vmax4(uint4 a, uint4 b) {
     return make_uint4(__vmaxs4(a.x, b.x), __vmaxs4(a.y, b.y), __vmaxs4(a.z, b.z), __vmaxs4(a.w, b.w));
@@ -242,6 +243,26 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
             int shift = 0, kind = 0;
             uint32_t mx = 0;
             const int hw = eoh * eow;
+            // dX: the store pass reads the forward tensor (ReLU gate, or the 2x2 windows of the pool gradient) row by row, a
+            // dependent global load per 16-column chunk.  Its addresses do not depend on the accumulators: prefetch those
+            // lines into L2 now, under the K loop (measured: the pool-gradient store pass was bound by that latency).
+            if (active && (epgx != nullptr || egate != nullptr)) {
+                for (int item = pair; item < eitems; item += epairs) {
+                    const int n_t = item % ent; const int m_t = item / ent;
+                    const int row = m_t * 256 + (int)rank * 128 + quarter * 32 + lane;
+                    if (row >= eM) continue;
+                    const int n0 = n_t * ebn;
+                    const int nlines = (min(ebn, eN - n0) + 127) >> 7;
+                    if (epgx != nullptr) {
+                        const int img = row / hw, r = row - img * hw, py = r / eow, px = r - py * eow, w2 = eow * 2;
+                        const int8_t* b00 = epgx + (((size_t)img * (eoh * 2) + 2 * py) * w2 + 2 * px) * eN + n0;
+                        for (int j = group; j < 4 * nlines; j += 4)
+                            prefetch_l2(b00 + (size_t)((j & 1) + ((j >> 1) & 1) * w2) * eN + (j >> 2) * 128);
+                    } else {
+                        for (int j = group; j < nlines; j += 4) prefetch_l2(egate + (size_t)row * eN + n0 + j * 128);
+                    }
+                }
+            }
             for (int pass = 0; pass < 2; ++pass) {
                 uint32_t tile_iter = 0;
                 if (active)
@@ -289,16 +310,7 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
                             continue;
                         }
                         uint32_t o[4];
-#pragma unroll
-                        for (int q = 0; q < 4; ++q) {
-                            int32_t r[4];
-#pragma unroll
-                            for (int k = 0; k < 4; ++k) {
-                                const int32_t x = (int32_t)v[4 * q + k];
-                                r[k] = kind == 0 ? niti_psto_fast(x, shift) : x;      // kind 0 has shift >= 2; kind 1: raw cast (Q3)
-                            }
-                            o[q] = pack4c(r[0], r[1], r[2], r[3]);
-                        }
+                        niti_rescale16(v, kind, shift, o);
                         if (erelu) { o[0] = __vmaxs4(o[0], 0u); o[1] = __vmaxs4(o[1], 0u); o[2] = __vmaxs4(o[2], 0u); o[3] = __vmaxs4(o[3], 0u); }
                         if (epgx == nullptr) {
                             const size_t off = (size_t)row * eN + col;

@@ -182,17 +182,8 @@ stem_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
                             }
                         } else if (row_ok) {
                             uint32_t o[4];
-#pragma unroll
-                            for (int q = 0; q < 4; ++q) {
-                                int32_t r[4];
-#pragma unroll
-                                for (int k = 0; k < 4; ++k) {
-                                    const int32_t x = (int32_t)v[4 * q + k];
-                                    r[k] = kind == 0 ? niti_psto_fast(x, shift) : x;  // kind 0 has shift >= 2; kind 1: raw cast (Q3)
-                                }
-                                o[q] = pack4s(r[0], r[1], r[2], r[3]);
-                                if (p.relu) o[q] = __vmaxs4(o[q], 0u);
-                            }
+                            niti_rescale16(v, kind, shift, o);
+                            if (p.relu) { o[0] = __vmaxs4(o[0], 0u); o[1] = __vmaxs4(o[1], 0u); o[2] = __vmaxs4(o[2], 0u); o[3] = __vmaxs4(o[3], 0u); }
                             *reinterpret_cast<uint4*>(p.y + (size_t)row * p.oc + c0) = make_uint4(o[0], o[1], o[2], o[3]);
                         }
                     }

@@ -544,16 +544,7 @@ igemm_fused_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
                         }
                     } else if (row_ok) {
                         uint32_t o[4];
-#pragma unroll
-                        for (int q = 0; q < 4; ++q) {
-                            int32_t r[4];
-#pragma unroll
-                            for (int k = 0; k < 4; ++k) {
-                                const int32_t x = (int32_t)v[4 * q + k];
-                                r[k] = kind == 0 ? niti_psto_fast(x, shift) : x;      // kind 0 has shift >= 2; kind 1: raw cast (Q3)
-                            }
-                            o[q] = pack4f(r[0], r[1], r[2], r[3]);
-                        }
+                        niti_rescale16(v, kind, shift, o);
                         const size_t off = (size_t)row * p.Ncols + n0 + c0;
                         if (e.relu) { o[0] = __vmaxs4(o[0], 0u); o[1] = __vmaxs4(o[1], 0u); o[2] = __vmaxs4(o[2], 0u); o[3] = __vmaxs4(o[3], 0u); }
                         if (e.gate != nullptr) {             // NITI_CPUReluGrad: pass where the forward value was > 0
