@@ -422,7 +422,9 @@ def main():
         "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "int8", "data": "synthetic",
         "config": {"workload": desc_text, "per_gpu_batch": batch, "global_batch": batch * world,
                    "parallelism": f"dp{world}", "launch": "cuda_graph" if use_graph else "eager",
-                   "dp_exchange": ("max|acc|: in-kernel NVLink peer-memory exchange; dW: bucketed NCCL all-reduce(SUM) overlapped with backward"
+                   "dp_exchange": (("max|acc|: in-kernel NVLink peer-memory exchange; dW: bucketed " +
+                                    ("two-shot sum over NVLink peer memory (niti_dp_allreduce_i32)" if getattr(net, "peer_sum", False)
+                                     else "NCCL all-reduce(SUM)") + " overlapped with backward")
                                    if net.peer_max else ("NCCL" if world > 1 else "none")),
                    "l2": "flushed between timed steps (256 MiB write)", "step_working_set_mib": round(ws_mb, 1),
                    "algorithmic_gop_per_step_per_gpu": net.algorithmic_ops() / 1e9},

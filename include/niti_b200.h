@@ -140,6 +140,22 @@ int niti_dp_error(niti_ctx*, int* out);
  * with world > 1 (NITI_B200_DP_RESERVE_SMS, default 16).  The collective library must be capped at no more CTAs than this
  * (NCCL_MAX_CTAS): with more, its CTAs wait for SMs held by kernels that are themselves waiting on a peer. */
 int niti_dp_reserved_sms(niti_ctx*);
+/* Gradient sum over ranks without a collective library.  The reference's dW contracts over the whole batch
+ * (NITI_GradientConv_Int8.cpp:218-268); with the batch sharded over g GPUs the int32 dW accumulators of all ranks are
+ * added before the shared exponent is taken.  The accumulators live in a library-allocated WINDOW that
+ * every peer maps over CUDA IPC; niti_dp_allreduce_i32 sums the words [off, off + n) of all ranks' windows in place in
+ * one launch (two-shot over NVLink peer loads/stores, ~niti_dp_reserved_sms CTAs, csrc/dp.cu dp_allreduce_kernel).
+ *   niti_dp_window_alloc    after niti_dp_connect: allocates `words` int32 (rounded up to 4), zeroed; returns the device
+ *                           pointer and its 64-byte IPC handle
+ *   niti_dp_window_connect  maps the peers' windows (handles = world x 64 bytes, rank-ordered)
+ *   niti_dp_allreduce_i32   off, n multiples of 4 words; slot in [0,64): every call of one step uses its own slot, the
+ *                           same slot on every rank; all ranks must issue the same calls in the same order.  The words
+ *                           must not be written on any rank between this call's launch there and its completion there.
+ *                           world 1: no-op.  A peer that never arrives sets the niti_dp_error flag. */
+int niti_dp_window_alloc(niti_ctx*, size_t words, int32_t** ptr_out, unsigned char handle_out[64]);
+int niti_dp_window_connect(niti_ctx*, const unsigned char* handles);
+int niti_dp_window_free(niti_ctx*);
+int niti_dp_allreduce_i32(niti_ctx*, size_t off, size_t n, int slot, niti_stream);
 /* *out != 0 when a grid-wide barrier of one of this context's persistent kernels gave up (see the concurrency rule at the
  * top): every result since the last clean poll is invalid.  Synchronises with the device. */
 int niti_sync_error(niti_ctx*, int* out);

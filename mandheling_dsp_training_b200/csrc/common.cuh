@@ -27,6 +27,7 @@ struct niti_ctx {
     // data-parallel scalar exchange over peer memory (dp.cuh); world <= 1 when not connected
     DpBuffer* dp_buf;
     DpView dp;
+    DpWindow dp_win;                  // gradient window of every rank (peer[rank] = the local one), or all null
     int dp_reserve;           // SMs left to the concurrent collective (dp.cu)
     // kernels whose dynamic shared memory limit was raised on THIS device (function attributes are per device)
     struct { const void* fn; int bytes; } smem_cfg[64];

@@ -7,6 +7,86 @@
 
 namespace {
 __global__ void dp_step_begin_kernel(DpBuffer* b) { b->epoch = b->epoch + 1u; }
+
+constexpr int kArThreads = 1024;
+
+__device__ __forceinline__ void ar_flag_store(unsigned long long* dst, uint32_t epoch) {
+    const unsigned long long w = (unsigned long long)epoch;
+    asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(dst), "l"(w) : "memory");
+}
+// spin until `src` (local memory, written by a peer) carries `epoch`; false when the budget ran out
+__device__ __forceinline__ bool ar_flag_wait(const unsigned long long* src, uint32_t epoch, long long timeout_cycles) {
+    const long long t0 = clock64();
+    for (;;) {
+        unsigned long long w;
+        asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(w) : "l"(src) : "memory");
+        if ((uint32_t)w == epoch) return true;
+        if (clock64() - t0 > timeout_cycles) return false;
+        __nanosleep(200);
+    }
+}
+__device__ __forceinline__ int4 ld_peer(const int4* p) {      // never from a stale L1 line: the words change every step
+    int4 v;
+    asm volatile("ld.volatile.global.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    return v;
+}
+
+// In-place SUM over ranks of the window words [off, off + n) — the reference's gradient is the sum over the whole batch
+// (NITI_GradientConv_Int8.cpp:218-268 contracts over every sample), so a batch sharded over g GPUs adds its int32 dW
+// accumulators before the shared exponent is taken.  Two-shot over NVLink peer memory in ONE launch:
+//   arrive   every rank tells every peer "my dW kernels for this bucket are done" (stream order on the sender)
+//   reduce   rank r owns slice r: loads it from all g windows (g-1 NVLink reads in flight per thread), adds, and
+//            stores the sum into all g windows (element i is read and written by its owner only: safe in place)
+//   complete the last CTA of a rank to finish tells every peer; the launch ends when every peer has told this rank, so
+//            whatever follows in the stream sees the complete sum.
+// Integer adds commute: bit-exact in any order.  ~16 CTAs on the SMs the contractions leave free (niti_dp_reserved_sms).
+template <int W>                                             // world rounded up to 2, 4 or 8: 8 / W vectors per thread and trip,
+__global__ void __launch_bounds__(kArThreads)                 // so eight 16-byte loads are in flight per thread at any world size
+dp_allreduce_kernel(const DpView v, const DpWindow w, size_t off, size_t n, int slot) {
+    __shared__ int last;
+    DpBuffer* mine = v.peer[v.rank];
+    const uint32_t epoch = *reinterpret_cast<volatile uint32_t*>(&mine->epoch);
+    const int tid = threadIdx.x;
+    if (blockIdx.x == 0 && tid < v.world) ar_flag_store(&v.peer[tid]->ar_in[slot][v.rank], epoch);
+    if (tid < v.world && tid != v.rank && !ar_flag_wait(&mine->ar_in[slot][tid], epoch, v.timeout_cycles)) mine->error = 1u;
+    __syncthreads();
+
+    constexpr int U = 8 / W;
+    const size_t nvec = n >> 2;                               // off and n are multiples of 4 words (host)
+    const size_t per = (nvec + v.world - 1) / v.world;
+    const size_t v0 = (size_t)v.rank * per, v1 = v0 + per < nvec ? v0 + per : nvec;
+    int4* win[W];
+#pragma unroll
+    for (int r = 0; r < W; ++r) win[r] = r < v.world ? reinterpret_cast<int4*>(w.peer[r] + off) : nullptr;
+    const size_t stride = (size_t)gridDim.x * kArThreads;
+    for (size_t i = v0 + (size_t)blockIdx.x * kArThreads + tid; i < v1; i += stride * U) {
+        int4 q[U][W];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+            for (int r = 0; r < W; ++r)
+                q[u][r] = (r < v.world && i + u * stride < v1) ? ld_peer(win[r] + i + u * stride) : make_int4(0, 0, 0, 0);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (i + u * stride >= v1) break;
+            int4 s = q[u][0];
+#pragma unroll
+            for (int r = 1; r < W; ++r) { s.x += q[u][r].x; s.y += q[u][r].y; s.z += q[u][r].z; s.w += q[u][r].w; }
+#pragma unroll
+            for (int r = 0; r < W; ++r) if (r < v.world) win[r][i + u * stride] = s;
+        }
+    }
+    __threadfence_system();                                   // this thread's peer stores are visible before the count below
+    __syncthreads();
+    if (tid == 0) last = atomicAdd(&mine->ar_count[slot], 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (last) {
+        __threadfence_system();
+        if (tid == 0) mine->ar_count[slot] = 0u;
+        if (tid < v.world) ar_flag_store(&v.peer[tid]->ar_out[slot][v.rank], epoch);
+        if (tid < v.world && tid != v.rank && !ar_flag_wait(&mine->ar_out[slot][tid], epoch, v.timeout_cycles)) mine->error = 1u;
+    }
+}
 }
 
 extern "C" int niti_dp_alloc(niti_ctx* ctx, unsigned char handle_out[64]) {
@@ -65,8 +145,73 @@ extern "C" int niti_dp_connect(niti_ctx* ctx, int rank, int world, const unsigne
     return NITI_OK;
 }
 
+// ---- gradient window: the int32 dW accumulators of the whole net live in library-allocated memory every peer maps ----
+extern "C" int niti_dp_window_alloc(niti_ctx* ctx, size_t words, int32_t** ptr_out, unsigned char handle_out[64]) {
+    if (!ctx || !ptr_out || !handle_out || words == 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_dp_window_alloc");
+    if (ctx->dp.world < 1 || !ctx->dp_buf) return niti_fail(ctx, NITI_ERR_ARG, "niti_dp_window_alloc: call niti_dp_connect first");
+    int32_t*& mine = ctx->dp_win.peer[ctx->dp.rank];
+    if (mine) return niti_fail(ctx, NITI_ERR_ARG, "niti_dp_window_alloc: a window exists (niti_dp_window_free first)");
+    words = (words + 3) & ~(size_t)3;
+    cudaError_t e = cudaMalloc(&mine, words * sizeof(int32_t));
+    if (e != cudaSuccess) { mine = nullptr; return niti_fail(ctx, NITI_ERR_CUDA, "niti_dp_window_alloc: cudaMalloc", e); }
+    cudaMemset(mine, 0, words * sizeof(int32_t));
+    cudaDeviceSynchronize();
+    cudaIpcMemHandle_t h;
+    e = cudaIpcGetMemHandle(&h, mine);
+    if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "niti_dp_window_alloc: cudaIpcGetMemHandle", e);
+    memcpy(handle_out, &h, 64);
+    ctx->dp_win.words = words;
+    *ptr_out = mine;
+    return NITI_OK;
+}
+
+extern "C" int niti_dp_window_connect(niti_ctx* ctx, const unsigned char* handles /* world x 64 */) {
+    if (!ctx || !handles || !ctx->dp_win.peer[ctx->dp.rank]) return niti_fail(ctx, NITI_ERR_ARG, "niti_dp_window_connect: no local window");
+    for (int r = 0; r < ctx->dp.world; ++r) {
+        if (r == ctx->dp.rank) continue;
+        cudaIpcMemHandle_t h;
+        memcpy(&h, handles + 64 * r, 64);
+        void* p = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "niti_dp_window_connect: cudaIpcOpenMemHandle", e);
+        ctx->dp_win.peer[r] = reinterpret_cast<int32_t*>(p);
+    }
+    return NITI_OK;
+}
+
+extern "C" int niti_dp_window_free(niti_ctx* ctx) {
+    if (!ctx) return NITI_ERR_ARG;
+    for (int r = 0; r < ctx->dp.world; ++r) {
+        if (!ctx->dp_win.peer[r]) continue;
+        if (r == ctx->dp.rank) cudaFree(ctx->dp_win.peer[r]); else cudaIpcCloseMemHandle(ctx->dp_win.peer[r]);
+    }
+    ctx->dp_win = DpWindow{};
+    return NITI_OK;
+}
+
+extern "C" int niti_dp_allreduce_i32(niti_ctx* ctx, size_t off, size_t n, int slot, niti_stream st) {
+    if (!ctx) return NITI_ERR_ARG;
+    if (ctx->dp.world <= 1) return NITI_OK;
+    if (slot < 0 || slot >= kDpArSlots || (off & 3) || (n & 3) || off + n > ctx->dp_win.words)
+        return niti_fail(ctx, NITI_ERR_ARG, "niti_dp_allreduce_i32: slot out of range, or range not 4-word aligned / outside the window");
+    for (int r = 0; r < ctx->dp.world; ++r)
+        if (!ctx->dp_win.peer[r]) return niti_fail(ctx, NITI_ERR_ARG, "niti_dp_allreduce_i32: window not connected");
+    if (n == 0) return NITI_OK;
+    int ctas = ctx->dp_reserve > 0 ? ctx->dp_reserve : 16;
+    if (const char* e = getenv("NITI_B200_DP_AR_CTAS")) { const int c = atoi(e); if (c >= 1 && c <= 148) ctas = c; }
+    const size_t per = ((n >> 2) + ctx->dp.world - 1) / ctx->dp.world;
+    const size_t need = (per + kArThreads - 1) / kArThreads;
+    if ((size_t)ctas > need) ctas = (int)(need ? need : 1);
+    const cudaStream_t cs = (cudaStream_t)st;
+    if (ctx->dp.world <= 2) dp_allreduce_kernel<2><<<ctas, kArThreads, 0, cs>>>(ctx->dp, ctx->dp_win, off, n, slot);
+    else if (ctx->dp.world <= 4) dp_allreduce_kernel<4><<<ctas, kArThreads, 0, cs>>>(ctx->dp, ctx->dp_win, off, n, slot);
+    else dp_allreduce_kernel<8><<<ctas, kArThreads, 0, cs>>>(ctx->dp, ctx->dp_win, off, n, slot);
+    return niti_check_launch(ctx, "dp_allreduce");
+}
+
 extern "C" int niti_dp_close(niti_ctx* ctx) {
     if (!ctx) return NITI_ERR_ARG;
+    niti_dp_window_free(ctx);
     for (int r = 0; r < ctx->dp.world; ++r)
         if (r != ctx->dp.rank && ctx->dp.peer[r]) cudaIpcCloseMemHandle(ctx->dp.peer[r]);
     ctx->dp = DpView{};

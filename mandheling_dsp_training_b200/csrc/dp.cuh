@@ -16,12 +16,24 @@
 
 constexpr int kDpMaxWorld = 8;
 constexpr int kDpSlots = 256;
+constexpr int kDpArSlots = 64;                        // gradient all-reduce calls per step (one per bucket)
 
 // layout of one rank's exchange buffer (device memory, cudaMalloc'ed so it can be exported with cudaIpcGetMemHandle)
 struct DpBuffer {
     unsigned long long word[kDpSlots][kDpMaxWorld];   // written by peers
     uint32_t epoch;                                   // local: current step number
     uint32_t error;                                   // local: set when a spin timed out (peer died)
+    // gradient all-reduce (dp.cu dp_allreduce_kernel): epoch-tagged arrival / completion flags written by peers, and the
+    // local count of CTAs that finished their share
+    unsigned long long ar_in[kDpArSlots][kDpMaxWorld];
+    unsigned long long ar_out[kDpArSlots][kDpMaxWorld];
+    uint32_t ar_count[kDpArSlots];
+};
+
+// every rank's gradient window (int32 words, cudaMalloc'ed and exported like the exchange buffer)
+struct DpWindow {
+    int32_t* peer[kDpMaxWorld];
+    size_t words;
 };
 
 struct DpView {                                       // passed by value to kernels

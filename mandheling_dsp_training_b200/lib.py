@@ -74,6 +74,10 @@ _SIGS = {
     "niti_dp_step_begin": (C.c_int, [_P, _P]),
     "niti_dp_error": (C.c_int, [_P, C.POINTER(C.c_int)]),
     "niti_dp_reserved_sms": (C.c_int, [_P]),
+    "niti_dp_window_alloc": (C.c_int, [_P, C.c_size_t, C.POINTER(_P), _P]),
+    "niti_dp_window_connect": (C.c_int, [_P, _P]),
+    "niti_dp_window_free": (C.c_int, [_P]),
+    "niti_dp_allreduce_i32": (C.c_int, [_P, C.c_size_t, C.c_size_t, C.c_int, _P]),
     "niti_sync_error": (C.c_int, [_P, C.POINTER(C.c_int)]),
     "niti_sgd_update": (C.c_int, [_P, _P, _P, C.c_size_t, _P]),
     "niti_conv_fwd": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, _P]),
@@ -274,6 +278,34 @@ class NitiB200:
         self._ck(self.lib.niti_dp_connect(self.h, rank, world, C.cast(buf, _P)))
         dist.barrier()
         self.dp_connected = True
+
+    def dp_window(self, dist, words):
+        """Allocate this rank's gradient window (int32 words, zeroed), map every peer's, and return the local one as a
+        torch tensor that aliases it (zero copy).  The dW accumulators of a data-parallel net live here so that
+        dp_allreduce can add them over NVLink peer memory (include/niti_b200.h niti_dp_allreduce_i32)."""
+        import torch
+        h = (C.c_ubyte * 64)()
+        ptr = _P()
+        self._ck(self.lib.niti_dp_window_alloc(self.h, words, C.byref(ptr), C.cast(h, _P)))
+        world = dist.get_world_size()
+        mine = torch.tensor(list(bytes(h)), dtype=torch.uint8, device=f"cuda:{self.device}")
+        allh = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allh, mine)
+        blob = b"".join(bytes(t.cpu().tolist()) for t in allh)
+        buf = (C.c_ubyte * len(blob)).from_buffer_copy(blob)
+        self._ck(self.lib.niti_dp_window_connect(self.h, C.cast(buf, _P)))
+        dist.barrier()
+        n = (words + 3) // 4 * 4
+
+        class _Window:                                   # the cudaMalloc'ed window as a CUDA array for torch.as_tensor
+            __cuda_array_interface__ = {"shape": (n,), "typestr": "<i4", "data": (ptr.value, False), "version": 3, "strides": None}
+        t = torch.as_tensor(_Window(), device=f"cuda:{self.device}")
+        assert t.data_ptr() == ptr.value and t.dtype == torch.int32
+        return t
+
+    def dp_allreduce(self, off, n, slot, stream=None):
+        """in-place SUM over ranks of window words [off, off + n) (multiples of 4); one slot per call site and step"""
+        self._ck(self.lib.niti_dp_allreduce_i32(self.h, off, n, slot, self._stream(stream)))
 
     def dp_reserved_sms(self):
         return self.lib.niti_dp_reserved_sms(self.h)

@@ -19,6 +19,7 @@ two reductions that span the batch are all-reduced between phase 1 and phase 2 o
 Integer sums and maxima are order-independent, so g devices reproduce the 1-device result exactly.
 """
 import contextlib
+import os
 
 import numpy as np
 import torch
@@ -192,6 +193,16 @@ class NitiNet:
                 self._buckets[L.index] = (L.dw_off, hi_end)
                 hi_end, size = L.dw_off, 0
         self._pending = []
+        # Gradient sum without a collective library: the accumulators move into a peer-mapped window and every bucket is
+        # added by one niti_dp_allreduce_i32 launch on a third stream (NCCL at 16 CTAs needed ~100 us per 9 MB bucket on
+        # 8 GPUs and left a 190 us tail exposed: profiles/timeline_r2_vgg_8gpu_nccl.txt).  NITI_B200_DP_ALLREDUCE=nccl
+        # keeps torch.distributed.all_reduce.
+        self.peer_sum = (self.peer_max and hasattr(nb, "dp_window") and self.dist.get_world_size() > 1
+                         and os.environ.get("NITI_B200_DP_ALLREDUCE", "peer") != "nccl")
+        if self.peer_sum:
+            self.dw_acc = nb.dp_window(self.dist, dw_total)
+            self.comm = torch.cuda.Stream(self.dev)
+            self._bucket_slot = {idx: k for k, idx in enumerate(sorted(self._buckets, reverse=True))}
         self.fused_ops = bool(fuse) and hasattr(nb, "conv_fwd_fused") and (self.dist is None or self.peer_max)
         # (acc, w, wt, max-abs slot, oc, taps, c, sub) per layer: the segments of the one-launch weight update
         self._upd_layers = [(self.dw_acc[L.dw_off: L.dw_off + L.n_w], L.w, L.wt,
@@ -398,7 +409,12 @@ class NitiNet:
                         self._timed("dw", L.ops, lambda: nb.conv_dw_acc(L.d, L.x, dy, acc_dw, None))
                     if self.dist is not None and L.index in self._buckets:
                         lo, hi = self._buckets[L.index]    # this bucket's dW sums are complete: start its exchange
-                        self._pending.append(self.dist.all_reduce(self.dw_acc[lo:hi], op=self.dist.ReduceOp.SUM, async_op=True))
+                        if self.peer_sum:
+                            self.comm.wait_stream(torch.cuda.current_stream(self.dev))
+                            with torch.cuda.stream(self.comm):
+                                nb.dp_allreduce(lo, (hi - lo + 3) // 4 * 4, self._bucket_slot[L.index])
+                        else:
+                            self._pending.append(self.dist.all_reduce(self.dw_acc[lo:hi], op=self.dist.ReduceOp.SUM, async_op=True))
                 if dx is not None:
                     slot = self.maxabs[nconv + L.index: nconv + L.index + 1]
                     if self.fused_ops:
@@ -438,6 +454,8 @@ class NitiNet:
         # gradient exchange (one bucket), then shared exponent + PSTO + int8 SGD, fused per layer
         if self.overlap_dw:
             torch.cuda.current_stream(self.dev).wait_stream(self.side)
+        if self.peer_sum:
+            torch.cuda.current_stream(self.dev).wait_stream(self.comm)
         for work in self._pending:
             work.wait()
         self._pending = []

@@ -26,7 +26,7 @@ def _data(seed, gbatch, chw):
     return x, rng.integers(0, 10, size=gbatch).astype(np.int32)
 
 
-def _worker(rank, world, port, out, case, timeout_ms):
+def _worker(rank, world, port, out, case, timeout_ms, allreduce="peer"):
     import torch.distributed as dist
     from mandheling_dsp_training_b200 import NitiB200, lib
     from mandheling_dsp_training_b200.step import NitiNet
@@ -34,6 +34,7 @@ def _worker(rank, world, port, out, case, timeout_ms):
     os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
     if timeout_ms:
         os.environ["NITI_B200_DP_TIMEOUT_MS"] = str(timeout_ms)
+    os.environ["NITI_B200_DP_ALLREDUCE"] = allreduce
     lib.dp_env()                                   # NCCL_MAX_CTAS <= the SMs the library leaves free (csrc/dp.cu)
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
@@ -41,6 +42,7 @@ def _worker(rank, world, port, out, case, timeout_ms):
     nb = NitiB200(rank)
     net = NitiNet(nb, spec, per, chw, device=rank, dist=dist)
     assert nb.dp_reserved_sms() >= int(os.environ["NCCL_MAX_CTAS"])
+    assert net.peer_sum == (allreduce == "peer")
     net.init_weights(seed=1)
     paths = set()
     err = 0
@@ -69,15 +71,16 @@ def _worker(rank, world, port, out, case, timeout_ms):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-@pytest.mark.parametrize("case", ["small", "fused3x3"])
-def test_nccl_data_parallel_bit_exact(tmp_path, case):
+@pytest.mark.parametrize("case,allreduce", [("small", "peer"), ("fused3x3", "peer"), ("small", "nccl")])
+def test_data_parallel_bit_exact(tmp_path, case, allreduce):
+    """gradient sum over NVLink peer memory (niti_dp_allreduce_i32, default) or NCCL; max|acc| always over peer memory"""
     import torch.multiprocessing as mp
     from mandheling_dsp_training_b200 import NitiB200
     from mandheling_dsp_training_b200.step import NitiNet
     spec, chw, gbatch, steps = CASES[case]
     world = 2
     out = str(tmp_path / "dp")
-    mp.spawn(_worker, args=(world, 29641 + (case != "small"), out, case, 0), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, 29641 + (case != "small") + 2 * (allreduce != "peer"), out, case, 0, allreduce), nprocs=world, join=True)
     nb = NitiB200(0)
     net = NitiNet(nb, spec, gbatch, chw, device=0)
     net.init_weights(seed=1)
@@ -122,3 +125,49 @@ def test_peer_exchange_timeout_is_reported(tmp_path):
     mp.spawn(_worker, args=(2, 29651, out, "small", 20), nprocs=2, join=True)
     z0 = np.load(out + ".0.npz")
     assert int(z0["err"]) == 1 and int(z0["raised"]) == 1
+
+
+def _ar_worker(rank, world, port, out):
+    import torch.distributed as dist
+    from mandheling_dsp_training_b200 import NitiB200, lib
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    lib.dp_env()
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    nb = NitiB200(rank)
+    nb.dp_connect(dist)
+    words = 3 * 1024 * 1024 + 8
+    win = nb.dp_window(dist, words)
+    ok = True
+    for step in range(3):
+        nb.dp_step_begin()
+        rng = np.random.default_rng(100 * step)                       # every rank can recompute every rank's words
+        parts = [rng.integers(-2 ** 28, 2 ** 28, size=words, dtype=np.int64).astype(np.int32) for _ in range(world)]
+        win.copy_(torch.from_numpy(parts[rank]))
+        torch.cuda.synchronize(); dist.barrier()
+        # three ranges, one slot each: tiny (fewer vectors than ranks x threads), ragged start, large
+        ranges = [(0, 8), (1024, 4 * 777), (8192, 3 * 1024 * 1024 - 8192)]
+        for slot, (off, n) in enumerate(ranges):
+            nb.dp_allreduce(off, n, slot)
+        torch.cuda.synchronize()
+        want = parts[rank].copy()
+        tot = np.sum(np.stack(parts).astype(np.int64), axis=0).astype(np.int32)
+        for off, n in ranges:
+            want[off:off + n] = tot[off:off + n]
+        ok = ok and np.array_equal(win.cpu().numpy(), want)
+        dist.barrier()
+    np.savez(out + f".{rank}.npz", ok=np.int32(ok), err=np.int32(nb.dp_error()))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_peer_allreduce_sums_the_window_ranges_in_place(tmp_path):
+    """niti_dp_allreduce_i32 on every visible GPU (2..8): ranges inside the window become the sum over ranks, the rest stays"""
+    import torch.multiprocessing as mp
+    world = min(torch.cuda.device_count(), 8)
+    out = str(tmp_path / "ar")
+    mp.spawn(_ar_worker, args=(world, 29661, out), nprocs=world, join=True)
+    for r in range(world):
+        z = np.load(out + f".{r}.npz")
+        assert int(z["ok"]) == 1 and int(z["err"]) == 0, r
