@@ -8,7 +8,7 @@
 namespace {
 __global__ void dp_step_begin_kernel(DpBuffer* b) { b->epoch = b->epoch + 1u; }
 
-constexpr int kArThreads = 1024;
+constexpr int kArMaxThreads = 1024;
 
 __device__ __forceinline__ void ar_flag_store(unsigned long long* dst, uint32_t epoch) {
     const unsigned long long w = (unsigned long long)epoch;
@@ -41,7 +41,7 @@ __device__ __forceinline__ int4 ld_peer(const int4* p) {      // never from a st
 //            whatever follows in the stream sees the complete sum.
 // Integer adds commute: bit-exact in any order.  ~16 CTAs on the SMs the contractions leave free (niti_dp_reserved_sms).
 template <int W>                                             // world rounded up to 2, 4 or 8: 8 / W vectors per thread and trip,
-__global__ void __launch_bounds__(kArThreads)                 // so eight 16-byte loads are in flight per thread at any world size
+__global__ void __launch_bounds__(kArMaxThreads)              // so eight 16-byte loads are in flight per thread at any world size
 dp_allreduce_kernel(const DpView v, const DpWindow w, size_t off, size_t n, int slot) {
     __shared__ int last;
     DpBuffer* mine = v.peer[v.rank];
@@ -58,8 +58,8 @@ dp_allreduce_kernel(const DpView v, const DpWindow w, size_t off, size_t n, int 
     int4* win[W];
 #pragma unroll
     for (int r = 0; r < W; ++r) win[r] = r < v.world ? reinterpret_cast<int4*>(w.peer[r] + off) : nullptr;
-    const size_t stride = (size_t)gridDim.x * kArThreads;
-    for (size_t i = v0 + (size_t)blockIdx.x * kArThreads + tid; i < v1; i += stride * U) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = v0 + (size_t)blockIdx.x * blockDim.x + tid; i < v1; i += stride * U) {
         int4 q[U][W];
 #pragma unroll
         for (int u = 0; u < U; ++u)
@@ -197,15 +197,18 @@ extern "C" int niti_dp_allreduce_i32(niti_ctx* ctx, size_t off, size_t n, int sl
     for (int r = 0; r < ctx->dp.world; ++r)
         if (!ctx->dp_win.peer[r]) return niti_fail(ctx, NITI_ERR_ARG, "niti_dp_allreduce_i32: window not connected");
     if (n == 0) return NITI_OK;
-    int ctas = ctx->dp_reserve > 0 ? ctx->dp_reserve : 16;
-    if (const char* e = getenv("NITI_B200_DP_AR_CTAS")) { const int c = atoi(e); if (c >= 1 && c <= 148) ctas = c; }
+    // shape of the launch: by default one 1024-thread CTA on each SM the contractions leave free; NITI_B200_DP_AR_CTAS /
+    // NITI_B200_DP_AR_THREADS override (small CTAs fit beside a resident contraction CTA: 8 K registers, no shared memory)
+    int ctas = ctx->dp_reserve > 0 ? ctx->dp_reserve : 16, threads = kArMaxThreads;
+    if (const char* e = getenv("NITI_B200_DP_AR_CTAS")) { const int c = atoi(e); if (c >= 1 && c <= 1024) ctas = c; }
+    if (const char* e = getenv("NITI_B200_DP_AR_THREADS")) { const int c = atoi(e); if (c >= 32 && c <= kArMaxThreads && c % 32 == 0) threads = c; }
     const size_t per = ((n >> 2) + ctx->dp.world - 1) / ctx->dp.world;
-    const size_t need = (per + kArThreads - 1) / kArThreads;
+    const size_t need = (per + threads - 1) / threads;
     if ((size_t)ctas > need) ctas = (int)(need ? need : 1);
     const cudaStream_t cs = (cudaStream_t)st;
-    if (ctx->dp.world <= 2) dp_allreduce_kernel<2><<<ctas, kArThreads, 0, cs>>>(ctx->dp, ctx->dp_win, off, n, slot);
-    else if (ctx->dp.world <= 4) dp_allreduce_kernel<4><<<ctas, kArThreads, 0, cs>>>(ctx->dp, ctx->dp_win, off, n, slot);
-    else dp_allreduce_kernel<8><<<ctas, kArThreads, 0, cs>>>(ctx->dp, ctx->dp_win, off, n, slot);
+    if (ctx->dp.world <= 2) dp_allreduce_kernel<2><<<ctas, threads, 0, cs>>>(ctx->dp, ctx->dp_win, off, n, slot);
+    else if (ctx->dp.world <= 4) dp_allreduce_kernel<4><<<ctas, threads, 0, cs>>>(ctx->dp, ctx->dp_win, off, n, slot);
+    else dp_allreduce_kernel<8><<<ctas, threads, 0, cs>>>(ctx->dp, ctx->dp_win, off, n, slot);
     return niti_check_launch(ctx, "dp_allreduce");
 }
 

@@ -142,8 +142,8 @@ def dp_env(reserve_sms=16):
     os.environ.setdefault("NITI_B200_DP_RESERVE_SMS", str(int(reserve_sms)))
     res = int(os.environ["NITI_B200_DP_RESERVE_SMS"])
     cap = os.environ.get("NCCL_MAX_CTAS")
-    if cap is None or not cap.isdigit() or int(cap) > res:
-        os.environ["NCCL_MAX_CTAS"] = str(res)
+    if cap is None or not cap.isdigit() or int(cap) > max(res, 1):
+        os.environ["NCCL_MAX_CTAS"] = str(max(res, 1))
 
 
 class NitiB200:
@@ -261,7 +261,8 @@ class NitiB200:
         not exceed the SMs the library leaves free, otherwise NCCL CTAs wait for SMs held by kernels spinning on a peer."""
         import torch
         reserve = int(os.environ.get("NITI_B200_DP_RESERVE_SMS", "16"))
-        if dist.get_backend() == "nccl" and dist.get_world_size() > 1:
+        nccl_sum = os.environ.get("NITI_B200_DP_ALLREDUCE", "peer") == "nccl"   # else NCCL never runs beside the contractions
+        if dist.get_backend() == "nccl" and dist.get_world_size() > 1 and nccl_sum:
             cap = os.environ.get("NCCL_MAX_CTAS")
             if cap is None or not cap.isdigit() or int(cap) > reserve or int(cap) < 1:
                 raise NitiError(f"data parallel needs NCCL_MAX_CTAS set (before the process group is created) to at most "
