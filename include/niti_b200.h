@@ -218,6 +218,14 @@ int niti_conv_dx_fused(niti_ctx*, const niti_conv_desc*, const int8_t* dy, const
 int niti_conv_fwd_fused_pool(niti_ctx*, const niti_conv_desc*, const int8_t* x, const int8_t* w, const int8_t* ex,
                              const int8_t* ew, int8_t* y, int8_t* ey, int relu, int8_t* y_pool, int32_t* acc, uint32_t* maxabs,
                              int dp_slot, niti_stream);
+/* Stem layer: the input is an image stored with d->c channels of which only the first c_live can be non-zero (the caller's
+ * guarantee — e.g. RGB padded to the 16-channel granule of the other kernels; w is [oc][kh][kw][d->c] as everywhere).  With
+ * c_live <= 4 the operand is assembled from one 4-byte word per pixel and tap (K = taps x 4 instead of taps x 16) and, when
+ * y_pool is given, the 2x2/2 max pool behind the conv is folded into the store (csrc/conv_stem2.cu).  Same results as
+ * niti_conv_fwd_fused[_pool], which it calls for every other shape.  y_pool may be NULL. */
+int niti_conv_stem_fwd(niti_ctx*, const niti_conv_desc*, int c_live, const int8_t* x, const int8_t* w, const int8_t* ex,
+                       const int8_t* ew, int8_t* y, int8_t* ey, int relu, int8_t* y_pool, int32_t* acc, uint32_t* maxabs,
+                       int dp_slot, niti_stream);
 /* niti_conv_dx_fused whose result is the gradient w.r.t. a 2x2/2 max-POOLED tensor, with the pool's gradient
  * (NITI_CPUPoolGrad_Int8.cpp:36-72: the first window element equal to the maximum takes it) and, when gate_relu != 0, the
  * ReLU gradient of the layer before the pool folded into the store: pool_x [n,2h,2w,c] is the pre-pool forward tensor,

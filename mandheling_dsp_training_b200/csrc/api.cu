@@ -36,6 +36,9 @@ int dw2_conv_dw_acc(niti_ctx*, const niti_conv_desc*, const int8_t*, const int8_
 
 // conv_stem.cu: single-launch forward op (conv + exponent + rescale) of <= 16-channel stem layers
 bool stem_fwd_eligible(const niti_conv_desc*);
+bool stem2_fwd_eligible(const niti_conv_desc*, int c_live, bool pool);
+int stem2_conv_fwd_fused(niti_ctx*, const niti_conv_desc*, const int8_t*, const int8_t*, const int8_t*, const int8_t*, int8_t*,
+                         int8_t*, int, int8_t*, uint32_t*, int, cudaStream_t);
 int stem_conv_fwd_fused(niti_ctx*, const niti_conv_desc*, const int8_t*, const int8_t*, const int8_t*, const int8_t*, int8_t*,
                         int8_t*, int, uint32_t*, int, cudaStream_t);
 
@@ -336,6 +339,20 @@ int niti_conv_fwd_fused_pool(niti_ctx* ctx, const niti_conv_desc* d, const int8_
     int rc = niti_conv_fwd_fused(ctx, d, x, w, ex, ew, y, ey, relu, acc, maxabs, dp_slot, st);
     if (rc) return rc;
     return niti_maxpool(ctx, y, d->n, oh, ow, d->oc, 2, 2, y_pool, st);
+}
+
+int niti_conv_stem_fwd(niti_ctx* ctx, const niti_conv_desc* d, int c_live, const int8_t* x, const int8_t* w, const int8_t* ex,
+                       const int8_t* ew, int8_t* y, int8_t* ey, int relu, int8_t* y_pool, int32_t* acc, uint32_t* maxabs,
+                       int dp_slot, niti_stream st) {
+    if (!ctx || !desc_ok(d) || !x || !w || !y || !maxabs) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_stem_fwd: bad argument");
+    if (dp_slot < 0 || dp_slot >= kDpSlots) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_stem_fwd: slot out of range");
+    if (c_live < 1 || c_live > d->c) return niti_fail(ctx, NITI_ERR_ARG, "niti_conv_stem_fwd: c_live outside [1, c]");
+    if ((ctx->path == NITI_PATH_AUTO || ctx->path == NITI_PATH_TMA2) && ctx->auto_tma2 && stem2_fwd_eligible(d, c_live, y_pool != nullptr)) {
+        ctx->last_path = "stem2";
+        return stem2_conv_fwd_fused(ctx, d, x, w, ex, ew, y, ey, relu, y_pool, maxabs, dp_slot, (cudaStream_t)st);
+    }
+    if (y_pool) return niti_conv_fwd_fused_pool(ctx, d, x, w, ex, ew, y, ey, relu, y_pool, acc, maxabs, dp_slot, st);
+    return niti_conv_fwd_fused(ctx, d, x, w, ex, ew, y, ey, relu, acc, maxabs, dp_slot, st);
 }
 
 int niti_conv_dx_fused_poolgrad(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* dy, const int8_t* w, const int8_t* wt,

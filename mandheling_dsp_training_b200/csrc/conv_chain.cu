@@ -71,9 +71,6 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
           "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
         : "r"(taddr) : "memory");
 }
-__device__ __forceinline__ uint32_t pack4c(int32_t a, int32_t b, int32_t c, int32_t d) {
-    return (uint32_t)(a & 0xff) | ((uint32_t)(b & 0xff) << 8) | ((uint32_t)(c & 0xff) << 16) | ((uint32_t)(d & 0xff) << 24);
-}
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ uint4 ldg_u4(const int8_t* p) { return *reinterpret_cast<const uint4*>(p); }
 __device__ __forceinline__ uint4 vmax4(uint4 a, uint4 b) {
@@ -272,7 +269,7 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
                     const int row = row0 + lane;
                     const int n0 = n_t * ebn;
                     if (pass == 0) {
-                        tc::mbar_wait(&tfull_bar[tile_iter], (tphase >> tile_iter) & 1u);
+                        tc::mbar_wait_backoff(&tfull_bar[tile_iter], (tphase >> tile_iter) & 1u);
                         tc::tc_fence_after();
                         if (etid == 0 && tile_iter == 0) chain_trace(a.trace, l, 2);
                     }
@@ -310,8 +307,7 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
                             continue;
                         }
                         uint32_t o[4];
-                        niti_rescale16(v, kind, shift, o);
-                        if (erelu) { o[0] = __vmaxs4(o[0], 0u); o[1] = __vmaxs4(o[1], 0u); o[2] = __vmaxs4(o[2], 0u); o[3] = __vmaxs4(o[3], 0u); }
+                        niti_rescale16(v, kind, shift, o, erelu != 0);
                         if (epgx == nullptr) {
                             const size_t off = (size_t)row * eN + col;
                             if (row_ok) {

@@ -35,9 +35,6 @@ struct StemParams {
     unsigned long long* tl;
 };
 
-__device__ __forceinline__ uint32_t pack4s(int32_t a, int32_t b, int32_t c, int32_t d) {
-    return (uint32_t)(a & 0xff) | ((uint32_t)(b & 0xff) << 8) | ((uint32_t)(c & 0xff) << 16) | ((uint32_t)(d & 0xff) << 24);
-}
 
 __device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t (&r)[16]) {
     asm volatile(
@@ -182,8 +179,7 @@ stem_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant_
                             }
                         } else if (row_ok) {
                             uint32_t o[4];
-                            niti_rescale16(v, kind, shift, o);
-                            if (p.relu) { o[0] = __vmaxs4(o[0], 0u); o[1] = __vmaxs4(o[1], 0u); o[2] = __vmaxs4(o[2], 0u); o[3] = __vmaxs4(o[3], 0u); }
+                            niti_rescale16(v, kind, shift, o, p.relu != 0);
                             *reinterpret_cast<uint4*>(p.y + (size_t)row * p.oc + c0) = make_uint4(o[0], o[1], o[2], o[3]);
                         }
                     }

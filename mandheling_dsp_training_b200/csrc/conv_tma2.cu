@@ -426,9 +426,6 @@ __device__ __forceinline__ void tmem_ld_x16(uint32_t taddr, uint32_t (&r)[16]) {
           "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
         : "r"(taddr) : "memory");
 }
-__device__ __forceinline__ uint32_t pack4f(int32_t a, int32_t b, int32_t c, int32_t d) {
-    return (uint32_t)(a & 0xff) | ((uint32_t)(b & 0xff) << 8) | ((uint32_t)(c & 0xff) << 16) | ((uint32_t)(d & 0xff) << 24);
-}
 
 template <int BN, int BKC>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kFusedThreads, 1)

@@ -85,6 +85,7 @@ _SIGS = {
     "niti_conv_dx_fused": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, _P, C.c_int, _P]),
     "niti_conv_fwd_fused_pool": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, C.c_int, _P, _P, _P, C.c_int, _P]),
     "niti_conv_dx_fused_poolgrad": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P, C.c_int, _P, _P, _P, C.c_int, _P]),
+    "niti_conv_stem_fwd": (C.c_int, [_P, C.POINTER(ConvDesc), C.c_int, _P, _P, _P, _P, _P, _P, C.c_int, _P, _P, _P, C.c_int, _P]),
     "niti_chain_op_eligible": (C.c_int, [_P, C.POINTER(ChainOp)]),
     "niti_chain_create": (C.c_int, [_P, _P, C.c_int, C.POINTER(_P)]),
     "niti_chain_run": (C.c_int, [_P, _P, _P]),
@@ -366,6 +367,12 @@ class NitiB200:
         self._ck(self.lib.niti_conv_fwd_fused_pool(self.h, C.byref(d), _ptr(x), _ptr(w), _ptr(ex), _ptr(ew), _ptr(y), _ptr(ey),
                                                    int(bool(relu)), _ptr(y_pool), _ptr(acc), _ptr(maxabs), int(dp_slot),
                                                    self._stream(stream)))
+
+    def conv_stem_fwd(self, d, c_live, x, w, ex, ew, y, ey, relu, y_pool, acc, maxabs, dp_slot=0, stream=None):
+        """stem layer (image input, only the first c_live channels of x can be non-zero) + ReLU (+ 2x2/2 max pool -> y_pool)"""
+        self._ck(self.lib.niti_conv_stem_fwd(self.h, C.byref(d), int(c_live), _ptr(x), _ptr(w), _ptr(ex), _ptr(ew), _ptr(y), _ptr(ey),
+                                             int(bool(relu)), _ptr(y_pool) if y_pool is not None else None, _ptr(acc), _ptr(maxabs),
+                                             int(dp_slot), self._stream(stream)))
 
     def conv_dx_fused_poolgrad(self, d, dy, w, wt, dx_prepool, pool_x, gate_relu, dx_pooled, acc, maxabs, dp_slot=0, stream=None):
         """dX op + max-pool gradient (+ ReLU gate) of the pool in front of this conv: writes the gradient w.r.t. pool_x"""

@@ -358,7 +358,12 @@ class NitiNet:
                 if self.fused_ops:
                     # whole op (conv + exponent + rescale + ReLU [+ max pool]) behind one call: one launch for stem layers
                     # (conv_stem.cu) and whenever the output tiles fit in tensor memory (conv_chain.cu)
-                    if L.pool_op is not None:
+                    if L.index == 0 and L.c_real <= 4 and hasattr(nb, "conv_stem_fwd"):
+                        # image layer: channels >= c_real of x_in are zero padding (set_input), conv_stem2.cu packs the live ones
+                        self._timed("fwd", L.ops, lambda: nb.conv_stem_fwd(L.d, L.c_real, L.x, L.w, L.ex, L.ew, L.y, L.ey, L.relu,
+                                                                          L.pool_op.y if L.pool_op is not None else None,
+                                                                          self.acc, slot, dp_slot=L.index))
+                    elif L.pool_op is not None:
                         self._timed("fwd", L.ops, lambda: nb.conv_fwd_fused_pool(L.d, L.x, L.w, L.ex, L.ew, L.y, L.ey, L.relu,
                                                                                 L.pool_op.y, self.acc, slot, dp_slot=L.index))
                     else:

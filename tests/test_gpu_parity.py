@@ -572,6 +572,43 @@ def test_conv_fwd_fused_pool_vs_oracle(nb, oracle, cfg):
     assert int(ey.item()) == want_e
 
 
+# (n, c_live, h, oc, k, stride, pad, pool)
+STEM2_SHAPES = [(8, 3, 32, 64, 3, 1, 1, True), (5, 3, 16, 32, 3, 1, 1, True), (3, 1, 28, 16, 5, 1, 2, False), (3, 1, 28, 16, 5, 1, 2, True),
+                (4, 3, 32, 64, 7, 2, 3, True), (2, 4, 12, 128, 3, 1, 1, False), (7, 2, 20, 48, 3, 1, 0, False)]
+
+
+@pytest.mark.parametrize("cfg", STEM2_SHAPES)
+def test_conv_stem_fwd_vs_oracle(nb, oracle, cfg):
+    """niti_conv_stem_fwd: image tensor stored with 16 channels of which c_live are real; conv + ReLU (+ 2x2/2 pool) against
+    the oracle on the c_live-channel problem.  28x28 + pool takes the unfused route (28 % 16 != 0), the others conv_stem2.cu."""
+    import torch
+    from tests.gpu_util import to_desc, dev, nhwc, nchw
+    n, cl, hw, oc, k, stride, pad, pool = cfg
+    s = shape(n, cl, hw, hw, oc, k, stride=stride, pad=pad)
+    rng = np.random.default_rng(hw * oc + cl)
+    x = _rand(rng, (n, cl, hw, hw)); w = _rand(rng, (oc, cl, k, k), -60, 60)
+    want_y, want_e, _ = oracle.conv_fwd(s, x, w, -7, -6)
+    want_y = oracle.relu(want_y)
+    oh = want_y.shape[2]
+    i8 = dict(dtype=torch.int8, device="cuda:0")
+    x16 = torch.zeros((n, hw, hw, 16), **i8); x16[..., :cl] = dev(nhwc(x))
+    w16 = torch.zeros((oc, k, k, 16), **i8); w16[..., :cl] = dev(nhwc(w))
+    w16[..., cl:] = 5                                   # dead channels of w meet zeros of x: must not matter
+    s16 = shape(n, 16, hw, hw, oc, k, stride=stride, pad=pad)
+    y = torch.full((n, oh, oh, oc), 99, **i8)
+    yp = torch.full((n, oh // 2, oh // 2, oc), 99, **i8) if pool else None
+    ey = torch.zeros(1, **i8); mx = torch.zeros(1, dtype=torch.int32, device="cuda:0")
+    acc = torch.empty(y.numel(), dtype=torch.int32, device="cuda:0")
+    nb.conv_stem_fwd(to_desc(s16), cl, x16, w16, torch.full((1,), -7, **i8), torch.full((1,), -6, **i8), y, ey, True, yp, acc, mx)
+    torch.cuda.synchronize()
+    assert np.array_equal(nchw(y.cpu().numpy()), want_y)
+    assert int(ey.item()) == want_e
+    if pool:
+        assert np.array_equal(nchw(yp.cpu().numpy()), oracle.maxpool(want_y, 2, 2))
+    if cl <= 4 and oc <= 128 and (not pool or oh % 16 == 0):
+        assert nb.last_path == "stem2"
+
+
 @pytest.mark.parametrize("cfg", POOL_SHAPES)
 @pytest.mark.parametrize("gate", [True, False])
 def test_conv_dx_fused_poolgrad_vs_oracle(nb, oracle, cfg, gate):
