@@ -285,6 +285,17 @@ int niti_loss_grad(niti_ctx*, const int8_t* logits, const int8_t* ascale, const 
 int niti_loss_grad_strided(niti_ctx*, const int8_t* logits, const int8_t* ascale, const int32_t* labels,
                            int batch, int classes, int stride, int8_t* grad, niti_stream);
 
+/* one-hot int32 targets [batch][classes] (the form NITI_CPULossGrad_Int8 receives, :148,170-178) -> class indices */
+int niti_onehot_labels(niti_ctx*, const int32_t* onehot, int batch, int classes, int32_t* labels, niti_stream);
+/* int8 Binary op with the reference's clip to +-127 (CPUBinary.cpp:246-330, BinaryUtils.hpp:276-299): op 0 ADD, 1 SUB, 2 MUL;
+ * broadcast -1: element-wise over n, 0: a is one element, 1: b is one element */
+int niti_binary_i8(niti_ctx*, int op, const int8_t* a, const int8_t* b, size_t n, int broadcast, int8_t* out, niti_stream);
+/* NITI_CPULeftPoolGrad_Int8.cpp:19-52 (zero insertion in front of a strided conv's dX): tensors as [slabs][h][w][4] blocks
+ * (NC4HW4, slabs = batch * ceil(c/4)); out(y, x) = in(y / sy, x / sx) where sy | y and sx | x, else 0 */
+int niti_zero_insert_c4(niti_ctx*, const int8_t* in, int slabs, int ih, int iw, int oh, int ow, int sy, int sx, int8_t* out, niti_stream);
+/* NITI_Pad_Int8.cpp:26-66: planes = batch * channels of [h][w] (NCHW); each plane lands at (pad, pad) of a zeroed [oh][ow] */
+int niti_pad2d(niti_ctx*, const int8_t* in, int planes, int ih, int iw, int pad, int oh, int ow, int8_t* out, niti_stream);
+
 /* ---- layout conversion at the boundary ----------------------------------------------------- */
 int niti_nchw_to_nhwc(niti_ctx*, const int8_t* src, int n, int c, int h, int w, int8_t* dst, niti_stream);
 int niti_nhwc_to_nchw(niti_ctx*, const int8_t* src, int n, int c, int h, int w, int8_t* dst, niti_stream);

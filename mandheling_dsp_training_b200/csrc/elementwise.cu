@@ -289,6 +289,49 @@ __global__ void __launch_bounds__(kThreads) gather_kernel(const int8_t* __restri
 }
 } // namespace
 
+// int8 Binary ADD / SUB / MUL with the result clipped to +-127 (BinaryUtils.hpp:276-299 niti_execute, NITI_int8_clip);
+// bc: -1 element-wise, 0: a is one element, 1: b is one element
+__global__ void __launch_bounds__(kThreads) binary_i8_kernel(int op, const int8_t* __restrict__ a, const int8_t* __restrict__ b,
+                                                             size_t n, int bc, int8_t* __restrict__ out) {
+    for (size_t i = (size_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (size_t)gridDim.x * kThreads) {
+        const int32_t x = (int32_t)a[bc == 0 ? 0 : i], y = (int32_t)b[bc == 1 ? 0 : i];
+        const int32_t r = op == 0 ? x + y : (op == 1 ? x - y : x * y);
+        out[i] = (int8_t)(r > 127 ? 127 : (r < -127 ? -127 : r));
+    }
+}
+
+// NITI_CPULeftPoolGrad_Int8.cpp:19-52: zero insertion, [slab][h][w][4] blocks: out(y, x) = in(y/sy, x/sx) when both divide
+__global__ void __launch_bounds__(kThreads) zero_insert_kernel(const uint32_t* __restrict__ in, int slabs, int ih, int iw, int oh, int ow,
+                                                               int sy, int sx, uint32_t* __restrict__ out) {
+    const size_t n = (size_t)slabs * oh * ow;
+    for (size_t i = (size_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (size_t)gridDim.x * kThreads) {
+        const int x = (int)(i % ow); const size_t t = i / ow;
+        const int y = (int)(t % oh); const size_t z = t / oh;
+        out[i] = (y % sy == 0 && x % sx == 0) ? in[(z * ih + y / sy) * iw + x / sx] : 0u;
+    }
+}
+
+// NITI_Pad_Int8.cpp:26-66: every [h][w] plane copied into the middle of a zeroed [oh][ow] plane (rows pad..oh-pad-1, from column pad)
+__global__ void __launch_bounds__(kThreads) pad2d_kernel(const int8_t* __restrict__ in, int planes, int ih, int iw, int pad, int oh, int ow,
+                                                         int8_t* __restrict__ out) {
+    const size_t n = (size_t)planes * oh * ow;
+    for (size_t i = (size_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (size_t)gridDim.x * kThreads) {
+        const int x = (int)(i % ow); const size_t t = i / ow;
+        const int y = (int)(t % oh); const size_t pl = t / oh;
+        const bool in_rows = y >= pad && y < oh - pad, in_cols = x >= pad && x < pad + iw;
+        out[i] = (in_rows && in_cols) ? in[(pl * ih + (y - pad)) * iw + (x - pad)] : (int8_t)0;
+    }
+}
+
+// one-hot int32 targets [batch][classes] -> class index: the first j with target == 1 (NITI_CPULossGrad_Int8.cpp:170-178)
+__global__ void onehot_labels_kernel(const int32_t* __restrict__ onehot, int batch, int classes, int32_t* __restrict__ labels) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= batch) return;
+    int lab = 0;
+    for (int j = 0; j < classes; ++j) if (onehot[(size_t)i * classes + j] == 1) { lab = j; break; }
+    labels[i] = lab;
+}
+
 extern "C" int niti_relu(niti_ctx* ctx, const int8_t* x, int8_t* y, size_t n, niti_stream st) {
     if (!ctx || (n && (!x || !y))) return niti_fail(ctx, NITI_ERR_ARG, "niti_relu");
     if (!n) return NITI_OK;
@@ -365,6 +408,40 @@ int niti_maxpool_grad_from_x(niti_ctx* ctx, const int8_t* x, const int8_t* dy, i
     if (le != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "launch maxpool_grad_vec", le);
     return niti_check_launch(ctx, "maxpool_grad_vec");
 }
+extern "C" int niti_binary_i8(niti_ctx* ctx, int op, const int8_t* a, const int8_t* b, size_t n, int broadcast, int8_t* out, niti_stream st) {
+    if (!ctx || !a || !b || !out || op < 0 || op > 2 || broadcast < -1 || broadcast > 1) return niti_fail(ctx, NITI_ERR_ARG, "niti_binary_i8: bad argument");
+    if (n == 0) return NITI_OK;
+    const size_t blocks = (n + kThreads - 1) / kThreads;
+    binary_i8_kernel<<<(unsigned)(blocks < 4096 ? blocks : 4096), kThreads, 0, (cudaStream_t)st>>>(op, a, b, n, broadcast, out);
+    return niti_check_launch(ctx, "binary_i8");
+}
+
+extern "C" int niti_zero_insert_c4(niti_ctx* ctx, const int8_t* in, int slabs, int ih, int iw, int oh, int ow, int sy, int sx,
+                                   int8_t* out, niti_stream st) {
+    if (!ctx || !in || !out || slabs <= 0 || ih <= 0 || iw <= 0 || oh <= 0 || ow <= 0 || sy <= 0 || sx <= 0)
+        return niti_fail(ctx, NITI_ERR_ARG, "niti_zero_insert_c4: bad argument");
+    if ((oh - 1) / sy >= ih || (ow - 1) / sx >= iw) return niti_fail(ctx, NITI_ERR_ARG, "niti_zero_insert_c4: input smaller than the strided output needs");
+    if ((reinterpret_cast<uintptr_t>(in) & 3u) || (reinterpret_cast<uintptr_t>(out) & 3u)) return niti_fail(ctx, NITI_ERR_ARG, "niti_zero_insert_c4: 4-byte alignment");
+    const size_t n = (size_t)slabs * oh * ow, blocks = (n + kThreads - 1) / kThreads;
+    zero_insert_kernel<<<(unsigned)(blocks < 4096 ? blocks : 4096), kThreads, 0, (cudaStream_t)st>>>(
+        reinterpret_cast<const uint32_t*>(in), slabs, ih, iw, oh, ow, sy, sx, reinterpret_cast<uint32_t*>(out));
+    return niti_check_launch(ctx, "zero_insert");
+}
+
+extern "C" int niti_pad2d(niti_ctx* ctx, const int8_t* in, int planes, int ih, int iw, int pad, int oh, int ow, int8_t* out, niti_stream st) {
+    if (!ctx || !in || !out || planes <= 0 || ih <= 0 || iw <= 0 || pad < 0 || oh - 2 * pad > ih || oh - 2 * pad < 0 || ow < iw + pad)
+        return niti_fail(ctx, NITI_ERR_ARG, "niti_pad2d: bad argument");
+    const size_t n = (size_t)planes * oh * ow, blocks = (n + kThreads - 1) / kThreads;
+    pad2d_kernel<<<(unsigned)(blocks < 4096 ? blocks : 4096), kThreads, 0, (cudaStream_t)st>>>(in, planes, ih, iw, pad, oh, ow, out);
+    return niti_check_launch(ctx, "pad2d");
+}
+
+extern "C" int niti_onehot_labels(niti_ctx* ctx, const int32_t* onehot, int batch, int classes, int32_t* labels, niti_stream st) {
+    if (!ctx || !onehot || !labels || batch <= 0 || classes <= 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_onehot_labels: bad argument");
+    onehot_labels_kernel<<<(batch + 127) / 128, 128, 0, (cudaStream_t)st>>>(onehot, batch, classes, labels);
+    return niti_check_launch(ctx, "onehot_labels");
+}
+
 extern "C" int niti_nchw_to_nhwc(niti_ctx* ctx, const int8_t* src, int n, int c, int h, int w, int8_t* dst, niti_stream st) {
     if (!ctx || !src || !dst || n <= 0 || c <= 0 || h <= 0 || w <= 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_nchw_to_nhwc");
     permute_kernel<<<grid_for(ctx, (size_t)n * c * h * w), kThreads, 0, (cudaStream_t)st>>>(

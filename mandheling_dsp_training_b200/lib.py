@@ -103,6 +103,10 @@ _SIGS = {
     "niti_maxpool_grad": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
     "niti_maxpool_grad_gated": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, C.c_int, _P]),
     "niti_loss_grad": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, _P, _P]),
+    "niti_onehot_labels": (C.c_int, [_P, _P, C.c_int, C.c_int, _P, _P]),
+    "niti_binary_i8": (C.c_int, [_P, C.c_int, _P, _P, C.c_size_t, C.c_int, _P, _P]),
+    "niti_zero_insert_c4": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
+    "niti_pad2d": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
     "niti_nchw_to_nhwc": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
     "niti_nhwc_to_nchw": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
     "niti_nc4hw4_to_nhwc": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),

@@ -1,4 +1,5 @@
 // B200Backend.cpp — Runtime / Backend plumbing of the B200 NITI plug-in (see B200Backend.hpp).
+#include <map>
 #include "B200Backend.hpp"
 #include <cstdio>
 #include <cstdlib>
@@ -136,7 +137,14 @@ Execution* B200Backend::onCreate(const std::vector<Tensor*>& inputs, const std::
     if (iter == map->end()) {
         return nullptr;        // the executor retries on its CPU backup backend (express/Executor.cpp:521-529)
     }
-    return iter->second->onCreate(inputs, outputs, op, this);
+    Execution* e = iter->second->onCreate(inputs, outputs, op, this);
+    if (e != nullptr) createdCounts()[(int)op->type()] += 1;      // evidence hook: which op types really got a B200 Execution
+    return e;
+}
+
+std::map<int, long long>& createdCounts() {
+    static std::map<int, long long> counts;
+    return counts;
 }
 
 void B200Backend::onExecuteBegin() const {

@@ -66,6 +66,11 @@ const NitiB200Api& nitiApi() {
     NITI_BIND(relu_grad, niti_relu_grad)
     NITI_BIND(maxpool, niti_maxpool)
     NITI_BIND(maxpool_grad, niti_maxpool_grad)
+    NITI_BIND(loss_grad, niti_loss_grad)
+    NITI_BIND(onehot_labels, niti_onehot_labels)
+    NITI_BIND(binary_i8, niti_binary_i8)
+    NITI_BIND(zero_insert_c4, niti_zero_insert_c4)
+    NITI_BIND(pad2d, niti_pad2d)
     NITI_BIND(gather_i8, niti_gather_i8)
     NITI_BIND(nc4hw4_to_nhwc, niti_nc4hw4_to_nhwc)
     NITI_BIND(nhwc_to_nc4hw4, niti_nhwc_to_nc4hw4)

@@ -30,6 +30,11 @@ struct NitiB200Api {
     decltype(&niti_relu_grad)         relu_grad         = nullptr;
     decltype(&niti_maxpool)           maxpool           = nullptr;
     decltype(&niti_maxpool_grad)      maxpool_grad      = nullptr;
+    decltype(&niti_loss_grad)         loss_grad         = nullptr;
+    decltype(&niti_onehot_labels)     onehot_labels     = nullptr;
+    decltype(&niti_binary_i8)         binary_i8         = nullptr;
+    decltype(&niti_zero_insert_c4)    zero_insert_c4    = nullptr;
+    decltype(&niti_pad2d)             pad2d             = nullptr;
     decltype(&niti_gather_i8)         gather_i8         = nullptr;
     decltype(&niti_nc4hw4_to_nhwc)    nc4hw4_to_nhwc    = nullptr;
     decltype(&niti_nhwc_to_nc4hw4)    nhwc_to_nc4hw4    = nullptr;

@@ -29,4 +29,10 @@ int MNNNitiB200Registered() { return MNN::B200::gRegistered ? 1 : 0; }
 int MNNNitiB200ForwardType() { return (int)MNN_FORWARD_B200; }
 // CUDA kernels launched so far by the live B200 runtime (tests use it to prove the ops ran on the device)
 long long MNNNitiB200LaunchCount() { return MNN::B200::launchCountOfLastRuntime(); }
+// Executions the B200 backend created for this op type so far (0: every op of that type went to the CPU backup backend)
+long long MNNNitiB200CreatedOps(int opType) {
+    auto& m = MNN::B200::createdCounts();
+    auto it = m.find(opType);
+    return it == m.end() ? 0 : it->second;
+}
 }

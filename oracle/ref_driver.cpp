@@ -128,7 +128,8 @@ int ref_maxpool_grad(const int8_t* x, const int8_t* dy, int n, int c, int h, int
     auto xv = _Convert(constI8(x, {n, c, h, w}), NC4HW4);
     auto res = _NITI_Maxpool_Int8(xv, _Scalar<int8_t>(0), {k, k}, {st, st});
     auto info = res[0]->getInfo();
-    auto dyv = _Convert(constI8(dy, {n, c, info->dim[2], info->dim[3]}), NC4HW4);
+    // the pool's output (and so its gradient) is NHWC in the reference's graphs (express/NeuralNetWorkOp.cpp:1911)
+    auto dyv = _Convert(constI8(dy, {n, c, info->dim[1], info->dim[2]}), NHWC);
     auto rule = OpGrad::get(OpType_NITI_Maxpool_Int8);
     if (!rule) return -2;
     auto grads = rule->onGrad(res[0]->expr().first, {dyv, nullptr});

@@ -67,6 +67,15 @@ def evaluate(ref, tag, out, steps, batch):
     out[f"{tag}_relu"] = ref.relu(a)
     out[f"{tag}_relu_grad"] = ref.relu_grad(a, g)
     out[f"{tag}_maxpool"] = ref.maxpool(a, 2, 2)
+    # f1 / f2 rows: pool gradient (non-overlapping and overlapping windows, many ties), int8 Binary SUB (the SGD update), loss gradient
+    gp = rng.integers(-127, 128, size=(4, 8, 4, 4), dtype=np.int8)
+    out[f"{tag}_pool_grad"] = ref.maxpool_grad(a, gp, 2, 2)
+    at = rng.integers(-2, 3, size=(3, 12, 9, 9), dtype=np.int8)
+    out[f"{tag}_pool_grad_k3s2"] = ref.maxpool_grad(at, rng.integers(-127, 128, size=(3, 12, 4, 4), dtype=np.int8), 3, 2)
+    out[f"{tag}_binary_sub"] = ref.sgd_update(rng.integers(-127, 128, size=5000, dtype=np.int8), rng.integers(-127, 128, size=5000, dtype=np.int8))
+    for j, asc in enumerate((-3, -9, 1)):
+        lg = rng.integers(-127, 128, size=(64, 12), dtype=np.int8)
+        out[f"{tag}_loss_grad{j}"] = ref.loss_grad(lg, asc, rng.integers(0, 10, size=64))
     rng = np.random.default_rng(1)
     ws = [xavier_int8(rng, oc, ic, k) for oc, ic, k in [(20, 1, 5), (52, 20, 5), (500, 832, 1), (12, 500, 1)]]
     rng = np.random.default_rng(0)
@@ -143,6 +152,10 @@ def main():
     before = plug.MNNNitiB200LaunchCount()
     evaluate(ref, "b200", out, steps, batch)
     out["launches"] = np.int64(plug.MNNNitiB200LaunchCount() - before)
+    plug.MNNNitiB200CreatedOps.restype = ctypes.c_longlong
+    # Executions the plug-in created per op type (schema/current/MNN_generated.h OpType values)
+    for name, code in (("binary", 7), ("pool_grad", 706), ("loss_grad", 711), ("pad", 714), ("left_pool_grad", 718)):
+        out[f"created_{name}"] = np.int64(plug.MNNNitiB200CreatedOps(code))
     np.savez(dst, **{k: (v if v is not None else np.zeros(0, np.int8)) for k, v in out.items()})
     same = [k[4:] for k in out if k.startswith("cpu_") and not k.endswith("_ms") and out[k] is not None
             and np.array_equal(out[k], out["b200_" + k[4:]])]

@@ -53,8 +53,15 @@ def test_matmul_and_gradient_split_conv_identical(res):
 
 
 def test_elementwise_ops_identical(res):
-    for k in ("relu", "relu_grad", "maxpool"):
+    for k in ("relu", "relu_grad", "maxpool", "pool_grad", "pool_grad_k3s2", "binary_sub", "loss_grad0", "loss_grad1", "loss_grad2"):
         assert np.array_equal(res["cpu_" + k], res["b200_" + k]), k
+
+
+def test_step_glue_ops_get_b200_executions(res):
+    """pool gradient, zero insertion (stride-2 dX), pad, loss gradient and the int8 Binary op of the
+    SGD update are created on the B200 backend, not on the executor's CPU backup backend"""
+    for k in ("binary", "pool_grad", "loss_grad", "pad", "left_pool_grad"):
+        assert int(res["created_" + k]) > 0, k
 
 
 def test_lenet_training_steps_identical(res):

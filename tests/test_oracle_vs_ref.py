@@ -91,3 +91,26 @@ def test_live_reference_gradient_split_conv(oracle, ref, cfg):
     dw, slices = oracle.conv_dw_split(s, x, dy)
     assert np.array_equal(dw, ref.grad_conv(s, x, dy, split=True))
     assert np.array_equal(oracle.conv_dw(s, x, dy)[0], ref.grad_conv(s, x, dy, split=False))
+
+
+@pytest.mark.parametrize("shp,k,s", [((4, 8, 8, 8), 2, 2), ((2, 16, 6, 6), 2, 2), ((3, 12, 9, 9), 3, 2), ((2, 20, 24, 24), 2, 2)])
+def test_live_reference_step_glue_ops(oracle, ref, shp, k, s):
+    """SURVEY.md section 8 f1/f2 against the unmodified reference: ReLU / ReLU-grad, max pool and its gradient (ties and
+    overlapping windows: the first maximum in row-major order takes the gradient, contributions wrap in int8), the int8
+    Binary SUB of the SGD update (clip to +-127) and the integer softmax-cross-entropy gradient."""
+    rng = np.random.default_rng(shp[1] * 100 + k)
+    x = rng.integers(-3, 4, size=shp, dtype=np.int8)
+    oh = (shp[2] - k) // s + 1
+    dy = rng.integers(-127, 128, size=(shp[0], shp[1], oh, oh), dtype=np.int8)
+    g = rng.integers(-127, 128, size=shp, dtype=np.int8)
+    assert np.array_equal(ref.relu(x), oracle.relu(x))
+    assert np.array_equal(ref.relu_grad(x, g), oracle.relu_grad(x, g))
+    y = oracle.maxpool(x, k, s)
+    assert np.array_equal(ref.maxpool(x, k, s), y)
+    assert np.array_equal(ref.maxpool_grad(x, dy, k, s), oracle.maxpool_grad(x, y, dy, k, s))
+    w = rng.integers(-127, 128, size=4096, dtype=np.int8); dw = rng.integers(-127, 128, size=4096, dtype=np.int8)
+    assert np.array_equal(ref.sgd_update(w, dw), oracle.sgd_update(w, dw))
+    for asc in (-9, -3, 1):
+        lg = rng.integers(-127, 128, size=(32, 12), dtype=np.int8)
+        lab = rng.integers(0, 10, size=32)
+        assert np.array_equal(ref.loss_grad(lg, asc, lab), oracle.loss_grad(lg, asc, lab))
