@@ -45,6 +45,9 @@ def parse():
                     help="weak: the workload's batch PER GPU; strong: the workload's batch is the GLOBAL batch, split over the GPUs")
     ap.add_argument("--no-dp-check", action="store_true", help="skip the data-parallel correctness witness (world > 1)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--via", default="cabi", choices=["cabi", "mnn"],
+                    help="mnn (workload lenet only): the reference's own training loop on its CPU backend and on the B200 MNN plug-in "
+                         "(BASELINE.json configs 1 and 2), timed by the reference's clock in one torch-free subprocess")
     ap.add_argument("--no-graph", action="store_true", help="launch eagerly instead of replaying a CUDA graph")
     return ap.parse_args()
 
@@ -213,8 +216,45 @@ class ClockSampler(threading.Thread):
                 "reasons": reasons, "samples": len(busy), "samples_total": len(self.samples)}
 
 
+def run_via_mnn(args):
+    """configs 1/2: MNIST NITIInt8 model, batch 64, the unmodified reference graph with the B200 plug-in as its backend.  The
+    plug-in copies every graph input host->device and every output device->host itself, so this is an end-to-end number."""
+    import subprocess
+    if args.workload != "lenet":
+        raise SystemExit("--via mnn measures the reference's MNIST model: use --workload lenet")
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    here = os.path.dirname(os.path.abspath(__file__))
+    batch = args.batch or WORKLOADS["lenet"][1]
+    steps = max(4, min(args.steps, 50))
+    p = subprocess.run([sys.executable, os.path.join(here, "tools", "mnn_lenet_bench.py"), str(steps), str(batch)],
+                       capture_output=True, text=True, timeout=1200)
+    lines = [l for l in p.stdout.splitlines() if l.startswith("{")]
+    if p.returncode != 0 or not lines:
+        raise SystemExit(f"mnn_lenet_bench failed ({p.returncode}):\n{p.stdout[-1500:]}\n{p.stderr[-1500:]}")
+    r = json.loads(lines[-1])
+    value = batch / (r["b200_ms_per_step"] * 1e-3)
+    print(json.dumps({
+        "metric": "int8_train_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": 1, "steps": r["steps"] - 1, "warmup": 1,
+        "ms_per_step": r["b200_ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8",
+        "data": "synthetic", "via": "mnn",
+        "config": {"workload": "MNIST NITIInt8 model (demo/mnistTrain.cpp:131-181), 1x28x28 synthetic, batch %d" % batch,
+                   "per_gpu_batch": batch, "global_batch": batch, "parallelism": "dp1",
+                   "launch": "reference Executor (express graph rebuilt per step, one Execution per op) on MNN_FORWARD_USER_0"},
+        "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": batch * 28 * 28 + batch * 10 * 4,
+                "d2h_bytes_per_step": batch * 12 + 4, "note": "host tensors in, loss out, copies made by the plug-in's onCopyBuffer"},
+        "gpu_launches": int(r["launches_per_step"] * (r["steps"] - 1)), "launches_per_step": r["launches_per_step"],
+        "identical_to_cpu_backend": r["identical"],
+        "cpu_baseline": {"value": batch / (r["cpu_ms_per_step"] * 1e-3), "unit": "samples/s", "cores": r["threads"], "kind": "reference",
+                         "sample": "the same %d steps of the same model on the reference's CPU backend, same process" % (r["steps"] - 1),
+                         "ms_per_step": r["cpu_ms_per_step"]},
+        "roofline": None}))
+
+
 def main():
     args = parse()
+    if args.via == "mnn":
+        return run_via_mnn(args)
     if args.impl == "reference":
         return run_reference_arm(args)
 

@@ -188,15 +188,14 @@ public:
         }
         auto code = runAll(mPre, "operand gather");
         if (code != NO_ERROR) return code;
+        // contraction + max|acc| + shared exponent + PSTO behind ONE call: a single launch wherever the output tiles fit in
+        // tensor memory (csrc/conv_chain.cu), the two-phase route through mAcc otherwise — same bytes either way
         int rc = a.zero_u32(ctx, mMax, 1, st);
-        if (rc == NITI_OK) rc = a.conv_fwd_acc(ctx, &mDesc, mX, mW, mAcc, mMax, st);
-        if (rc != NITI_OK) return check(rc, "niti_conv_fwd_acc");
-        if (mDeconv) {
-            rc = a.rescale_act(ctx, mAcc, mOutCount, mMax, mY, nullptr, nullptr, nullptr, st);
-        } else {
-            rc = a.rescale_act(ctx, mAcc, mOutCount, mMax, mY, dev(inputs[2]), dev(inputs[3]), dev(outputs[1]), st);
+        if (rc == NITI_OK) {
+            if (mDeconv) rc = a.conv_fwd_fused(ctx, &mDesc, mX, mW, nullptr, nullptr, mY, nullptr, 0, mAcc, mMax, 0, st);
+            else rc = a.conv_fwd_fused(ctx, &mDesc, mX, mW, dev(inputs[2]), dev(inputs[3]), mY, dev(outputs[1]), 0, mAcc, mMax, 0, st);
         }
-        if (rc != NITI_OK) return check(rc, "niti_rescale_act");
+        if (rc != NITI_OK) return check(rc, "niti_conv_fwd_fused");
         return runAll(mPost, "result gather");
     }
 

@@ -52,6 +52,7 @@ const NitiB200Api& nitiApi() {
     NITI_BIND(ctx_destroy, niti_ctx_destroy)
     NITI_BIND(last_error, niti_last_error)
     NITI_BIND(conv_fwd_acc, niti_conv_fwd_acc)
+    NITI_BIND(conv_fwd_fused, niti_conv_fwd_fused)
     NITI_BIND(conv_dx_acc, niti_conv_dx_acc)
     NITI_BIND(conv_dw_acc, niti_conv_dw_acc)
     NITI_BIND(matmul_nt_acc, niti_matmul_nt_acc)

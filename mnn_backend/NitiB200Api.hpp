@@ -16,6 +16,7 @@ struct NitiB200Api {
     decltype(&niti_ctx_destroy)       ctx_destroy       = nullptr;
     decltype(&niti_last_error)        last_error        = nullptr;
     decltype(&niti_conv_fwd_acc)      conv_fwd_acc      = nullptr;
+    decltype(&niti_conv_fwd_fused)    conv_fwd_fused    = nullptr;
     decltype(&niti_conv_dx_acc)       conv_dx_acc       = nullptr;
     decltype(&niti_conv_dw_acc)       conv_dw_acc       = nullptr;
     decltype(&niti_matmul_nt_acc)     matmul_nt_acc     = nullptr;

@@ -93,3 +93,40 @@ def test_dsp_named_op_types_dispatch_and_match_the_dsp_restatement(res_dsp):
             assert int(res[f"dsp_conv{kind}_{i}"]) == 1, (kind, i)
         for kind in (2, 3, 4, 5, 6, 7):         # 6 = DSP_MATMUL_GRADIENT (north-star op), 7 = DSP_MATMUL
             assert int(res[f"dsp_dw{kind}_{i}"]) == 1, (kind, i)
+
+
+def _write_idx(path, magic, dims, data):
+    with open(path, "wb") as f:
+        f.write(int(magic).to_bytes(4, "big"))
+        for d in dims:
+            f.write(int(d).to_bytes(4, "big"))
+        f.write(data.tobytes())
+
+
+DEMO = os.path.join(ROOT, "oracle", "_ref", "runTrainDemo.out")
+PRELOAD = os.path.join(ROOT, "mnn_backend", "libMNN_niti_b200_preload.so")
+
+
+@pytest.mark.skipif(not os.path.exists(DEMO) or not os.path.exists(PRELOAD), reason="demo binary or preload shim not built")
+def test_unmodified_demo_binary_trains_on_the_plugin_through_the_preload_shim(tmp_path):
+    """`LD_PRELOAD=libMNN_niti_b200_preload.so MNN_NITI_B200_AS_DEFAULT=1 runTrainDemo.out NITIInt8Train dir`
+    — the reference's shipped demo binary (built from its own sources, oracle/Makefile.ref) on synthetic MNIST-format files.
+    It runs 50 epochs; a few seconds of it are enough: the shim announced the switch, iterations report finite losses."""
+    rng = np.random.default_rng(0)
+    d = tmp_path / "mnist"; d.mkdir()
+    _write_idx(d / "train-images-idx3-ubyte", 2051, (60000, 28, 28), rng.integers(0, 256, size=(60000, 28, 28), dtype=np.uint8))
+    _write_idx(d / "train-labels-idx1-ubyte", 2049, (60000,), rng.integers(0, 10, size=60000, dtype=np.uint8))
+    _write_idx(d / "t10k-images-idx3-ubyte", 2051, (10000, 28, 28), rng.integers(0, 256, size=(10000, 28, 28), dtype=np.uint8))
+    _write_idx(d / "t10k-labels-idx1-ubyte", 2049, (10000,), rng.integers(0, 10, size=10000, dtype=np.uint8))
+    cwd = tmp_path / "cwd"; cwd.mkdir()
+    for name in ("DSP.txt", "parallel.txt"):                 # the mode files the reference reads from its working directory
+        (cwd / name).write_text("2\n" if name == "DSP.txt" else "0\n")
+    p = subprocess.Popen(["timeout", "-s", "INT", "25", "env", "LD_PRELOAD=" + PRELOAD, "MNN_NITI_B200_AS_DEFAULT=1",
+                          DEMO, "NITIInt8Train", str(d) + "/"], cwd=str(cwd),
+                         stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    out, err = p.communicate(timeout=120)
+    print(out[-1500:]); print(err[-1500:])
+    assert "MNN_FORWARD_CPU -> MNN_FORWARD_USER_0" in err, "the shim did not redirect the demo's executor config"
+    losses = [float(l.split("loss:")[1].split()[0]) for l in out.splitlines() if "loss:" in l]
+    assert len(losses) >= 5, f"only {len(losses)} iterations reported"
+    assert all(np.isfinite(v) for v in losses)
