@@ -439,7 +439,7 @@ def main():
             traffic = json.load(open(tpath)).get(args.workload)
         except Exception:
             traffic = None
-    roofline = {"bound": "tensor", "kernel": "igemm_fused_kernel / dw2_kernel / stem_fwd_kernel (TMA im2col + tcgen05 kind::i8 implicit GEMM). fwd and dX launches are whole ops: contraction + max|acc| + grid barrier + rescale to int8 in the timed launch; dW includes its split-K clear",
+    roofline = {"bound": "tensor", "kernel": "chain_kernel (layer-walking fwd chain and dX) / dw2_kernel / stem2_fwd_kernel (TMA im2col + tcgen05 kind::i8 implicit GEMM). fwd and dX launches are whole ops: contraction + max|acc| + grid barrier + rescale to int8 (+ ReLU, pool / pool-grad) in the timed launch",
                 "achieved": achieved, "peak": peak_tops, "unit": "TOP/s",
                 "frac": (achieved / peak_tops) if peak_tops else None, "traffic": traffic,
                 "peak_source": peak_src, "launches_timed": tc_n,
@@ -477,6 +477,9 @@ def main():
         "cpu_baseline": cpu_baseline,
         "dp_check": dp_check,
         "tensor_frac_of_step": (net.algorithmic_ops() / (total_ms / args.steps * 1e-3) / 1e12 / peak_tops) if peak_tops else None,
+        # fused kernels store with the exponent predicted from the previous step and re-store on a miss (conv_chain.cu);
+        # counted over the whole run (warm-up, timed, e2e and per-kernel passes): the stored values never depend on it
+        "exponent_prediction": dict(zip(("hits", "misses", "not_speculated"), nb.speculate_stats())) if hasattr(nb, "speculate_stats") else None,
     }
     print(json.dumps(line), flush=True)
     if world > 1:

@@ -64,10 +64,21 @@ int         niti_ctx_create(int device, niti_ctx** out);
 int         niti_ctx_destroy(niti_ctx* ctx);
 const char* niti_last_error(niti_ctx* ctx);
 int         niti_set_path(niti_ctx* ctx, int path);
+/* Exponent prediction of the fused forward / dX kernels.  mode 0: off; 1: adaptive (default; NITI_B200_SPECULATE sets it at
+ * creation); 2: always.  NITI's shared exponent needs max|acc| of the whole output tensor before anything can be stored.
+ * With prediction, a fused kernel stores in the same sweep that reduces the maximum, using the shift the same tensor (same
+ * dp_slot) had the last time it was computed, and re-stores (stem layer: recomputes) only when the true maximum lands in
+ * another bit width.  Adaptive = speculate when a miss is cheap (several tiles per CTA pair, stem layer) or the slot's last
+ * predictions held.  The stored int8 values and the exponent are those of the true maximum in every mode (tests compare the
+ * modes bit for bit). */
+int         niti_set_speculate(niti_ctx* ctx, int mode);
+/* predictions that held / missed / layers that did not speculate, since the context was created (synchronises the device;
+ * skipped may be NULL) */
+int         niti_speculate_stats(niti_ctx* ctx, unsigned long long* hits, unsigned long long* misses, unsigned long long* skipped);
 int         niti_version(void);
 /* kernels launched through this context since creation (bench.py's gpu_launches evidence) */
 int64_t     niti_launch_count(niti_ctx* ctx);
-/* name of the kernel family the last conv/matmul call used: "simt", "tc", "tma", "tma2", "fused" or "stem" */
+/* name of the kernel family the last conv/matmul call used: "simt", "tc", "tma", "tma2", "fused", "chain", "stem" or "stem2" */
 const char* niti_last_path(niti_ctx* ctx);
 
 /* ---- phase 1: int32 accumulators + running max|acc| ---------------------------------------
@@ -326,8 +337,8 @@ int niti_conv_fwd_host(niti_ctx*, const niti_conv_desc*, const int8_t* x_nhwc, c
 
 /* ---- probes ------------------------------------------------------------------------------- */
 /* phase trace for kernel development: when device_buf != NULL the fused kernels write %globaltimer (ns) stamps to
- * device_buf[block * 8 + phase] (phases: 0 entry, 1 set-up done, 2 first tile accumulated, 3 max pass done, 4 grid barrier
- * passed, 5 rescale + store done, 6 exit); device_buf must hold 8 words per CTA of the largest grid.  NULL disables. */
+ * device_buf[block * 8 + phase] (phases: 0 entry, 1 set-up done, 2 first tile accumulated, 3 max (+ predicted store) sweep done,
+ * 4 grid barrier passed, 5 re-store done (prediction missed; else = 4), 6 next layer released, 7 exit); device_buf must hold 8 words per CTA of the largest grid.  NULL disables. */
 int niti_debug_trace(niti_ctx*, unsigned long long* device_buf);
 /* launch timeline for kernel development: while device_buf != NULL every instrumented launch issued through this context
  * takes the next record {first CTA entry, last CTA exit} (%globaltimer ns; the caller presets records to {~0, 0}) — records are

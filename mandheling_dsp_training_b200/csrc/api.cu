@@ -170,9 +170,15 @@ int niti_ctx_create(int device, niti_ctx** out) {
         delete ctx;
         return NITI_ERR_UNSUPPORTED;
     }
-    e = cudaMalloc(&ctx->ws_u32, 64 * sizeof(uint32_t));
+    e = cudaMalloc(&ctx->ws_u32, (64 + 2 * kDpSlots + 4) * sizeof(uint32_t));
     if (e != cudaSuccess) { delete ctx; return NITI_ERR_CUDA; }
-    cudaMemset(ctx->ws_u32, 0, 64 * sizeof(uint32_t));
+    cudaMemset(ctx->ws_u32, 0, (64 + 2 * kDpSlots + 4) * sizeof(uint32_t));
+    ctx->pred = ctx->ws_u32 + 64;
+    const char* dwc = getenv("NITI_B200_DW_CTAS");        // CTAs a dW launch may spread its split-K over (default: every SM)
+    ctx->dw_ctas = dwc ? atoi(dwc) : 0;
+    const char* sp = getenv("NITI_B200_SPECULATE");        // 0: two-sweep schedule (max pass | barrier | store pass) for A/B runs
+    ctx->speculate = sp ? atoi(sp) : 1;
+    if (ctx->speculate < 0 || ctx->speculate > 2) ctx->speculate = 1;
     *out = ctx;
     return NITI_OK;
 }
@@ -193,6 +199,20 @@ const char* niti_last_error(niti_ctx* ctx) { return ctx ? ctx->err : "null conte
 int niti_set_path(niti_ctx* ctx, int path) {
     if (!ctx || path < NITI_PATH_AUTO || path > NITI_PATH_TMA2) return NITI_ERR_ARG;
     ctx->path = path; return NITI_OK;
+}
+int niti_set_speculate(niti_ctx* ctx, int on) {
+    if (!ctx) return NITI_ERR_ARG;
+    if (on < 0 || on > 2) return NITI_ERR_ARG;
+    ctx->speculate = on; return NITI_OK;
+}
+int niti_speculate_stats(niti_ctx* ctx, unsigned long long* hits, unsigned long long* misses, unsigned long long* skipped) {
+    if (!ctx || !hits || !misses) return NITI_ERR_ARG;
+    uint32_t v[3] = {0, 0, 0};
+    cudaError_t e = cudaMemcpy(v, ctx->pred + 2 * kDpSlots, sizeof(v), cudaMemcpyDeviceToHost);     // synchronises the device
+    if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "niti_speculate_stats", e);
+    *hits = v[0]; *misses = v[1];
+    if (skipped) *skipped = v[2];
+    return NITI_OK;
 }
 int64_t niti_launch_count(niti_ctx* ctx) { return ctx ? ctx->launches : -1; }
 const char* niti_last_path(niti_ctx* ctx) { return ctx ? ctx->last_path : "none"; }

@@ -23,6 +23,9 @@ struct niti_ctx {
     // workspace for the whole-op entry points
     int32_t* ws_acc;  size_t ws_acc_bytes;
     uint32_t* ws_u32;         // [0] max-abs slot of whole-op calls
+    uint32_t* pred;           // [kDpSlots] last max|acc| + [kDpSlots] confidence + {hits, misses, not speculated}: per exchange slot: the fused kernels' exponent prediction (conv_chain.cu)
+    int speculate;            // NITI_B200_SPECULATE: 0 off, 1 adaptive (default), 2 always
+    int dw_ctas;              // NITI_B200_DW_CTAS: upper bound on a dW launch's split-K spread (0 = sm_count)
     int8_t* ws_i8;    size_t ws_i8_bytes;   // transposed weights for dX, host-call staging
     // data-parallel scalar exchange over peer memory (dp.cuh); world <= 1 when not connected
     DpBuffer* dp_buf;
@@ -144,6 +147,12 @@ static inline int conv_out_w(const niti_conv_desc* d) {
 NITI_DEVICE_INLINE int niti_bitwidth(uint32_t m) { return m <= 1u ? 0 : 32 - __clz(m - 1u); }
 
 // `1 << s` as the reference's x86-64 build evaluates it (count masked to 5 bits)
+// rule A of NITI_Conv_Int8.cpp:262-307 as (kind, shift): kind 0 = PSTO by `shift` (>= 2), kind 1 = raw cast (quirk Q3)
+NITI_DEVICE_INLINE void niti_rule_a(int bitwidth, int& kind, int& shift) {
+    const int s = bitwidth - 7;
+    if (s > 1) { shift = s; kind = 0; } else if (s == 1) { shift = 2; kind = 0; } else { shift = 0; kind = 1; }
+}
+
 NITI_DEVICE_INLINE int32_t niti_shl1(int s) { return (int32_t)(1u << ((unsigned)s & 31u)); }
 
 // NITI_MNNPstoShiftInt32 for shift >= 2 (the hot case).  The reference splits |x| = q*2^s + rem, rem = hi*2^hs + lo
@@ -186,6 +195,74 @@ NITI_DEVICE_INLINE int32_t niti_psto(int32_t x, int shift) {
     return shift >= 2 ? niti_psto_fast(x, shift) : niti_psto_general(x, shift);
 }
 
+// ---- rule A store on both integer pipes -------------------------------------------------------------------------------
+// The store sweeps of the fused kernels are bound by the ALU pipe (IADD3 / LOP3 / SHF / PRMT / VIMNMX issue every other cycle
+// per SM sub-partition; IMAD goes to the FMA pipe, which those sweeps leave idle).  For shift s >= 2 the rounding above is
+// algebraically      r = (a' - (a' & m) * C2) >> s,   a' = |x| + KK,
+// with m = 2^hs - 1, c = 1 + odd, K = m*c + odd, KK = K << hs, C2 = 1 + (c << hs):  (~a & m) = m - (a & m), adding KK moves K
+// into the high part without touching the low hs bits, and a' - lo*C2 = ((a' >> hs) - lo*c) << hs exactly, so the two shifts
+// merge.  That is IMAD, LOP3, IMAD, SHF per element (ReLU: the clamp at 0 is max(x + KK, KK)); the four results (each <= 128)
+// are packed with IMADs, clamped to 127 in packed form (p - ((p >> 7) & 0x01010101)) and, for signed outputs, negated in
+// packed form: -p = (0x80 - p) ^ 0x80 per byte without borrows (p <= 127), selected by a PRMT sign-replicate mask.
+// 4.75 (ReLU) / 5.75 (signed) ALU-pipe instructions per element instead of 7.5 / 10.5; checked exhaustively against the
+// literal form on the host (all shifts 2..22, 3.4e7 values incl. the +-2^(s+7) edges) and by the parity tests.
+// Valid while |x| + KK < 2^31: shift <= 22; beyond that niti_rescale16 takes the element-wise path.
+// `one`: a register holding 1 that the compiler cannot fold (so x*one + KK stays an IMAD instead of becoming an ALU add).
+struct NitiRuleA {
+    uint32_t KK, negC2, m, one, c256, c65536, minus1;
+    int s;
+};
+NITI_DEVICE_INLINE NitiRuleA niti_rule_a_consts(int shift, uint32_t one) {
+    NitiRuleA k;
+    const int hs = shift >> 1;
+    const uint32_t odd = (uint32_t)shift & 1u, c = 1u + odd;
+    k.m = (1u << hs) - 1u;
+    k.KK = (k.m * c + odd) << hs;
+    k.negC2 = 0u - (1u + (c << hs));
+    k.one = one; k.c256 = one << 8; k.c65536 = one << 16; k.minus1 = 0u - one;
+    k.s = shift;
+    return k;
+}
+NITI_DEVICE_INLINE uint32_t niti_imad(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t d;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+NITI_DEVICE_INLINE uint32_t niti_pack_clamp4(uint32_t r0, uint32_t r1, uint32_t r2, uint32_t r3, const NitiRuleA& k) {
+    const uint32_t p = niti_imad(niti_imad(r3, k.c256, r2), k.c65536, niti_imad(r1, k.c256, r0));
+    return niti_imad((p >> 7) & 0x01010101u, k.minus1, p);
+}
+NITI_DEVICE_INLINE void niti_rescale16_fast(const uint32_t (&v)[16], const NitiRuleA& k, uint32_t (&o)[4], bool relu) {
+    if (relu) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            uint32_t r[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t ap = (uint32_t)max((int32_t)niti_imad(v[4 * q + j], k.one, k.KK), (int32_t)k.KK);
+                r[j] = niti_imad(ap & k.m, k.negC2, ap) >> k.s;
+            }
+            o[q] = niti_pack_clamp4(r[0], r[1], r[2], r[3], k);
+        }
+    } else {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            uint32_t r[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int32_t x = (int32_t)v[4 * q + j];
+                const uint32_t ap = niti_imad((uint32_t)(x < 0 ? -x : x), k.one, k.KK);
+                r[j] = niti_imad(ap & k.m, k.negC2, ap) >> k.s;
+            }
+            const uint32_t p = niti_pack_clamp4(r[0], r[1], r[2], r[3], k);
+            // byte i of sm = 0xff where element i is negative (PRMT selector bit 3 replicates the selected byte's sign)
+            const uint32_t sm = __byte_perm(__byte_perm(v[4 * q], v[4 * q + 1], 0x00FB), __byte_perm(v[4 * q + 2], v[4 * q + 3], 0x00FB), 0x5410);
+            const uint32_t neg = niti_imad(p, k.minus1, 0x80808080u);
+            o[q] = ((p & ~sm) | (neg & sm)) ^ (sm & 0x80808080u);
+        }
+    }
+}
+
 // 16 accumulators of one thread -> 16 int8 in four words (rule A store).  kind and shift are uniform over the tensor: ONE
 // branch, then 16 independent rounding chains the compiler interleaves — selecting per element costs a branch per element
 // and leaves each 14-instruction chain serial (measured: the store pass ran at < 1/3 of the issue rate).
@@ -210,6 +287,11 @@ NITI_DEVICE_INLINE void niti_rescale16(const uint32_t (&v)[16], int kind, int sh
             o[q] = (v[4 * q] & 0xffu) | ((v[4 * q + 1] & 0xffu) << 8) | ((v[4 * q + 2] & 0xffu) << 16) | ((v[4 * q + 3] & 0xffu) << 24);
         if (relu) { o[0] = __vmaxs4(o[0], 0u); o[1] = __vmaxs4(o[1], 0u); o[2] = __vmaxs4(o[2], 0u); o[3] = __vmaxs4(o[3], 0u); }
     }
+}
+// the same with the two-pipe form where it is valid (k = niti_rule_a_consts(shift, one), made once per tensor)
+NITI_DEVICE_INLINE void niti_rescale16(const uint32_t (&v)[16], int kind, int shift, const NitiRuleA& k, uint32_t (&o)[4], bool relu) {
+    if (kind == 0 && shift <= 22) niti_rescale16_fast(v, k, o, relu);
+    else niti_rescale16(v, kind, shift, o, relu);
 }
 
 NITI_DEVICE_INLINE uint32_t niti_abs_u32(int32_t v) { return (uint32_t)(v < 0 ? -v : v); }

@@ -26,6 +26,7 @@ namespace {
 constexpr int kChainThreads = 576;   // warp 0: TMA producer, warp 1: MMA issuer + TMEM owner, warps 2-17: epilogue
 constexpr int kChainMaxTiles = 8;    // resident accumulator tiles per CTA pair (512 TMEM columns / 64)
 constexpr int kChainMaxStages = 8;
+constexpr uint32_t kSpecConfident = 2; // consecutive predictions that must have held before a single-tile layer speculates
 constexpr int kChainSmem = 232448;   // all of it: one CTA per SM is a requirement (512 TMEM columns + grid barriers)
 constexpr int kChainStageArea = ((kChainSmem - 1024 - 512) / 1024) * 1024;
 
@@ -54,6 +55,8 @@ struct ChainArgs {
     DpView dp;
     unsigned long long* trace;        // [layer][block][8] globaltimer stamps, or nullptr
     unsigned long long* tl;           // launch timeline record, or nullptr
+    uint32_t* pred;                   // [kDpSlots] last max|acc| per slot, [kDpSlots] confidence, {hits, misses, not speculated} (exponent prediction)
+    int speculate;                    // 0: pass 0 only reduces the maximum, pass 1 always stores (two-sweep schedule); 1: adaptive; 2: always
     int trigger_late;
 };
 
@@ -228,6 +231,7 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
         const int etid = tid - 64;
         uint32_t tphase = 0;                                 // per-tile phase bits of tfull_bar
         uint32_t nbar = 0;                                   // grid barriers passed so far
+        const uint32_t eone = (uint32_t)(a.speculate >= 0);  // 1, opaque to the compiler (common.cuh niti_rule_a_consts)
         if (etid == 0) chain_trace(a.trace, 0, 1);
         for (int l = 0; l < a.nlayers; ++l) {
             const ChainLayer& L = kTable ? a.table[l] : single;
@@ -260,6 +264,26 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
                     }
                 }
             }
+            // ---- speculative single pass ------------------------------------------------------------------------------
+            // NITI's exponent needs max|acc| over the WHOLE tensor, which used to cost two sweeps over tensor memory with a
+            // grid barrier between them (max pass | barrier | store pass | layer barrier).  The bit width of that maximum
+            // hardly ever changes from one training step to the next, so pass 0 reduces the maximum AND stores with the
+            // shift predicted from the previous step's maximum (a.pred[slot]), tile by tile as the MMAs complete — the
+            // epilogue of tile i now overlaps the K loop of tile i+1 — and ONE grid barrier both publishes the maximum and
+            // completes the layer.  Every CTA then checks the prediction against the true global maximum (a grid-uniform
+            // decision); only on a miss does pass 1 re-store from tensor memory (still intact: the next layer's MMAs are
+            // held back by layer_bar) behind a second barrier.  What is stored is always rounded with the true exponent.
+            // A miss costs a second sweep and a second barrier, so a layer speculates when that is cheap or unlikely: when its
+            // CTA pairs hold several tiles (the predicted-store work hides under the K loops of the later tiles, a miss then
+            // costs what the two-sweep schedule always pays) or when the slot's prediction held the last kSpecConfident
+            // times (a.pred[kDpSlots + slot], updated whether or not the layer speculated).  Measured on VGG-11 with a new
+            // batch every step: 36 % of the predictions miss — gradient maxima hover around powers of two.
+            const uint32_t pred = __ldcg(a.pred + edps);
+            const uint32_t conf = __ldcg(a.pred + kDpSlots + edps);
+            const bool espec = a.speculate == 2 || (a.speculate == 1 && (conf >= kSpecConfident || eitems > epairs));
+            niti_rule_a(niti_bitwidth(pred), kind, shift);
+            NitiRuleA rk = niti_rule_a_consts(shift, eone);
+            int mxs = 0, mns = 0;                            // signed running max / min: one VIMNMX3 each per two accumulators
             for (int pass = 0; pass < 2; ++pass) {
                 uint32_t tile_iter = 0;
                 if (active)
@@ -277,15 +301,15 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
                     const bool row_ok = row < eM;
                     // pixel coordinates of this row (pool / pool-gradient addressing)
                     int img = 0, py = 0, px = 0;
-                    if (pass == 1 && (epool || epgx != nullptr)) { img = row / hw; const int r = row - img * hw; py = r / eow; px = r - py * eow; }
+                    if (epool || epgx != nullptr) { img = row / hw; const int r = row - img * hw; py = r / eow; px = r - py * eow; }
 #pragma unroll 1
                     for (int c0 = group * 16; c0 < ebn; c0 += 64) {
                         if (n0 + c0 >= eN) break;       // warp-uniform (Ncols % 16 == 0)
-                        // pass 1: the global loads the store needs are issued before the tensor-memory read so the latencies overlap
+                        // the global loads the store needs are issued before the tensor-memory read so the latencies overlap
                         const int col = n0 + c0;
                         uint4 x00, x01, x10, x11, gv;
                         size_t b00 = 0, b10 = 0;
-                        if (pass == 1 && row_ok) {
+                        if (row_ok) {
                             if (epgx != nullptr) {
                                 const int w2 = eow * 2;
                                 b00 = (((size_t)img * (eoh * 2) + 2 * py) * w2 + 2 * px) * eN + col;
@@ -302,12 +326,15 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
                         if (pass == 0) {
                             if (row_ok) {
 #pragma unroll
-                                for (int q = 0; q < 16; ++q) mx = max(mx, niti_abs_u32((int32_t)v[q]));
+                                for (int q = 0; q < 16; q += 2) {
+                                    mxs = __vimax3_s32(mxs, (int32_t)v[q], (int32_t)v[q + 1]);
+                                    mns = __vimin3_s32(mns, (int32_t)v[q], (int32_t)v[q + 1]);
+                                }
                             }
-                            continue;
+                            if (!espec) continue;
                         }
                         uint32_t o[4];
-                        niti_rescale16(v, kind, shift, o, erelu != 0);
+                        niti_rescale16(v, kind, shift, rk, o, erelu != 0);
                         if (epgx == nullptr) {
                             const size_t off = (size_t)row * eN + col;
                             if (row_ok) {
@@ -347,13 +374,15 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
                         }
                     }
                 }
+                const bool last_layer = l + 1 == a.nlayers;
                 if (pass == 0) {
-                    // ---- global max|acc|: warp max -> atomicMax -> grid barrier -> (data parallel: peer exchange) ----
-                    // one global atomic per CTA, not per warp: 16 x 148 atomics on one word serialise in L2 for microseconds
-                    mx = warp_max_u32(mx);
+                    // ---- global max|acc|: warp max -> one atomicMax per CTA -> grid barrier -> (data parallel: peer exchange) ----
+                    // (16 x 148 atomics on one word serialise in L2 for microseconds, hence the shared-memory stage)
+                    mx = warp_max_u32((uint32_t)max(mxs, -mns));
                     if (lane == 0 && mx) atomicMax(cta_max, mx);
-                    asm volatile("bar.sync 1, 512;" ::: "memory");
-                    if (a.trigger_late && l == a.nlayers - 1) niti_pdl_trigger();
+                    tc::tc_fence_before();
+                    asm volatile("bar.sync 1, 512;" ::: "memory");       // this CTA's maximum is final and its stores are issued
+                    if (a.trigger_late && last_layer) niti_pdl_trigger();
                     if (etid == 0) {
                         const uint32_t cm = *cta_max; *cta_max = 0u;
                         if (cm) atomicMax(emax, cm);
@@ -363,11 +392,30 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
                         *bcast = dp_exchange_max(a.dp, edps, __ldcg(emax), blockIdx.x == 0);
                     }
                     asm volatile("bar.sync 1, 512;" ::: "memory");
-                    const int b = niti_bitwidth(*bcast);
-                    const int s = b - 7;
-                    if (s > 1) { shift = s; kind = 0; } else if (s == 1) { shift = 2; kind = 0; } else { shift = 0; kind = 1; }
-                    if (blockIdx.x == 0 && etid == 0 && eeo != nullptr)
-                        *eeo = (int8_t)((eea ? (int)*eea : 0) + (eeb ? (int)*eeb : 0) + (kind == 1 ? 0 : shift));
+                    const uint32_t gmax = *bcast;
+                    int kind2, shift2;
+                    niti_rule_a(niti_bitwidth(gmax), kind2, shift2);
+                    if (blockIdx.x == 0 && etid == 0) {
+                        if (eeo != nullptr) *eeo = (int8_t)((eea ? (int)*eea : 0) + (eeb ? (int)*eeb : 0) + (kind2 == 1 ? 0 : shift2));
+                        const bool held = kind2 == kind && shift2 == shift;
+                        a.pred[edps] = gmax;                             // every CTA read the old values before it arrived above
+                        a.pred[kDpSlots + edps] = held ? min(conf + 1u, 3u) : 0u;
+                        atomicAdd(a.pred + 2 * kDpSlots + (espec ? (held ? 0 : 1) : 2), 1u);
+                    }
+                    if (espec && kind2 == kind && shift2 == shift) {     // prediction held (grid-uniform): the layer is complete
+                        if (etid == 0) chain_trace(a.trace, l, 5);
+                        break;
+                    }
+                    kind = kind2; shift = shift2;
+                    rk = niti_rule_a_consts(shift, eone);
+                } else {
+                    // prediction missed: the re-store is complete in this CTA; the next layer needs it complete everywhere
+                    tc::tc_fence_before();
+                    asm volatile("bar.sync 1, 512;" ::: "memory");
+                    if (etid == 0) {
+                        chain_trace(a.trace, l, 5);
+                        if (!last_layer) { ++nbar; niti_grid_barrier(a.sync, nbar * gridDim.x); }
+                    }
                 }
             }
             // this pair's tiles of the layer are drained: flip their phase bits
@@ -375,15 +423,9 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
                 const int mine = (eitems - pair + epairs - 1) / epairs;
                 tphase ^= (1u << mine) - 1u;
             }
-            tc::tc_fence_before();
-            asm volatile("bar.sync 1, 512;" ::: "memory");   // every epilogue warp of this CTA has stored (and read TMEM)
-            if (etid == 0) {
-                chain_trace(a.trace, l, 5);
-                if (l + 1 < a.nlayers) {
-                    ++nbar; niti_grid_barrier(a.sync, nbar * gridDim.x);          // the layer's output is complete everywhere
-                    tc::mbar_arrive(layer_bar);                                    // release this CTA's producer
-                    chain_trace(a.trace, l, 6);
-                }
+            if (etid == 0 && l + 1 < a.nlayers) {
+                tc::mbar_arrive(layer_bar);                                        // release this CTA's producer
+                chain_trace(a.trace, l, 6);
             }
         }
         if (etid == 0) {                                     // last CTA out re-arms the grid barrier for the next launch
@@ -485,7 +527,7 @@ static int chain_launch(niti_ctx* ctx, const ChainLayer* single, const ChainLaye
     if (int rc = niti_func_smem(ctx, table ? (const void*)chain_kernel<true> : (const void*)chain_kernel<false>, kChainSmem,
                                 "cudaFuncSetAttribute(chain_kernel)")) return rc;
     ChainArgs a{};
-    a.table = table; a.nlayers = nlayers; a.sync = ctx->ws_u32 + 52; a.dp = ctx->dp; a.trace = ctx->trace;
+    a.table = table; a.nlayers = nlayers; a.sync = ctx->ws_u32 + 52; a.dp = ctx->dp; a.trace = ctx->trace; a.pred = ctx->pred; a.speculate = ctx->speculate;
     a.tl = niti_tl_next(ctx, nlayers > 1 ? "chain" : (single && single->flip ? "dx_fused" : "fwd_fused"));
     a.trigger_late = (ctx->pdl & NITI_PDL_TRIGGER_LATE) ? 1 : 0;
     static const ChainLayer zero{};

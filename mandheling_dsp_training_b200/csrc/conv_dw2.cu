@@ -269,7 +269,10 @@ int dw2_conv_dw_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, con
     p.npix = d->n * oh * ow; p.num_kb = (p.npix + 127) / 128;
     p.oc_tiles = (d->oc + 127) / 128; p.c_tiles = d->c / bkc; p.ngroups = (d->kh * d->kw + G - 1) / G;
     const long tiles = (long)p.oc_tiles * p.ngroups * p.c_tiles;
-    int splits = (int)(ctx->sm_count / tiles);
+    // split-K spread: every split adds one full reduce-add of the tile (128 x G*BKC int32) to L2, so the spread trades
+    // isolated latency against SM-time — which is what counts in the step, where dW runs beside the dX chain
+    const int spread = (ctx->dw_ctas > 0 && ctx->dw_ctas < ctx->sm_count) ? ctx->dw_ctas : ctx->sm_count;
+    int splits = (int)(spread / tiles);
     if (splits > p.num_kb) splits = p.num_kb;
     if (splits < 1) splits = 1;
     p.kb_per_split = (p.num_kb + splits - 1) / splits;

@@ -9,7 +9,9 @@
 // Because the builders choose which pixel a tile row holds, a warp's 32 accumulator rows can be made 2 image rows x 16
 // columns: the 2x2 pooling partners of a pixel are then lanes l^1 and l^16 of the same warp and the pool that follows the
 // stem conv is two shuffles in the store pass (the separate pool launch and its 17 MB re-read disappear).
-// Like conv_stem.cu it RECOMPUTES the contraction for the store pass instead of parking 67 MB of int32 in HBM.
+// The exponent needs max|acc| of the whole tensor, 67 MB of int32 that is never parked in HBM: pass 0 reduces the maximum AND
+// stores with the shift predicted from the previous step's maximum (see conv_chain.cu); only when the prediction misses is the
+// contraction RECOMPUTED for a second store pass (conv_stem.cu always ran it twice).
 //
 // Operand layouts (un-swizzled K-major core matrices, 8 rows x 16 B):
 //   A stage: [Kp/16 chunks][128 rows][16 B]   LBO (next 16 B of K) = 2048 B, SBO (next 8 rows) = 128 B
@@ -52,6 +54,7 @@ struct Stem2Params {
     int relu;
     uint32_t* sync;                              // {arrival counter, exit counter}
     DpView dp; int dp_slot;
+    uint32_t* pred; int speculate;               // exponent prediction: last max|acc| of this slot (conv_chain.cu)
     unsigned long long* tl;
 };
 
@@ -94,7 +97,9 @@ stem2_fwd_kernel(const Stem2Params p) {
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + kS2AccStages);
     uint32_t* bcast = tmem_slot + 1;
     uint32_t* cta_max = tmem_slot + 2;
+    uint32_t* redo_flag = tmem_slot + 3;                                         // pass 1 needed (prediction missed / speculation off)
     int* tapoff = reinterpret_cast<int*>(tmem_slot + 4);                         // [taps] (dy << 16) | (dx & 0xffff)
+    uint64_t* decide_bar = reinterpret_cast<uint64_t*>(tapoff + kS2MaxTaps);     // redo_flag is valid
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     niti_tl_enter(p.tl);
@@ -103,6 +108,7 @@ stem2_fwd_kernel(const Stem2Params p) {
     if (tid == 0) {
         for (int s = 0; s < kS2MaxStages; ++s) { tc::mbar_init(&full_bar[s], 4); tc::mbar_init(&empty_bar[s], 1); }
         for (int a = 0; a < kS2AccStages; ++a) { tc::mbar_init(&tfull_bar[a], 1); tc::mbar_init(&tempty_bar[a], 16); }
+        tc::mbar_init(decide_bar, 1);
         tc::fence_barrier_init();
         *cta_max = 0u;
     }
@@ -135,7 +141,11 @@ stem2_fwd_kernel(const Stem2Params p) {
         const uint64_t bd0 = bdc | (uint64_t)(tc::smem_u32(bsm) >> 4);
         const int ksteps = p.Kp >> 5;
         uint32_t n = 0, tile_iter = 0;
-        for (int pass = 0; pass < 2; ++pass)
+        for (int pass = 0; pass < 2; ++pass) {
+            if (pass == 1) {                                                      // second pass only when the epilogue asks for it
+                tc::mbar_wait(decide_bar, 0u);
+                if (*reinterpret_cast<volatile uint32_t*>(redo_flag) == 0u) break;
+            }
             for (int i = 0; i < my_tiles; ++i, ++tile_iter, ++n) {
                 const uint32_t a = tile_iter % kS2AccStages, aph = (tile_iter / kS2AccStages) & 1u;
                 const uint32_t s = p.resident ? (uint32_t)i : n % kS2Stages, ph = p.resident ? 0u : (n / kS2Stages) & 1u;
@@ -151,6 +161,7 @@ stem2_fwd_kernel(const Stem2Params p) {
                     tc::umma_commit(&tfull_bar[a]);
                 }
             }
+        }
     } else if (warp <= 8) {
         // ------------------------------ operand builders ------------------------------
         // two groups of 128 threads (one tile row each) take alternate tiles, so two tiles' loads are in flight; all of a
@@ -158,7 +169,13 @@ stem2_fwd_kernel(const Stem2Params p) {
         const int bt = tid - 32, grp = bt >> 7, r = bt & 127;
         const int chunks = p.Kp >> 4;
         const uint32_t total = (p.resident ? 1u : 2u) * (uint32_t)my_tiles;
+        bool decided = false;
         for (uint32_t n = (uint32_t)grp; n < total; n += 2) {
+            if (n >= (uint32_t)my_tiles && !decided) {                                // pass 2 (ring mode) only on request
+                tc::mbar_wait(decide_bar, 0u);
+                decided = true;
+                if (*reinterpret_cast<volatile uint32_t*>(redo_flag) == 0u) break;
+            }
             const int i = (int)(n >= (uint32_t)my_tiles ? n - my_tiles : n);          // pass 2 repeats the tiles of pass 1
             const int tile = (int)blockIdx.x + i * (int)gridDim.x;
             int n_ = 0, y_ = 0, x_ = 0;
@@ -202,12 +219,16 @@ stem2_fwd_kernel(const Stem2Params p) {
         const int etid = tid - 288;
         uint32_t tile_iter = 0, mx = 0;
         int shift = 0, kind = 0;
+        const bool spec = p.speculate != 0;                                      // a miss costs what the recompute schedule always paid: no gating
+        niti_rule_a(niti_bitwidth(__ldcg(p.pred + p.dp_slot)), kind, shift);     // predicted from the previous step (conv_chain.cu)
+        const uint32_t eone = (uint32_t)(p.speculate >= 0);                      // 1, opaque to the compiler
+        NitiRuleA rk = niti_rule_a_consts(shift, eone);
+        int mxs = 0, mns = 0;
         for (int pass = 0; pass < 2; ++pass) {
             for (int i = 0; i < my_tiles; ++i, ++tile_iter) {
                 const int tile = (int)blockIdx.x + i * (int)gridDim.x;
                 int n_ = 0, y_ = 0, x_ = 0;
-                const bool row_ok = pass == 0 ? (p.pool ? tile * 4 + quarter < p.units : tile * 128 + quarter * 32 + lane < p.M)
-                                              : s2_pixel(p, tile, quarter * 32 + lane, n_, y_, x_);
+                const bool row_ok = s2_pixel(p, tile, quarter * 32 + lane, n_, y_, x_);
                 const uint32_t a = tile_iter % kS2AccStages, aph = (tile_iter / kS2AccStages) & 1u;
                 tc::mbar_wait_backoff(&tfull_bar[a], aph);
                 tc::tc_fence_after();
@@ -219,12 +240,15 @@ stem2_fwd_kernel(const Stem2Params p) {
                     if (pass == 0) {
                         if (row_ok) {
 #pragma unroll
-                            for (int q = 0; q < 16; ++q) mx = max(mx, niti_abs_u32((int32_t)v[q]));
+                            for (int q = 0; q < 16; q += 2) {
+                                mxs = __vimax3_s32(mxs, (int32_t)v[q], (int32_t)v[q + 1]);
+                                mns = __vimin3_s32(mns, (int32_t)v[q], (int32_t)v[q + 1]);
+                            }
                         }
-                        continue;
+                        if (!spec) continue;
                     }
                     uint32_t o[4];
-                    niti_rescale16(v, kind, shift, o, p.relu != 0);
+                    niti_rescale16(v, kind, shift, rk, o, p.relu != 0);
                     if (row_ok)
                         *reinterpret_cast<uint4*>(p.y + (((size_t)n_ * p.oh + y_) * p.ow + x_) * p.oc + c0) = make_uint4(o[0], o[1], o[2], o[3]);
                     if (p.pool) {
@@ -244,24 +268,35 @@ stem2_fwd_kernel(const Stem2Params p) {
                 __syncwarp();
                 if (lane == 0) tc::mbar_arrive(&tempty_bar[a]);
             }
-            if (pass == 0) {
-                // ---- global max|acc|: warp max -> CTA max -> one atomicMax -> grid barrier -> (data parallel: peer exchange) ----
-                mx = warp_max_u32(mx);
-                if (lane == 0 && mx) atomicMax(cta_max, mx);
-                asm volatile("bar.sync 1, 512;" ::: "memory");
-                if (etid == 0) {
-                    const uint32_t cm = *cta_max;
-                    if (cm) atomicMax(p.maxabs, cm);
-                    tmax::grid_barrier(p.sync, gridDim.x);
-                    *bcast = dp_exchange_max(p.dp, p.dp_slot, __ldcg(p.maxabs), blockIdx.x == 0);
-                }
-                asm volatile("bar.sync 1, 512;" ::: "memory");
-                const int b = niti_bitwidth(*bcast);
-                const int s = b - 7;
-                if (s > 1) { shift = s; kind = 0; } else if (s == 1) { shift = 2; kind = 0; } else { shift = 0; kind = 1; }
-                if (blockIdx.x == 0 && etid == 0 && p.exp_out != nullptr)
-                    *p.exp_out = (int8_t)((p.exp_a ? (int)*p.exp_a : 0) + (p.exp_b ? (int)*p.exp_b : 0) + (kind == 1 ? 0 : shift));
+            if (pass == 1) break;
+            // ---- global max|acc|: warp max -> CTA max -> one atomicMax -> grid barrier -> (data parallel: peer exchange) ----
+            mx = warp_max_u32((uint32_t)max(mxs, -mns));
+            if (lane == 0 && mx) atomicMax(cta_max, mx);
+            asm volatile("bar.sync 1, 512;" ::: "memory");
+            if (etid == 0) {
+                const uint32_t cm = *cta_max;
+                if (cm) atomicMax(p.maxabs, cm);
+                tmax::grid_barrier(p.sync, gridDim.x);
+                *bcast = dp_exchange_max(p.dp, p.dp_slot, __ldcg(p.maxabs), blockIdx.x == 0);
             }
+            asm volatile("bar.sync 1, 512;" ::: "memory");
+            const uint32_t gmax = *bcast;
+            int kind2, shift2;
+            niti_rule_a(niti_bitwidth(gmax), kind2, shift2);
+            const bool hit = spec && kind2 == kind && shift2 == shift;          // grid-uniform
+            if (etid == 0) {
+                *reinterpret_cast<volatile uint32_t*>(redo_flag) = hit ? 0u : 1u;
+                tc::mbar_arrive(decide_bar);                                     // releases the MMA issuer and the builders (release.cta)
+                if (blockIdx.x == 0) {
+                    if (p.exp_out != nullptr)
+                        *p.exp_out = (int8_t)((p.exp_a ? (int)*p.exp_a : 0) + (p.exp_b ? (int)*p.exp_b : 0) + (kind2 == 1 ? 0 : shift2));
+                    p.pred[p.dp_slot] = gmax;                                    // every CTA read the old value before the barrier
+                    atomicAdd(p.pred + 2 * kDpSlots + (spec ? (hit ? 0 : 1) : 2), 1u);
+                }
+            }
+            if (hit) break;
+            kind = kind2; shift = shift2;
+            rk = niti_rule_a_consts(shift, eone);
         }
         asm volatile("bar.sync 1, 512;" ::: "memory");
         if (etid == 0) {                                     // last CTA out re-arms the grid barrier
@@ -283,7 +318,7 @@ stem2_fwd_kernel(const Stem2Params p) {
 // ------------------------------------------------------------------------------------------------
 static int stem2_smem(const niti_conv_desc* d, int stages) {
     const int taps = d->kh * d->kw, kp = (taps * 4 + 31) & ~31;
-    return stages * kp * 128 + ((kp * d->oc + 127) & ~127) + 2 * kS2MaxStages * 8 + 512 + kS2MaxTaps * 4 + 1024;
+    return stages * kp * 128 + ((kp * d->oc + 127) & ~127) + 2 * kS2MaxStages * 8 + 512 + kS2MaxTaps * 4 + 64 + 1024;
 }
 
 // c_live: how many leading channels of x may be non-zero (the caller's guarantee: an image tensor padded to d->c channels)
@@ -315,7 +350,7 @@ int stem2_conv_fwd_fused(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x
     p.d_upi.init(p.pool ? p.units_per_img : 1); p.d_xb.init(p.pool ? p.xblocks : 1); p.d_ow.init(ow); p.d_oh.init(oh);
     p.y = y; p.y_pool = y_pool; p.maxabs = maxabs; p.exp_a = ex; p.exp_b = ew; p.exp_out = ey; p.relu = relu;
     p.sync = ctx->ws_u32 + 48;
-    p.dp = ctx->dp; p.dp_slot = dp_slot; p.tl = niti_tl_next(ctx, "stem2_fwd");
+    p.dp = ctx->dp; p.dp_slot = dp_slot; p.pred = ctx->pred; p.speculate = ctx->speculate; p.tl = niti_tl_next(ctx, "stem2_fwd");
     // one CTA per SM, enforced through the shared-memory request: every CTA allocates all 512 TMEM columns and waits at a
     // grid barrier (see conv_tma2.cu launch_fused)
     const int grid = p.m_tiles < ctx->sm_count ? p.m_tiles : ctx->sm_count;

@@ -51,6 +51,8 @@ _SIGS = {
     "niti_ctx_destroy": (C.c_int, [_P]),
     "niti_last_error": (C.c_char_p, [_P]),
     "niti_set_path": (C.c_int, [_P, C.c_int]),
+    "niti_set_speculate": (C.c_int, [_P, C.c_int]),
+    "niti_speculate_stats": (C.c_int, [_P, C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong), C.POINTER(C.c_ulonglong)]),
     "niti_version": (C.c_int, []),
     "niti_launch_count": (C.c_int64, [_P]),
     "niti_last_path": (C.c_char_p, [_P]),
@@ -188,6 +190,16 @@ class NitiB200:
 
     def set_path(self, path):
         self._ck(self.lib.niti_set_path(self.h, path))
+
+    def set_speculate(self, mode):
+        """exponent prediction of the fused kernels: 0 off, 1 adaptive (default), 2 always (include/niti_b200.h)"""
+        self._ck(self.lib.niti_set_speculate(self.h, int(mode)))
+
+    def speculate_stats(self):
+        """(hits, misses, not speculated) of the fused kernels' exponent prediction since the context was created"""
+        h, m, k = C.c_ulonglong(0), C.c_ulonglong(0), C.c_ulonglong(0)
+        self._ck(self.lib.niti_speculate_stats(self.h, C.byref(h), C.byref(m), C.byref(k)))
+        return int(h.value), int(m.value), int(k.value)
 
     @property
     def launches(self):

@@ -124,7 +124,8 @@ class NitiNet:
         self.ops, self.convs = [], []
         cur, cur_e = self.x_in, self.ex_in
         dw_total = 0
-        for item in (fuse_spec(spec) if fuse else [it + ((False,) if it[0] == "conv" else ()) for it in spec]):
+        fused = fuse_spec(spec) if fuse else [it + ((False,) if it[0] == "conv" else ()) for it in spec]
+        for item in fused:
             kind = item[0]
             L = _Op(); L.kind = kind; L.relu = False; L.alias = False
             L.fwd_fused = L.bwd_fused = False              # pool ops: done inside the neighbouring conv launches
@@ -132,6 +133,10 @@ class NitiNet:
             if kind == "conv":
                 _, oc, k, st, pad, relu = item
                 oc_p = (oc + pad_oc - 1) // pad_oc * pad_oc if pad_oc else oc
+                if pad_oc and item is fused[-1] and self.convs and k == 1 and oc_p < 64:
+                    # the classifier's dX contracts over its output channels: 64 of them (one K block of the fused kernel,
+                    # niti_conv_dx_fused) instead of 16 on the cp.async kernel + transpose + rescale launches; zero rows, exact
+                    oc_p = 64
                 L.d = make_desc(batch, c, h, w, oc_p, k, stride=st, pad=pad)
                 L.c_real, L.oc_real = c_real, oc
                 L.relu = relu

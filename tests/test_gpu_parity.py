@@ -684,3 +684,50 @@ def test_chain_of_forward_ops_equals_the_ops_one_by_one(nb, oracle):
             assert np.array_equal(nchw(yp.cpu().numpy()), wyp)
         assert int(ey.item()) == we
     assert nb.sync_error() == 0
+
+
+# ------------------------------------------------------------------ exponent prediction (niti_set_speculate)
+@pytest.mark.parametrize("cfg", [(64, 64, 16, 16, 128, 3, 1, 1), (4, 128, 4, 4, 256, 3, 1, 1), (256, 512, 1, 1, 512, 1, 1, 0)])
+def test_exponent_prediction_hit_miss_and_off_are_bit_identical(nb, run, oracle, cfg):
+    """The fused kernels store with the shift predicted from the slot's previous max|acc| and re-store on a miss
+    (conv_chain.cu).  Same op, same slot: prediction off (two sweeps) | on after a tensor of another magnitude (miss: re-store)
+    | on again (hit: single sweep) | on after a SMALLER tensor (miss the other way) — y, exponent and max|acc| always the oracle's."""
+    n, c, h, w, oc, k, st, p = cfg
+    s = shape(n, c, h, w, oc, k, stride=st, pad=p)
+    rng = np.random.default_rng(7)
+    x = _rand(rng, (n, c, h, w)); wt = _rand(rng, (oc, c, k, k), -64, 64)
+    x_small = _rand(rng, (n, c, h, w), -2, 2)
+    dy = _rand(rng, (n, oc, s.oh, s.ow), -50, 50)
+    oy, oe, oacc = oracle.conv_fwd(s, x, wt, -3, -9)
+    oys, oes, _ = oracle.conv_fwd(s, x_small, wt, -3, -9)
+    odx, _ = oracle.conv_dx(s, dy, wt)
+    assert oe != oes                                        # the two inputs land in different bit widths
+
+    def check_big():
+        y, e, mx = run.conv_fwd_fused(s, x, wt, -3, -9, True)
+        assert e == oe and mx == int(np.abs(oacc.astype(np.int64)).max())
+        assert np.array_equal(y, oracle.relu(oy))
+    h0, m0, k0 = nb.speculate_stats()
+    try:
+        nb.set_speculate(0); check_big()
+        assert nb.speculate_stats() == (h0, m0, k0 + 1)
+        nb.set_speculate(2)                                                    # always speculate: forces the miss paths
+        y, e, _ = run.conv_fwd_fused(s, x_small, wt, -3, -9, False)          # leaves a small maximum in the slot
+        assert e == oes and np.array_equal(y, oys)
+        check_big()                                                            # miss (predicted shift too small)
+        check_big()                                                            # hit
+        y, e, _ = run.conv_fwd_fused(s, x_small, wt, -3, -9, False)          # miss (predicted shift too large)
+        assert e == oes and np.array_equal(y, oys)
+        for _ in range(2):                                                     # dX: miss, then hit
+            dx, _ = run.conv_dx_fused(s, dy, wt, gate=x)
+            assert np.array_equal(dx, oracle.relu_grad(x, odx))
+        h1, m1, k1 = nb.speculate_stats()
+        assert (h1 - h0, m1 - m0, k1 - k0) == (2, 4, 1)
+        nb.set_speculate(1)                                                    # adaptive: single-tile layers wait for two holds
+        for _ in range(4):
+            check_big()
+        h2, m2, k2 = nb.speculate_stats()
+        assert h2 + m2 + k2 == h1 + m1 + k1 + 4 and m2 - m1 <= 1 and h2 - h1 >= 1
+    finally:
+        nb.set_speculate(1)
+    assert nb.sync_error() == 0

@@ -2,8 +2,9 @@
 
 usage: python tools/phase_trace.py [vgg11|lenet|resnet18] [batch] > profiles/phase_rN_<workload>.txt
 Each fused launch writes %globaltimer stamps per CTA: 0 entry, 1 set-up done (barrier init, TMEM alloc, tensor-map prefetch,
-cluster sync, griddepcontrol.wait), 2 first tile accumulated (K loop of the first resident tile), 3 max pass done (TMEM sweep 1),
-4 grid barrier passed, 5 rescale + store done (TMEM sweep 2), 6 exit.  Printed per launch: median over CTAs of each phase's
+cluster sync, griddepcontrol.wait), 2 first tile accumulated (K loop of the first resident tile), 3 max + predicted-store sweep done (one TMEM sweep, overlapping the
+K loops of the CTA's later tiles), 4 grid barrier passed, 5 re-store done (only when the exponent prediction missed; else = 4),
+6 next layer released, 7 exit.  Printed per launch: median over CTAs of each phase's
 duration in us, the launch's wall time from the first entry to the last exit, and its event-timed duration."""
 import os
 import sys
@@ -45,9 +46,9 @@ def main():
     torch.cuda.synchronize()
     nb.debug_trace(None)
     # stamps (csrc/conv_chain.cu): per launch [0][block][0] entry, [0][block][1] set-up done, [last][block][7] exit; per layer
-    # 2 first tile accumulated, 3 max pass done, 4 exponent barrier (+ peer exchange) passed, 5 rescale + store done,
-    # 6 layer barrier passed (not after the last layer)
-    names = ["K loop (first tile)", "max pass", "exponent barrier", "rescale+store", "layer barrier"]
+    # 2 first tile accumulated, 3 max + predicted-store sweep done, 4 grid barrier (+ peer exchange) passed,
+    # 5 re-store + second barrier done (prediction missed; otherwise stamped right after 4), 6 next layer released
+    names = ["K loop (first tile)", "max+store sweep", "grid barrier", "re-store (miss)", "release"]
     print(f"# phase trace, {wl} batch {batch}, one eager step (every launch synchronised: cold pipeline, no PDL overlap)")
     print("# per launch: kind path GOP | event us | in-kernel span us (first entry .. last exit) | set-up us")
     print("#   per layer: CTAs | median us per phase: " + " | ".join(names))
