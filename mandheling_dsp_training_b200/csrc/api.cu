@@ -124,6 +124,19 @@ int niti_ws_i8(niti_ctx* ctx, size_t bytes, int8_t** out) {
     return NITI_OK;
 }
 
+// zero-inserted dY of strided dX ops (own buffer: the i8 workspace above may be in use for weights in the same call chain)
+static int niti_ws_z(niti_ctx* ctx, size_t bytes, int8_t** out) {
+    if (bytes > ctx->ws_z_bytes) {
+        if (ctx->ws_z) cudaFree(ctx->ws_z);
+        ctx->ws_z = nullptr; ctx->ws_z_bytes = 0;
+        cudaError_t e = cudaMalloc(&ctx->ws_z, bytes);
+        if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "workspace (zero-inserted dY) cudaMalloc", e);
+        ctx->ws_z_bytes = bytes;
+    }
+    *out = ctx->ws_z;
+    return NITI_OK;
+}
+
 static bool desc_ok(const niti_conv_desc* d) {
     if (!d) return false;
     if (d->n <= 0 || d->c <= 0 || d->h <= 0 || d->w <= 0 || d->oc <= 0 || d->kh <= 0 || d->kw <= 0) return false;
@@ -188,6 +201,7 @@ int niti_ctx_destroy(niti_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->ws_acc) cudaFree(ctx->ws_acc);
     if (ctx->ws_i8) cudaFree(ctx->ws_i8);
+    if (ctx->ws_z) cudaFree(ctx->ws_z);
     if (ctx->ws_u32) cudaFree(ctx->ws_u32);
     niti_dp_close(ctx);
     if (ctx->dp_buf) cudaFree(ctx->dp_buf);
@@ -331,6 +345,22 @@ int niti_conv_dx_fused(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* dy,
         niti_chain_op op{};
         op.d = *d; op.op = 1; op.in = dy; op.w = wt; op.out = dx; op.gate = gate; op.maxabs = maxabs; op.dp_slot = dp_slot;
         if (ctx->use_chain && chain_op_eligible(ctx, &op)) { ctx->last_path = "fused"; return chain_run_single(ctx, &op, (cudaStream_t)st); }
+        if (ctx->use_chain && d->stride > 1 && d->oc % 16 == 0) {
+            // Strided conv: dX is the stride-1 dX of dY with stride-1 zeros inserted between its pixels — the lowering the
+            // reference's grad rule emits (NITI_CPULeftPoolGrad_Int8 in front of NITI_DeConv_Int8,
+            // tools/train/source/grad/NITI_Conv_Int8_Grad.cpp:90-106).  The zeros cost stride^2 times the MMAs, on the fused
+            // TMA/tcgen05 kernel instead of the cp.async kernel (55-80 TOP/s on the ResNet transitions) + transposes + rescale.
+            niti_conv_desc d1 = *d; d1.stride = 1;
+            niti_chain_op op1 = op; op1.d = d1;
+            const int zh = conv_out_h(&d1), zw = conv_out_w(&d1);
+            if (chain_op_eligible(ctx, &op1)) {
+                int8_t* z; int rcz = niti_ws_z(ctx, (size_t)d->n * zh * zw * d->oc, &z); if (rcz) return rcz;
+                if ((rcz = niti_zero_insert_nhwc(ctx, dy, d->n, conv_out_h(d), conv_out_w(d), d->oc, d->stride, zh, zw, z, st))) return rcz;
+                op1.in = z;
+                ctx->last_path = "fused";
+                return chain_run_single(ctx, &op1, (cudaStream_t)st);
+            }
+        }
         if (fused_dx_eligible(ctx, d)) {
             ctx->last_path = "fused";
             return fused_conv_dx(ctx, d, dy, wt, dx, gate, maxabs, dp_slot, (cudaStream_t)st);

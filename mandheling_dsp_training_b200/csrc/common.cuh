@@ -23,10 +23,11 @@ struct niti_ctx {
     // workspace for the whole-op entry points
     int32_t* ws_acc;  size_t ws_acc_bytes;
     uint32_t* ws_u32;         // [0] max-abs slot of whole-op calls
-    uint32_t* pred;           // [kDpSlots] last max|acc| + [kDpSlots] confidence + {hits, misses, not speculated}: per exchange slot: the fused kernels' exponent prediction (conv_chain.cu)
+    uint32_t* pred;           // [kDpSlots] predictor state + [kDpSlots] confidence + {hits, misses, not speculated}: per exchange slot: the fused kernels' exponent prediction (conv_chain.cu)
     int speculate;            // NITI_B200_SPECULATE: 0 off, 1 adaptive (default), 2 always
     int dw_ctas;              // NITI_B200_DW_CTAS: upper bound on a dW launch's split-K spread (0 = sm_count)
     int8_t* ws_i8;    size_t ws_i8_bytes;   // transposed weights for dX, host-call staging
+    int8_t* ws_z;     size_t ws_z_bytes;    // zero-inserted dY of strided dX ops (api.cu niti_conv_dx_fused)
     // data-parallel scalar exchange over peer memory (dp.cuh); world <= 1 when not connected
     DpBuffer* dp_buf;
     DpView dp;
@@ -127,6 +128,8 @@ int  niti_check_launch(niti_ctx* ctx, const char* what);
 // 2x2/2 max-pool gradient that takes the window maximum from x itself (elementwise.cu)
 int  niti_maxpool_grad_from_x(niti_ctx* ctx, const int8_t* x, const int8_t* dy, int n, int h, int w, int c, int8_t* dx, int gate_relu,
                               niti_stream st);
+// out[n][y][x][:] = in[n][y/s][x/s][:] where s divides y and x (and the source pixel exists), else 0; c % 16 == 0 (elementwise.cu)
+int  niti_zero_insert_nhwc(niti_ctx* ctx, const int8_t* in, int n, int ih, int iw, int c, int s, int oh, int ow, int8_t* out, niti_stream st);
 int  niti_ws_acc(niti_ctx* ctx, size_t bytes, int32_t** out);
 int  niti_ws_i8(niti_ctx* ctx, size_t bytes, int8_t** out);
 
@@ -151,6 +154,22 @@ NITI_DEVICE_INLINE int niti_bitwidth(uint32_t m) { return m <= 1u ? 0 : 32 - __c
 NITI_DEVICE_INLINE void niti_rule_a(int bitwidth, int& kind, int& shift) {
     const int s = bitwidth - 7;
     if (s > 1) { shift = s; kind = 0; } else if (s == 1) { shift = 2; kind = 0; } else { shift = 0; kind = 1; }
+}
+
+// Exponent predictor of the fused kernels (conv_chain.cu): per exchange slot, a window of two adjacent bit widths {lo, lo+1} and a
+// 2-bit saturating counter choosing between them — max|acc| of a tensor hovers around a power of two from step to step, and the
+// majority of the last few steps predicts better than the last step (a Bernoulli(p) alternation: max(p, 1-p) instead of
+// p^2 + (1-p)^2).  A bit width outside the window moves the window so that the next prediction is the width just seen.
+// state = lo << 2 | counter.
+NITI_DEVICE_INLINE int niti_pred_bitwidth(uint32_t state) { return (int)(state >> 2) + ((state & 3u) >= 2u ? 1 : 0); }
+NITI_DEVICE_INLINE uint32_t niti_pred_update(uint32_t state, int seen) {
+    int lo = (int)(state >> 2), c = (int)(state & 3u);
+    if (seen == lo) c = c > 0 ? c - 1 : 0;
+    else if (seen == lo + 1) c = c < 3 ? c + 1 : 3;
+    else if (seen == lo - 1) { lo = seen; c = 1; }
+    else if (seen == lo + 2) { lo = seen - 1; c = 2; }
+    else { lo = seen; c = 0; }
+    return ((uint32_t)lo << 2) | (uint32_t)c;
 }
 
 NITI_DEVICE_INLINE int32_t niti_shl1(int s) { return (int32_t)(1u << ((unsigned)s & 31u)); }

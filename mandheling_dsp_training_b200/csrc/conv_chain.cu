@@ -39,6 +39,7 @@ struct alignas(128) ChainLayer {
     int cchunks, num_kb;              // channel chunks per tap; K blocks per tile
     int n_tiles, items, pairs;        // items = m_tiles * n_tiles, distributed over `pairs` CTA pairs
     int bn, bkc, stages;
+    int nslots, stream;               // accumulator slots of bn columns in tensor memory; stream: tiles per pair > nslots (slots are recycled)
     int8_t* y; const int8_t* gate;
     const int8_t* exp_a; const int8_t* exp_b; int8_t* exp_out;
     uint32_t* maxabs;
@@ -55,7 +56,7 @@ struct ChainArgs {
     DpView dp;
     unsigned long long* trace;        // [layer][block][8] globaltimer stamps, or nullptr
     unsigned long long* tl;           // launch timeline record, or nullptr
-    uint32_t* pred;                   // [kDpSlots] last max|acc| per slot, [kDpSlots] confidence, {hits, misses, not speculated} (exponent prediction)
+    uint32_t* pred;                   // [kDpSlots] predictor state per slot (common.cuh niti_pred_*), [kDpSlots] confidence, {hits, misses, not speculated}
     int speculate;                    // 0: pass 0 only reduces the maximum, pass 1 always stores (two-sweep schedule); 1: adaptive; 2: always
     int trigger_late;
 };
@@ -91,18 +92,31 @@ __device__ __forceinline__ uint4 vgt0(uint4 a) {
 
 // kTable: walk a.table[0..nlayers) in global memory; otherwise the one layer passed by value (its tensor maps are then read
 // straight from the kernel-parameter bank instead of through a generic pointer that may point either way)
-template <bool kTable>
+//
+// Tensor memory is a ring of L.nslots accumulator slots of L.bn columns; tile t of a CTA pair accumulates in slot
+// t % nslots.  RESIDENT layers (tiles per pair <= nslots) keep every tile until the layer's exponent is settled, so a
+// missed prediction (or no speculation) re-stores straight from tensor memory.  STREAMING layers (outputs larger than the
+// 9.7 M accumulators of tensor memory: ResNet's 56^2 / 28^2 stages, GEMMs with M >= 64 k) hand a slot back to the MMA
+// issuer as soon as its tile is swept — the sweep of tile i runs under the K loop of tile i+1 — and a miss RECOMPUTES the
+// layer (the stem kernels' schedule); with speculation a streaming layer costs one contraction and no int32 ever reaches HBM.
+// Per layer the epilogue tells the two issuing warps what comes next through `flag` + layer_bar: 0 = layer complete
+// everywhere, go on; 1 = run this layer's loads / MMAs once more (store pass of a streaming layer).
+// kStream: some layer of the chain is a streaming layer.  Chains of resident layers only (all of VGG-11 at batch 256) compile
+// without the slot hand-back and the per-layer verdict wait of the issuing warps (measured: 13 us per 10-layer chain).
+template <bool kTable, bool kStream>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kChainThreads, 1)
 chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
     extern __shared__ uint8_t smem_raw_chain[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw_chain) + 1023) & ~(uintptr_t)1023);
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kChainStageArea);            // used in the leader only
     uint64_t* empty_bar = full_bar + kChainMaxStages;                                    // per CTA
-    uint64_t* tfull_bar = empty_bar + kChainMaxStages;                                   // per CTA, one per resident tile
-    uint64_t* layer_bar = tfull_bar + kChainMaxTiles;                                    // per CTA: the next layer's operand is in memory
+    uint64_t* tfull_bar = empty_bar + kChainMaxStages;                                   // per CTA, one per accumulator slot
+    uint64_t* tempty_bar = tfull_bar + kChainMaxTiles;                                   // leader only: slot swept by all 32 epilogue warps of the pair
+    uint64_t* layer_bar = tempty_bar + kChainMaxTiles;                                   // per CTA: `flag` is valid
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(layer_bar + 1);
     uint32_t* bcast = tmem_slot + 1;
     uint32_t* cta_max = tmem_slot + 2;                                                   // this CTA's max|acc| of the current layer
+    volatile uint32_t* flag = tmem_slot + 3;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const uint32_t rank = cluster_ctarank();
@@ -114,7 +128,7 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
 
     if (tid == 0) {
         for (int s = 0; s < kChainMaxStages; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], 1); }
-        for (int t = 0; t < kChainMaxTiles; ++t) tc::mbar_init(&tfull_bar[t], 1);
+        for (int t = 0; t < kChainMaxTiles; ++t) { tc::mbar_init(&tfull_bar[t], 1); tc::mbar_init(&tempty_bar[t], 32); }
         tc::mbar_init(layer_bar, 1);
         tc::fence_barrier_init();
     }
@@ -139,88 +153,107 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
     if (warp == 0) {
         // ------------------------------ TMA producer (both CTAs) ------------------------------
         uint32_t pphase = 0;                             // per-stage phase bits of empty_bar
+        uint32_t lphase = 0;                             // phase of layer_bar
         for (int l = 0; l < a.nlayers; ++l) {
             const ChainLayer& L = kTable ? a.table[l] : single;
-            if (l > 0) {
-                tc::mbar_wait(layer_bar, (uint32_t)(l - 1) & 1u);       // previous layer stored everywhere (grid barrier passed)
-                tmax::fence_proxy_async_all();                          // generic-proxy stores -> async-proxy (TMA) reads
-            }
             // the layer record is read ONCE into registers: every asm below clobbers memory, so fields left in the
             // (global or param) record would be re-loaded on each use — measured +25 % on the K loop
             const int Lpairs = L.pairs, Litems = L.items, Lntiles = L.n_tiles, LM = L.M, Lbn = L.bn, Lbkc = L.bkc;
             const int Low = L.out_w, Loh = L.out_h, Lstride = L.stride, Llw = L.lower_w, Llh = L.lower_h, Lnumkb = L.num_kb;
             const int Lcch = L.cchunks, Lkw = L.kw, Lkh = L.kh, Lflip = L.flip, Ldil = L.dil, Lstages = L.stages;
-            if (pair >= Lpairs) continue;
             const uint32_t a_bytes = 128u * (uint32_t)Lbkc, stage = a_bytes + (uint32_t)(Lbn / 2) * (uint32_t)Lbkc;
             // tap walk without divisions: forward runs (ky, kx) up from (0, 0), dX (flipped kernel) down from (kh-1, kw-1)
             const int kx_first = Lflip ? (Lkw - 1) * Ldil : 0, kx_last = Lflip ? 0 : (Lkw - 1) * Ldil;
             const int kstep = Lflip ? -Ldil : Ldil;
             const int ky_first = Lflip ? (Lkh - 1) * Ldil : 0;
             int s = 0;
-            for (int item = pair; item < Litems; item += Lpairs) {
-                const int n_t = item % Lntiles; const int m_t = item / Lntiles;
-                int m0 = m_t * 256 + (int)rank * 128;
-                if (m0 >= LM) m0 = 0;                    // fully out-of-range half: load valid rows, results are masked
-                const int nrow0 = n_t * Lbn + (int)rank * (Lbn / 2);
-                const int q = m0 % Low; const int t = m0 / Low;
-                const int pp = t % Loh; const int bn_ = t / Loh;
-                const int bw = q * Lstride + Llw, bh = pp * Lstride + Llh;
-                int cc = 0, kx = kx_first, ky = ky_first, kcol = 0;      // channel chunk, tap offsets, K coordinate of block kb
-                for (int kb = 0; kb < Lnumkb; ++kb) {
-                    tc::mbar_wait(&empty_bar[s], ((pphase >> s) & 1u) ^ 1u);
-                    pphase ^= 1u << s;
-                    const uint32_t a_dst = tc::smem_u32(smem) + (uint32_t)s * stage;
-                    if (tc::elect_one()) {
-                        if (rank == 0) mbar_expect_tx(&full_bar[s], 2u * stage);
-                        tma2_load_im2col(&L.mapA, a_dst, &full_bar[s], cc, bw, bh, bn_, (uint16_t)kx, (uint16_t)ky);
-                        tma2_load_2d(&L.mapB, a_dst + a_bytes, &full_bar[s], kcol, nrow0);
-                    }
-                    if (++s == Lstages) s = 0;
-                    kcol += Lbkc; cc += Lbkc;
-                    if (cc == Lcch * Lbkc) {
-                        cc = 0;
-                        if (kx == kx_last) { kx = kx_first; ky += kstep; } else kx += kstep;
+            for (;;) {
+                if (pair < Lpairs)
+                for (int item = pair; item < Litems; item += Lpairs) {
+                    const int n_t = item % Lntiles; const int m_t = item / Lntiles;
+                    int m0 = m_t * 256 + (int)rank * 128;
+                    if (m0 >= LM) m0 = 0;                    // fully out-of-range half: load valid rows, results are masked
+                    const int nrow0 = n_t * Lbn + (int)rank * (Lbn / 2);
+                    const int q = m0 % Low; const int t = m0 / Low;
+                    const int pp = t % Loh; const int bn_ = t / Loh;
+                    const int bw = q * Lstride + Llw, bh = pp * Lstride + Llh;
+                    int cc = 0, kx = kx_first, ky = ky_first, kcol = 0;      // channel chunk, tap offsets, K coordinate of block kb
+                    for (int kb = 0; kb < Lnumkb; ++kb) {
+                        tc::mbar_wait(&empty_bar[s], ((pphase >> s) & 1u) ^ 1u);
+                        pphase ^= 1u << s;
+                        const uint32_t a_dst = tc::smem_u32(smem) + (uint32_t)s * stage;
+                        if (tc::elect_one()) {
+                            if (rank == 0) mbar_expect_tx(&full_bar[s], 2u * stage);
+                            tma2_load_im2col(&L.mapA, a_dst, &full_bar[s], cc, bw, bh, bn_, (uint16_t)kx, (uint16_t)ky);
+                            tma2_load_2d(&L.mapB, a_dst + a_bytes, &full_bar[s], kcol, nrow0);
+                        }
+                        if (++s == Lstages) s = 0;
+                        kcol += Lbkc; cc += Lbkc;
+                        if (cc == Lcch * Lbkc) {
+                            cc = 0;
+                            if (kx == kx_last) { kx = kx_first; ky += kstep; } else kx += kstep;
+                        }
                     }
                 }
+                if (!kStream && l + 1 == a.nlayers) break;                   // nothing follows and nothing is ever re-run
+                tc::mbar_wait(layer_bar, lphase); lphase ^= 1u;              // the epilogue's verdict on this layer
+                if (!kStream || *flag == 0u) break;                          // complete everywhere (grid barrier passed)
             }
+            tmax::fence_proxy_async_all();                                   // generic-proxy stores -> async-proxy (TMA) reads
         }
     } else if (warp == 1) {
         if (rank == 0) {
             // ------------------------------ MMA issuer (leader CTA only) ------------------------------
             uint32_t cphase = 0;                             // per-stage phase bits of full_bar
+            uint32_t euse = 0;                               // per-slot use parity (tempty_bar)
+            uint32_t lphase = 0;
             for (int l = 0; l < a.nlayers; ++l) {
                 const ChainLayer& L = kTable ? a.table[l] : single;
                 const int Lpairs = L.pairs, Litems = L.items, Lbn = L.bn, Lbkc = L.bkc, Lnumkb = L.num_kb, Lstages = L.stages;
-                if (pair >= Lpairs) continue;
+                const uint32_t Lslots = (uint32_t)L.nslots;
                 const uint32_t idesc = tc::make_idesc_i8(256, Lbn, 0, 0);
                 const uint32_t a_bytes = 128u * (uint32_t)Lbkc, stage = a_bytes + (uint32_t)(Lbn / 2) * (uint32_t)Lbkc;
                 // shared-memory descriptor = layer constant | (address >> 4): K-major, LBO 16 B, SBO 8 rows, swizzle of the row
                 const uint64_t dconst = make_desc2(0u, 16, 8u * (uint32_t)Lbkc, (Lbkc == 128) ? 2u : 4u);
-                int s = 0; uint32_t tile_iter = 0;
-                for (int item = pair; item < Litems; item += Lpairs, ++tile_iter) {
-                    const uint32_t d_tmem = tmem_base + tile_iter * (uint32_t)Lbn;        // every tile keeps its own columns
-                    for (int kb = 0; kb < Lnumkb; ++kb) {
-                        tc::mbar_wait(&full_bar[s], (cphase >> s) & 1u);
-                        cphase ^= 1u << s;
-                        tc::tc_fence_after();
-                        const uint32_t a_base = tc::smem_u32(smem) + (uint32_t)s * stage;
-                        const uint64_t ad = dconst | (uint64_t)(a_base >> 4);
-                        const uint64_t bd = dconst | (uint64_t)((a_base + a_bytes) >> 4);
-                        if (tc::elect_one()) {
-                            if (Lbkc == 128) {
-                                umma2_i8(d_tmem, ad, bd, idesc, (uint32_t)(kb != 0));
-                                umma2_i8(d_tmem, ad + 2, bd + 2, idesc, 1u);
-                                umma2_i8(d_tmem, ad + 4, bd + 4, idesc, 1u);
-                                umma2_i8(d_tmem, ad + 6, bd + 6, idesc, 1u);
-                            } else {
-                                umma2_i8(d_tmem, ad, bd, idesc, (uint32_t)(kb != 0));
-                                umma2_i8(d_tmem, ad + 2, bd + 2, idesc, 1u);
-                            }
-                            umma2_commit_mc(&empty_bar[s], 3);   // frees this stage in both CTAs
-                            if (kb == Lnumkb - 1) umma2_commit_mc(&tfull_bar[tile_iter], 3);
+                int s = 0;
+                for (;;) {
+                    uint32_t slot = 0;
+                    if (pair < Lpairs)
+                    for (int item = pair; item < Litems; item += Lpairs) {
+                        const uint32_t d_tmem = tmem_base + slot * (uint32_t)Lbn;
+                        // the slot's previous tile has been swept by all 32 epilogue warps of the pair (first use: passes)
+                        if (kStream) {
+                            tc::mbar_wait(&tempty_bar[slot], ((euse >> slot) & 1u) ^ 1u);
+                            euse ^= 1u << slot;
+                            tc::tc_fence_after();
                         }
-                        if (++s == Lstages) s = 0;
+                        for (int kb = 0; kb < Lnumkb; ++kb) {
+                            tc::mbar_wait(&full_bar[s], (cphase >> s) & 1u);
+                            cphase ^= 1u << s;
+                            tc::tc_fence_after();
+                            const uint32_t a_base = tc::smem_u32(smem) + (uint32_t)s * stage;
+                            const uint64_t ad = dconst | (uint64_t)(a_base >> 4);
+                            const uint64_t bd = dconst | (uint64_t)((a_base + a_bytes) >> 4);
+                            if (tc::elect_one()) {
+                                if (Lbkc == 128) {
+                                    umma2_i8(d_tmem, ad, bd, idesc, (uint32_t)(kb != 0));
+                                    umma2_i8(d_tmem, ad + 2, bd + 2, idesc, 1u);
+                                    umma2_i8(d_tmem, ad + 4, bd + 4, idesc, 1u);
+                                    umma2_i8(d_tmem, ad + 6, bd + 6, idesc, 1u);
+                                } else {
+                                    umma2_i8(d_tmem, ad, bd, idesc, (uint32_t)(kb != 0));
+                                    umma2_i8(d_tmem, ad + 2, bd + 2, idesc, 1u);
+                                }
+                                umma2_commit_mc(&empty_bar[s], 3);   // frees this stage in both CTAs
+                                if (kb == Lnumkb - 1) umma2_commit_mc(&tfull_bar[slot], 3);
+                            }
+                            if (++s == Lstages) s = 0;
+                        }
+                        if (++slot == Lslots) slot = 0;
                     }
+                    if (!kStream) break;                     // resident chains: the next layer's loads are gated by the producer
+                    tc::mbar_wait(layer_bar, lphase); lphase ^= 1u;
+                    if (*flag == 0u) break;
                 }
             }
         }
@@ -229,7 +262,7 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
         const int quarter = warp & 3;                        // TMEM lane quarter this warp may read
         const int group = (warp - 2) >> 2;                   // four warps share a quarter: every 4th 16-column chunk each
         const int etid = tid - 64;
-        uint32_t tphase = 0;                                 // per-tile phase bits of tfull_bar
+        uint32_t tuse = 0;                                   // per-slot use parity (tfull_bar)
         uint32_t nbar = 0;                                   // grid barriers passed so far
         const uint32_t eone = (uint32_t)(a.speculate >= 0);  // 1, opaque to the compiler (common.cuh niti_rule_a_consts)
         if (etid == 0) chain_trace(a.trace, 0, 1);
@@ -238,9 +271,11 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
             // layer record -> registers (see the producer)
             const int eM = L.M, eN = L.Ncols, eoh = L.out_h, eow = L.out_w, ent = L.n_tiles, eitems = L.items, epairs = L.pairs;
             const int ebn = L.bn, erelu = L.relu, epool = L.pool, epgg = L.pg_gate, edps = L.dp_slot;
+            const uint32_t eslots = (uint32_t)L.nslots; const bool estream = kStream && L.stream != 0;
             int8_t* const ey = L.y; const int8_t* const egate = L.gate; int8_t* const eyp = L.y_pool; const int8_t* const epgx = L.pg_x;
             uint32_t* const emax = L.maxabs; const int8_t* const eea = L.exp_a; const int8_t* const eeb = L.exp_b; int8_t* const eeo = L.exp_out;
             const bool active = pair < epairs;
+            const bool last_layer = l + 1 == a.nlayers;
             int shift = 0, kind = 0;
             uint32_t mx = 0;
             const int hw = eoh * eow;
@@ -248,7 +283,8 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
             // dependent global load per 16-column chunk.  Its addresses do not depend on the accumulators: prefetch those
             // lines into L2 now, under the K loop (measured: the pool-gradient store pass was bound by that latency).
             if (active && (epgx != nullptr || egate != nullptr)) {
-                for (int item = pair; item < eitems; item += epairs) {
+                int ahead = 0;
+                for (int item = pair; item < eitems && ahead < kChainMaxTiles; item += epairs, ++ahead) {
                     const int n_t = item % ent; const int m_t = item / ent;
                     const int row = m_t * 256 + (int)rank * 128 + quarter * 32 + lane;
                     if (row >= eM) continue;
@@ -267,12 +303,13 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
             // ---- speculative single pass ------------------------------------------------------------------------------
             // NITI's exponent needs max|acc| over the WHOLE tensor, which used to cost two sweeps over tensor memory with a
             // grid barrier between them (max pass | barrier | store pass | layer barrier).  The bit width of that maximum
-            // hardly ever changes from one training step to the next, so pass 0 reduces the maximum AND stores with the
+            // seldom changes from one training step to the next, so pass 0 reduces the maximum AND stores with the
             // shift predicted from the previous step's maximum (a.pred[slot]), tile by tile as the MMAs complete — the
-            // epilogue of tile i now overlaps the K loop of tile i+1 — and ONE grid barrier both publishes the maximum and
+            // epilogue of tile i overlaps the K loop of tile i+1 — and ONE grid barrier both publishes the maximum and
             // completes the layer.  Every CTA then checks the prediction against the true global maximum (a grid-uniform
-            // decision); only on a miss does pass 1 re-store from tensor memory (still intact: the next layer's MMAs are
-            // held back by layer_bar) behind a second barrier.  What is stored is always rounded with the true exponent.
+            // decision); only on a miss does pass 1 store again (resident layers: from tensor memory, still intact because
+            // the next layer's MMAs are held back by layer_bar; streaming layers: from a second run of the contraction)
+            // behind a second barrier.  What is stored is always rounded with the true exponent.
             // A miss costs a second sweep and a second barrier, so a layer speculates when that is cheap or unlikely: when its
             // CTA pairs hold several tiles (the predicted-store work hides under the K loops of the later tiles, a miss then
             // costs what the two-sweep schedule always pays) or when the slot's prediction held the last kSpecConfident
@@ -281,23 +318,26 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
             const uint32_t pred = __ldcg(a.pred + edps);
             const uint32_t conf = __ldcg(a.pred + kDpSlots + edps);
             const bool espec = a.speculate == 2 || (a.speculate == 1 && (conf >= kSpecConfident || eitems > epairs));
-            niti_rule_a(niti_bitwidth(pred), kind, shift);
+            niti_rule_a(niti_pred_bitwidth(pred), kind, shift);
             NitiRuleA rk = niti_rule_a_consts(shift, eone);
             int mxs = 0, mns = 0;                            // signed running max / min: one VIMNMX3 each per two accumulators
             for (int pass = 0; pass < 2; ++pass) {
-                uint32_t tile_iter = 0;
+                uint32_t slot = 0;
                 if (active)
-                for (int item = pair; item < eitems; item += epairs, ++tile_iter) {
+                for (int item = pair; item < eitems; item += epairs) {
                     const int n_t = item % ent; const int m_t = item / ent;
                     const int row0 = m_t * 256 + (int)rank * 128 + quarter * 32;
                     const int row = row0 + lane;
                     const int n0 = n_t * ebn;
-                    if (pass == 0) {
-                        tc::mbar_wait_backoff(&tfull_bar[tile_iter], (tphase >> tile_iter) & 1u);
+                    const uint32_t myslot = slot;
+                    if (++slot == eslots) slot = 0;
+                    if (pass == 0 || estream) {              // a fresh set of accumulators: wait for its last MMA
+                        tc::mbar_wait_backoff(&tfull_bar[myslot], (tuse >> myslot) & 1u);
+                        tuse ^= 1u << myslot;
                         tc::tc_fence_after();
-                        if (etid == 0 && tile_iter == 0) chain_trace(a.trace, l, 2);
+                        if (etid == 0 && item == pair && pass == 0) chain_trace(a.trace, l, 2);
                     }
-                    if (row0 >= eM) continue;               // warp-uniform
+                    if (row0 < eM) {                         // warp-uniform
                     const bool row_ok = row < eM;
                     // pixel coordinates of this row (pool / pool-gradient addressing)
                     int img = 0, py = 0, px = 0;
@@ -309,7 +349,7 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
                         const int col = n0 + c0;
                         uint4 x00, x01, x10, x11, gv;
                         size_t b00 = 0, b10 = 0;
-                        if (row_ok) {
+                        if (row_ok && (pass == 1 || espec)) {
                             if (epgx != nullptr) {
                                 const int w2 = eow * 2;
                                 b00 = (((size_t)img * (eoh * 2) + 2 * py) * w2 + 2 * px) * eN + col;
@@ -321,7 +361,7 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
                             }
                         }
                         uint32_t v[16];
-                        tmem_ld16(tmem_base + ((uint32_t)(quarter * 32) << 16) + tile_iter * (uint32_t)ebn + (uint32_t)c0, v);
+                        tmem_ld16(tmem_base + ((uint32_t)(quarter * 32) << 16) + myslot * (uint32_t)ebn + (uint32_t)c0, v);
                         tc::tmem_ld_wait();
                         if (pass == 0) {
                             if (row_ok) {
@@ -373,8 +413,13 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
                             *reinterpret_cast<uint4*>(ey + b10 + eN) = vand4(g, e3);
                         }
                     }
+                    }
+                    if (estream) {                           // this warp is done with the slot: hand it back to the MMA issuer
+                        tc::tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive_remote_relaxed(&tempty_bar[myslot], 0u);
+                    }
                 }
-                const bool last_layer = l + 1 == a.nlayers;
                 if (pass == 0) {
                     // ---- global max|acc|: warp max -> one atomicMax per CTA -> grid barrier -> (data parallel: peer exchange) ----
                     // (16 x 148 atomics on one word serialise in L2 for microseconds, hence the shared-memory stage)
@@ -395,21 +440,24 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
                     const uint32_t gmax = *bcast;
                     int kind2, shift2;
                     niti_rule_a(niti_bitwidth(gmax), kind2, shift2);
+                    const bool held = kind2 == kind && shift2 == shift;
                     if (blockIdx.x == 0 && etid == 0) {
                         if (eeo != nullptr) *eeo = (int8_t)((eea ? (int)*eea : 0) + (eeb ? (int)*eeb : 0) + (kind2 == 1 ? 0 : shift2));
-                        const bool held = kind2 == kind && shift2 == shift;
-                        a.pred[edps] = gmax;                             // every CTA read the old values before it arrived above
+                        a.pred[edps] = niti_pred_update(pred, niti_bitwidth(gmax));   // every CTA read the old values before it arrived above
                         a.pred[kDpSlots + edps] = held ? min(conf + 1u, 3u) : 0u;
                         atomicAdd(a.pred + 2 * kDpSlots + (espec ? (held ? 0 : 1) : 2), 1u);
                     }
-                    if (espec && kind2 == kind && shift2 == shift) {     // prediction held (grid-uniform): the layer is complete
+                    if (espec && held) {                                 // prediction held (grid-uniform): the layer is complete
                         if (etid == 0) chain_trace(a.trace, l, 5);
                         break;
                     }
                     kind = kind2; shift = shift2;
                     rk = niti_rule_a_consts(shift, eone);
+                    // run the contraction once more.  Only pairs that hold tiles are told: their issuing warps cannot fall a
+                    // phase behind (the epilogue needs their work before its next arrive); an idle pair sees one arrive per layer
+                    if (estream && active && etid == 0) { *flag = 1u; tc::mbar_arrive(layer_bar); }
                 } else {
-                    // prediction missed: the re-store is complete in this CTA; the next layer needs it complete everywhere
+                    // second pass done in this CTA; the next layer needs it complete everywhere
                     tc::tc_fence_before();
                     asm volatile("bar.sync 1, 512;" ::: "memory");
                     if (etid == 0) {
@@ -418,13 +466,17 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
                     }
                 }
             }
-            // this pair's tiles of the layer are drained: flip their phase bits
-            if (active) {
+            // resident layers: every slot this pair used goes back to the MMA issuer now (all reads of it are done)
+            if (kStream && active && !estream) {
+                tc::tc_fence_before();
+                __syncwarp();
                 const int mine = (eitems - pair + epairs - 1) / epairs;
-                tphase ^= (1u << mine) - 1u;
+                if (lane == 0)
+                    for (int t = 0; t < mine; ++t) mbar_arrive_remote_relaxed(&tempty_bar[t], 0u);
             }
-            if (etid == 0 && l + 1 < a.nlayers) {
-                tc::mbar_arrive(layer_bar);                                        // release this CTA's producer
+            if (etid == 0 && (kStream || !last_layer)) {
+                *flag = 0u;
+                tc::mbar_arrive(layer_bar);                                        // release this CTA's producer (and MMA issuer)
                 chain_trace(a.trace, l, 6);
             }
         }
@@ -444,20 +496,29 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
-// tile shape + residency plan: the largest BN that still gives >= ~2/3 of the CTA pairs a tile; every pair must be able to
-// keep all its tiles in its 512 TMEM columns
-bool chain_plan(int max_pairs, int M, int Ncols, int* bn_out, int* pairs_out, int* items_out) {
+// tile shape + schedule: resident when every pair can keep all its tiles in its 512 TMEM columns — then the largest BN that
+// still gives >= ~2/3 of the CTA pairs a tile — otherwise streaming (slots recycled, conv_chain.cu kernel comment) with the
+// widest tile the output allows (operand bytes per MMA fall with BN)
+bool chain_plan(int max_pairs, int M, int Ncols, int* bn_out, int* pairs_out, int* items_out, int* stream_out = nullptr) {
     const long m_tiles = (M + 255) / 256;
     int bn = 64;
     for (int cand : {256, 128}) {
         if (Ncols > cand / 2 && m_tiles * ((Ncols + cand - 1) / cand) >= (2 * max_pairs) / 3) { bn = cand; break; }
     }
     if (Ncols <= 64) bn = 64; else if (Ncols <= 128 && bn > 128) bn = 128;
-    const long items = m_tiles * ((Ncols + bn - 1) / bn);
-    const int pairs = (int)(items < max_pairs ? items : max_pairs);
-    const long per_pair = (items + pairs - 1) / pairs;
-    if (per_pair * bn > 512 || per_pair > kChainMaxTiles) return false;
+    long items = m_tiles * ((Ncols + bn - 1) / bn);
+    int pairs = (int)(items < max_pairs ? items : max_pairs);
+    long per_pair = (items + pairs - 1) / pairs;
+    int stream = 0;
+    if (per_pair * bn > 512 || per_pair > kChainMaxTiles) {
+        stream = 1;
+        bn = Ncols > 128 ? 256 : (Ncols > 64 ? 128 : 64);
+        items = m_tiles * ((Ncols + bn - 1) / bn);
+        if (items > 0x3fffffff) return false;
+        pairs = (int)(items < max_pairs ? items : max_pairs);
+    }
     *bn_out = bn; *pairs_out = pairs; *items_out = (int)items;
+    if (stream_out) *stream_out = stream;
     return true;
 }
 
@@ -475,11 +536,11 @@ int chain_lower(niti_ctx* ctx, const niti_chain_op* op, ChainLayer* L) {
     const int oh = conv_out_h(d), ow = conv_out_w(d);
     const int max_pairs = ctx->sm_count / 2;
     *L = ChainLayer{};
-    int bn, pairs, items;
+    int bn, pairs, items, stream = 0;
     if (op->op == 0) {
         if (!tma2_fwd_eligible(d) || d->oc % 16 != 0) return NITI_ERR_UNSUPPORTED;
         L->M = d->n * oh * ow; L->Ncols = d->oc;
-        if (!chain_plan(max_pairs, L->M, L->Ncols, &bn, &pairs, &items)) return NITI_ERR_UNSUPPORTED;
+        if (!chain_plan(max_pairs, L->M, L->Ncols, &bn, &pairs, &items, &stream)) return NITI_ERR_UNSUPPORTED;
         L->bkc = d->c % 128 == 0 ? 128 : 64;
         L->out_h = oh; L->out_w = ow; L->kh = d->kh; L->kw = d->kw; L->dil = d->dil; L->stride = d->stride;
         L->lower_h = -d->pad; L->lower_w = -d->pad; L->flip = 0;
@@ -498,7 +559,7 @@ int chain_lower(niti_ctx* ctx, const niti_chain_op* op, ChainLayer* L) {
         if (!tma2_dx_eligible(d) || d->c % 16 != 0) return NITI_ERR_UNSUPPORTED;
         const int pph = (d->kh - 1) * d->dil - d->pad, ppw = (d->kw - 1) * d->dil - d->pad;   // padding of the equivalent forward conv
         L->M = d->n * d->h * d->w; L->Ncols = d->c;
-        if (!chain_plan(max_pairs, L->M, L->Ncols, &bn, &pairs, &items)) return NITI_ERR_UNSUPPORTED;
+        if (!chain_plan(max_pairs, L->M, L->Ncols, &bn, &pairs, &items, &stream)) return NITI_ERR_UNSUPPORTED;
         L->bkc = d->oc % 128 == 0 ? 128 : 64;
         L->out_h = d->h; L->out_w = d->w; L->kh = d->kh; L->kw = d->kw; L->dil = d->dil; L->stride = 1;
         L->lower_h = -pph; L->lower_w = -ppw; L->flip = 1;
@@ -511,6 +572,7 @@ int chain_lower(niti_ctx* ctx, const niti_chain_op* op, ChainLayer* L) {
         if (op->pool_x != nullptr) { L->pg_x = op->pool_x; L->pg_gate = op->pool_gate; L->gate = nullptr; }
     }
     L->n_tiles = (L->Ncols + bn - 1) / bn; L->items = items; L->pairs = pairs; L->bn = bn;
+    L->nslots = 512 / bn > kChainMaxTiles ? kChainMaxTiles : 512 / bn; L->stream = stream;
     const int stage = 128 * L->bkc + (bn / 2) * L->bkc;
     L->stages = kChainStageArea / stage > kChainMaxStages ? kChainMaxStages : kChainStageArea / stage;
     L->y = op->out; L->maxabs = op->maxabs; L->dp_slot = op->dp_slot;
@@ -520,21 +582,26 @@ int chain_lower(niti_ctx* ctx, const niti_chain_op* op, ChainLayer* L) {
 struct niti_chain {
     ChainLayer* table;                // device
     int nlayers, grid;
+    bool streams;                     // some layer recycles its accumulator slots
     std::vector<ChainLayer> host;
 };
 
-static int chain_launch(niti_ctx* ctx, const ChainLayer* single, const ChainLayer* table, int nlayers, int grid, cudaStream_t st) {
-    if (int rc = niti_func_smem(ctx, table ? (const void*)chain_kernel<true> : (const void*)chain_kernel<false>, kChainSmem,
-                                "cudaFuncSetAttribute(chain_kernel)")) return rc;
+template <bool kTable, bool kStream>
+static int chain_launch_t(niti_ctx* ctx, const ChainLayer& byvalue, const ChainArgs& a, int grid, cudaStream_t st) {
+    if (int rc = niti_func_smem(ctx, (const void*)chain_kernel<kTable, kStream>, kChainSmem, "cudaFuncSetAttribute(chain_kernel)")) return rc;
+    cudaError_t e = niti_launch(ctx, NITI_PDL_FUSED, chain_kernel<kTable, kStream>, dim3(grid), dim3(kChainThreads), (size_t)kChainSmem, st, byvalue, a);
+    if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "launch chain_kernel", e);
+    return niti_check_launch(ctx, "chain_kernel");
+}
+
+static int chain_launch(niti_ctx* ctx, const ChainLayer* single, const ChainLayer* table, int nlayers, int grid, bool streams, cudaStream_t st) {
     ChainArgs a{};
     a.table = table; a.nlayers = nlayers; a.sync = ctx->ws_u32 + 52; a.dp = ctx->dp; a.trace = ctx->trace; a.pred = ctx->pred; a.speculate = ctx->speculate;
     a.tl = niti_tl_next(ctx, nlayers > 1 ? "chain" : (single && single->flip ? "dx_fused" : "fwd_fused"));
     a.trigger_late = (ctx->pdl & NITI_PDL_TRIGGER_LATE) ? 1 : 0;
     static const ChainLayer zero{};
-    cudaError_t e = table ? niti_launch(ctx, NITI_PDL_FUSED, chain_kernel<true>, dim3(grid), dim3(kChainThreads), (size_t)kChainSmem, st, zero, a)
-                          : niti_launch(ctx, NITI_PDL_FUSED, chain_kernel<false>, dim3(grid), dim3(kChainThreads), (size_t)kChainSmem, st, *single, a);
-    if (e != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "launch chain_kernel", e);
-    return niti_check_launch(ctx, "chain_kernel");
+    if (table) return streams ? chain_launch_t<true, true>(ctx, zero, a, grid, st) : chain_launch_t<true, false>(ctx, zero, a, grid, st);
+    return streams ? chain_launch_t<false, true>(ctx, *single, a, grid, st) : chain_launch_t<false, false>(ctx, *single, a, grid, st);
 }
 
 // single op through the chain kernel (the fused forward / dX entry points of api.cu)
@@ -542,7 +609,7 @@ int chain_run_single(niti_ctx* ctx, const niti_chain_op* op, cudaStream_t st) {
     ChainLayer L;
     int rc = chain_lower(ctx, op, &L);
     if (rc != NITI_OK) return rc;
-    return chain_launch(ctx, &L, nullptr, 1, 2 * L.pairs, st);
+    return chain_launch(ctx, &L, nullptr, 1, 2 * L.pairs, L.stream != 0, st);
 }
 
 bool chain_op_eligible(niti_ctx* ctx, const niti_chain_op* op) {
@@ -581,6 +648,7 @@ extern "C" int niti_chain_create(niti_ctx* ctx, const niti_chain_op* ops, int n,
             return rc == NITI_ERR_UNSUPPORTED ? niti_fail(ctx, rc, "niti_chain_create: an op is outside the fused kernel's contract") : rc;
         }
         if (c->host[i].pairs > max_pairs) max_pairs = c->host[i].pairs;
+        if (c->host[i].stream) c->streams = true;
     }
     c->nlayers = n; c->grid = 2 * max_pairs;
     cudaError_t e = cudaMalloc(&c->table, sizeof(ChainLayer) * (size_t)n);
@@ -594,7 +662,7 @@ extern "C" int niti_chain_create(niti_ctx* ctx, const niti_chain_op* ops, int n,
 extern "C" int niti_chain_run(niti_ctx* ctx, niti_chain* c, niti_stream st) {
     if (!ctx || !c || !c->table) return niti_fail(ctx, NITI_ERR_ARG, "niti_chain_run: bad argument");
     ctx->last_path = "chain";
-    return chain_launch(ctx, nullptr, c->table, c->nlayers, c->grid, (cudaStream_t)st);
+    return chain_launch(ctx, nullptr, c->table, c->nlayers, c->grid, c->streams, (cudaStream_t)st);
 }
 
 extern "C" int niti_chain_destroy(niti_ctx* ctx, niti_chain* c) {

@@ -200,10 +200,16 @@ stem2_fwd_kernel(const Stem2Params p) {
                 for (int g = 0; g < 4; ++g)
                     if (g < chunks) *reinterpret_cast<uint4*>(dst + g * 2048) = make_uint4(q[4 * g], q[4 * g + 1], q[4 * g + 2], q[4 * g + 3]);
             } else {
+                // 16 words (four 16-byte chunks) in flight per thread: with one chunk at a time a 7x7 row (49 taps, 13 chunks) paid 13
+                // L2 latencies per tile and the builders, not the tensor pipe or the stores, set the pace (ResNet stem: 0.66 ms)
                 if (!p.resident) tc::mbar_wait(&empty_bar[s], ph ^ 1u);
-                for (int g = 0; g < chunks; ++g) {
-                    const uint32_t q0 = word(4 * g), q1 = word(4 * g + 1), q2 = word(4 * g + 2), q3 = word(4 * g + 3);
-                    *reinterpret_cast<uint4*>(dst + g * 2048) = make_uint4(q0, q1, q2, q3);
+                for (int g0 = 0; g0 < chunks; g0 += 4) {
+                    uint32_t q[16];
+#pragma unroll
+                    for (int t = 0; t < 16; ++t) q[t] = word(4 * g0 + t);
+#pragma unroll
+                    for (int g = 0; g < 4; ++g)
+                        if (g0 + g < chunks) *reinterpret_cast<uint4*>(dst + (g0 + g) * 2048) = make_uint4(q[4 * g], q[4 * g + 1], q[4 * g + 2], q[4 * g + 3]);
                 }
             }
             tmax::fence_proxy_async_all();               // generic-proxy stores -> tensor-core (async proxy) reads
@@ -220,7 +226,8 @@ stem2_fwd_kernel(const Stem2Params p) {
         uint32_t tile_iter = 0, mx = 0;
         int shift = 0, kind = 0;
         const bool spec = p.speculate != 0;                                      // a miss costs what the recompute schedule always paid: no gating
-        niti_rule_a(niti_bitwidth(__ldcg(p.pred + p.dp_slot)), kind, shift);     // predicted from the previous step (conv_chain.cu)
+        const uint32_t pstate = __ldcg(p.pred + p.dp_slot);
+        niti_rule_a(niti_pred_bitwidth(pstate), kind, shift);                    // predicted from the previous steps (common.cuh)
         const uint32_t eone = (uint32_t)(p.speculate >= 0);                      // 1, opaque to the compiler
         NitiRuleA rk = niti_rule_a_consts(shift, eone);
         int mxs = 0, mns = 0;
@@ -290,7 +297,7 @@ stem2_fwd_kernel(const Stem2Params p) {
                 if (blockIdx.x == 0) {
                     if (p.exp_out != nullptr)
                         *p.exp_out = (int8_t)((p.exp_a ? (int)*p.exp_a : 0) + (p.exp_b ? (int)*p.exp_b : 0) + (kind2 == 1 ? 0 : shift2));
-                    p.pred[p.dp_slot] = gmax;                                    // every CTA read the old value before the barrier
+                    p.pred[p.dp_slot] = niti_pred_update(pstate, niti_bitwidth(gmax));   // every CTA read the old value before the barrier
                     atomicAdd(p.pred + 2 * kDpSlots + (spec ? (hit ? 0 : 1) : 2), 1u);
                 }
             }

@@ -311,6 +311,20 @@ __global__ void __launch_bounds__(kThreads) zero_insert_kernel(const uint32_t* _
     }
 }
 
+// the same for NHWC tensors in 16-byte channel groups (strided dX: api.cu niti_conv_dx_fused)
+__global__ void __launch_bounds__(kThreads) zero_insert_nhwc_kernel(const uint4* __restrict__ in, int n, int ih, int iw, int c16, int s, int oh, int ow,
+                                                                    uint4* __restrict__ out) {
+    const size_t total = (size_t)n * oh * ow * c16;
+    for (size_t i = (size_t)blockIdx.x * kThreads + threadIdx.x; i < total; i += (size_t)gridDim.x * kThreads) {
+        const int g = (int)(i % c16); size_t t = i / c16;
+        const int x = (int)(t % ow); t /= ow;
+        const int y = (int)(t % oh); const size_t b = t / oh;
+        const int sy = y / s, sx = x / s;
+        const bool live = sy * s == y && sx * s == x && sy < ih && sx < iw;
+        out[i] = live ? in[((b * ih + sy) * iw + sx) * c16 + g] : make_uint4(0u, 0u, 0u, 0u);
+    }
+}
+
 // NITI_Pad_Int8.cpp:26-66: every [h][w] plane copied into the middle of a zeroed [oh][ow] plane (rows pad..oh-pad-1, from column pad)
 __global__ void __launch_bounds__(kThreads) pad2d_kernel(const int8_t* __restrict__ in, int planes, int ih, int iw, int pad, int oh, int ow,
                                                          int8_t* __restrict__ out) {
@@ -426,6 +440,14 @@ extern "C" int niti_zero_insert_c4(niti_ctx* ctx, const int8_t* in, int slabs, i
     zero_insert_kernel<<<(unsigned)(blocks < 4096 ? blocks : 4096), kThreads, 0, (cudaStream_t)st>>>(
         reinterpret_cast<const uint32_t*>(in), slabs, ih, iw, oh, ow, sy, sx, reinterpret_cast<uint32_t*>(out));
     return niti_check_launch(ctx, "zero_insert");
+}
+
+int niti_zero_insert_nhwc(niti_ctx* ctx, const int8_t* in, int n, int ih, int iw, int c, int s, int oh, int ow, int8_t* out, niti_stream st) {
+    if (!ctx || !in || !out || n <= 0 || ih <= 0 || iw <= 0 || c <= 0 || c % 16 != 0 || s <= 0 || oh <= 0 || ow <= 0 || !aligned16(in) || !aligned16(out))
+        return niti_fail(ctx, NITI_ERR_ARG, "niti_zero_insert_nhwc: bad argument");
+    zero_insert_nhwc_kernel<<<grid_for(ctx, (size_t)n * oh * ow * (c / 16)), kThreads, 0, (cudaStream_t)st>>>(
+        reinterpret_cast<const uint4*>(in), n, ih, iw, c / 16, s, oh, ow, reinterpret_cast<uint4*>(out));
+    return niti_check_launch(ctx, "zero_insert_nhwc");
 }
 
 extern "C" int niti_pad2d(niti_ctx* ctx, const int8_t* in, int planes, int ih, int iw, int pad, int oh, int ow, int8_t* out, niti_stream st) {

@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIBPATH = os.path.join(_HERE, "libniti_b200.so")
+_LIBPATH = os.environ.get("NITI_B200_LIB") or os.path.join(_HERE, "libniti_b200.so")     # override: A/B runs of two builds
 
 PATH_AUTO, PATH_SIMT, PATH_TC, PATH_TMA, PATH_TMA2 = 0, 1, 2, 3, 4
 

@@ -133,10 +133,10 @@ class NitiNet:
             if kind == "conv":
                 _, oc, k, st, pad, relu = item
                 oc_p = (oc + pad_oc - 1) // pad_oc * pad_oc if pad_oc else oc
-                if pad_oc and item is fused[-1] and self.convs and k == 1 and oc_p < 64:
-                    # the classifier's dX contracts over its output channels: 64 of them (one K block of the fused kernel,
-                    # niti_conv_dx_fused) instead of 16 on the cp.async kernel + transpose + rescale launches; zero rows, exact
-                    oc_p = 64
+                if pad_oc and item is fused[-1] and self.convs and k == 1:
+                    # the classifier's dX contracts over its output channels: whole 64-channel K blocks of the fused kernel
+                    # (niti_conv_dx_fused) instead of the cp.async kernel + transpose + rescale launches; zero rows, exact
+                    oc_p = (oc_p + 63) // 64 * 64
                 L.d = make_desc(batch, c, h, w, oc_p, k, stride=st, pad=pad)
                 L.c_real, L.oc_real = c_real, oc
                 L.relu = relu
