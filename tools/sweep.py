@@ -1,6 +1,7 @@
 """BASELINE.json config 5: int8 conv fwd / dX / dW and GEMM shape sweep over the VGG-11 (b256) and ResNet-18
-(b128) layer shapes of SURVEY.md section 8 — TOP/s of the phase-1 contraction kernel (int8 x int8 -> int32 + max|acc|)
-against the measured dense INT8 tcgen05 peak.  ops = 2*M*N*K with the unpadded extents.
+(b128) layer shapes of SURVEY.md section 8 — TOP/s of the phase-1 contraction kernel (int8 x int8 -> int32 + max|acc|; columns
+fwd / dx / dw) and of the WHOLE fused op the training step launches (contraction + max|acc| + exponent + rule A + int8 store in one
+launch, no int32 in HBM; columns fwd_fused / dx_fused) against the measured dense INT8 tcgen05 peak.  ops = 2*M*N*K with the unpadded extents.
 
 Each shape: operands resident in HBM, 3 warm-up launches, then `iters` launches timed with CUDA events on the
 launching stream, a 256 MiB write between launches to flush L2 (timed separately and subtracted? no: the event
@@ -64,13 +65,20 @@ def main():
         acc_x = torch.empty(n * h * w * c, dtype=torch.int32, device="cuda")
         acc_w = torch.empty(oc * k * k * c, dtype=torch.int32, device="cuda")
         mx = torch.zeros(4, dtype=torch.int32, device="cuda")
+        # whole ops as the training step runs them (one launch: contraction + max|acc| + exponent + rule A + int8 store; the
+        # exponent prediction has settled after the warm-up launches, so the timed launches are single-sweep hits)
+        y8 = torch.empty((n, oh, ow, oc), dtype=torch.int8, device="cuda"); x8 = torch.empty((n, h, w, c), dtype=torch.int8, device="cuda")
+        ey = torch.zeros(1, dtype=torch.int8, device="cuda"); e7 = torch.full((1,), -7, dtype=torch.int8, device="cuda")
+        wtt = wt.permute(3, 1, 2, 0).contiguous()
         calls = {"fwd": lambda: nb.conv_fwd_acc(d, x, wt, acc_y, mx),
                  "dx": lambda: nb.conv_dx_acc(d, dy, wt, acc_x, mx),
-                 "dw": lambda: nb.conv_dw_acc(d, x, dy, acc_w, mx)}
+                 "dw": lambda: nb.conv_dw_acc(d, x, dy, acc_w, mx),
+                 "fwd_fused": lambda: nb.conv_fwd_fused(d, x, wt, e7, e7, y8, ey, True, acc_y, mx[1:2], dp_slot=1),
+                 "dx_fused": lambda: nb.conv_dx_fused(d, dy, wt, wtt, x8, None, acc_x, mx[2:3], dp_slot=2)}
         row = {"shape": name, "M": n * oh * ow, "N": oc, "K": c * k * k, "gop": ops / 1e9}
         for kind, fn in calls.items():
-            for _ in range(3):
-                fn()
+            for _ in range(4):
+                mx.zero_(); fn()
             torch.cuda.synchronize()
             ts = []
             for _ in range(args.iters):
@@ -78,6 +86,7 @@ def main():
                     flush.zero_()
                 a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 torch.cuda._sleep(1_000_000)      # ~0.5 ms: the host (ctypes call + 2-3 tensor-map encodes) runs ahead of the device
+                mx.zero_()
                 a.record(); fn(); b.record()
                 torch.cuda.synchronize()
                 ts.append(a.elapsed_time(b) * 1e-3)
@@ -86,8 +95,8 @@ def main():
                          "path": nb.last_path}
         rows.append(row)
         print(json.dumps(row), flush=True)
-        del x, wt, dy, acc_y, acc_x, acc_w
-    best = max(r[k]["TOP/s"] for r in rows for k in ("fwd", "dx", "dw"))
+        del x, wt, dy, acc_y, acc_x, acc_w, y8, x8, wtt
+    best = max(r[k]["TOP/s"] for r in rows for k in ("fwd", "dx", "dw", "fwd_fused", "dx_fused"))
     summary = {"peak_TOPs_measured": round(peak, 1), "best_TOPs": best, "best_frac": round(best / peak, 4),
                "l2": "not flushed" if args.no_flush else "flushed (256 MiB write) before every timed launch",
                "iters": args.iters, "rows": rows}
