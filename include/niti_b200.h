@@ -295,6 +295,12 @@ int niti_loss_grad(niti_ctx*, const int8_t* logits, const int8_t* ascale, const 
  * to the tensor cores' granule); the padding columns of grad are written as 0 */
 int niti_loss_grad_strided(niti_ctx*, const int8_t* logits, const int8_t* ascale, const int32_t* labels,
                            int batch, int classes, int stride, int8_t* grad, niti_stream);
+/* the float loss scalar of NITI_CPULoss_Int8::onExecute (source/backend/cpu/NITI_CPULoss_Int8.cpp:68-131): -mean over the batch of
+ * log softmax(2^ascale * logits)[label], with the reference's polynomial exp (compute/CommonOptFunction.cpp:1431-1456) and its
+ * summation order.  Monitoring only (floating point: matches the reference to 1e-5 relative); rows `stride` bytes apart,
+ * row_scratch: `batch` floats of device scratch, loss_out: one device float. */
+int niti_loss_value(niti_ctx*, const int8_t* logits, const int8_t* ascale, const int32_t* labels, int batch, int classes,
+                    int stride, float* row_scratch, float* loss_out, niti_stream);
 
 /* one-hot int32 targets [batch][classes] (the form NITI_CPULossGrad_Int8 receives, :148,170-178) -> class indices */
 int niti_onehot_labels(niti_ctx*, const int32_t* onehot, int batch, int classes, int32_t* labels, niti_stream);

@@ -242,6 +242,48 @@ __global__ void loss_grad_kernel(const int8_t* __restrict__ logits, const int8_t
     niti_tl_exit(tl);
 }
 
+// The float loss scalar the demo prints (NITI_CPULoss_Int8.cpp:68-131): -mean_i log softmax(2^ascale * logits_i)[label_i] with MNN's
+// polynomial exp (compute/CommonOptFunction.cpp:1431-1456).  Not on the training path (the gradient is loss_grad_kernel); here so
+// that a step's loss is read back as 4 bytes instead of the logits.  One block; rows in parallel, then summed in row order like
+// the reference (float addition is not associative).
+__global__ void __launch_bounds__(256) loss_value_kernel(const int8_t* __restrict__ logits, const int8_t* __restrict__ ascale_p,
+                                                         const int32_t* __restrict__ labels, int batch, int classes, int stride,
+                                                         float* __restrict__ rows, float* __restrict__ out) {
+    const float scale = exp2f((float)*ascale_p);             // exact for integer exponents, like powf(2, ascale)
+    for (int i = threadIdx.x; i < batch; i += blockDim.x) {
+        const int8_t* row = logits + (size_t)i * stride;
+        float mx = scale * (float)row[0];
+        for (int j = 1; j < classes; ++j) mx = fmaxf(mx, scale * (float)row[j]);
+        const float xLimit = 87.f, param = 0.6931471805599453f;
+        float sum = 0.f, picked = 0.f;
+        const int lab = labels[i];
+        for (int j = 0; j < classes; ++j) {
+            float x = __fsub_rn(__fmul_rn(scale, (float)row[j]), mx);
+            x = x > -xLimit ? x : -xLimit;
+            x = x < xLimit ? x : xLimit;
+            const int div = (int)__fdiv_rn(x, param);
+            const float basic = __int_as_float((div + 127) << 23);
+            const float t = __fsub_rn(x, __fmul_rn((float)div, param));
+            // the reference's Horner chain with separate multiplies and adds (no contraction into FMAs)
+            float pl = __fadd_rn(__fmul_rn(1.0f / 120, t), 1.0f / 24);
+            pl = __fadd_rn(__fmul_rn(pl, t), 1.0f / 6);
+            pl = __fadd_rn(__fmul_rn(pl, t), 0.5f);
+            pl = __fadd_rn(__fmul_rn(pl, t), 1.0f);
+            pl = __fadd_rn(__fmul_rn(pl, t), 1.0f);
+            const float e = __fmul_rn(basic, pl);
+            sum = __fadd_rn(sum, e);
+            if (j == lab) picked = e;
+        }
+        rows[i] = logf(__fmul_rn(picked, __fdiv_rn(1.f, sum)));
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float total = 0.f;
+        for (int i = 0; i < batch; ++i) total = __fadd_rn(total, rows[i]);
+        *out = __fmul_rn(__fdiv_rn(total, (float)batch), -1.f);
+    }
+}
+
 // generic 4-d permutation of int8 tensors through index arithmetic (boundary only; small tensors)
 // dst[a][b][c][d] (sizes A,B,C,D) = src[a*sa + b*sb + c*sc + d*sd]
 __global__ void __launch_bounds__(kThreads) permute_kernel(const int8_t* __restrict__ src, int8_t* __restrict__ dst,
@@ -405,6 +447,13 @@ extern "C" int niti_loss_grad_strided(niti_ctx* ctx, const int8_t* logits, const
                                  batch, classes, stride, grad, niti_tl_next(ctx, "loss_grad"));
     if (le != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "launch loss_grad", le);
     return niti_check_launch(ctx, "loss_grad");
+}
+extern "C" int niti_loss_value(niti_ctx* ctx, const int8_t* logits, const int8_t* ascale, const int32_t* labels, int batch, int classes,
+                               int stride, float* row_scratch, float* loss_out, niti_stream st) {
+    if (!ctx || !logits || !ascale || !labels || !row_scratch || !loss_out || batch <= 0 || classes < 2 || stride < classes)
+        return niti_fail(ctx, NITI_ERR_ARG, "niti_loss_value: bad argument (classes >= 2: the reference's softmax reads two entries)");
+    loss_value_kernel<<<1, 256, 0, (cudaStream_t)st>>>(logits, ascale, labels, batch, classes, stride, row_scratch, loss_out);
+    return niti_check_launch(ctx, "loss_value");
 }
 extern "C" int niti_loss_grad(niti_ctx* ctx, const int8_t* logits, const int8_t* ascale, const int32_t* labels,
                               int batch, int classes, int8_t* grad, niti_stream st) {

@@ -105,6 +105,7 @@ _SIGS = {
     "niti_maxpool_grad": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
     "niti_maxpool_grad_gated": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, C.c_int, _P]),
     "niti_loss_grad": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, _P, _P]),
+    "niti_loss_value": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, _P, _P, _P]),
     "niti_onehot_labels": (C.c_int, [_P, _P, C.c_int, C.c_int, _P, _P]),
     "niti_binary_i8": (C.c_int, [_P, C.c_int, _P, _P, C.c_size_t, C.c_int, _P, _P]),
     "niti_zero_insert_c4": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
@@ -450,6 +451,11 @@ class NitiB200:
     def loss_grad_strided(self, logits, ascale, labels, batch, classes, stride, grad, stream=None):
         self._ck(self.lib.niti_loss_grad_strided(self.h, _ptr(logits), _ptr(ascale), _ptr(labels), batch, classes, stride, _ptr(grad),
                                                  self._stream(stream)))
+
+    def loss_value(self, logits, ascale, labels, batch, classes, stride, row_scratch, loss_out, stream=None):
+        """float loss scalar of NITI_CPULoss_Int8 (monitoring) into the 1-element device tensor loss_out"""
+        self._ck(self.lib.niti_loss_value(self.h, _ptr(logits), _ptr(ascale), _ptr(labels), batch, classes, stride, _ptr(row_scratch),
+                                          _ptr(loss_out), self._stream(stream)))
 
     def loss_grad(self, logits, ascale, labels, batch, classes, grad, stream=None):
         self._ck(self.lib.niti_loss_grad(self.h, _ptr(logits), _ptr(ascale), _ptr(labels), batch, classes, _ptr(grad), self._stream(stream)))

@@ -233,6 +233,7 @@ class NitiNet:
                 j -= 1
             L.src = self.ops[j] if j >= 0 else None
             L.pg = None
+        self._bwd_chain = None
         if not (self.fused_ops and hasattr(nb, "conv_fwd_fused_pool")):
             return
 
@@ -273,6 +274,43 @@ class NitiNet:
                 flush(); plan.append(("op", i))
         flush()
         self._fwd_plan = plan
+        self._plan_backward_chain()
+
+    # pixels per GPU below which a dX launch is latency-bound (a partial wave of <= 64 CTAs whose 8-10 us are launch, prologue,
+    # two barriers and drain): those layers' dX ops run as ONE persistent launch, their dW launches follow it on the side stream
+    BWD_CHAIN_MAX_PIXELS = int(os.environ.get("NITI_B200_BWD_CHAIN_PIXELS", "1024"))
+
+    def _dx_chain_op(self, L):
+        nconv = len(self.convs)
+        prev = self.ops[self.ops.index(L) - 1]
+        gate = L.src is not None and L.src.relu
+        pg = getattr(L, "pg", None)
+        slot = self.maxabs[nconv + L.index: nconv + L.index + 1]
+        if pg is not None:
+            return self.nb.chain_op(L.d, 1, L.dy, L.wt, pg[1], slot, nconv + L.index, pool_x=pg[0].x, pool_gate=pg[2])
+        return self.nb.chain_op(L.d, 1, L.dy, L.wt, prev.dy, slot, nconv + L.index, gate=L.x if gate else None)
+
+    def _plan_backward_chain(self):
+        """The deepest layers (classifier, FC, 2x2 / 4x4 feature maps) in backward order, as long as each dX is fused-eligible,
+        small and writes straight into the gradient tensor the next one reads."""
+        self._bwd_chain = None
+        nb = self.nb
+        if not (self.fused_ops and hasattr(nb, "chain_create")) or os.environ.get("NITI_B200_BWD_CHAIN", "1") == "0":
+            return
+        layers = []
+        for L in reversed(self.convs):
+            if L.index == 0 or L.wt is None:
+                break
+            i = self.ops.index(L)
+            prev = self.ops[i - 1]
+            pg = getattr(L, "pg", None)
+            # the op in front must be the producer itself (ReLU folded), an alias flatten, or a pool folded into this dX
+            simple = prev.kind == "conv" or (prev.kind == "flatten" and prev.alias) or (prev.kind == "pool" and pg is not None)
+            if not simple or L.d.n * L.d.h * L.d.w > self.BWD_CHAIN_MAX_PIXELS or not nb.chain_op_eligible(self._dx_chain_op(L)):
+                break
+            layers.append(L)
+        if len(layers) >= 2:
+            self._bwd_chain = (nb.chain_create([self._dx_chain_op(L) for L in layers]), layers)
 
     def _chain_op(self, L):
         P = L.pool_op
@@ -411,20 +449,17 @@ class NitiNet:
             dx = prev.dy if prev is not None else None       # gradient w.r.t. this op's input
             gate = L.src is not None and L.src.relu          # input came through a folded ReLU
             if L.kind == "conv":
-                acc_dw = self.dw_acc[L.dw_off: L.dw_off + L.n_w]
-                with self._beside():
-                    if self.overlap_dw:
-                        self._timed("dw", L.ops, lambda: nb.conv_dw_accumulate(L.d, L.x, dy, acc_dw))
-                    else:
-                        self._timed("dw", L.ops, lambda: nb.conv_dw_acc(L.d, L.x, dy, acc_dw, None))
-                    if self.dist is not None and L.index in self._buckets:
-                        lo, hi = self._buckets[L.index]    # this bucket's dW sums are complete: start its exchange
-                        if self.peer_sum:
-                            self.comm.wait_stream(torch.cuda.current_stream(self.dev))
-                            with torch.cuda.stream(self.comm):
-                                nb.dp_allreduce(lo, (hi - lo + 3) // 4 * 4, self._bucket_slot[L.index])
-                        else:
-                            self._pending.append(self.dist.all_reduce(self.dw_acc[lo:hi], op=self.dist.ReduceOp.SUM, async_op=True))
+                chained = self._bwd_chain is not None and L in self._bwd_chain[1]
+                if chained and L is not self._bwd_chain[1][0]:
+                    continue                                   # its dX ran in the chain, its dW right behind the chain
+                self._launch_dw(L)
+                if chained:
+                    # the latency-bound dX ops of the deepest layers in one persistent launch, then their dW launches
+                    layers = self._bwd_chain[1]
+                    self._timed("dx", sum(M.ops for M in layers), lambda: nb.chain_run(self._bwd_chain[0]))
+                    for M in layers[1:]:
+                        self._launch_dw(M)
+                    continue
                 if dx is not None:
                     slot = self.maxabs[nconv + L.index: nconv + L.index + 1]
                     if self.fused_ops:
@@ -477,6 +512,25 @@ class NitiNet:
             slot = self.maxabs[2 * nconv + L.index: 2 * nconv + L.index + 1]
             nb.absmax(acc_dw, L.n_w, slot)
             nb.rescale_grad(acc_dw, L.n_w, slot, 2, None, L.w)
+
+    def _launch_dw(self, L):
+        """dW of one layer on the side stream (its dY is complete on the main stream) and, data parallel, the exchange of the
+        gradient bucket this layer closes"""
+        nb = self.nb
+        acc_dw = self.dw_acc[L.dw_off: L.dw_off + L.n_w]
+        with self._beside():
+            if self.overlap_dw:
+                self._timed("dw", L.ops, lambda: nb.conv_dw_accumulate(L.d, L.x, L.dy, acc_dw))
+            else:
+                self._timed("dw", L.ops, lambda: nb.conv_dw_acc(L.d, L.x, L.dy, acc_dw, None))
+            if self.dist is not None and L.index in self._buckets:
+                lo, hi = self._buckets[L.index]    # this bucket's dW sums are complete: start its exchange
+                if self.peer_sum:
+                    self.comm.wait_stream(torch.cuda.current_stream(self.dev))
+                    with torch.cuda.stream(self.comm):
+                        nb.dp_allreduce(lo, (hi - lo + 3) // 4 * 4, self._bucket_slot[L.index])
+                else:
+                    self._pending.append(self.dist.all_reduce(self.dw_acc[lo:hi], op=self.dist.ReduceOp.SUM, async_op=True))
 
     def step(self):
         self.forward()

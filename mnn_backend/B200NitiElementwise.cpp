@@ -165,6 +165,36 @@ private:
     int mBatch = 0, mClasses = 0;
 };
 
+// the float loss scalar (NITI_CPULoss_Int8.cpp:68-131): same operands as the gradient op, one float out
+class B200NitiLoss : public Execution {
+public:
+    explicit B200NitiLoss(Backend* bn) : Execution(bn) {}
+    virtual ErrorCode onResize(const std::vector<Tensor*>& inputs, const std::vector<Tensor*>& outputs) override {
+        auto logits = inputs[0];
+        mBatch = logits->batch();
+        mClasses = logits->elementSize() / mBatch;
+        mTargetClasses = inputs[2]->elementSize() / mBatch;      // one-hot rows may be narrower than the logit rows (:98-108)
+        mLabels.reset(Tensor::createDevice<int32_t>({mBatch}));
+        mRows.reset(Tensor::createDevice<float>({mBatch}));
+        if (!backend()->onAcquireBuffer(mLabels.get(), Backend::DYNAMIC) || !backend()->onAcquireBuffer(mRows.get(), Backend::DYNAMIC)) return OUT_OF_MEMORY;
+        backend()->onReleaseBuffer(mLabels.get(), Backend::DYNAMIC);
+        backend()->onReleaseBuffer(mRows.get(), Backend::DYNAMIC);
+        return NO_ERROR;
+    }
+    virtual ErrorCode onExecute(const std::vector<Tensor*>& inputs, const std::vector<Tensor*>& outputs) override {
+        auto bn = static_cast<B200Backend*>(backend());
+        int32_t* labels = (int32_t*)(uintptr_t)mLabels->deviceId();
+        int rc = bn->api().onehot_labels(bn->ctx(), (const int32_t*)(uintptr_t)inputs[2]->deviceId(), mBatch, mTargetClasses, labels, bn->stream());
+        if (rc == NITI_OK)
+            rc = bn->api().loss_value(bn->ctx(), dev(inputs[0]), dev(inputs[1]), labels, mBatch, mClasses, mClasses,
+                                      (float*)(uintptr_t)mRows->deviceId(), (float*)(uintptr_t)outputs[0]->deviceId(), bn->stream());
+        return toErrorCode(rc, bn, "niti_loss_value");
+    }
+private:
+    std::shared_ptr<Tensor> mLabels, mRows;
+    int mBatch = 0, mClasses = 0, mTargetClasses = 0;
+};
+
 class B200NitiBinary : public Execution {
 public:
     B200NitiBinary(Backend* bn, int op) : Execution(bn), mOp(op) {}
@@ -239,6 +269,19 @@ public:
         return new B200NitiLossGrad(backend);
     }
 };
+class LossCreator : public B200Backend::Creator {
+public:
+    virtual Execution* onCreate(const std::vector<Tensor*>& inputs, const std::vector<Tensor*>& outputs,
+                                const MNN::Op* op, Backend* backend) const override {
+        if (inputs.size() < 3 || outputs.empty() || !isInt8(inputs[0]) || !isInt8(inputs[1])) return nullptr;
+        auto logits = inputs[0]; auto target = inputs[2];
+        const int b = logits->batch();
+        if (b <= 0 || logits->elementSize() <= 0 || logits->elementSize() % b != 0 || logits->elementSize() / b < 2) return nullptr;
+        if (TensorUtils::getDescribe(logits)->dimensionFormat == MNN_DATA_FORMAT_NC4HW4) return nullptr;      // [b][classes] rows expected
+        if (target->getType().bits != 32 || target->elementSize() % b != 0 || target->elementSize() > logits->elementSize()) return nullptr;
+        return new B200NitiLoss(backend);
+    }
+};
 class BinaryCreator : public B200Backend::Creator {
 public:
     virtual Execution* onCreate(const std::vector<Tensor*>& inputs, const std::vector<Tensor*>& outputs,
@@ -258,6 +301,7 @@ REGISTER_B200_OP_CREATOR(PoolGradCreator, OpType_NITI_PoolGrad_Int8);
 REGISTER_B200_OP_CREATOR(LeftPoolGradCreator, OpType_NITI_LeftPoolGrad_Int8);
 REGISTER_B200_OP_CREATOR(PadCreator, OpType_NITI_PAD_Int8);
 REGISTER_B200_OP_CREATOR(LossGradCreator, OpType_NITI_LOSS_Grad_Int8);
+REGISTER_B200_OP_CREATOR(LossCreator, OpType_NITI_LOSS_Int8);
 REGISTER_B200_OP_CREATOR(BinaryCreator, OpType_BinaryOp);
 REGISTER_B200_OP_CREATOR(ReluCreator, OpType_NITI_Relu_Int8);
 REGISTER_B200_OP_CREATOR(ReluGradCreator, OpType_NITI_ReluGrad_Int8);

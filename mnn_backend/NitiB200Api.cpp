@@ -68,6 +68,7 @@ const NitiB200Api& nitiApi() {
     NITI_BIND(maxpool, niti_maxpool)
     NITI_BIND(maxpool_grad, niti_maxpool_grad)
     NITI_BIND(loss_grad, niti_loss_grad)
+    NITI_BIND(loss_value, niti_loss_value)
     NITI_BIND(onehot_labels, niti_onehot_labels)
     NITI_BIND(binary_i8, niti_binary_i8)
     NITI_BIND(zero_insert_c4, niti_zero_insert_c4)

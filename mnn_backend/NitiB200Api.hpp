@@ -32,6 +32,7 @@ struct NitiB200Api {
     decltype(&niti_maxpool)           maxpool           = nullptr;
     decltype(&niti_maxpool_grad)      maxpool_grad      = nullptr;
     decltype(&niti_loss_grad)         loss_grad         = nullptr;
+    decltype(&niti_loss_value)        loss_value        = nullptr;
     decltype(&niti_onehot_labels)     onehot_labels     = nullptr;
     decltype(&niti_binary_i8)         binary_i8         = nullptr;
     decltype(&niti_zero_insert_c4)    zero_insert_c4    = nullptr;

@@ -413,3 +413,34 @@ void niti_o_loss_grad(const int8_t* logits, int ascale, const int32_t* labels, i
     for (long i = 0; i < nel; ++i) grad[i] = (int8_t)r[i];
     free(r); free(g); free(e);
 }
+
+/* NITI_CPULoss_Int8.cpp:68-131 — the monitoring loss.  Float arithmetic in the reference's order: dequantise with powf(2, ascale),
+ * MNNSoftmax per row (CommonOptFunction.cpp:1431-1456: max over the row, exp(x) = 2^div * degree-5 polynomial of the remainder,
+ * normalise by the reciprocal of the sum), logf, pick the target class (one-hot row, :98-108), sum rows in order, -mean. */
+#include <math.h>
+float niti_o_loss_value(const int8_t* logits, int ascale, const int32_t* labels, int batch, int classes) {
+    const float scale = powf(2.0f, (float)ascale);
+    float total = 0.f;
+    for (int i = 0; i < batch; ++i) {
+        const int8_t* row = logits + (size_t)i * classes;
+        float mx = scale * row[0];
+        for (int j = 1; j < classes; ++j) { const float v = scale * row[j]; mx = v > mx ? v : mx; }
+        const float xLimit = 87, param = 0.6931471805599453f;
+        float sum = 0.f, picked = 0.f;
+        for (int j = 0; j < classes; ++j) {
+            float x = scale * row[j] - mx;
+            x = x > -xLimit ? x : -xLimit;
+            x = x < xLimit ? x : xLimit;
+            const int div = (int)(x / param);
+            const int div2 = (div + 127) << 23;
+            const float rem = x - div * param;
+            float basic; memcpy(&basic, &div2, 4);
+            const float t = rem;
+            const float e = basic * (((((1.0f / 120 * t + 1.0f / 24) * t + 1.0f / 6) * t + 0.5f) * t + 1.0f) * t + 1.0f);
+            sum += e;
+            if (j == labels[i]) picked = e;
+        }
+        total += logf(picked * (1.f / sum));
+    }
+    return total / batch * (-1);
+}

@@ -90,6 +90,9 @@ void niti_o_maxpool_grad(const int8_t* x, const int8_t* y, const int8_t* dy, int
                          int k, int s, int8_t* dx);
 void niti_o_loss_grad(const int8_t* logits, int ascale, const int32_t* labels, int batch, int classes,
                       int8_t* grad);
+/* the float loss scalar the demo prints (NITI_CPULoss_Int8.cpp:68-131): -mean_i log softmax(2^ascale * logits_i)[label_i] with
+ * MNN's polynomial exp (compute/CommonOptFunction.cpp:1431-1456, the build without MNN_USE_SSE) */
+float niti_o_loss_value(const int8_t* logits, int ascale, const int32_t* labels, int batch, int classes);
 
 #ifdef __cplusplus
 }

@@ -90,6 +90,8 @@ class Oracle:
         L.niti_o_maxpool.argtypes = [_i8p] + [C.c_int] * 6 + [_i8p]
         L.niti_o_maxpool_grad.argtypes = [_i8p, _i8p, _i8p] + [C.c_int] * 6 + [_i8p]
         L.niti_o_loss_grad.argtypes = [_i8p, C.c_int, _i32p, C.c_int, C.c_int, _i8p]
+        L.niti_o_loss_value.argtypes = [_i8p, C.c_int, _i32p, C.c_int, C.c_int]
+        L.niti_o_loss_value.restype = C.c_float
 
     # ---- accumulators (int32) ; each returns (acc, worst_partial_sum)
     def conv_fwd_acc(self, s, x, w):
@@ -223,6 +225,10 @@ class Oracle:
         self.lib.niti_o_loss_grad(_c(logits), int(ascale), _c(labels, np.int32), b, k, g)
         return g
 
+    def loss_value(self, logits, ascale, labels):
+        b, k = logits.shape
+        return float(self.lib.niti_o_loss_value(_c(logits), int(ascale), _c(labels, np.int32), b, k))
+
 
 class Reference:
     """The unmodified reference, via oracle/_ref/libniti_ref_driver.so (None-able: see available())."""
@@ -253,6 +259,7 @@ class Reference:
         L.ref_maxpool.argtypes = [_i8p] + [C.c_int] * 6 + [_i8p]
         L.ref_maxpool_grad.argtypes = [_i8p, _i8p] + [C.c_int] * 6 + [_i8p]
         L.ref_loss_grad.argtypes = [_i8p, C.c_int, _i32p, C.c_int, C.c_int, _i8p]
+        L.ref_loss_value.argtypes = [_i8p, C.c_int, _i32p, C.c_int, C.c_int, C.POINTER(C.c_float)]
 
     @staticmethod
     def _sp(s):
@@ -327,6 +334,15 @@ class Reference:
         rc = self.lib.ref_loss_grad(_c(logits), int(ascale), onehot, b, k, g)
         assert rc == 0, rc
         return g
+
+    def loss_value(self, logits, ascale, labels):
+        b, k = logits.shape
+        onehot = np.zeros((b, k), np.int32)
+        onehot[np.arange(b), labels] = 1
+        out = C.c_float(0)
+        rc = self.lib.ref_loss_value(_c(logits), int(ascale), onehot, b, k, C.byref(out))
+        assert rc == 0, rc
+        return float(out.value)
 
     # ---- whole training steps through the reference's Module / OpGrad / NITI_SGD (ref_driver.cpp) ----
     def use_backend(self, forward_type, plugin=None, threads=4):

@@ -150,6 +150,16 @@ int ref_loss_grad(const int8_t* logits, int ascale, const int* onehot, int b, in
     copyOut(grads[0], grad);
     return 0;
 }
+// the loss scalar itself: OpType_NITI_LOSS_Int8 -> NITI_CPULoss_Int8::onExecute (source/backend/cpu/NITI_CPULoss_Int8.cpp:68-131)
+int ref_loss_value(const int8_t* logits, int ascale, const int* onehot, int b, int classes, float* out) {
+    auto lv = constI8(logits, {b, classes, 1, 1});
+    auto tv = _Const(onehot, {b, classes}, NCHW, halide_type_of<int32_t>());
+    auto loss = _NITI_LOSS_SUM(lv, _Scalar<int8_t>((int8_t)ascale), tv, b, classes, 1, 1);
+    auto lp = loss->readMap<float>();
+    if (lp == nullptr) return -2;
+    *out = lp[0];
+    return 0;
+}
 
 
 // ---- backend selection ----------------------------------------------------------------------------

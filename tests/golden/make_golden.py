@@ -85,6 +85,7 @@ def main():
         lab = rng.integers(0, 10, size=64).astype(np.int32)
         ew[f"loss_grad.{a}.logits"], ew[f"loss_grad.{a}.labels"] = lg, lab
         ew[f"loss_grad.{a}.grad"] = ref.loss_grad(lg, a, lab)
+        ew[f"loss_value.{a}"] = np.float32(ref.loss_value(lg, a, lab))
     np.savez_compressed(os.path.join(OUT, "elementwise_cases.npz"), **ew)
 
     # ---- OpType_NITI_MatMul_Int8 (a4) and OpType_NITI_GradientSplitCONV_Int8 (a5): neither has a producer the demo

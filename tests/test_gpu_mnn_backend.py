@@ -60,15 +60,17 @@ def test_elementwise_ops_identical(res):
 def test_step_glue_ops_get_b200_executions(res):
     """pool gradient, zero insertion (stride-2 dX), pad, loss gradient and the int8 Binary op of the
     SGD update are created on the B200 backend, not on the executor's CPU backup backend"""
-    for k in ("binary", "pool_grad", "loss_grad", "pad", "left_pool_grad"):
+    for k in ("binary", "pool_grad", "loss_grad", "loss", "pad", "left_pool_grad"):
         assert int(res["created_" + k]) > 0, k
 
 
 def test_lenet_training_steps_identical(res):
     """3 steps of the MNIST NITIInt8 model at the demo's batch size 64: logits, exponents, losses and all updated
     weights equal between the reference CPU backend and the B200 backend."""
-    for k in ("logits", "e_logits", "loss", "w0", "w1", "w2", "w3"):
+    for k in ("logits", "e_logits", "w0", "w1", "w2", "w3"):
         assert np.array_equal(res["cpu_lenet_" + k], res["b200_lenet_" + k]), k
+    # the loss scalar is the one floating-point op of the loop (NITI_CPULoss_Int8, now a B200 Execution too): 1e-5 relative
+    assert np.allclose(res["cpu_lenet_loss"], res["b200_lenet_loss"], rtol=1e-5, atol=0), (res["cpu_lenet_loss"], res["b200_lenet_loss"])
 
 
 @pytest.fixture(scope="module")

@@ -418,6 +418,16 @@ def test_elementwise_vs_oracle_and_golden(nb, oracle, golden_ew):
         nb.loss_grad(dev(lg), torch.tensor([a], dtype=torch.int8, device="cuda"), dev(lab.astype(np.int32)),
                      lg.shape[0], lg.shape[1], out)
         assert np.array_equal(out.cpu().numpy(), g[f"loss_grad.{a}.grad"]), a
+        # the float loss scalar (NITI_CPULoss_Int8): floating point — tolerance 1e-5 relative against the reference's value
+        # and the oracle; also through padded rows (stride 16)
+        rows = torch.empty(lg.shape[0], dtype=torch.float32, device="cuda"); loss = torch.zeros(1, dtype=torch.float32, device="cuda")
+        asc = torch.tensor([a], dtype=torch.int8, device="cuda")
+        nb.loss_value(dev(lg), asc, dev(lab.astype(np.int32)), lg.shape[0], lg.shape[1], lg.shape[1], rows, loss)
+        assert float(loss.item()) == pytest.approx(float(g[f"loss_value.{a}"]), rel=1e-5), a
+        assert float(loss.item()) == pytest.approx(oracle.loss_value(lg, a, lab), rel=1e-5), a
+        padded = torch.zeros((lg.shape[0], 16), dtype=torch.int8, device="cuda"); padded[:, :lg.shape[1]] = dev(lg)
+        nb.loss_value(padded, asc, dev(lab.astype(np.int32)), lg.shape[0], lg.shape[1], 16, rows, loss)
+        assert float(loss.item()) == pytest.approx(float(g[f"loss_value.{a}"]), rel=1e-5), a
 
 
 def test_layout_round_trips(nb):

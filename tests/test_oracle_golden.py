@@ -57,6 +57,8 @@ def test_elementwise_match_reference(oracle, golden_ew):
     for a in (-9, -7, -5, -3, 0, 1):
         got = oracle.loss_grad(g[f"loss_grad.{a}.logits"], a, g[f"loss_grad.{a}.labels"])
         assert np.array_equal(got, g[f"loss_grad.{a}.grad"]), a
+        # float loss scalar of NITI_CPULoss_Int8: tolerance 1e-6 relative (same operations, same order)
+        assert oracle.loss_value(g[f"loss_grad.{a}.logits"], a, g[f"loss_grad.{a}.labels"]) == pytest.approx(float(g[f"loss_value.{a}"]), rel=1e-6)
 
 
 def test_psto_properties(oracle):

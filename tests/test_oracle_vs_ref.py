@@ -114,3 +114,5 @@ def test_live_reference_step_glue_ops(oracle, ref, shp, k, s):
         lg = rng.integers(-127, 128, size=(32, 12), dtype=np.int8)
         lab = rng.integers(0, 10, size=32)
         assert np.array_equal(ref.loss_grad(lg, asc, lab), oracle.loss_grad(lg, asc, lab))
+        # the float loss scalar (NITI_CPULoss_Int8): same operations in the same order -> 1e-6 relative
+        assert oracle.loss_value(lg, asc, lab) == pytest.approx(ref.loss_value(lg, asc, lab), rel=1e-6)
