@@ -276,10 +276,11 @@ class NitiNet:
         self._fwd_plan = plan
         self._plan_backward_chain()
 
-    # pixels per GPU below which a dX launch is latency-bound (a partial wave of <= 64 CTAs whose 8-10 us are launch, prologue,
-    # two barriers and drain): those layers' dX ops run as ONE persistent launch, their dW launches follow it on the side stream
-    BWD_CHAIN_MAX_PIXELS = int(os.environ.get("NITI_B200_BWD_CHAIN_PIXELS", "1024"))
-
+    # Backward chain (opt-in, NITI_B200_BWD_CHAIN_PIXELS=<pixels per GPU>): the dX ops of the deepest layers (<= that many pixels)
+    # as ONE persistent launch, their dW launches behind it.  Measured on VGG-11 b256 (profiles/ab/knob_bwd_chain.txt): off
+    # 463.3 us/step, 256 px (3 FC layers) 469.2, 1024 px (+ conv8, conv7) 479.6, 4096 px 484.5 — the launches it saves cost less
+    # than the dW kernels it pushes behind the chain (they no longer run beside these dX ops and pile up after the last dX).
+    # Default: off.
     def _dx_chain_op(self, L):
         nconv = len(self.convs)
         prev = self.ops[self.ops.index(L) - 1]
@@ -295,7 +296,8 @@ class NitiNet:
         small and writes straight into the gradient tensor the next one reads."""
         self._bwd_chain = None
         nb = self.nb
-        if not (self.fused_ops and hasattr(nb, "chain_create")) or os.environ.get("NITI_B200_BWD_CHAIN", "1") == "0":
+        max_pixels = int(os.environ.get("NITI_B200_BWD_CHAIN_PIXELS", "0"))
+        if not (self.fused_ops and hasattr(nb, "chain_create")) or max_pixels <= 0:
             return
         layers = []
         for L in reversed(self.convs):
@@ -306,7 +308,7 @@ class NitiNet:
             pg = getattr(L, "pg", None)
             # the op in front must be the producer itself (ReLU folded), an alias flatten, or a pool folded into this dX
             simple = prev.kind == "conv" or (prev.kind == "flatten" and prev.alias) or (prev.kind == "pool" and pg is not None)
-            if not simple or L.d.n * L.d.h * L.d.w > self.BWD_CHAIN_MAX_PIXELS or not nb.chain_op_eligible(self._dx_chain_op(L)):
+            if not simple or L.d.n * L.d.h * L.d.w > max_pixels or not nb.chain_op_eligible(self._dx_chain_op(L)):
                 break
             layers.append(L)
         if len(layers) >= 2:

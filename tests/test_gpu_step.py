@@ -85,3 +85,22 @@ def test_cuda_graph_replay_equals_eager(nb, spec, chw, batch):
     for wa, wb in zip(a.weights_oihw(), b.weights_oihw()):
         assert np.array_equal(wa, wb)
     assert torch.equal(a.logits, b.logits)
+
+
+def test_backward_chain_is_bit_identical(nb, monkeypatch):
+    """NITI_B200_BWD_CHAIN_PIXELS: the deepest layers' dX ops as one persistent launch (their dW launches behind it) gives the
+    same weights and logits as the default schedule (one dX launch per layer)"""
+    x, labels = _data(8, (3, 16, 16), 5)
+    xin = torch.from_numpy(np.ascontiguousarray(np.transpose(x, (0, 2, 3, 1))))
+    a = NitiNet(nb, VGG_NET, 8, (3, 16, 16)); a.init_weights(seed=4)
+    monkeypatch.setenv("NITI_B200_BWD_CHAIN_PIXELS", "4096")
+    b = NitiNet(nb, VGG_NET, 8, (3, 16, 16)); b.init_weights(seed=4)
+    assert a._bwd_chain is None and b._bwd_chain is not None and len(b._bwd_chain[1]) >= 3
+    for net in (a, b):
+        net.set_input(xin, -7, torch.from_numpy(labels))
+    for _ in range(3):
+        a.step(); b.step()
+    torch.cuda.synchronize()
+    for wa, wb in zip(a.weights_oihw(), b.weights_oihw()):
+        assert np.array_equal(wa, wb)
+    assert torch.equal(a.logits, b.logits)
