@@ -189,6 +189,8 @@ int niti_ctx_create(int device, niti_ctx** out) {
     ctx->pred = ctx->ws_u32 + 64;
     const char* dwc = getenv("NITI_B200_DW_CTAS");        // CTAs a dW launch may spread its split-K over (default: every SM)
     ctx->dw_ctas = dwc ? atoi(dwc) : 0;
+    const char* dwg = getenv("NITI_B200_DW_G");
+    ctx->dw_g = dwg ? atoi(dwg) : 0;
     const char* sp = getenv("NITI_B200_SPECULATE");        // 0: two-sweep schedule (max pass | barrier | store pass) for A/B runs
     ctx->speculate = sp ? atoi(sp) : 1;
     if (ctx->speculate < 0 || ctx->speculate > 2) ctx->speculate = 1;

@@ -26,6 +26,7 @@ struct niti_ctx {
     uint32_t* pred;           // [kDpSlots] predictor state + [kDpSlots] confidence + {hits, misses, not speculated}: per exchange slot: the fused kernels' exponent prediction (conv_chain.cu)
     int speculate;            // NITI_B200_SPECULATE: 0 off, 1 adaptive (default), 2 always
     int dw_ctas;              // NITI_B200_DW_CTAS: upper bound on a dW launch's split-K spread (0 = sm_count)
+    int dw_g;                 // NITI_B200_DW_G: taps per dW item forced to 1 or 3 (0 = estimate, conv_dw2.cu)
     int8_t* ws_i8;    size_t ws_i8_bytes;   // transposed weights for dX, host-call staging
     int8_t* ws_z;     size_t ws_z_bytes;    // zero-inserted dY of strided dX ops (api.cu niti_conv_dx_fused)
     // data-parallel scalar exchange over peer memory (dp.cuh); world <= 1 when not connected

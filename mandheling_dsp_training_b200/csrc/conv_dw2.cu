@@ -262,16 +262,34 @@ int dw2_conv_dw_acc(niti_ctx* ctx, const niti_conv_desc* d, const int8_t* x, con
     if (!tmax::driver_ok()) return niti_fail(ctx, NITI_ERR_CUDA, "cuTensorMapEncode* entry points unavailable");
     const int oh = conv_out_h(d), ow = conv_out_w(d);
     const int bkc = d->c == 16 ? 16 : (d->c % 128 == 0 ? 128 : 64);
-    const int G = bkc == 16 ? 16 : (d->kw == 3 ? 3 : 1);
+    const int spread = (ctx->dw_ctas > 0 && ctx->dw_ctas < ctx->sm_count) ? ctx->dw_ctas : ctx->sm_count;
+    // Taps per item.  G = 3 (a filter row shares one dY tile: 1/3 fewer operand bytes per MAC) makes few, wide tiles, so the
+    // split-K spread over the SMs is deep and every split adds a 128 x 3*BKC int32 tile to L2 (28 MB of reduce-add per VGG
+    // launch, which set the 12-17 us of those launches); G = 1 makes 3x the tiles, 1/3 the reduce-add traffic and longer K
+    // loops per CTA.  Pick by a two-term estimate: operand bytes one CTA pulls through its L2 port (~100 GB/s) + reduce-add
+    // bytes of the launch (~3.5 TB/s aggregate).  NITI_B200_DW_G forces 1 or 3.
+    int G = bkc == 16 ? 16 : (d->kw == 3 ? 3 : 1);
+    if (G == 3) {
+        const long num_kb = ((long)d->n * oh * ow + 127) / 128;
+        double est[2];
+        for (int i = 0; i < 2; ++i) {
+            const int g = i == 0 ? 3 : 1;
+            const long tiles = (long)((d->oc + 127) / 128) * ((d->kh * d->kw + g - 1) / g) * (d->c / bkc);
+            long splits = spread / tiles; if (splits > num_kb) splits = num_kb; if (splits < 1) splits = 1;
+            const long kb_per = (num_kb + splits - 1) / splits;
+            const long waves = (tiles * splits + spread - 1) / spread;
+            est[i] = (double)waves * kb_per * (128.0 * 128 + g * 128.0 * bkc) / 100e3 +            // us at 100 GB/s per CTA
+                     (double)tiles * splits * (128.0 * g * bkc * 4) / 3.5e6;                      // us at 3.5 TB/s
+        }
+        if (est[1] < est[0]) G = 1;
+        if (ctx->dw_g == 1 || ctx->dw_g == 3) G = ctx->dw_g;
+    }
     Dw2Params p{};
     p.oc = d->oc; p.c = d->c; p.kh = d->kh; p.kw = d->kw; p.dil = d->dil; p.stride = d->stride;
     p.out_h = oh; p.out_w = ow; p.lower_h = -d->pad; p.lower_w = -d->pad;
     p.npix = d->n * oh * ow; p.num_kb = (p.npix + 127) / 128;
     p.oc_tiles = (d->oc + 127) / 128; p.c_tiles = d->c / bkc; p.ngroups = (d->kh * d->kw + G - 1) / G;
     const long tiles = (long)p.oc_tiles * p.ngroups * p.c_tiles;
-    // split-K spread: every split adds one full reduce-add of the tile (128 x G*BKC int32) to L2, so the spread trades
-    // isolated latency against SM-time — which is what counts in the step, where dW runs beside the dX chain
-    const int spread = (ctx->dw_ctas > 0 && ctx->dw_ctas < ctx->sm_count) ? ctx->dw_ctas : ctx->sm_count;
     int splits = (int)(spread / tiles);
     if (splits > p.num_kb) splits = p.num_kb;
     if (splits < 1) splits = 1;
