@@ -17,7 +17,7 @@
  * Everything is asynchronous on the given stream and CUDA-graph capturable: no host sync and no
  * host-visible scalar on the path.  Allocation: the phase-1/phase-2 and fused entry points allocate nothing; the whole-op
  * conveniences that take no scratch pointer (niti_conv_fwd/dx/dw, niti_matmul_nt, niti_conv_dw_split, a NULL `acc`, a
- * NULL `wt`) grow a context workspace with cudaMalloc on first use — call them once eagerly before capturing (under
+ * NULL `wt`) and niti_conv_dx_fused on a STRIDED layer (its zero-inserted dY) grow a context workspace with cudaMalloc on first use — call them once eagerly before capturing (under
  * capture the growth fails with NITI_ERR_CUDA rather than corrupting the graph), and re-capture after a call that grew it.
  *
  * Concurrency rule: the persistent kernels behind niti_conv_fwd_fused, niti_conv_dx_fused, niti_conv_fwd/dx[_acc] (split-K),

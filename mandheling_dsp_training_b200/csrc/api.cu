@@ -403,6 +403,13 @@ int niti_conv_stem_fwd(niti_ctx* ctx, const niti_conv_desc* d, int c_live, const
         ctx->last_path = "stem2";
         return stem2_conv_fwd_fused(ctx, d, x, w, ex, ew, y, ey, relu, y_pool, maxabs, dp_slot, (cudaStream_t)st);
     }
+    if (y_pool && (ctx->path == NITI_PATH_AUTO || ctx->path == NITI_PATH_TMA2) && ctx->auto_tma2 && stem2_fwd_eligible(d, c_live, false)) {
+        // the pool does not fold (output width not a multiple of 16: MNIST's 24): stem kernel, then the pool kernel
+        ctx->last_path = "stem2";
+        int rc = stem2_conv_fwd_fused(ctx, d, x, w, ex, ew, y, ey, relu, nullptr, maxabs, dp_slot, (cudaStream_t)st);
+        if (rc) return rc;
+        return niti_maxpool(ctx, y, d->n, conv_out_h(d), conv_out_w(d), d->oc, 2, 2, y_pool, st);
+    }
     if (y_pool) return niti_conv_fwd_fused_pool(ctx, d, x, w, ex, ew, y, ey, relu, y_pool, acc, maxabs, dp_slot, st);
     return niti_conv_fwd_fused(ctx, d, x, w, ex, ew, y, ey, relu, acc, maxabs, dp_slot, st);
 }

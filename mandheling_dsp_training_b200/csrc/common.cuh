@@ -76,7 +76,9 @@ __device__ __forceinline__ void niti_pdl_wait() { asm volatile("griddepcontrol.w
 __device__ __forceinline__ void niti_pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 enum { NITI_PDL_FUSED = 1, NITI_PDL_STEM = 2, NITI_PDL_UPDATE = 4, NITI_PDL_ELEMENTWISE = 8,
-       NITI_PDL_WITH_DP = 256,        // keep it on when the peer exchange is connected (experiments)
+       NITI_PDL_WITH_DP = 256,        // keep it on when the peer exchange is connected, whatever sums the gradient
+       NITI_PDL_WITH_PEER_SUM = 1024, // keep it on data-parallel when the library's own kernel sums the gradient (niti_dp_window
+                                      // mapped): early-placed CTAs then compete with a 16-CTA kernel of ours, not with NCCL
        NITI_PDL_TRIGGER_LATE = 512 }; // fused kernels release the next launch at their exponent barrier instead of at entry
 
 template <typename... KArgs, typename... Args>
@@ -89,7 +91,8 @@ inline cudaError_t niti_launch(const niti_ctx* ctx, int cls, void (*kernel)(KArg
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; // cls: NITI_PDL_* kernel class bit.  Data parallel (peer exchange connected): off — CTAs placed ahead of time would sit on
     // the SMs reserved for the concurrent NCCL all-reduce (dp.cu).
-    cfg.numAttrs = (ctx && (ctx->pdl & cls) && (ctx->dp.world <= 1 || (ctx->pdl & 256))) ? 1 : 0;   // bit 8: allow with DP (experiments)
+    cfg.numAttrs = (ctx && (ctx->pdl & cls) &&
+                    (ctx->dp.world <= 1 || (ctx->pdl & NITI_PDL_WITH_DP) || ((ctx->pdl & NITI_PDL_WITH_PEER_SUM) && ctx->dp_win.words > 0))) ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 

@@ -133,9 +133,10 @@ class NitiNet:
             if kind == "conv":
                 _, oc, k, st, pad, relu = item
                 oc_p = (oc + pad_oc - 1) // pad_oc * pad_oc if pad_oc else oc
-                if pad_oc and item is fused[-1] and self.convs and k == 1:
-                    # the classifier's dX contracts over its output channels: whole 64-channel K blocks of the fused kernel
-                    # (niti_conv_dx_fused) instead of the cp.async kernel + transpose + rescale launches; zero rows, exact
+                if pad_oc and os.environ.get("NITI_B200_PAD_OC64", "1") != "0":
+                    # Output channels are the next layer's input channels and this layer's dX contraction length: whole
+                    # 64-channel K blocks keep every layer on the TMA-fed fused kernels (LeNet's 20 / 52 / 12, a 12- or 1000-way
+                    # classifier) instead of the cp.async kernel + transpose + rescale launches.  Zero rows / columns: exact.
                     oc_p = (oc_p + 63) // 64 * 64
                 L.d = make_desc(batch, c, h, w, oc_p, k, stride=st, pad=pad)
                 L.c_real, L.oc_real = c_real, oc
