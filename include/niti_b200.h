@@ -189,6 +189,10 @@ typedef struct {
     int32_t oc, taps, c, sub;
 } niti_update_seg;
 int niti_update_batched(niti_ctx*, const niti_update_seg* segs, int nseg, niti_stream);
+/* the same as two stream-ordered launches (max|acc| per segment, then rule B + SGD): holds no grid barrier, so it is exempt from
+ * the one-barrier-call-at-a-time rule above and may run on a second stream beside the dX / dW kernels — the step updates the
+ * deep layers this way while backward is still working on the shallow ones */
+int niti_update_batched_phases(niti_ctx*, const niti_update_seg* segs, int nseg, niti_stream);
 /* Requantisation of the DSP-named op types (OpType_NITI_DSP_*_Int8), which the reference runs as
  * hexagon_nn graphs: shift = ceiling_log2(max|acc|) - 7, out = sat[-128,127](round-half-up(acc / 2^shift)) / post_div,
  * exp_out = exp_a + exp_b + shift.  Replaces hexagon_nn/2.10.1/hexagon/ops/src/niti_op_supernode_new.c:4614-4634 +

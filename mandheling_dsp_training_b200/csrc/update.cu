@@ -75,14 +75,17 @@ __device__ __forceinline__ void upd_vec_tile(const int32_t* ap, int8_t* wp, int 
     }
 }
 
+// mode 0: both phases around the grid barrier (persistent, every CTA resident); mode 1: phase 1 only; mode 2: phase 2 only —
+// the two-launch form holds no barrier, so it may run beside other kernels of the context (niti_update_batched_phases)
 __global__ void __launch_bounds__(kUpdThreads)
-update_batched_kernel(const __grid_constant__ UpdSegs S, uint32_t* sync, unsigned long long* tl) {
+update_batched_kernel(const __grid_constant__ UpdSegs S, uint32_t* sync, unsigned long long* tl, int mode) {
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     niti_pdl_trigger();
     niti_pdl_wait();                                         // programmatic dependent launch: see common.cuh
     niti_tl_enter(tl);
 
     // ---------------- phase 1: max|acc| per segment ----------------
+    if (mode != 2)
     // The accumulators of all segments form one concatenated run of 16-byte vectors; every WARP takes one contiguous slice of
     // it (1-2 segments), keeps eight loads per lane in flight and publishes with at most one atomic per segment it touched —
     // no block-level reduction, so nothing serialises the load latencies of different segments.  (Same-address atomics from
@@ -123,9 +126,12 @@ update_batched_kernel(const __grid_constant__ UpdSegs S, uint32_t* sync, unsigne
     }
 
     // ---------------- grid barrier (self re-arming) ----------------
-    __syncthreads();
-    if (tid == 0) grid_barrier_upd(sync, gridDim.x);
-    __syncthreads();
+    if (mode == 1) { niti_tl_exit(tl); return; }
+    if (mode == 0) {
+        __syncthreads();
+        if (tid == 0) grid_barrier_upd(sync, gridDim.x);
+        __syncthreads();
+    }
 
     // ---------------- phase 2: rule B + SGD (+ transposed copy) ----------------
     const uint32_t ntiles = S.tile_begin[S.n];
@@ -173,7 +179,7 @@ update_batched_kernel(const __grid_constant__ UpdSegs S, uint32_t* sync, unsigne
 
     // ---------------- last CTA out re-arms the barrier for the next launch ----------------
     __syncthreads();
-    if (tid == 0) {
+    if (tid == 0 && mode == 0) {
         if (atomicAdd(sync + 1, 1u) == gridDim.x - 1) { sync[0] = 0u; sync[1] = 0u; __threadfence(); }
     }
     niti_tl_exit(tl);
@@ -181,7 +187,7 @@ update_batched_kernel(const __grid_constant__ UpdSegs S, uint32_t* sync, unsigne
 
 } // namespace
 
-extern "C" int niti_update_batched(niti_ctx* ctx, const niti_update_seg* segs, int nseg, niti_stream st) {
+static int update_launch(niti_ctx* ctx, const niti_update_seg* segs, int nseg, cudaStream_t st, bool phases) {
     if (!ctx || !segs || nseg <= 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_update_batched: bad argument");
     int blocks_per_sm = 0;                                    // occupancy is a per-device property: no process-wide cache
     {
@@ -208,11 +214,24 @@ extern "C" int niti_update_batched(niti_ctx* ctx, const niti_update_seg* segs, i
             tiles += upd_vec_ok(g) ? (uint32_t)((g.oc / 16) * ((cols + 127) / 128)) : (uint32_t)(((g.oc + 31) / 32) * ((cols + 31) / 32));
         }
         S.tile_begin[S.n] = tiles; S.vec_begin[S.n] = vecs;
-        const int grid = ctx->sm_count * blocks_per_sm;            // all CTAs co-resident: the grid barrier needs it
-        cudaError_t lerr = niti_launch(ctx, NITI_PDL_UPDATE, update_batched_kernel, dim3(grid), dim3(kUpdThreads), 0, (cudaStream_t)st, S, ctx->ws_u32 + 40, niti_tl_next(ctx, "update_batched"));
-        if (lerr != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "launch update_batched", lerr);
-        int rc = niti_check_launch(ctx, "update_batched");
-        if (rc) return rc;
+        const int grid = ctx->sm_count * blocks_per_sm;            // mode 0: all CTAs co-resident, the grid barrier needs it
+        if (!phases) {
+            cudaError_t lerr = niti_launch(ctx, NITI_PDL_UPDATE, update_batched_kernel, dim3(grid), dim3(kUpdThreads), 0, st, S, ctx->ws_u32 + 40, niti_tl_next(ctx, "update_batched"), 0);
+            if (lerr != cudaSuccess) return niti_fail(ctx, NITI_ERR_CUDA, "launch update_batched", lerr);
+            if (int rc = niti_check_launch(ctx, "update_batched")) return rc;
+            continue;
+        }
+        for (int mode = 1; mode <= 2; ++mode) {                    // plain stream-ordered launches: no barrier, no residency rule
+            update_batched_kernel<<<grid, kUpdThreads, 0, st>>>(S, ctx->ws_u32 + 40, niti_tl_next(ctx, mode == 1 ? "update_max" : "update_apply"), mode);
+            if (int rc = niti_check_launch(ctx, "update_batched (phases)")) return rc;
+        }
     }
     return NITI_OK;
+}
+
+extern "C" int niti_update_batched(niti_ctx* ctx, const niti_update_seg* segs, int nseg, niti_stream st) {
+    return update_launch(ctx, segs, nseg, (cudaStream_t)st, false);
+}
+extern "C" int niti_update_batched_phases(niti_ctx* ctx, const niti_update_seg* segs, int nseg, niti_stream st) {
+    return update_launch(ctx, segs, nseg, (cudaStream_t)st, true);
 }

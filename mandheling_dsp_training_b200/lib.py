@@ -62,6 +62,7 @@ _SIGS = {
     "niti_conv_dw_accumulate": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P]),
     "niti_conv_dx_acc_wt": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P]),
     "niti_update_batched": (C.c_int, [_P, _P, C.c_int, _P]),
+    "niti_update_batched_phases": (C.c_int, [_P, _P, C.c_int, _P]),
     "niti_matmul_nt_acc": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P, _P, _P, _P]),
     "niti_zero_u32": (C.c_int, [_P, _P, C.c_int, _P]),
     "niti_absmax": (C.c_int, [_P, _P, C.c_size_t, _P, _P]),
@@ -237,6 +238,10 @@ class NitiB200:
     def update_batched(self, segs, stream=None):
         """segs: ctypes array of UpdateSeg (host); read at call time"""
         self._ck(self.lib.niti_update_batched(self.h, C.cast(segs, _P), len(segs), self._stream(stream)))
+
+    def update_batched_phases(self, segs, stream=None):
+        """the same as two barrier-free launches (may run on a second stream beside the dX / dW kernels)"""
+        self._ck(self.lib.niti_update_batched_phases(self.h, C.cast(segs, _P), len(segs), self._stream(stream)))
 
     def conv_dw_acc(self, d, x, dy, acc, maxabs=None, stream=None):
         self._ck(self.lib.niti_conv_dw_acc(self.h, C.byref(d), _ptr(x), _ptr(dy), _ptr(acc), _ptr(maxabs), self._stream(stream)))

@@ -135,11 +135,18 @@ Execution* B200Backend::onCreate(const std::vector<Tensor*>& inputs, const std::
     auto map = gCreators();
     auto iter = map->find(op->type());
     if (iter == map->end()) {
+        declinedCounts()[(int)op->type()] += 1;
         return nullptr;        // the executor retries on its CPU backup backend (express/Executor.cpp:521-529)
     }
     Execution* e = iter->second->onCreate(inputs, outputs, op, this);
     if (e != nullptr) createdCounts()[(int)op->type()] += 1;      // evidence hook: which op types really got a B200 Execution
+    else declinedCounts()[(int)op->type()] += 1;
     return e;
+}
+
+std::map<int, long long>& declinedCounts() {
+    static std::map<int, long long> counts;
+    return counts;
 }
 
 std::map<int, long long>& createdCounts() {

@@ -104,7 +104,9 @@ public:
     static ::MNN::B200::B200CreatorRegister<name> _b200_register_##name##_##opType(opType)
 
 long long launchCountOfLastRuntime();
-std::map<int, long long>& createdCounts();   // Executions created so far, by op type
+std::map<int, long long>& createdCounts();
+// op types the backend declined (no creator, or the creator returned nullptr): they ran on the executor's CPU backup backend
+std::map<int, long long>& declinedCounts();   // Executions created so far, by op type
 
 // NITI_* -> ErrorCode
 ErrorCode toErrorCode(int nitiCode, const B200Backend* bn, const char* what);

@@ -30,6 +30,15 @@ int MNNNitiB200ForwardType() { return (int)MNN_FORWARD_B200; }
 // CUDA kernels launched so far by the live B200 runtime (tests use it to prove the ops ran on the device)
 long long MNNNitiB200LaunchCount() { return MNN::B200::launchCountOfLastRuntime(); }
 // Executions the B200 backend created for this op type so far (0: every op of that type went to the CPU backup backend)
+// the same for op types that went to the CPU backup backend; opType < 0: writes up to `cap` {type, count} pairs into `out`
+// and returns how many types there are
+long long MNNNitiB200DeclinedOps(int opType, long long* out, int cap) {
+    auto& m = MNN::B200::declinedCounts();
+    if (opType >= 0) { auto it = m.find(opType); return it == m.end() ? 0 : it->second; }
+    int i = 0;
+    for (auto& kv : m) { if (out && i < cap) { out[2 * i] = kv.first; out[2 * i + 1] = kv.second; } ++i; }
+    return i;
+}
 long long MNNNitiB200CreatedOps(int opType) {
     auto& m = MNN::B200::createdCounts();
     auto it = m.find(opType);

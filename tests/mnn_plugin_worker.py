@@ -156,6 +156,11 @@ def main():
     # Executions the plug-in created per op type (schema/current/MNN_generated.h OpType values)
     for name, code in (("binary", 7), ("pool_grad", 706), ("loss_grad", 711), ("loss", 710), ("pad", 714), ("left_pool_grad", 718)):
         out[f"created_{name}"] = np.int64(plug.MNNNitiB200CreatedOps(code))
+    # op types that still ran on the executor's CPU backup backend (reported, not asserted: Raster / Convert / shape ops)
+    plug.MNNNitiB200DeclinedOps.restype = ctypes.c_longlong
+    buf = (ctypes.c_longlong * 128)()
+    nd = int(plug.MNNNitiB200DeclinedOps(-1, buf, 64))
+    print("declined op types {type: count}:", {int(buf[2 * i]): int(buf[2 * i + 1]) for i in range(min(nd, 64))})
     np.savez(dst, **{k: (v if v is not None else np.zeros(0, np.int8)) for k, v in out.items()})
     same = [k[4:] for k in out if k.startswith("cpu_") and not k.endswith("_ms") and out[k] is not None
             and np.array_equal(out[k], out["b200_" + k[4:]])]
