@@ -12,6 +12,7 @@ fi
 timeout 500 python bench.py > gpurun_out/${tag}_bench_vgg.json 2> gpurun_out/${tag}_bench_vgg.err; echo bench vgg rc=$?
 timeout 300 python bench.py --workload lenet --no-cpu-baseline > gpurun_out/${tag}_bench_lenet.json 2> gpurun_out/${tag}_bench_lenet.err; echo bench lenet rc=$?
 timeout 400 python bench.py --workload resnet18 --no-cpu-baseline --steps 30 > gpurun_out/${tag}_bench_resnet18.json 2> gpurun_out/${tag}_bench_resnet18.err; echo bench resnet rc=$?
+timeout 400 python bench.py --workload lenet --via mnn > gpurun_out/${tag}_bench_lenet_via_mnn.json 2> gpurun_out/${tag}_bench_lenet_via_mnn.err; echo bench lenet via mnn rc=$?
 python tools/phase_trace.py vgg11 256 > gpurun_out/${tag}_phase_vgg.txt 2>&1; echo phase rc=$?
 python tools/timeline.py vgg11 256 > gpurun_out/${tag}_timeline_vgg.txt 2>&1; echo timeline rc=$?
 timeout 600 python tools/sweep.py --iters 10 --out gpurun_out/${tag}_sweep.json > gpurun_out/${tag}_sweep.log 2>&1; echo sweep rc=$?
@@ -31,7 +32,7 @@ python tools/prof_step.py vgg11 256 3 > gpurun_out/${tag}_prof_plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/${tag}_launches.csv python tools/prof_step.py vgg11 256 3 > gpurun_out/${tag}_ncu_list.log 2>&1
 echo launch list rc=$?
 python tools/prof_step.py vgg11 256 2 > gpurun_out/${tag}_prof_plain2.log 2>&1 &&
-ncu --set full --clock-control none -k 'regex:chain_kernel|dw2_kernel|stem2|update_batched' -s 23 -c 23 -o gpurun_out/${tag}_prof \
+ncu --set full --clock-control none -k 'regex:chain_kernel|dw2_kernel|stem2|update_batched' -s 26 -c 26 -o gpurun_out/${tag}_prof \
     python tools/prof_step.py vgg11 256 2 > gpurun_out/${tag}_ncu_full.log 2>&1
 echo ncu full rc=$?
 ncu -i gpurun_out/${tag}_prof.ncu-rep --page raw --csv > gpurun_out/${tag}_prof_raw.csv 2>/dev/null; echo export rc=$?
