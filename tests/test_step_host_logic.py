@@ -90,3 +90,24 @@ def test_data_parallel_is_bit_exact_world2(tmp_path):
         assert np.array_equal(r0[f"arr_{i}"], w) and np.array_equal(r1[f"arr_{i}"], w)
     full = net.logits.numpy().reshape(gbatch, -1)
     assert np.array_equal(np.concatenate([r0["logits"].reshape(2, -1), r1["logits"].reshape(2, -1)]), full)
+
+
+def test_gradient_buckets_cover_the_bucket_once_and_the_last_one_is_the_first_conv():
+    """dW all-reduce buckets (step.NitiNet._buckets): closed in backward order at >= 8 MiB, contiguous, covering every layer's
+    accumulators exactly once; the bucket that closes last holds only the first conv, so the exchange left behind the last dW is
+    a few KB."""
+    from mandheling_dsp_training_b200.step import vgg11_spec
+    net = _build(vgg11_spec(), 2, (3, 32, 32))
+    total = net.dw_acc.numel()
+    spans = sorted(net._buckets.values())
+    assert spans[0][0] == 0 and spans[-1][1] == total
+    for (lo, hi), (lo2, hi2) in zip(spans, spans[1:]):
+        assert hi == lo2 and lo < hi                         # contiguous, non-empty
+    first = net.convs[0]
+    assert net._buckets[0] == (first.dw_off, net.convs[1].dw_off)
+    assert 1 in net._buckets                                 # conv2..: their own bucket, closed before the first conv's dW
+    for idx, (lo, hi) in net._buckets.items():
+        if idx > 1:
+            assert (hi - lo) * 4 >= (8 << 20)                # every other bucket reached the size threshold
+    for L in net.convs:                                      # every layer lies inside exactly one bucket
+        assert sum(1 for lo, hi in spans if lo <= L.dw_off and L.dw_off + L.n_w <= hi) == 1
