@@ -193,9 +193,8 @@ class NitiNet:
         # dW all-reduce buckets, closed in backward order (last conv first) once they hold >= 8 MiB, so the exchange
         # of the deep layers overlaps the rest of backward: list of (lowest conv index, start word, end word)
         self._buckets, hi_end, size = {}, dw_total, 0
-        # ... and the bucket that closes LAST holds only the first conv (an image layer: kilobytes), so the exchange left on the
-        # critical path behind the last dW is a latency-bound sum of a few KB instead of the 4 MB of conv1..conv4 (8xB200: 41 us
-        # between the last dW and the update, profiles/timeline_r2_vgg_8gpu.txt)
+        # ... and the bucket that closes LAST holds only the first conv (an image layer: kilobytes), so no large exchange starts
+        # behind the last dW (8xB200: the 41 us between the last dW and the update did not move — launch-chain latency, not bytes)
         for L in reversed(self.convs):
             size += L.n_w * 4
             if size >= (8 << 20) or L.index == 0 or (L.index == 1 and len(self.convs) >= 3):
