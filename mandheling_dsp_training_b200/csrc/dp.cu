@@ -42,8 +42,9 @@ __device__ __forceinline__ int4 ld_peer(const int4* p) {      // never from a st
 // Integer adds commute: bit-exact in any order.  ~16 CTAs on the SMs the contractions leave free (niti_dp_reserved_sms).
 template <int W>                                             // world rounded up to 2, 4 or 8: 8 / W vectors per thread and trip,
 __global__ void __launch_bounds__(kArMaxThreads)              // so eight 16-byte loads are in flight per thread at any world size
-dp_allreduce_kernel(const DpView v, const DpWindow w, size_t off, size_t n, int slot) {
+dp_allreduce_kernel(const DpView v, const DpWindow w, size_t off, size_t n, int slot, unsigned long long* tl) {
     __shared__ int last;
+    niti_tl_enter(tl);
     DpBuffer* mine = v.peer[v.rank];
     const uint32_t epoch = *reinterpret_cast<volatile uint32_t*>(&mine->epoch);
     const int tid = threadIdx.x;
@@ -85,6 +86,8 @@ dp_allreduce_kernel(const DpView v, const DpWindow w, size_t off, size_t n, int 
         if (tid == 0) mine->ar_count[slot] = 0u;
         if (tid < v.world) ar_flag_store(&v.peer[tid]->ar_out[slot][v.rank], epoch);
         if (tid < v.world && tid != v.rank && !ar_flag_wait(&mine->ar_out[slot][tid], epoch, v.timeout_cycles)) mine->error = 1u;
+        __syncthreads();
+        niti_tl_exit(tl);                                     // launch timeline: the last CTA's exit = the sum is complete everywhere
     }
 }
 }
@@ -206,9 +209,10 @@ extern "C" int niti_dp_allreduce_i32(niti_ctx* ctx, size_t off, size_t n, int sl
     const size_t need = (per + threads - 1) / threads;
     if ((size_t)ctas > need) ctas = (int)(need ? need : 1);
     const cudaStream_t cs = (cudaStream_t)st;
-    if (ctx->dp.world <= 2) dp_allreduce_kernel<2><<<ctas, threads, 0, cs>>>(ctx->dp, ctx->dp_win, off, n, slot);
-    else if (ctx->dp.world <= 4) dp_allreduce_kernel<4><<<ctas, threads, 0, cs>>>(ctx->dp, ctx->dp_win, off, n, slot);
-    else dp_allreduce_kernel<8><<<ctas, threads, 0, cs>>>(ctx->dp, ctx->dp_win, off, n, slot);
+    unsigned long long* tl = niti_tl_next(ctx, "dp_allreduce");
+    if (ctx->dp.world <= 2) dp_allreduce_kernel<2><<<ctas, threads, 0, cs>>>(ctx->dp, ctx->dp_win, off, n, slot, tl);
+    else if (ctx->dp.world <= 4) dp_allreduce_kernel<4><<<ctas, threads, 0, cs>>>(ctx->dp, ctx->dp_win, off, n, slot, tl);
+    else dp_allreduce_kernel<8><<<ctas, threads, 0, cs>>>(ctx->dp, ctx->dp_win, off, n, slot, tl);
     return niti_check_launch(ctx, "dp_allreduce");
 }
 
