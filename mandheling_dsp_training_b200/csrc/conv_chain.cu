@@ -138,6 +138,12 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
         const ChainLayer& Lp = kTable ? a.table[(tid - 32) >> 1] : single;
         prefetch_tmap2(((tid - 32) & 1) ? &Lp.mapB : &Lp.mapA);
     }
+    // ... and the layer records themselves: every role reads record l+1 on the critical path of the layer transition, a DRAM
+    // miss (~1 us) per layer whenever the table has left L2 (the bench flushes L2 between steps); pull every line into L2 now
+    if (kTable && tid >= 64) {
+        const char* tb = reinterpret_cast<const char*>(a.table);
+        for (int off = (tid - 64) * 128; off < a.nlayers * (int)sizeof(ChainLayer); off += (kChainThreads - 64) * 128) prefetch_l2(tb + off);
+    }
     if (warp == 1) tmem_alloc2<512>(tmem_slot);
     tc::tc_fence_before();
     cluster_sync_all();
