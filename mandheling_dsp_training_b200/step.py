@@ -225,10 +225,12 @@ class NitiNet:
         if (self.batched_update and self.dist is None and hasattr(nb, "update_batched_phases") and len(self.convs) >= 4
                 and os.environ.get("NITI_B200_EARLY_UPDATE", "1") != "0"):
             k = len(self.convs) // 2
-            self._early_from = k
-            self.upd_stream = torch.cuda.Stream(self.dev)
-            self._upd_segs_early = nb.make_update_segs(self._upd_layers[k:])
-            self._upd_segs_late = nb.make_update_segs(self._upd_layers[:k])
+            # small nets (LeNet) are launch-bound: two more launches cost more than the shorter tail saves
+            if sum(L.n_w for L in self.convs[k:]) >= int(os.environ.get("NITI_B200_EARLY_UPDATE_MIN", str(2 << 20))):
+                self._early_from = k
+                self.upd_stream = torch.cuda.Stream(self.dev)
+                self._upd_segs_early = nb.make_update_segs(self._upd_layers[k:])
+                self._upd_segs_late = nb.make_update_segs(self._upd_layers[:k])
         # dW beside dX: both only read dY, and the dX chain is the critical path of backward, so dW (and, data parallel,
         # the bucket all-reduces behind it) is enqueued on a second stream.  Needs the barrier-free accumulate entry
         # point (niti_conv_dw_accumulate) and the gradient bucket cleared once per step (done beside forward).

@@ -104,3 +104,26 @@ def test_backward_chain_is_bit_identical(nb, monkeypatch):
     for wa, wb in zip(a.weights_oihw(), b.weights_oihw()):
         assert np.array_equal(wa, wb)
     assert torch.equal(a.logits, b.logits)
+
+
+def test_early_update_is_bit_identical(nb, monkeypatch):
+    """the deep layers' rule B + SGD as two barrier-free launches on a third stream beside the rest of backward
+    (niti_update_batched_phases) gives the same weights and logits as the one-launch update at the end of the step"""
+    x, labels = _data(8, (3, 16, 16), 6)
+    xin = torch.from_numpy(np.ascontiguousarray(np.transpose(x, (0, 2, 3, 1))))
+    monkeypatch.setenv("NITI_B200_EARLY_UPDATE", "0")
+    a = NitiNet(nb, VGG_NET, 8, (3, 16, 16)); a.init_weights(seed=5)
+    monkeypatch.setenv("NITI_B200_EARLY_UPDATE", "1")
+    monkeypatch.setenv("NITI_B200_EARLY_UPDATE_MIN", "0")
+    b = NitiNet(nb, VGG_NET, 8, (3, 16, 16)); b.init_weights(seed=5)
+    assert a._early_from is None and b._early_from is not None
+    for net in (a, b):
+        net.set_input(xin, -7, torch.from_numpy(labels))
+    replay = b.capture()                 # the captured graph carries the third stream too
+    b.init_weights(seed=5)
+    for _ in range(3):
+        a.step(); replay()
+    torch.cuda.synchronize()
+    for wa, wb in zip(a.weights_oihw(), b.weights_oihw()):
+        assert np.array_equal(wa, wb)
+    assert torch.equal(a.logits, b.logits)
