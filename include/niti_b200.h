@@ -69,7 +69,7 @@ int         niti_set_path(niti_ctx* ctx, int path);
  * With prediction, a fused kernel stores in the same sweep that reduces the maximum, using the shift the same tensor (same
  * dp_slot) had the last time it was computed, and re-stores (stem layer: recomputes) only when the true maximum lands in
  * another bit width.  Adaptive = speculate when a miss is cheap (several tiles per CTA pair, stem layer) or the slot's last
- * predictions held.  The stored int8 values and the exponent are those of the true maximum in every mode (tests compare the
+ * NITI_B200_SPEC_CONFIDENT predictions held (default 0: always).  The stored int8 values and the exponent are those of the true maximum in every mode (tests compare the
  * modes bit for bit). */
 int         niti_set_speculate(niti_ctx* ctx, int mode);
 /* predictions that held / missed / layers that did not speculate, since the context was created (synchronises the device;

@@ -1,4 +1,5 @@
 // api.cu — context, workspace and the C-ABI dispatch of libniti_b200.so (see include/niti_b200.h).
+#include <vector>
 #include "common.cuh"
 #include <cstdio>
 #include <cstring>
@@ -183,10 +184,14 @@ int niti_ctx_create(int device, niti_ctx** out) {
         delete ctx;
         return NITI_ERR_UNSUPPORTED;
     }
-    e = cudaMalloc(&ctx->ws_u32, (64 + 2 * kDpSlots + 4) * sizeof(uint32_t));
+    e = cudaMalloc(&ctx->ws_u32, (64 + kPredWords) * sizeof(uint32_t));
     if (e != cudaSuccess) { delete ctx; return NITI_ERR_CUDA; }
-    cudaMemset(ctx->ws_u32, 0, (64 + 2 * kDpSlots + 4) * sizeof(uint32_t));
+    cudaMemset(ctx->ws_u32, 0, (64 + kPredWords) * sizeof(uint32_t));
     ctx->pred = ctx->ws_u32 + 64;
+    {   // chooser bits start at 2: the input-scale predictor leads until the window predictor proves better (common.cuh)
+        std::vector<uint32_t> init(kDpSlots, 2u << 16);
+        cudaMemcpy(ctx->pred + kDpSlots, init.data(), kDpSlots * sizeof(uint32_t), cudaMemcpyHostToDevice);
+    }
     const char* dwc = getenv("NITI_B200_DW_CTAS");        // CTAs a dW launch may spread its split-K over (default: every SM)
     ctx->dw_ctas = dwc ? atoi(dwc) : 0;
     const char* dwg = getenv("NITI_B200_DW_G");
@@ -194,6 +199,8 @@ int niti_ctx_create(int device, niti_ctx** out) {
     const char* sp = getenv("NITI_B200_SPECULATE");        // 0: two-sweep schedule (max pass | barrier | store pass) for A/B runs
     ctx->speculate = sp ? atoi(sp) : 1;
     if (ctx->speculate < 0 || ctx->speculate > 2) ctx->speculate = 1;
+    const char* sc = getenv("NITI_B200_SPEC_CONFIDENT");
+    ctx->spec_confident = sc ? atoi(sc) : 0;
     *out = ctx;
     return NITI_OK;
 }

@@ -25,6 +25,7 @@ struct niti_ctx {
     uint32_t* ws_u32;         // [0] max-abs slot of whole-op calls
     uint32_t* pred;           // [kDpSlots] predictor state + [kDpSlots] confidence + {hits, misses, not speculated}: per exchange slot: the fused kernels' exponent prediction (conv_chain.cu)
     int speculate;            // NITI_B200_SPECULATE: 0 off, 1 adaptive (default), 2 always
+    int spec_confident;       // NITI_B200_SPEC_CONFIDENT: holds a single-tile layer waits for before it speculates (default 0)
     int dw_ctas;              // NITI_B200_DW_CTAS: upper bound on a dW launch's split-K spread (0 = sm_count)
     int dw_g;                 // NITI_B200_DW_G: taps per dW item forced to 1 or 3 (0 = estimate, conv_dw2.cu)
     int8_t* ws_i8;    size_t ws_i8_bytes;   // transposed weights for dX, host-call staging
@@ -174,6 +175,49 @@ NITI_DEVICE_INLINE uint32_t niti_pred_update(uint32_t state, int seen) {
     else if (seen == lo + 2) { lo = seen - 1; c = 2; }
     else { lo = seen; c = 0; }
     return ((uint32_t)lo << 2) | (uint32_t)c;
+}
+
+// Second predictor: the INPUT SCALE.  A layer's input is the previous op's output, normalised to int8 by that op's exponent; how
+// much of the int8 range it fills (max|acc| >> shift = 64..128, its "norm") changes from batch to batch by up to 2x and moves this
+// layer's max|acc| with it.  So  est = max|acc|(t-1) * norm_in(t) / norm_in(t-1), where norm_in(t) is known before this layer runs:
+// every fused kernel leaves the norm of what it just produced in one context word (kPredLastNorm), and the next fused launch of the
+// stream — whose operand that output is, in a training step — reads it.  A 2-bit counter per slot (bits 16-17 of the confidence
+// word) picks the predictor that has been right more often.  Layout of the prediction area (uint32 words, S = kDpSlots):
+// [0,S) window state | [S,2S) confidence + chooser | [2S,2S+3) hit / miss / not-speculated counters | [2S+4,3S+4) last max|acc| |
+// [3S+4,4S+4) last input norm | [4S+4] norm of the most recent fused op's output.
+constexpr int kPredLastGmax = 2 * kDpSlots + 4, kPredLastIn = 3 * kDpSlots + 4, kPredLastNorm = 4 * kDpSlots + 4, kPredWords = 4 * kDpSlots + 8;
+struct NitiPrediction { int bw_window, bw_ratio, bw; uint32_t in_now, state, confw; bool use_ratio; };
+NITI_DEVICE_INLINE NitiPrediction niti_predict(const uint32_t* pred, int slot, uint32_t in_now) {
+    NitiPrediction p;
+    p.state = __ldcg(pred + slot); p.confw = __ldcg(pred + kDpSlots + slot); p.in_now = in_now;
+    const uint32_t lg = __ldcg(pred + kPredLastGmax + slot), lin = __ldcg(pred + kPredLastIn + slot);
+    p.bw_window = niti_pred_bitwidth(p.state);
+    p.bw_ratio = p.bw_window;
+    if (lg != 0u && lin != 0u && in_now != 0u) {
+        const unsigned long long est = (unsigned long long)lg * in_now / lin;
+        p.bw_ratio = niti_bitwidth(est > 0xffffffffull ? 0xffffffffu : (uint32_t)est);
+    }
+    p.use_ratio = ((p.confw >> 16) & 3u) >= 2u;
+    p.bw = p.use_ratio ? p.bw_ratio : p.bw_window;
+    return p;
+}
+// norm of an op's output: what rule A leaves of the maximum (the raw-cast branch keeps it as it is)
+NITI_DEVICE_INLINE uint32_t niti_out_norm(uint32_t gmax, int kind, int shift) { return kind == 1 ? gmax : (gmax >> shift); }
+// CTA 0, after the layer's barrier: fold the truth into both predictors (every CTA read the old words before it arrived)
+NITI_DEVICE_INLINE void niti_predict_update(uint32_t* pred, int slot, const NitiPrediction& p, uint32_t gmax, bool held, bool speculated) {
+    const int bt = niti_bitwidth(gmax);
+    int k1, s1, kw, sw, kr, sr;
+    niti_rule_a(bt, k1, s1); niti_rule_a(p.bw_window, kw, sw); niti_rule_a(p.bw_ratio, kr, sr);
+    const bool win_ok = kw == k1 && sw == s1, rat_ok = kr == k1 && sr == s1;
+    uint32_t chooser = (p.confw >> 16) & 3u;
+    if (rat_ok && !win_ok) chooser = chooser < 3u ? chooser + 1u : 3u;
+    if (win_ok && !rat_ok) chooser = chooser > 0u ? chooser - 1u : 0u;
+    const uint32_t conf = p.confw & 0xffffu;
+    pred[slot] = niti_pred_update(p.state, bt);
+    pred[kDpSlots + slot] = (held ? (conf < 3u ? conf + 1u : 3u) : 0u) | (chooser << 16);
+    pred[kPredLastGmax + slot] = gmax;
+    pred[kPredLastIn + slot] = p.in_now;
+    atomicAdd(pred + 2 * kDpSlots + (speculated ? (held ? 0 : 1) : 2), 1u);
 }
 
 NITI_DEVICE_INLINE int32_t niti_shl1(int s) { return (int32_t)(1u << ((unsigned)s & 31u)); }

@@ -26,7 +26,6 @@ namespace {
 constexpr int kChainThreads = 576;   // warp 0: TMA producer, warp 1: MMA issuer + TMEM owner, warps 2-17: epilogue
 constexpr int kChainMaxTiles = 8;    // resident accumulator tiles per CTA pair (512 TMEM columns / 64)
 constexpr int kChainMaxStages = 8;
-constexpr uint32_t kSpecConfident = 2; // consecutive predictions that must have held before a single-tile layer speculates
 constexpr int kChainSmem = 232448;   // all of it: one CTA per SM is a requirement (512 TMEM columns + grid barriers)
 constexpr int kChainStageArea = ((kChainSmem - 1024 - 512) / 1024) * 1024;
 
@@ -57,6 +56,7 @@ struct ChainArgs {
     unsigned long long* trace;        // [layer][block][8] globaltimer stamps, or nullptr
     unsigned long long* tl;           // launch timeline record, or nullptr
     uint32_t* pred;                   // [kDpSlots] predictor state per slot (common.cuh niti_pred_*), [kDpSlots] confidence, {hits, misses, not speculated}
+    int spec_confident;               // consecutive predictions that must have held before a single-tile layer speculates
     int speculate;                    // 0: pass 0 only reduces the maximum, pass 1 always stores (two-sweep schedule); 1: adaptive; 2: always
     int trigger_late;
 };
@@ -271,6 +271,7 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
         uint32_t tuse = 0;                                   // per-slot use parity (tfull_bar)
         uint32_t nbar = 0;                                   // grid barriers passed so far
         const uint32_t eone = (uint32_t)(a.speculate >= 0);  // 1, opaque to the compiler (common.cuh niti_rule_a_consts)
+        uint32_t prev_norm = 0u;                             // norm of the previous layer's output (exponent prediction)
         if (etid == 0) chain_trace(a.trace, 0, 1);
         for (int l = 0; l < a.nlayers; ++l) {
             const ChainLayer& L = kTable ? a.table[l] : single;
@@ -318,13 +319,21 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
             // behind a second barrier.  What is stored is always rounded with the true exponent.
             // A miss costs a second sweep and a second barrier, so a layer speculates when that is cheap or unlikely: when its
             // CTA pairs hold several tiles (the predicted-store work hides under the K loops of the later tiles, a miss then
-            // costs what the two-sweep schedule always pays) or when the slot's prediction held the last kSpecConfident
+            // costs what the two-sweep schedule always pays) or when the slot's prediction held the last `spec_confident`
             // times (a.pred[kDpSlots + slot], updated whether or not the layer speculated).  Measured on VGG-11 with a new
-            // batch every step: 36 % of the predictions miss — gradient maxima hover around powers of two.
-            const uint32_t pred = __ldcg(a.pred + edps);
-            const uint32_t conf = __ldcg(a.pred + kDpSlots + edps);
-            const bool espec = a.speculate == 2 || (a.speculate == 1 && (conf >= kSpecConfident || eitems > epairs));
-            niti_rule_a(niti_pred_bitwidth(pred), kind, shift);
+            // batch every step: the window predictor alone missed 23-36 % (maxima hover around powers of two), with the
+            // input-scale predictor 21 % miss — at that rate speculating always (spec_confident = 0, the default) beats waiting
+            // for two holds: 444.9 vs 448.9 us/step.
+            // Two predictors (common.cuh): the window over the slot's recent bit widths, and last max|acc| scaled by how much of
+            // the int8 range this layer's INPUT fills now against last time — the norm the producing op left behind (previous
+            // layer of this chain: in a register; first layer: the context word the previous fused launch wrote).
+            const uint32_t in_now = l == 0 ? __ldcg(a.pred + kPredLastNorm) : prev_norm;
+            bool espec;
+            {   // (the prediction record is not kept live over the layer: CTA 0 re-reads the same words when it folds the truth in)
+                const NitiPrediction pr = niti_predict(a.pred, edps, in_now);
+                espec = a.speculate == 2 || (a.speculate == 1 && ((pr.confw & 0xffffu) >= (uint32_t)a.spec_confident || eitems > epairs));
+                niti_rule_a(pr.bw, kind, shift);
+            }
             NitiRuleA rk = niti_rule_a_consts(shift, eone);
             int mxs = 0, mns = 0;                            // signed running max / min: one VIMNMX3 each per two accumulators
             for (int pass = 0; pass < 2; ++pass) {
@@ -447,11 +456,11 @@ chain_kernel(const __grid_constant__ ChainLayer single, const ChainArgs a) {
                     int kind2, shift2;
                     niti_rule_a(niti_bitwidth(gmax), kind2, shift2);
                     const bool held = kind2 == kind && shift2 == shift;
+                    prev_norm = niti_out_norm(gmax, kind2, shift2);      // the next layer's input norm (grid-uniform)
                     if (blockIdx.x == 0 && etid == 0) {
                         if (eeo != nullptr) *eeo = (int8_t)((eea ? (int)*eea : 0) + (eeb ? (int)*eeb : 0) + (kind2 == 1 ? 0 : shift2));
-                        a.pred[edps] = niti_pred_update(pred, niti_bitwidth(gmax));   // every CTA read the old values before it arrived above
-                        a.pred[kDpSlots + edps] = held ? min(conf + 1u, 3u) : 0u;
-                        atomicAdd(a.pred + 2 * kDpSlots + (espec ? (held ? 0 : 1) : 2), 1u);
+                        niti_predict_update(a.pred, edps, niti_predict(a.pred, edps, in_now), gmax, held, espec);   // every CTA read the old words before it arrived above
+                        if (last_layer) a.pred[kPredLastNorm] = prev_norm;          // for the next fused launch of the stream
                     }
                     if (espec && held) {                                 // prediction held (grid-uniform): the layer is complete
                         if (etid == 0) chain_trace(a.trace, l, 5);
@@ -602,7 +611,7 @@ static int chain_launch_t(niti_ctx* ctx, const ChainLayer& byvalue, const ChainA
 
 static int chain_launch(niti_ctx* ctx, const ChainLayer* single, const ChainLayer* table, int nlayers, int grid, bool streams, cudaStream_t st) {
     ChainArgs a{};
-    a.table = table; a.nlayers = nlayers; a.sync = ctx->ws_u32 + 52; a.dp = ctx->dp; a.trace = ctx->trace; a.pred = ctx->pred; a.speculate = ctx->speculate;
+    a.table = table; a.nlayers = nlayers; a.sync = ctx->ws_u32 + 52; a.dp = ctx->dp; a.trace = ctx->trace; a.pred = ctx->pred; a.speculate = ctx->speculate; a.spec_confident = ctx->spec_confident;
     a.tl = niti_tl_next(ctx, nlayers > 1 ? "chain" : (single && single->flip ? "dx_fused" : "fwd_fused"));
     a.trigger_late = (ctx->pdl & NITI_PDL_TRIGGER_LATE) ? 1 : 0;
     static const ChainLayer zero{};

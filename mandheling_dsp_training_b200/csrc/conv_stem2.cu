@@ -226,8 +226,10 @@ stem2_fwd_kernel(const Stem2Params p) {
         uint32_t tile_iter = 0, mx = 0;
         int shift = 0, kind = 0;
         const bool spec = p.speculate != 0;                                      // a miss costs what the recompute schedule always paid: no gating
-        const uint32_t pstate = __ldcg(p.pred + p.dp_slot);
-        niti_rule_a(niti_pred_bitwidth(pstate), kind, shift);                    // predicted from the previous steps (common.cuh)
+        // image layer: its input norm is the data's, so only the window predictor applies (in_now = 0 switches the ratio off)
+        NitiPrediction pr = niti_predict(p.pred, p.dp_slot, 0u);
+        pr.bw = pr.bw_window; pr.bw_ratio = pr.bw_window;
+        niti_rule_a(pr.bw, kind, shift);                                         // predicted from the previous steps (common.cuh)
         const uint32_t eone = (uint32_t)(p.speculate >= 0);                      // 1, opaque to the compiler
         NitiRuleA rk = niti_rule_a_consts(shift, eone);
         int mxs = 0, mns = 0;
@@ -297,8 +299,8 @@ stem2_fwd_kernel(const Stem2Params p) {
                 if (blockIdx.x == 0) {
                     if (p.exp_out != nullptr)
                         *p.exp_out = (int8_t)((p.exp_a ? (int)*p.exp_a : 0) + (p.exp_b ? (int)*p.exp_b : 0) + (kind2 == 1 ? 0 : shift2));
-                    p.pred[p.dp_slot] = niti_pred_update(pstate, niti_bitwidth(gmax));   // every CTA read the old value before the barrier
-                    atomicAdd(p.pred + 2 * kDpSlots + (spec ? (hit ? 0 : 1) : 2), 1u);
+                    niti_predict_update(p.pred, p.dp_slot, pr, gmax, kind2 == kind && shift2 == shift, spec);   // every CTA read the old words before the barrier
+                    p.pred[kPredLastNorm] = niti_out_norm(gmax, kind2, shift2);   // input norm of the chain's first layer
                 }
             }
             if (hit) break;
