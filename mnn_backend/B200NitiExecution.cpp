@@ -155,6 +155,14 @@ public:
         if (formatOf(x) == MNN_DATA_FORMAT_NC4HW4 && c % 4 != 0 && c != 1) return NOT_SUPPORT;   // quirk Q6
         mDesc = niti_conv_desc{n, c, h, wd, oc, geo.kh, geo.kw, geo.stride, geo.pad, geo.dil};
         mOutCount = (size_t)n * oh * ow * oc;
+        // exponent-prediction slot of the fused kernel: the express graph (and with it every Execution) is rebuilt each step, so
+        // the slot is derived from the op's geometry — the same layer lands on the same slot in every step; a collision only
+        // costs prediction accuracy, never results (include/niti_b200.h niti_set_speculate)
+        {
+            unsigned long long hsh = 1469598103934665603ull;
+            for (int v : {n, c, h, wd, oc, geo.kh, geo.kw, geo.stride, geo.pad, geo.dil, mDeconv ? 1 : 0}) { hsh ^= (unsigned long long)(unsigned)v; hsh *= 1099511628211ull; }
+            mSlot = 1 + (int)(hsh % 255ull);
+        }
 
         const int kk = geo.kh * geo.kw;
         mX = (int8_t*)mScratch.get((size_t)n * h * wd * c);
@@ -192,8 +200,8 @@ public:
         // tensor memory (csrc/conv_chain.cu), the two-phase route through mAcc otherwise — same bytes either way
         int rc = a.zero_u32(ctx, mMax, 1, st);
         if (rc == NITI_OK) {
-            if (mDeconv) rc = a.conv_fwd_fused(ctx, &mDesc, mX, mW, nullptr, nullptr, mY, nullptr, 0, mAcc, mMax, 0, st);
-            else rc = a.conv_fwd_fused(ctx, &mDesc, mX, mW, dev(inputs[2]), dev(inputs[3]), mY, dev(outputs[1]), 0, mAcc, mMax, 0, st);
+            if (mDeconv) rc = a.conv_fwd_fused(ctx, &mDesc, mX, mW, nullptr, nullptr, mY, nullptr, 0, mAcc, mMax, mSlot, st);
+            else rc = a.conv_fwd_fused(ctx, &mDesc, mX, mW, dev(inputs[2]), dev(inputs[3]), mY, dev(outputs[1]), 0, mAcc, mMax, mSlot, st);
         }
         if (rc != NITI_OK) return check(rc, "niti_conv_fwd_fused");
         return runAll(mPost, "result gather");
@@ -203,6 +211,7 @@ private:
     const Convolution2DCommon* mCommon;
     bool mDeconv;
     bool mRaggedIn = false;
+    int mSlot = 0;
     niti_conv_desc mDesc;
     size_t mOutCount = 0;
     int8_t *mX = nullptr, *mW = nullptr, *mY = nullptr;
