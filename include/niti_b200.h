@@ -341,6 +341,30 @@ int niti_copy_d2h(niti_ctx*, void* dst_host, const void* src_dev, size_t bytes, 
 int niti_copy_d2d(niti_ctx*, void* dst_dev, const void* src_dev, size_t bytes, niti_stream);
 int niti_stream_sync(niti_ctx*, niti_stream);
 
+/* ---- for callers that may not allocate device memory ---------------------------------------
+ * No counterpart in the reference (its NITI_Matmul_Int8 scratch comes from the MNN backend's buffer pool); this is an
+ * addition of this library.  Same result as niti_matmul_nt — C[e,h] = rule B, sub 3, of sum_l A[e,l] * B[h,l], bit for bit —
+ * but without a niti_ctx and without any cudaMalloc / cudaFree, now or on an earlier call.  It exists for hosts that get a
+ * fixed device-memory budget at start-up and cannot ask the driver for more afterwards (a runtime embedded in someone
+ * else's memory plan, an allocator that is sealed after set-up), and for call sites where an allocation is not allowed or
+ * would stall the whole device (latency-critical sections).  The int32 accumulators and the max|acc| word, which the
+ * other whole-op calls keep in a context workspace, live in an array compiled into the library's device image instead:
+ * NITI_STATIC_SCRATCH_MAX_WORDS accumulators + a 256-byte header = 4 MiB + 256 B on EVERY GPU that loads the library,
+ * held until the process exits whether or not this call is ever made.
+ *   - e * h must not exceed NITI_STATIC_SCRATCH_MAX_WORDS: larger products return NITI_ERR_UNSUPPORTED with a message
+ *     (split A by rows, or use niti_matmul_nt).  l is unlimited.  a, b, c: device memory of the CURRENT device, any
+ *     alignment (4-byte aligned a, b with l % 4 == 0 take the faster load path).
+ *   - The first call on each device looks up that device's address of the array (cudaGetSymbolAddress, which may also
+ *     load the module).  Make that first call during set-up, with the device current and before any stream capture begins;
+ *     later calls only launch kernels on `st`.
+ *   - All calls on one device share the one array.  Each call resets the max|acc| word itself and overwrites the
+ *     accumulators it reads, so back-to-back calls on ONE stream are safe; two calls that can overlap on the GPU (different
+ *     streams without an event between them, or two host threads) race on it and give wrong results.
+ *   - err (optional, err_len bytes) receives a NUL-terminated message when the return value is not NITI_OK. */
+#define NITI_STATIC_SCRATCH_MAX_WORDS (1u << 20)
+int niti_matmul_nt_static(int e, int h, int l, const int8_t* a, const int8_t* b, int8_t* c, niti_stream st,
+                          char* err, size_t err_len);
+
 /* ---- host-buffer convenience (the e2e leg): H2D, op, D2H inside the call ------------------- */
 int niti_conv_fwd_host(niti_ctx*, const niti_conv_desc*, const int8_t* x_nhwc, const int8_t* w_ohwi,
                        int8_t ex, int8_t ew, int8_t* y_nhwc, int8_t* ey);

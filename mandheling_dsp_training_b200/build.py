@@ -9,7 +9,7 @@ CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(CSRC, "_obj")
 LIB = os.path.join(HERE, "libniti_b200.so")
 SOURCES = ["api.cu", "rescale.cu", "elementwise.cu", "conv_simt.cu", "conv_tc.cu", "conv_tma.cu", "conv_tma2.cu",
-           "update.cu", "dp.cu", "conv_dw2.cu", "conv_stem.cu", "conv_stem2.cu", "conv_chain.cu"]
+           "update.cu", "dp.cu", "conv_dw2.cu", "conv_stem.cu", "conv_stem2.cu", "conv_chain.cu", "static_scratch.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC"]
 

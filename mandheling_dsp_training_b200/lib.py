@@ -97,6 +97,7 @@ _SIGS = {
     "niti_conv_dx": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P]),
     "niti_conv_dw": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, _P, _P]),
     "niti_matmul_nt": (C.c_int, [_P, C.c_int, C.c_int, C.c_int, _P, _P, _P, _P]),
+    "niti_matmul_nt_static": (C.c_int, [C.c_int, C.c_int, C.c_int, _P, _P, _P, _P, C.c_char_p, C.c_size_t]),
     "niti_rescale_grad_split": (C.c_int, [_P, _P, C.c_size_t, C.c_int, _P, C.c_int, _P, _P]),
     "niti_split_count": (C.c_int, [C.c_int, C.c_int, C.c_int]),
     "niti_conv_dw_split": (C.c_int, [_P, C.POINTER(ConvDesc), _P, _P, C.c_int, _P, _P]),
