@@ -35,6 +35,7 @@ struct niti_ctx {
     DpView dp;
     DpWindow dp_win;                  // gradient window of every rank (peer[rank] = the local one), or all null
     int dp_reserve;           // SMs left to the concurrent collective (dp.cu)
+    int upd_blocks_per_sm;    // update_batched_kernel's resident CTAs per SM on this device (update.cu; 0 = not queried yet)
     // kernels whose dynamic shared memory limit was raised on THIS device (function attributes are per device)
     struct { const void* fn; int bytes; } smem_cfg[64];
     int n_smem_cfg;

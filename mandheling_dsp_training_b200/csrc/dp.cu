@@ -202,9 +202,17 @@ extern "C" int niti_dp_allreduce_i32(niti_ctx* ctx, size_t off, size_t n, int sl
     if (n == 0) return NITI_OK;
     // shape of the launch: by default one 1024-thread CTA on each SM the contractions leave free; NITI_B200_DP_AR_CTAS /
     // NITI_B200_DP_AR_THREADS override (small CTAs fit beside a resident contraction CTA: 8 K registers, no shared memory)
-    int ctas = ctx->dp_reserve > 0 ? ctx->dp_reserve : 16, threads = kArMaxThreads;
+    // Its CTAs spin on peers, so every one of them must be resident on an SM the one-CTA-per-SM contraction grids do not
+    // own: with no reserve (NITI_B200_DP_RESERVE_SMS=0) a contraction kernel that cannot become fully resident would stall
+    // the peers' max exchange until the spin budget runs out.  Refuse instead; callers fall back to a library all-reduce.
+    if (ctx->dp_reserve <= 0)
+        return niti_fail(ctx, NITI_ERR_UNSUPPORTED, "niti_dp_allreduce_i32: no SMs reserved for it (NITI_B200_DP_RESERVE_SMS=0); "
+                                                    "sum the window with the collective library instead");
+    int ctas = ctx->dp_reserve, threads = kArMaxThreads;
     if (const char* e = getenv("NITI_B200_DP_AR_CTAS")) { const int c = atoi(e); if (c >= 1 && c <= 1024) ctas = c; }
     if (const char* e = getenv("NITI_B200_DP_AR_THREADS")) { const int c = atoi(e); if (c >= 32 && c <= kArMaxThreads && c % 32 == 0) threads = c; }
+    const int resident = ctx->dp_reserve * (2048 / threads);      // CTAs of this size the reserved SMs hold at once
+    if (ctas > resident) ctas = resident;
     const size_t per = ((n >> 2) + ctx->dp.world - 1) / ctx->dp.world;
     const size_t need = (per + threads - 1) / threads;
     if ((size_t)ctas > need) ctas = (int)(need ? need : 1);

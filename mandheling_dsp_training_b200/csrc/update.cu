@@ -189,13 +189,14 @@ update_batched_kernel(const __grid_constant__ UpdSegs S, uint32_t* sync, unsigne
 
 static int update_launch(niti_ctx* ctx, const niti_update_seg* segs, int nseg, cudaStream_t st, bool phases) {
     if (!ctx || !segs || nseg <= 0) return niti_fail(ctx, NITI_ERR_ARG, "niti_update_batched: bad argument");
-    int blocks_per_sm = 0;                                    // occupancy is a per-device property: no process-wide cache
-    {
+    // occupancy is a property of the device: cached on the context (one context = one device), not process-wide
+    if (ctx->upd_blocks_per_sm <= 0) {
         int occ = 0;
         cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, update_batched_kernel, kUpdThreads, 0);
         if (e != cudaSuccess || occ < 1) return niti_fail(ctx, NITI_ERR_CUDA, "niti_update_batched: occupancy query", e);
-        blocks_per_sm = occ > 4 ? 4 : occ;
+        ctx->upd_blocks_per_sm = occ > 4 ? 4 : occ;
     }
+    const int blocks_per_sm = ctx->upd_blocks_per_sm;
     for (int first = 0; first < nseg; first += kMaxSegs) {
         UpdSegs S;
         S.n = nseg - first < kMaxSegs ? nseg - first : kMaxSegs;

@@ -326,6 +326,10 @@ class NitiB200:
             __cuda_array_interface__ = {"shape": (n,), "typestr": "<i4", "data": (ptr.value, False), "version": 3, "strides": None}
         t = torch.as_tensor(_Window(), device=f"cuda:{self.device}")
         assert t.data_ptr() == ptr.value and t.dtype == torch.int32
+        # The memory belongs to the context, not to torch: keep the context alive as long as the tensor is referenced
+        # from Python (views made by slicing share the base tensor), and never use it after dp_close / close.
+        t._niti_owner = self
+        self._dp_window_tensor = t
         return t
 
     def dp_allreduce(self, off, n, slot, stream=None):

@@ -204,9 +204,10 @@ class NitiNet:
         # Gradient sum without a collective library: the accumulators move into a peer-mapped window and every bucket is
         # added by one niti_dp_allreduce_i32 launch on a third stream (NCCL at 16 CTAs needed ~100 us per 9 MB bucket on
         # 8 GPUs and left a 190 us tail exposed: profiles/timeline_r2_vgg_8gpu_nccl.txt).  NITI_B200_DP_ALLREDUCE=nccl
-        # keeps torch.distributed.all_reduce.
+        # keeps torch.distributed.all_reduce, and so does a job that reserves no SMs (the peer-sum CTAs need SMs of their own).
         self.peer_sum = (self.peer_max and hasattr(nb, "dp_window") and self.dist.get_world_size() > 1
-                         and os.environ.get("NITI_B200_DP_ALLREDUCE", "peer") != "nccl")
+                         and os.environ.get("NITI_B200_DP_ALLREDUCE", "peer") != "nccl"
+                         and (not hasattr(nb, "dp_reserved_sms") or nb.dp_reserved_sms() > 0))
         if self.peer_sum:
             self.dw_acc = nb.dp_window(self.dist, dw_total)
             self.comm = torch.cuda.Stream(self.dev)
@@ -577,8 +578,10 @@ class NitiNet:
         self.nb.check_errors()
 
     def capture(self):
-        """CUDA-graph the step.  Returns a callable that replays it.  Data-parallel: the NCCL all-reduces are captured
-        into the graph with the kernels (every rank must capture and replay in lock-step)."""
+        """CUDA-graph the step.  Returns a callable that replays it.  Data-parallel: the gradient sum (by default the
+        peer-sum launches on the third stream, NCCL all-reduces with NITI_B200_DP_ALLREDUCE=nccl) is captured into the graph
+        with the kernels; every rank must capture and replay in lock-step.  A replay loop must still poll check() at its
+        sync points: a peer that stops answering only raises the sticky device flag."""
         s = torch.cuda.Stream(self.dev)
         s.wait_stream(torch.cuda.current_stream(self.dev))
         with torch.cuda.stream(s):
