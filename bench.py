@@ -44,6 +44,7 @@ def parse():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="weak: the workload's batch PER GPU; strong: the workload's batch is the GLOBAL batch, split over the GPUs")
     ap.add_argument("--no-dp-check", action="store_true", help="skip the data-parallel correctness witness (world > 1)")
+    ap.add_argument("--no-parity-check", action="store_true", help="skip the reference-fixture parity witness (1 GPU, vgg11)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--via", default="cabi", choices=["cabi", "mnn"],
                     help="mnn (workload lenet only): the reference's own training loop on its CPU backend and on the B200 MNN plug-in "
@@ -138,26 +139,36 @@ def time_reference(workload, batch, steps, warmup, budget_s=45.0, warm_batch=Non
 def run_reference_arm(args):
     """The reference arm: the reference's own CPU implementation on this box's host cores, SAME config as our arm (the
     workload's batch) unless --ref-batch overrides it (then `reduced` is set).  A batch-256 VGG-11 step is about a minute
-    of CPU time, so the timed region is as many whole steps as fit `--ref-budget` seconds (steps_done), after one warm-up
-    step on 16 samples (pages the code in; a full-size warm-up would double the run)."""
+    of CPU time, so the timed region is as many whole steps as fit `--ref-budget` seconds (steps_done), after `--warmup`
+    warm-up steps on 16 samples each (they page the code in; full-size warm-ups would multiply the run time)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     batch = args.ref_batch or (args.batch or WORKLOADS[args.workload][1])
     reduced = batch != (args.batch or WORKLOADS[args.workload][1])
-    cb, s_per_step, done = time_reference(args.workload, batch, args.steps, 1, budget_s=args.ref_budget, warm_batch=min(16, batch))
+    warm = max(1, args.warmup)
+    warm_batch = min(16, batch)
+    cb, s_per_step, done = time_reference(args.workload, batch, args.steps, warm, budget_s=args.ref_budget, warm_batch=warm_batch)
     scaling = {}
     for b in (4, 16, 64):                               # how the CPU path scales with batch (threads over the batch)
         if b < batch:
             r, _, _ = time_reference(args.workload, b, 1, 0, budget_s=1.0)
             scaling[str(b)] = round(r["value"], 3)
     scaling[str(batch)] = round(cb["value"], 3)
+    world = max(1, args.gpus)
+    # `config` carries the same keys, with the same values, as the B200 arm's line for the same flags.  Under --gpus N (weak)
+    # the job's global batch is batch x N; the host then times a BOUNDED sample of it: whole steps of `batch` samples (CPU
+    # samples/s does not depend on how the global batch is cut into steps, see ref_batch_scaling), as the cpu_baseline says.
+    gbatch = batch * world if args.scaling == "weak" else batch
     line = {"impl": "reference", "metric": "int8_train_samples_per_sec", "value": cb["value"], "unit": "samples/s",
-            "n_gpus": args.gpus, "steps": args.steps, "steps_done": done, "warmup": args.warmup, "ms_per_step": s_per_step * 1e3,
+            "n_gpus": args.gpus, "steps": args.steps, "steps_done": done, "warmup": warm, "ms_per_step": s_per_step * 1e3,
             "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "int8", "data": "synthetic",
-            "config": {"workload": WORKLOADS[args.workload][2], "per_gpu_batch": batch, "global_batch": batch,
-                       "reduced": reduced, "ref_batch_scaling": scaling,
-                       "note": "one host runs the whole batch; value does not grow with --gpus"},
+            "config": {"workload": WORKLOADS[args.workload][2], "per_gpu_batch": batch if args.scaling == "weak" else batch // world,
+                       "global_batch": gbatch, "parallelism": f"dp{world}",
+                       "notes": {"launch": "reference CPU backend, one host process", "reduced": reduced, "ref_batch_scaling": scaling,
+                                 "timed_step_batch": batch, "warmup_step_batch": warm_batch,
+                                 "simd": "oracle/_ref is built without MNN_USE_SSE (oracle/Makefile.ref): the NITI GEMM unit is scalar C either way, the float glue ops (Raster, Cast) run their portable C loops",
+                                 "sample": "one host runs whole steps of timed_step_batch samples; value does not grow with --gpus"}},
             "cpu_baseline": cb,
             "e2e": {"value": cb["value"], "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
@@ -295,7 +306,13 @@ def main():
     hx = [torch.from_numpy(rng.integers(-127, 128, size=(batch, chw[1], chw[2], chw[0]), dtype=np.int8)).pin_memory() for _ in range(nbuf)]
     hl = [torch.from_numpy(rng.integers(0, 10, size=batch).astype(np.int32)).pin_memory() for _ in range(nbuf)]
     dx = [t.cuda() for t in hx]; dl = [t.cuda() for t in hl]
-    host_logits = torch.empty(net.logits_buf.shape, dtype=torch.int8).pin_memory()   # rows padded to 16 classes travel as they are
+    # the classifier's rows are padded to 64 channels on the device; only the real classes travel back (gathered on the device)
+    dev_logits = torch.empty(net.logits.shape, dtype=torch.int8, device="cuda")
+    host_logits = torch.empty(net.logits.shape, dtype=torch.int8).pin_memory()
+
+    def read_back():
+        dev_logits.copy_(net.logits)
+        host_logits.copy_(dev_logits, non_blocking=True)
 
     flush = torch.empty(256 << 20, dtype=torch.int8, device="cuda")      # > 126 MB L2
 
@@ -318,7 +335,7 @@ def main():
     sampler = ClockSampler(local); sampler.start()
     # ---- warm-up (through the e2e path, so pinned copies and the D2H are warm too)
     for i in range(max(3, args.warmup)):
-        net.set_input(hx[i % nbuf], -7, hl[i % nbuf]); step_fn(); host_logits.copy_(net.logits_buf, non_blocking=True)
+        net.set_input(hx[i % nbuf], -7, hl[i % nbuf]); step_fn(); read_back()
     barrier()
 
     # ---- device-resident timed region: K steps, L2 flushed between steps, CUDA events per step
@@ -368,7 +385,7 @@ def main():
     for i in range(args.steps):
         net.set_input(hx[i % nbuf], -7, hl[i % nbuf])
         step_fn()
-        host_logits.copy_(net.logits_buf, non_blocking=True)
+        read_back()
         torch.cuda.current_stream().synchronize()              # the caller consumes the result every step
     t1.record()
     barrier()
@@ -390,7 +407,7 @@ def main():
         net.init_weights(seed=1)
         for i in range(3):
             net.set_input(gx[i, rank * batch:(rank + 1) * batch].cuda(), -7, gl[i, rank * batch:(rank + 1) * batch].cuda())
-            net.step()                                       # eager: the captured graph and the eager path must agree anyway
+            step_fn()                                        # the captured graph the timed region replays (eager under --no-graph)
         net.check()
         mine = torch.cat([L.w.reshape(-1) for L in net.convs] + [net.e_logits.reshape(-1)])
         allw = [torch.empty_like(mine) for _ in range(world)]
@@ -409,8 +426,21 @@ def main():
             equals_1gpu = bool(torch.equal(one, mine)) and bool(torch.equal(net1.logits_buf[:batch], net.logits_buf))
             del net1, nb1
         dp_check = {"weights_equal_across_ranks": bool(same_ranks), "equals_1gpu_global_batch": equals_1gpu, "steps": 3,
-                    "global_batch": batch * world}
+                    "global_batch": batch * world, "launch": "cuda_graph replay on every rank" if use_graph else "eager"}
         dist.barrier()
+
+    # ---- parity witness on the benchmarked configuration: the same net, stepped through a captured graph from seeded inputs,
+    # against the logits / exponents / updated weights the UNMODIFIED reference produced for those inputs (committed
+    # fixture; regenerate with tests/golden/make_golden_vgg.py where /root/reference exists)
+    parity_check = None
+    if world == 1 and args.workload == "vgg11" and batch in (4, 256) and not args.no_parity_check:
+        try:
+            from tests.gpu_util import vgg_reference_case
+            nbp = NitiB200(local)                            # own context: its workspaces must not move under the timed graph
+            parity_check = vgg_reference_case(nbp, batch, replay=use_graph)
+            nbp.close()
+        except Exception as ex:      # pragma: no cover
+            parity_check = {"error": str(ex)}
 
     clocks = sampler.summary()         # sampled over warm-up + all timed regions
     if world > 1:
@@ -460,14 +490,14 @@ def main():
         "metric": "int8_train_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": world,
         "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": total_ms / args.steps,
         "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "int8", "data": "synthetic",
-        "config": {"workload": desc_text, "per_gpu_batch": batch, "global_batch": batch * world,
-                   "parallelism": f"dp{world}", "launch": "cuda_graph" if use_graph else "eager",
-                   "dp_exchange": (("max|acc|: in-kernel NVLink peer-memory exchange; dW: bucketed " +
-                                    ("two-shot sum over NVLink peer memory (niti_dp_allreduce_i32)" if getattr(net, "peer_sum", False)
-                                     else "NCCL all-reduce(SUM)") + " overlapped with backward")
-                                   if net.peer_max else ("NCCL" if world > 1 else "none")),
-                   "l2": "flushed between timed steps (256 MiB write)", "step_working_set_mib": round(ws_mb, 1),
-                   "algorithmic_gop_per_step_per_gpu": net.algorithmic_ops() / 1e9},
+        "config": {"workload": desc_text, "per_gpu_batch": batch, "global_batch": batch * world, "parallelism": f"dp{world}",
+                   "notes": {"launch": "cuda_graph" if use_graph else "eager",
+                             "dp_exchange": (("max|acc|: in-kernel NVLink peer-memory exchange; dW: bucketed " +
+                                              ("two-shot sum over NVLink peer memory (niti_dp_allreduce_i32)" if getattr(net, "peer_sum", False)
+                                               else "NCCL all-reduce(SUM)") + " overlapped with backward")
+                                             if net.peer_max else ("NCCL" if world > 1 else "none")),
+                             "l2": "flushed between timed steps (256 MiB write)", "step_working_set_mib": round(ws_mb, 1),
+                             "algorithmic_gop_per_step_per_gpu": net.algorithmic_ops() / 1e9}},
         "e2e": {"value": e2e_value, "unit": "samples/s",
                 "h2d_bytes_per_step": int(hx[0].numel() + hl[0].numel() * 4) * world,
                 "d2h_bytes_per_step": int(host_logits.numel()) * world},
@@ -476,6 +506,7 @@ def main():
         "roofline": roofline,
         "cpu_baseline": cpu_baseline,
         "dp_check": dp_check,
+        "parity_check": parity_check,
         "tensor_frac_of_step": (net.algorithmic_ops() / (total_ms / args.steps * 1e-3) / 1e12 / peak_tops) if peak_tops else None,
         # fused kernels store with the exponent predicted from the previous step and re-store on a miss (conv_chain.cu);
         # counted over the whole run (warm-up, timed, e2e and per-kernel passes): the stored values never depend on it

@@ -125,3 +125,34 @@ class Runner:
         torch.cuda.synchronize()
         o = out.cpu().numpy().reshape(acc.shape)
         return (o, wd.cpu().numpy().reshape(w.shape)) if w is not None else o
+
+
+def vgg_reference_case(nb, batch, replay=True, dist=None):
+    """VGG-11 (3x32x32, 12 logits) on the device from the seeded inputs of tests/golden/make_golden_vgg.py, compared with
+    what the UNMODIFIED reference produced for the same inputs (tests/golden/vgg11_ref_steps.npz).  replay=True steps
+    through the captured CUDA graph — the thing bench.py times.  Returns the comparison as a dict (bench.py's parity_check)."""
+    from tests.golden.make_golden_vgg import case_inputs, weight_digest, STEPS, OUT
+    g = np.load(OUT)
+    spec, x, labels, ws = case_inputs(batch)
+    from mandheling_dsp_training_b200.step import NitiNet
+    net = NitiNet(nb, spec, batch, (3, 32, 32))
+    net.load_weights(ws)
+    nhwc = [torch.from_numpy(np.ascontiguousarray(np.transpose(x[s], (0, 2, 3, 1)))).cuda() for s in range(STEPS)]
+    lab = [torch.from_numpy(labels[s]).cuda() for s in range(STEPS)]
+    net.set_input(nhwc[0], -7, lab[0])
+    step = net.step
+    if replay:
+        step = net.capture()          # its eager warm-up step moves the weights: reload before the compared steps
+        net.load_weights(ws)
+    logits_ok, exp_ok = True, True
+    for s in range(STEPS):
+        net.set_input(nhwc[s], -7, lab[s])
+        step()
+        torch.cuda.synchronize()
+        logits_ok &= bool(np.array_equal(net.logits.cpu().numpy().reshape(batch, -1), g[f"b{batch}.logits"][s]))
+        exp_ok &= int(net.e_logits.item()) == int(g[f"b{batch}.e_logits"][s])
+    net.check()
+    digests = [weight_digest(w) for w in net.weights_oihw()]
+    return {"config": f"VGG-11 int8 NITI, 3x32x32, batch {batch}", "steps": STEPS, "launch": "cuda_graph" if replay else "eager",
+            "logits_equal": logits_ok, "exp_equal": exp_ok, "weights_equal": digests == [str(d) for d in g[f"b{batch}.w_sha256"]],
+            "against": "tests/golden/vgg11_ref_steps.npz (outputs of the unmodified reference's training loop, tests/golden/make_golden_vgg.py)"}

@@ -7,6 +7,7 @@ import torch
 from oracle.oracle import shape
 from mandheling_dsp_training_b200.step import NitiNet, lenet_spec
 from oracle.step_twin import oracle_step
+from tests.gpu_util import vgg_reference_case
 
 pytestmark = pytest.mark.gpu
 
@@ -127,3 +128,12 @@ def test_early_update_is_bit_identical(nb, monkeypatch):
     for wa, wb in zip(a.weights_oihw(), b.weights_oihw()):
         assert np.array_equal(wa, wb)
     assert torch.equal(a.logits, b.logits)
+
+
+@pytest.mark.parametrize("batch,replay", [(4, False), (4, True), (256, True)])
+def test_vgg11_steps_equal_the_reference_at_the_benchmarked_size(nb, batch, replay):
+    """The configuration BASELINE.json's metric is quoted on (VGG-11, batch 256, C=3 stem, five folded pools, alias flatten,
+    12 of 64 padded classes), stepped through the captured graph, against the reference's own logits, exponents and updated
+    weights for the same seeded batch — a direct pin, no oracle in between."""
+    r = vgg_reference_case(nb, batch, replay)
+    assert r["logits_equal"] and r["exp_equal"] and r["weights_equal"], r

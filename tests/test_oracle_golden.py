@@ -156,3 +156,20 @@ def test_split_cases_cover_the_rule(golden_split):
     assert counts == [1, 2, 2, 4]
     # the alignment really divides somewhere, and a zero slice exists
     assert any(not np.array_equal(golden_split[f"sp{i}.dw"], golden_split[f"sp{i}.dw_unsplit"]) for i in range(4))
+
+
+def test_oracle_step_equals_reference_vgg11_steps(oracle):
+    """oracle_step on the whole VGG-11 graph (C=3 stem, 3x3 pad 1, five pools, alias flatten, 12 classes) against what the
+    unmodified reference's Module / OpGrad / NITI_SGD loop produced (tests/golden/vgg11_ref_steps.npz, batch 4)."""
+    import os
+    from oracle.oracle import shape
+    from oracle.step_twin import oracle_step
+    from tests.golden.make_golden_vgg import case_inputs, weight_digest, STEPS, OUT
+    g = np.load(OUT)
+    spec, x, labels, ws = case_inputs(4)
+    w2 = [(w.copy(), e) for w, e in ws]
+    for s in range(STEPS):
+        lg, e = oracle_step(oracle, spec, x[s], -7, labels[s], w2, shape)
+        assert np.array_equal(lg.reshape(4, -1), g["b4.logits"][s])
+        assert e == g["b4.e_logits"][s]
+    assert [weight_digest(w) for w, _ in w2] == [str(d) for d in g["b4.w_sha256"]]
