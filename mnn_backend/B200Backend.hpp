@@ -82,11 +82,17 @@ public:
     niti_ctx* ctx() const { return mRuntime->ctx(); }
     const NitiB200Api& api() const { return mRuntime->api(); }
     niti_stream stream() const { return nullptr; }       // the executor is single-threaded and serial (Executor.cpp:767-796)
+    // How many Executions of this backend asked with the same key before (0 for the first).  The executor builds a fresh
+    // Backend for every ComputeCache and creates its Executions in graph order, so "the k-th op of this geometry" names the
+    // same layer in every training step: repeated blocks (VGG's two 512->512 layers, a ResNet stage) get predictor slots of
+    // their own instead of sharing one.
+    int occurrenceOf(unsigned long long key) { return mOccurrence[key]++; }
 
 private:
     const B200Runtime* mRuntime;
     std::map<void*, std::pair<StorageType, size_t>> mOwned;   // live buffers of this backend: type, bucket size
     std::multimap<size_t, void*> mReusable;                    // DYNAMIC blocks released during planning
+    std::map<unsigned long long, int> mOccurrence;
 };
 
 class B200RuntimeCreator : public RuntimeCreator {

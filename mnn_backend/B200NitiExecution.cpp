@@ -156,11 +156,14 @@ public:
         mDesc = niti_conv_desc{n, c, h, wd, oc, geo.kh, geo.kw, geo.stride, geo.pad, geo.dil};
         mOutCount = (size_t)n * oh * ow * oc;
         // exponent-prediction slot of the fused kernel: the express graph (and with it every Execution) is rebuilt each step, so
-        // the slot is derived from the op's geometry — the same layer lands on the same slot in every step; a collision only
-        // costs prediction accuracy, never results (include/niti_b200.h niti_set_speculate)
+        // the slot is derived from the op's geometry plus its rank among the ops of that geometry in this backend's graph — the
+        // same layer lands on the same slot in every step, and two layers of equal geometry do not share a predictor; a
+        // collision only costs prediction accuracy, never results (include/niti_b200.h niti_set_speculate)
         {
             unsigned long long hsh = 1469598103934665603ull;
             for (int v : {n, c, h, wd, oc, geo.kh, geo.kw, geo.stride, geo.pad, geo.dil, mDeconv ? 1 : 0}) { hsh ^= (unsigned long long)(unsigned)v; hsh *= 1099511628211ull; }
+            if (mOccurrence < 0 || hsh != mGeoKey) { mGeoKey = hsh; mOccurrence = bn()->occurrenceOf(hsh); }    // once per Execution and geometry: a second onResize keeps it
+            hsh ^= (unsigned long long)(unsigned)mOccurrence; hsh *= 1099511628211ull;
             mSlot = 1 + (int)(hsh % 255ull);
         }
 
@@ -212,6 +215,8 @@ private:
     bool mDeconv;
     bool mRaggedIn = false;
     int mSlot = 0;
+    int mOccurrence = -1;
+    unsigned long long mGeoKey = 0;
     niti_conv_desc mDesc;
     size_t mOutCount = 0;
     int8_t *mX = nullptr, *mW = nullptr, *mY = nullptr;
