@@ -39,3 +39,9 @@ def golden_mm():
 def golden_split():
     import numpy as np
     return np.load(os.path.join(ROOT, "tests", "golden", "split_cases.npz"))
+
+
+@pytest.fixture(scope="session")
+def golden_rgb():
+    import numpy as np
+    return np.load(os.path.join(ROOT, "tests", "golden", "conv_rgb_cases.npz"))

@@ -35,6 +35,14 @@ CONV_CASES = {
     "zero_dy": (2, 4, 6, 6, 8, 3, 1, 1, -127, 127, 127, 0),
 }
 
+# 3-channel image stems (VGG-11 / ResNet-18 first layer; C % 4 != 0, so forward + dW only — dX is outside the reference's
+# contract, quirk Q6).  Written to their own file, conv_rgb_cases.npz, so conv_cases.npz keeps its bytes.
+RGB_CASES = {
+    "rgb_stem_3x3_p1": (2, 3, 32, 32, 64, 3, 1, 1, -127, 127, 127, 40),
+    "rgb_stem_3x3_p1_small": (4, 3, 16, 16, 32, 3, 1, 1, -127, 127, 90, 20),
+    "rgb_stem_7x7_s2_p3": (2, 3, 32, 32, 64, 7, 2, 3, -127, 127, 127, 40),
+}
+
 
 def tensors(name, case):
     n, c, h, w, oc, k, st, p, xlo, xhi, wmax, dymax = case
@@ -47,6 +55,20 @@ def tensors(name, case):
     if name == "small_mag_shift1":
         wt = np.maximum(np.abs(wt), 4).astype(np.int8)
     return s, x, wt, dy
+
+
+def main_rgb(ref, orc):
+    conv = {}
+    for name, case in RGB_CASES.items():
+        s, x, wt, dy = tensors(name, case)
+        y, e = ref.conv_fwd(s, x, wt, -7, -7)
+        _, dw = ref.conv_bwd(s, x, wt, dy)
+        conv[name + ".shape"] = np.array([getattr(s, f) for f, _ in s._fields_], np.int32)
+        conv[name + ".x"], conv[name + ".w"], conv[name + ".dy"] = x, wt, dy
+        conv[name + ".y"], conv[name + ".exp"], conv[name + ".dw"] = y, np.int32(e), dw
+        worst = max(orc.conv_fwd_acc(s, x, wt)[1], orc.conv_dw_acc(s, x, dy)[1])
+        assert worst < 2 ** 24, (name, worst)
+    np.savez_compressed(os.path.join(OUT, "conv_rgb_cases.npz"), **conv)
 
 
 def main():
@@ -69,6 +91,7 @@ def main():
         worst = max(orc.conv_fwd_acc(s, x, wt)[1], orc.conv_dw_acc(s, x, dy)[1])
         assert worst < 2 ** 24, (name, worst)
     np.savez_compressed(os.path.join(OUT, "conv_cases.npz"), **conv)
+    main_rgb(ref, orc)
 
     rng = np.random.default_rng(7)
     ew = {}
@@ -129,4 +152,7 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    if "--rgb-only" in sys.argv:
+        main_rgb(Reference(threads=4), Oracle())
+    else:
+        main()

@@ -173,3 +173,19 @@ def test_oracle_step_equals_reference_vgg11_steps(oracle):
         assert np.array_equal(lg.reshape(4, -1), g["b4.logits"][s])
         assert e == g["b4.e_logits"][s]
     assert [weight_digest(w) for w, _ in w2] == [str(d) for d in g["b4.w_sha256"]]
+
+
+RGB = ["rgb_stem_3x3_p1", "rgb_stem_3x3_p1_small", "rgb_stem_7x7_s2_p3"]
+
+
+@pytest.mark.parametrize("name", RGB)
+def test_rgb_stem_cases_match_reference(oracle, golden_rgb, name):
+    """3-channel image layers (C % 4 != 0: the reference's NC4HW4 packing pads the channel block): forward + dW as the
+    unmodified reference computed them.  dX of such a layer is outside the reference's contract (quirk Q6) and never needed
+    (the image has no gradient)."""
+    g = golden_rgb
+    s, x, w, dy = load_case(g, name)
+    assert s.c == 3
+    y, e, _ = oracle.conv_fwd(s, x, w, -7, -7)
+    assert np.array_equal(y, g[name + ".y"]) and e == int(g[name + ".exp"])
+    assert np.array_equal(oracle.conv_dw(s, x, dy)[0], g[name + ".dw"])
