@@ -798,3 +798,31 @@ def test_streaming_fused_ops_vs_pinned_simt_and_oracle_rescale(nb, oracle, shape
     finally:
         nb.set_speculate(1)
     assert nb.sync_error() == 0
+
+
+@pytest.mark.parametrize("name", ["rgb_stem_3x3_p1", "rgb_stem_3x3_p1_small", "rgb_stem_7x7_s2_p3"])
+def test_rgb_stem_golden_reference_vectors(nb, run, golden_rgb, name):
+    """a1/a3 on 3-channel image layers against outputs of the unmodified reference (tests/golden/conv_rgb_cases.npz): the
+    generic C-ABI ops on the 3-channel tensors, then the product route — niti_conv_stem_fwd and the dW kernels on the image
+    zero-padded to 16 channels, as the training step stores it."""
+    import torch
+    from tests.gpu_util import PATH_AUTO, to_desc, dev, nhwc, nchw
+    nb.set_path(PATH_AUTO)
+    g = golden_rgb
+    s, x, w, dy = _case(g, name)
+    y, e = run.conv_fwd(s, x, w, -7, -7)
+    assert np.array_equal(y, g[name + ".y"]) and e == int(g[name + ".exp"])
+    assert np.array_equal(run.conv_dw(s, x, dy), g[name + ".dw"])
+    # product route: 16-channel storage, 3 live
+    i8 = dict(dtype=torch.int8, device="cuda:0")
+    x16 = torch.zeros((s.n, s.h, s.w, 16), **i8); x16[..., :3] = dev(nhwc(x))
+    w16 = torch.zeros((s.oc, s.kh, s.kw, 16), **i8); w16[..., :3] = dev(nhwc(w))
+    s16 = shape(s.n, 16, s.h, s.w, s.oc, s.kh, stride=s.stride, pad=s.pad)
+    yd = torch.full((s.n, s.oh, s.ow, s.oc), 99, **i8)
+    ey = torch.zeros(1, **i8); mx = torch.zeros(1, dtype=torch.int32, device="cuda:0")
+    acc = torch.empty(yd.numel(), dtype=torch.int32, device="cuda:0")
+    nb.conv_stem_fwd(to_desc(s16), 3, x16, w16, torch.full((1,), -7, **i8), torch.full((1,), -7, **i8), yd, ey, False, None, acc, mx)
+    torch.cuda.synchronize()
+    assert np.array_equal(nchw(yd.cpu().numpy()), g[name + ".y"]) and int(ey.item()) == int(g[name + ".exp"])
+    dw16 = run.conv_dw(s16, nchw(x16.cpu().numpy()), dy)
+    assert np.array_equal(dw16[:, :3], g[name + ".dw"]) and not dw16[:, 3:].any()
